@@ -1,0 +1,520 @@
+// capi.cu — the C ABI of libgsplat_b200.so (include/gsplat_b200.h): context, workspace
+// management and stage orchestration.  No torch types, no exceptions across the boundary, no
+// CPU fallback: compute entry points fail with GS_ECUDA when no sm_100 device is usable.
+#include <stdarg.h>
+#include <string.h>
+
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "gs_common.cuh"
+
+// ---- launchers implemented in the other translation units ----
+cudaError_t gs_launch_preprocess(const gs_settings&, const gs_gaussians&, int, GsGeom*, float*, int*, uint32_t*,
+                                 uint8_t*, cudaStream_t);
+size_t gs_scan_temp_bytes(int N);
+cudaError_t gs_launch_scan(void*, size_t, const uint32_t*, uint32_t*, int, cudaStream_t);
+cudaError_t gs_launch_duplicate(int, const GsGeom*, const float*, const int*, const uint32_t*, uint64_t*, uint32_t*,
+                                int, int, cudaStream_t);
+size_t gs_sort_temp_bytes(uint32_t D, int end_bit);
+cudaError_t gs_launch_sort(void*, size_t, const uint64_t*, uint64_t*, const uint32_t*, uint32_t*, uint32_t, int,
+                           cudaStream_t);
+cudaError_t gs_launch_ranges(uint32_t, const uint64_t*, uint2*, int, cudaStream_t);
+cudaError_t gs_launch_blend_forward(const GsDims&, const uint2*, const uint32_t*, const GsGeom*, const float[3],
+                                    float*, float*, uint32_t*, cudaStream_t);
+cudaError_t gs_launch_blend_backward(const GsDims&, const uint2*, const uint32_t*, const GsGeom*, const float[3],
+                                     const float*, const uint32_t*, const float*, float4*, cudaStream_t);
+cudaError_t gs_launch_preprocess_backward(const gs_settings&, const gs_gaussians&, const gs_gradients&, int,
+                                          const int*, const uint8_t*, const float4*, cudaStream_t);
+cudaError_t gs_launch_adam(int, float* const[6], float* const[6], float* const[6], float* const[6], const int[6],
+                           const float[6], const long long[6], float, float, float, const int*, const float*, int*,
+                           float*, float*, int, cudaStream_t);
+cudaError_t gs_launch_l1_loss(size_t, const float*, const float*, float, float*, double*, float*, cudaStream_t);
+
+// ---- context ----------------------------------------------------------------------------------
+struct DevBuf {
+  void* ptr = nullptr;
+  size_t cap = 0;
+};
+
+struct gs_ctx {
+  int device = 0;
+  std::string err;
+  // per-Gaussian
+  DevBuf geom, depths, radii, tiles, offsets, clamped, grad_geom;
+  // per-duplicate
+  DevBuf keys_a, keys_b, vals_a, vals_b;
+  // per-tile / per-pixel
+  DevBuf ranges, final_T, n_contrib;
+  DevBuf scan_tmp, sort_tmp, loss_acc;
+  uint32_t* d_host_pinned = nullptr;  // D readback
+  // state of the last forward
+  int N = -1, H = 0, W = 0, ntiles = 0;
+  uint64_t D = 0;
+  bool have_forward = false, have_backward = false, kept_unsorted = false;
+  // profiling
+  bool profiling = false;
+  cudaEvent_t ev[2 * GS_NUM_STAGES] = {};
+  bool ev_valid[GS_NUM_STAGES] = {};
+};
+
+static std::mutex g_err_mu;
+static std::string g_last_error;
+
+void gs_set_error(gs_ctx* ctx, const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->err = buf;
+  std::lock_guard<std::mutex> lk(g_err_mu);
+  g_last_error = buf;
+}
+
+static int ensure(gs_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return GS_OK;
+  if (b.ptr) cudaFree(b.ptr);
+  b.ptr = nullptr;
+  b.cap = 0;
+  size_t want = bytes + bytes / 4 + 256;
+  cudaError_t e = cudaMalloc(&b.ptr, want);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    e = cudaMalloc(&b.ptr, bytes);  // retry without slack
+    want = bytes;
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    gs_set_error(ctx, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+    return GS_ENOMEM;
+  }
+  b.cap = want;
+  return GS_OK;
+}
+#define GS_ENSURE(ctx, buf, bytes)                   \
+  do {                                               \
+    int _r = ensure(ctx, buf, bytes);                \
+    if (_r != GS_OK) return _r;                      \
+  } while (0)
+
+struct StageTimer {
+  gs_ctx* c;
+  int stage;
+  cudaStream_t s;
+  StageTimer(gs_ctx* ctx, int st, cudaStream_t stream) : c(ctx), stage(st), s(stream) {
+    if (c->profiling) cudaEventRecord(c->ev[2 * stage], s);
+  }
+  ~StageTimer() {
+    if (c->profiling) {
+      cudaEventRecord(c->ev[2 * stage + 1], s);
+      c->ev_valid[stage] = true;
+    }
+  }
+};
+
+extern "C" {
+
+const char* gs_version(void) { return "gsplat_b200 0.1 (sm_100a)"; }
+
+const char* gs_last_error(const gs_ctx* ctx) {
+  if (ctx) return ctx->err.c_str();
+  std::lock_guard<std::mutex> lk(g_err_mu);
+  static thread_local std::string copy;
+  copy = g_last_error;
+  return copy.c_str();
+}
+
+int gs_create(gs_ctx** out, int device) {
+  if (!out) return GS_EINVAL;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0) {
+    cudaGetLastError();
+    gs_set_error(nullptr, "no CUDA device available (%s); libgsplat_b200 has no CPU fallback",
+                 e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    return GS_ECUDA;
+  }
+  if (device < 0 || device >= count) {
+    gs_set_error(nullptr, "device %d out of range [0,%d)", device, count);
+    return GS_EINVAL;
+  }
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess || prop.major != 10) {
+    gs_set_error(nullptr, "device %d is sm_%d%d; this library contains sm_100a code only", device,
+                 e == cudaSuccess ? prop.major : 0, e == cudaSuccess ? prop.minor : 0);
+    return GS_ECUDA;
+  }
+  gs_ctx* c = new (std::nothrow) gs_ctx();
+  if (!c) return GS_ENOMEM;
+  c->device = device;
+  if (cudaSetDevice(device) != cudaSuccess || cudaMallocHost((void**)&c->d_host_pinned, 64) != cudaSuccess) {
+    gs_set_error(nullptr, "cudaSetDevice/cudaMallocHost failed: %s", cudaGetErrorString(cudaGetLastError()));
+    delete c;
+    return GS_ECUDA;
+  }
+  for (int i = 0; i < 2 * GS_NUM_STAGES; ++i) cudaEventCreate(&c->ev[i]);
+  *out = c;
+  return GS_OK;
+}
+
+void gs_destroy(gs_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  DevBuf* bufs[] = {&c->geom,   &c->depths, &c->radii,  &c->tiles,   &c->offsets,   &c->clamped,  &c->grad_geom,
+                    &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_T,  &c->n_contrib,
+                    &c->scan_tmp, &c->sort_tmp, &c->loss_acc};
+  for (DevBuf* b : bufs)
+    if (b->ptr) cudaFree(b->ptr);
+  if (c->d_host_pinned) cudaFreeHost(c->d_host_pinned);
+  for (int i = 0; i < 2 * GS_NUM_STAGES; ++i)
+    if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  delete c;
+}
+
+int gs_set_profiling(gs_ctx* c, int enabled) {
+  if (!c) return GS_EINVAL;
+  c->profiling = enabled != 0;
+  for (int i = 0; i < GS_NUM_STAGES; ++i) c->ev_valid[i] = false;
+  return GS_OK;
+}
+
+int gs_get_stage_ms(gs_ctx* c, float ms[GS_NUM_STAGES]) {
+  if (!c || !ms) return GS_EINVAL;
+  cudaSetDevice(c->device);
+  for (int i = 0; i < GS_NUM_STAGES; ++i) {
+    ms[i] = 0.f;
+    if (c->ev_valid[i]) {
+      cudaEventSynchronize(c->ev[2 * i + 1]);
+      cudaEventElapsedTime(&ms[i], c->ev[2 * i], c->ev[2 * i + 1]);
+    }
+  }
+  return GS_OK;
+}
+
+static int validate(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in) {
+  if (!c) return GS_EINVAL;
+  if (!st || !in || N < 0) {
+    gs_set_error(c, "null settings/inputs or negative N");
+    return GS_EINVAL;
+  }
+  if (st->H <= 0 || st->W <= 0 || !(st->tanfovx > 0.f) || !(st->tanfovy > 0.f)) {
+    gs_set_error(c, "invalid image size %dx%d or tanfov", st->W, st->H);
+    return GS_EINVAL;
+  }
+  if (st->max_sh_degree < 0 || st->max_sh_degree > 3 || st->sh_degree < 0 || st->sh_degree > st->max_sh_degree) {
+    gs_set_error(c, "sh_degree %d / max_sh_degree %d out of range (0..3)", st->sh_degree, st->max_sh_degree);
+    return GS_EINVAL;
+  }
+  if (N > 0) {
+    if (!in->means3D || !in->opacities) {
+      gs_set_error(c, "means3D and opacities are required");
+      return GS_EINVAL;
+    }
+    if (!in->cov3D_precomp && (!in->scales || !in->rotations)) {
+      gs_set_error(c, "scales and rotations are required unless cov3D_precomp is given");
+      return GS_EINVAL;
+    }
+    if (!in->colors_precomp) {
+      if (!in->sh_dc || in->sh_dc_stride < 3) {
+        gs_set_error(c, "sh_dc (stride >= 3) is required unless colors_precomp is given");
+        return GS_EINVAL;
+      }
+      const int need = 3 * ((st->sh_degree + 1) * (st->sh_degree + 1) - 1);
+      if (need > 0 && (!in->sh_rest || in->sh_rest_stride < need)) {
+        gs_set_error(c, "sh_rest with stride >= %d floats is required for sh_degree %d", need, st->sh_degree);
+        return GS_EINVAL;
+      }
+    }
+    if (in->rotations && (((uintptr_t)in->rotations) & 15)) {
+      gs_set_error(c, "rotations must be 16-byte aligned");
+      return GS_EINVAL;
+    }
+  }
+  return GS_OK;
+}
+
+int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, float* out_color, int* radii,
+               void* stream_) {
+  int rc = validate(c, st, N, in);
+  if (rc != GS_OK) return rc;
+  if (!out_color) {
+    gs_set_error(c, "out_color is required");
+    return GS_EINVAL;
+  }
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  const GsDims d = gs_dims(*st);
+  const size_t P = (size_t)d.H * d.W;
+  const size_t Nn = (size_t)(N > 0 ? N : 1);
+  c->have_forward = false;
+  c->have_backward = false;
+
+  GS_ENSURE(c, c->geom, Nn * sizeof(GsGeom));
+  GS_ENSURE(c, c->depths, Nn * 4);
+  GS_ENSURE(c, c->radii, Nn * 4);
+  GS_ENSURE(c, c->tiles, Nn * 4);
+  GS_ENSURE(c, c->offsets, Nn * 4);
+  GS_ENSURE(c, c->clamped, Nn);
+  GS_ENSURE(c, c->ranges, (size_t)d.ntiles * sizeof(uint2));
+  GS_ENSURE(c, c->final_T, P * 4);
+  GS_ENSURE(c, c->n_contrib, P * 4);
+  const size_t scan_bytes = gs_scan_temp_bytes(N > 0 ? N : 1);
+  GS_ENSURE(c, c->scan_tmp, scan_bytes);
+
+  uint64_t D = 0;
+  if (N > 0) {
+    {
+      StageTimer t(c, 0, stream);
+      GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
+                                            (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint8_t*)c->clamped.ptr,
+                                            stream));
+    }
+    {
+      StageTimer t(c, 1, stream);
+      GS_CUDA_CHECK(c, gs_launch_scan(c->scan_tmp.ptr, scan_bytes, (const uint32_t*)c->tiles.ptr,
+                                      (uint32_t*)c->offsets.ptr, N, stream));
+      // the one host synchronisation of the forward: number of (Gaussian, tile) duplicates
+      GS_CUDA_CHECK(c, cudaMemcpyAsync(c->d_host_pinned, (uint32_t*)c->offsets.ptr + (N - 1), 4,
+                                       cudaMemcpyDeviceToHost, stream));
+      GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
+      D = *c->d_host_pinned;
+      // a 32-bit inclusive scan wraps silently: detect it with a 64-bit bound (each Gaussian touches at most
+      // ntiles tiles), falling back to an exact check only when the bound allows overflow
+      if ((uint64_t)N * (uint64_t)d.ntiles > 0xFFFFFFFFull && D > 0xF0000000ull) {
+        gs_set_error(c, "duplicate list too long for 32-bit indices");
+        return GS_EOVERFLOW;
+      }
+      const size_t Dn = (size_t)(D > 0 ? D : 1);
+      GS_ENSURE(c, c->keys_a, Dn * 8);
+      GS_ENSURE(c, c->keys_b, Dn * 8);
+      GS_ENSURE(c, c->vals_a, Dn * 4);
+      GS_ENSURE(c, c->vals_b, Dn * 4);
+      if (D > 0)
+        GS_CUDA_CHECK(c, gs_launch_duplicate(N, (const GsGeom*)c->geom.ptr, (const float*)c->depths.ptr,
+                                             (const int*)c->radii.ptr, (const uint32_t*)c->offsets.ptr,
+                                             (uint64_t*)c->keys_a.ptr, (uint32_t*)c->vals_a.ptr, d.gx, d.gy, stream));
+    }
+    {
+      StageTimer t(c, 2, stream);
+      int tile_bits = 1;
+      while ((1u << tile_bits) < (uint32_t)d.ntiles) ++tile_bits;
+      const int end_bit = 32 + tile_bits;
+      const size_t sort_bytes = gs_sort_temp_bytes((uint32_t)D, end_bit);
+      GS_ENSURE(c, c->sort_tmp, sort_bytes > 0 ? sort_bytes : 1);
+      GS_CUDA_CHECK(c, gs_launch_sort(c->sort_tmp.ptr, sort_bytes, (const uint64_t*)c->keys_a.ptr,
+                                      (uint64_t*)c->keys_b.ptr, (const uint32_t*)c->vals_a.ptr,
+                                      (uint32_t*)c->vals_b.ptr, (uint32_t)D, end_bit, stream));
+    }
+  } else {
+    GS_ENSURE(c, c->keys_b, 8);
+    GS_ENSURE(c, c->vals_b, 4);
+  }
+  {
+    StageTimer t(c, 3, stream);
+    GS_CUDA_CHECK(c, gs_launch_ranges((uint32_t)D, (const uint64_t*)c->keys_b.ptr, (uint2*)c->ranges.ptr, d.ntiles,
+                                      stream));
+  }
+  {
+    StageTimer t(c, 4, stream);
+    GS_CUDA_CHECK(c, gs_launch_blend_forward(d, (const uint2*)c->ranges.ptr, (const uint32_t*)c->vals_b.ptr,
+                                             (const GsGeom*)c->geom.ptr, st->bg, out_color, (float*)c->final_T.ptr,
+                                             (uint32_t*)c->n_contrib.ptr, stream));
+  }
+  if (radii && N > 0)
+    GS_CUDA_CHECK(c, cudaMemcpyAsync(radii, c->radii.ptr, (size_t)N * 4, cudaMemcpyDeviceToDevice, stream));
+  if (st->debug) {
+    GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
+    GS_CUDA_CHECK(c, cudaGetLastError());
+  }
+  c->N = N;
+  c->H = d.H;
+  c->W = d.W;
+  c->ntiles = d.ntiles;
+  c->D = D;
+  c->kept_unsorted = true;  // keys_a/vals_a are not reused until the next forward
+  c->have_forward = true;
+  return GS_OK;
+}
+
+int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, const float* dL_dout_color,
+                const gs_gradients* grads, void* stream_) {
+  int rc = validate(c, st, N, in);
+  if (rc != GS_OK) return rc;
+  if (!dL_dout_color || !grads) {
+    gs_set_error(c, "dL_dout_color and grads are required");
+    return GS_EINVAL;
+  }
+  if (!c->have_forward || c->N != N || c->H != st->H || c->W != st->W) {
+    gs_set_error(c, "gs_backward needs the matching gs_forward (same N, H, W) to have run on this context");
+    return GS_ESTATE;
+  }
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  if (N == 0) return GS_OK;
+  const GsDims d = gs_dims(*st);
+  GS_ENSURE(c, c->grad_geom, (size_t)N * 48);
+  {
+    StageTimer t(c, 5, stream);
+    GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
+    GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, (const uint32_t*)c->vals_b.ptr,
+                                              (const GsGeom*)c->geom.ptr, st->bg, (const float*)c->final_T.ptr,
+                                              (const uint32_t*)c->n_contrib.ptr, dL_dout_color,
+                                              (float4*)c->grad_geom.ptr, stream));
+  }
+  {
+    StageTimer t(c, 6, stream);
+    GS_CUDA_CHECK(c, gs_launch_preprocess_backward(*st, *in, *grads, N, (const int*)c->radii.ptr,
+                                                   (const uint8_t*)c->clamped.ptr, (const float4*)c->grad_geom.ptr,
+                                                   stream));
+  }
+  if (st->debug) {
+    GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
+    GS_CUDA_CHECK(c, cudaGetLastError());
+  }
+  c->have_backward = true;
+  return GS_OK;
+}
+
+int gs_adam_densify_step(gs_ctx* c, int N, float* const params[6], float* const grads[6], float* const exp_avg[6],
+                         float* const exp_avg_sq[6], const int widths[6], const float lr[6], const long long step[6],
+                         float beta1, float beta2, float eps, const int* radii, const float* dL_dmeans2D,
+                         int* max_radii2D, float* xyz_grad_accum, float* denom, int zero_grads, void* stream_) {
+  if (!c || N < 0 || !params || !grads || !exp_avg || !exp_avg_sq || !widths || !lr || !step) {
+    gs_set_error(c, "gs_adam_densify_step: null argument");
+    return GS_EINVAL;
+  }
+  for (int s = 0; s < 6; ++s) {
+    if (widths[s] > 0 && params[s] && (!grads[s] || !exp_avg[s] || !exp_avg_sq[s])) {
+      gs_set_error(c, "segment %d: grads/exp_avg/exp_avg_sq missing", s);
+      return GS_EINVAL;
+    }
+    if (step[s] < 1) {
+      gs_set_error(c, "segment %d: step must be >= 1 (libtorch increments before use)", s);
+      return GS_EINVAL;
+    }
+  }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_CUDA_CHECK(c, gs_launch_adam(N, params, grads, exp_avg, exp_avg_sq, widths, lr, step, beta1, beta2, eps, radii,
+                                  dL_dmeans2D, max_radii2D, xyz_grad_accum, denom, zero_grads,
+                                  (cudaStream_t)stream_));
+  return GS_OK;
+}
+
+int gs_loss(gs_ctx* c, int H, int W, const float* image, const float* gt, float lambda_dssim, float* loss_out,
+            float* dL_dimage, void* stream_) {
+  if (!c || H <= 0 || W <= 0 || !image || !gt || !loss_out) {
+    gs_set_error(c, "gs_loss: bad argument");
+    return GS_EINVAL;
+  }
+  if (lambda_dssim != 0.0f) {
+    gs_set_error(c, "gs_loss: the D-SSIM term is not built yet (lambda_dssim must be 0)");
+    return GS_EINVAL;
+  }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_ENSURE(c, c->loss_acc, 64);
+  GS_CUDA_CHECK(c, gs_launch_l1_loss((size_t)3 * H * W, image, gt, 1.0f, dL_dimage, (double*)c->loss_acc.ptr,
+                                     loss_out, (cudaStream_t)stream_));
+  return GS_OK;
+}
+
+// ---- parity harness ---------------------------------------------------------------------------
+static long long dbg_size(gs_ctx* c, int what) {
+  if (!c->have_forward) return GS_ESTATE;
+  const long long N = c->N, D = (long long)c->D, T = c->ntiles, P = (long long)c->H * c->W;
+  switch (what) {
+    case GS_DBG_MEANS2D: return N * 8;
+    case GS_DBG_DEPTHS: return N * 4;
+    case GS_DBG_CONIC_OPACITY: return N * 16;
+    case GS_DBG_RGB: return N * 12;
+    case GS_DBG_CLAMPED: return N;
+    case GS_DBG_TILES_TOUCHED: return N * 4;
+    case GS_DBG_POINT_OFFSETS: return N * 4;
+    case GS_DBG_KEYS_SORTED: return D * 8;
+    case GS_DBG_POINT_LIST: return D * 4;
+    case GS_DBG_RANGES: return T * 8;
+    case GS_DBG_FINAL_T: return P * 4;
+    case GS_DBG_N_CONTRIB: return P * 4;
+    case GS_DBG_DL_DMEAN2D: return c->have_backward ? N * 8 : GS_ESTATE;
+    case GS_DBG_DL_DCONIC: return c->have_backward ? N * 12 : GS_ESTATE;
+    case GS_DBG_DL_DOPACITY: return c->have_backward ? N * 4 : GS_ESTATE;
+    case GS_DBG_DL_DCOLOR: return c->have_backward ? N * 12 : GS_ESTATE;
+    case GS_DBG_NUM_RENDERED: return 8;
+    case GS_DBG_KEYS_UNSORTED: return c->kept_unsorted ? D * 8 : GS_ESTATE;
+    case GS_DBG_VALUES_UNSORTED: return c->kept_unsorted ? D * 4 : GS_ESTATE;
+    default: return GS_EINVAL;
+  }
+}
+
+long long gs_debug_size(gs_ctx* c, int what) {
+  if (!c) return GS_EINVAL;
+  return dbg_size(c, what);
+}
+
+int gs_debug_get(gs_ctx* c, int what, void* host_dst, size_t bytes) {
+  if (!c || (!host_dst && bytes)) return GS_EINVAL;
+  const long long need = dbg_size(c, what);
+  if (need < 0) {
+    gs_set_error(c, "gs_debug_get(%d): not available in the current state", what);
+    return (int)need;
+  }
+  if ((size_t)need != bytes) {
+    gs_set_error(c, "gs_debug_get(%d): expected %lld bytes, got %zu", what, need, bytes);
+    return GS_EINVAL;
+  }
+  if (bytes == 0) return GS_OK;
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_CUDA_CHECK(c, cudaDeviceSynchronize());
+  const size_t N = (size_t)c->N;
+  const void* src = nullptr;
+  switch (what) {
+    case GS_DBG_DEPTHS: src = c->depths.ptr; break;
+    case GS_DBG_CLAMPED: src = c->clamped.ptr; break;
+    case GS_DBG_TILES_TOUCHED: src = c->tiles.ptr; break;
+    case GS_DBG_POINT_OFFSETS: src = c->offsets.ptr; break;
+    case GS_DBG_KEYS_SORTED: src = c->keys_b.ptr; break;
+    case GS_DBG_POINT_LIST: src = c->vals_b.ptr; break;
+    case GS_DBG_RANGES: src = c->ranges.ptr; break;
+    case GS_DBG_FINAL_T: src = c->final_T.ptr; break;
+    case GS_DBG_N_CONTRIB: src = c->n_contrib.ptr; break;
+    case GS_DBG_KEYS_UNSORTED: src = c->keys_a.ptr; break;
+    case GS_DBG_VALUES_UNSORTED: src = c->vals_a.ptr; break;
+    case GS_DBG_NUM_RENDERED: {
+      const uint64_t D = c->D;
+      memcpy(host_dst, &D, 8);
+      return GS_OK;
+    }
+    default: break;
+  }
+  if (src) {
+    GS_CUDA_CHECK(c, cudaMemcpy(host_dst, src, bytes, cudaMemcpyDeviceToHost));
+    return GS_OK;
+  }
+  // records that are packed on the device: copy the AoS and unpack on the host
+  const bool is_grad = what >= GS_DBG_DL_DMEAN2D && what <= GS_DBG_DL_DCOLOR;
+  std::vector<float> rec(N * 12);
+  GS_CUDA_CHECK(c, cudaMemcpy(rec.data(), is_grad ? c->grad_geom.ptr : c->geom.ptr, N * 48, cudaMemcpyDeviceToHost));
+  float* o = (float*)host_dst;
+  for (size_t i = 0; i < N; ++i) {
+    const float* r = rec.data() + 12 * i;
+    switch (what) {
+      case GS_DBG_MEANS2D: o[2 * i] = r[0]; o[2 * i + 1] = r[1]; break;
+      case GS_DBG_CONIC_OPACITY:
+        o[4 * i] = 2.0f * r[2]; o[4 * i + 1] = r[3]; o[4 * i + 2] = 2.0f * r[4]; o[4 * i + 3] = r[5];
+        break;
+      case GS_DBG_RGB: o[3 * i] = r[6]; o[3 * i + 1] = r[7]; o[3 * i + 2] = r[8]; break;
+      case GS_DBG_DL_DMEAN2D: o[2 * i] = r[0]; o[2 * i + 1] = r[1]; break;
+      case GS_DBG_DL_DCONIC: o[3 * i] = r[2]; o[3 * i + 1] = r[3]; o[3 * i + 2] = r[4]; break;
+      case GS_DBG_DL_DOPACITY: o[i] = r[5]; break;
+      case GS_DBG_DL_DCOLOR: o[3 * i] = r[6]; o[3 * i + 1] = r[7]; o[3 * i + 2] = r[8]; break;
+      default: return GS_EINVAL;
+    }
+  }
+  return GS_OK;
+}
+
+}  // extern "C"

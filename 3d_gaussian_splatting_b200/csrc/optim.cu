@@ -1,0 +1,185 @@
+// optim.cu — K5: fused Adam over the six parameter groups of
+// GaussianModel::setup (src/scene/gaussian_model.cpp:323-345) + densification statistics
+// (fields at src/scene/gaussian_model.h:18-20), and the L1 photometric loss.
+// Adam follows libtorch's Adam::step order with its defaults (only lr is set by the reference):
+//   m = m*b1 + g*(1-b1); v = v*b2 + g*g*(1-b2); denom = sqrt(v)/sqrt(1-b2^t) + eps;
+//   p -= lr/(1-b1^t) * m/denom.
+// Purely HBM-bound: 28 B per parameter float (+4 B when the gradient is re-zeroed); 16-byte
+// vector accesses, 4 independent vectors per thread in flight, no shared memory.
+#include "gs_common.cuh"
+
+#define AD_THREADS 256
+#define AD_VEC_PER_THREAD 4
+#define AD_FLOATS_PER_BLOCK (AD_THREADS * AD_VEC_PER_THREAD * 4)
+
+struct AdamSeg {
+  float* p;
+  float* g;
+  float* m;
+  float* v;
+  size_t n;         // floats in this segment
+  int block_start;  // first block of this segment
+  int vec_ok;       // all four pointers 16-byte aligned
+  float step_size, bc2_sqrt;
+};
+struct AdamArgs {
+  AdamSeg seg[6];
+  int stats_block_start, total_blocks;
+  float b1, b2, omb1, omb2, eps;
+  int zero_grads;
+  int N;
+  const int* radii;
+  const float* dL_dmeans2D;
+  int* max_radii2D;
+  float* xyz_grad_accum;
+  float* denom;
+};
+
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamArgs& a, const AdamSeg& s) {
+  const float mi = __fadd_rn(__fmul_rn(m, a.b1), __fmul_rn(g, a.omb1));
+  const float vi = __fadd_rn(__fmul_rn(v, a.b2), __fmul_rn(__fmul_rn(g, g), a.omb2));
+  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), s.bc2_sqrt), a.eps);
+  m = mi;
+  v = vi;
+  p = __fsub_rn(p, __fmul_rn(s.step_size, __fdiv_rn(mi, denom)));
+}
+
+__global__ void __launch_bounds__(AD_THREADS) adam_stats_kernel(const __grid_constant__ AdamArgs a) {
+  const int b = blockIdx.x;
+  if (b >= a.stats_block_start) {
+    // ---- densification statistics, one thread per Gaussian ----
+    const int i = (b - a.stats_block_start) * AD_THREADS + threadIdx.x;
+    if (i < a.N) {
+      const int r = a.radii[i];
+      if (r > 0) {
+        if (r > a.max_radii2D[i]) a.max_radii2D[i] = r;
+        const float2 g = reinterpret_cast<const float2*>(a.dL_dmeans2D)[i];
+        a.xyz_grad_accum[i] += __fsqrt_rn(__fadd_rn(__fmul_rn(g.x, g.x), __fmul_rn(g.y, g.y)));
+        a.denom[i] += 1.0f;
+      }
+    }
+    return;
+  }
+  int si = 0;
+#pragma unroll
+  for (int k = 1; k < 6; ++k)
+    if (b >= a.seg[k].block_start) si = k;
+  const AdamSeg& s = a.seg[si];
+  const size_t base = (size_t)(b - s.block_start) * AD_FLOATS_PER_BLOCK;
+  if (s.vec_ok && base + AD_FLOATS_PER_BLOCK <= s.n) {
+    float4 p[AD_VEC_PER_THREAD], g[AD_VEC_PER_THREAD], m[AD_VEC_PER_THREAD], v[AD_VEC_PER_THREAD];
+    const size_t v0 = base / 4 + threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
+      const size_t idx = v0 + (size_t)k * AD_THREADS;
+      p[k] = reinterpret_cast<const float4*>(s.p)[idx];
+      g[k] = reinterpret_cast<const float4*>(s.g)[idx];
+      m[k] = reinterpret_cast<const float4*>(s.m)[idx];
+      v[k] = reinterpret_cast<const float4*>(s.v)[idx];
+    }
+#pragma unroll
+    for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
+      adam_one(p[k].x, g[k].x, m[k].x, v[k].x, a, s);
+      adam_one(p[k].y, g[k].y, m[k].y, v[k].y, a, s);
+      adam_one(p[k].z, g[k].z, m[k].z, v[k].z, a, s);
+      adam_one(p[k].w, g[k].w, m[k].w, v[k].w, a, s);
+    }
+#pragma unroll
+    for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
+      const size_t idx = v0 + (size_t)k * AD_THREADS;
+      reinterpret_cast<float4*>(s.p)[idx] = p[k];
+      reinterpret_cast<float4*>(s.m)[idx] = m[k];
+      reinterpret_cast<float4*>(s.v)[idx] = v[k];
+      if (a.zero_grads) reinterpret_cast<float4*>(s.g)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  } else {
+    // ragged tail / unaligned segment: scalar, still coalesced
+    for (size_t idx = base + threadIdx.x; idx < s.n && idx < base + AD_FLOATS_PER_BLOCK; idx += AD_THREADS) {
+      float p = s.p[idx], m = s.m[idx], v = s.v[idx];
+      adam_one(p, s.g[idx], m, v, a, s);
+      s.p[idx] = p;
+      s.m[idx] = m;
+      s.v[idx] = v;
+      if (a.zero_grads) s.g[idx] = 0.f;
+    }
+  }
+}
+
+cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6], float* const exp_avg[6],
+                           float* const exp_avg_sq[6], const int widths[6], const float lr[6],
+                           const long long step[6], float beta1, float beta2, float eps, const int* radii,
+                           const float* dL_dmeans2D, int* max_radii2D, float* xyz_grad_accum, float* denom,
+                           int zero_grads, cudaStream_t stream) {
+  AdamArgs a;
+  int blocks = 0;
+  for (int s = 0; s < 6; ++s) {
+    AdamSeg& g = a.seg[s];
+    g.p = params[s];
+    g.g = grads[s];
+    g.m = exp_avg[s];
+    g.v = exp_avg_sq[s];
+    g.n = (params[s] && widths[s] > 0) ? (size_t)N * widths[s] : 0;
+    g.block_start = blocks;
+    g.vec_ok = ((((uintptr_t)g.p | (uintptr_t)g.g | (uintptr_t)g.m | (uintptr_t)g.v) & 15) == 0);
+    // libtorch evaluates the bias corrections in double and applies them as fp32 scalars
+    const double bc1 = 1.0 - pow((double)beta1, (double)step[s]);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step[s]);
+    g.step_size = (float)((double)lr[s] / bc1);
+    g.bc2_sqrt = (float)sqrt(bc2);
+    blocks += (int)((g.n + AD_FLOATS_PER_BLOCK - 1) / AD_FLOATS_PER_BLOCK);
+  }
+  a.stats_block_start = blocks;
+  const bool stats = radii && dL_dmeans2D && max_radii2D && xyz_grad_accum && denom;
+  if (stats) blocks += (N + AD_THREADS - 1) / AD_THREADS;
+  a.total_blocks = blocks;
+  a.b1 = beta1;
+  a.b2 = beta2;
+  a.omb1 = (float)(1.0 - (double)beta1);
+  a.omb2 = (float)(1.0 - (double)beta2);
+  a.eps = eps;
+  a.zero_grads = zero_grads;
+  a.N = N;
+  a.radii = radii;
+  a.dL_dmeans2D = dL_dmeans2D;
+  a.max_radii2D = max_radii2D;
+  a.xyz_grad_accum = xyz_grad_accum;
+  a.denom = denom;
+  if (blocks == 0) return cudaSuccess;
+  adam_stats_kernel<<<blocks, AD_THREADS, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
+// ---- L1 loss --------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+l1_loss_kernel(size_t n, const float* __restrict__ img, const float* __restrict__ gt, float scale,
+               float* __restrict__ dL_dimg, double* __restrict__ acc) {
+  float local = 0.f;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float d = img[i] - gt[i];
+    local += fabsf(d);
+    if (dL_dimg) dL_dimg[i] = d > 0.f ? scale : (d < 0.f ? -scale : 0.f);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  __shared__ float s_part[8];
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = local;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int k = 0; k < 8; ++k) t += s_part[k];
+    atomicAdd(acc, (double)t);
+  }
+}
+__global__ void loss_finalize_kernel(const double* acc, double inv_n, float* loss_out) {
+  *loss_out = (float)(acc[0] * inv_n);
+}
+
+cudaError_t gs_launch_l1_loss(size_t n, const float* img, const float* gt, float weight, float* dL_dimg, double* acc,
+                              float* loss_out, cudaStream_t stream) {
+  cudaError_t e = cudaMemsetAsync(acc, 0, sizeof(double), stream);
+  if (e != cudaSuccess) return e;
+  const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+  l1_loss_kernel<<<blocks > 0 ? blocks : 1, 256, 0, stream>>>(n, img, gt, weight / (float)n, dL_dimg, acc);
+  loss_finalize_kernel<<<1, 1, 0, stream>>>(acc, (double)weight / (double)n, loss_out);
+  return cudaGetLastError();
+}

@@ -1,0 +1,260 @@
+// preprocess.cu — K1: per-Gaussian frustum cull, EWA projection, conic, radius, tile
+// rectangle and SH -> RGB.  One thread per Gaussian.
+//
+// This translation unit is compiled with --fmad=false: every fp32 operation is rounded
+// individually and written in the same order as the CPU oracle, so that radii,
+// tiles_touched, depths (-> sort keys) and in practice all fp outputs are bit-identical.
+// cov3D follows the reference's parametrisation: q=(r,x,y,z) normalised inside
+// (src/utils/general_utils.cpp:12-40), L = R*diag(mod*s) (:88-99), Sigma = L*L^T packed
+// [xx,xy,xz,yy,yz,zz] (src/scene/gaussian_model.cpp:18-28).
+//
+// Memory: xyz/scale/rot/opacity are read straight from the reference's row-major (N,C)
+// tensors (a warp covers a contiguous span; L1 absorbs the stride-C pattern).  The SH rows
+// (up to 180 B per Gaussian) are staged through shared memory with fully coalesced loads and
+// an odd row pitch so the per-thread row reads are bank-conflict free.
+#include "gs_common.cuh"
+
+#define PP_THREADS 256
+
+struct PreprocessArgs {
+  gs_gaussians in;
+  int N;
+  GsGeom* geom;
+  float* depths;
+  int* radii;
+  uint32_t* tiles_touched;
+  uint8_t* clamped;
+  float focal_x, focal_y;
+  int gx, gy;
+  int rest_width;  // active SH floats per Gaussian beyond dc: 3*((deg+1)^2-1)
+  int rest_pitch;  // smem row pitch (odd)
+};
+
+__device__ __forceinline__ void cov3d_from_scale_rot(const float s[3], float mod, const float q[4], float c6[6]) {
+  float norm = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  float r = q[0] / norm, x = q[1] / norm, y = q[2] / norm, z = q[3] / norm;
+  float R00 = 1.0f - 2.0f * (y * y + z * z);
+  float R01 = 2.0f * (x * y - r * z);
+  float R02 = 2.0f * (x * z + r * y);
+  float R10 = 2.0f * (x * y + r * z);
+  float R11 = 1.0f - 2.0f * (x * x + z * z);
+  float R12 = 2.0f * (y * z - r * x);
+  float R20 = 2.0f * (x * z - r * y);
+  float R21 = 2.0f * (y * z + r * x);
+  float R22 = 1.0f - 2.0f * (x * x + y * y);
+  float s0 = mod * s[0], s1 = mod * s[1], s2 = mod * s[2];
+  float L00 = R00 * s0, L01 = R01 * s1, L02 = R02 * s2;
+  float L10 = R10 * s0, L11 = R11 * s1, L12 = R12 * s2;
+  float L20 = R20 * s0, L21 = R21 * s1, L22 = R22 * s2;
+  c6[0] = L00 * L00 + L01 * L01 + L02 * L02;
+  c6[1] = L00 * L10 + L01 * L11 + L02 * L12;
+  c6[2] = L00 * L20 + L01 * L21 + L02 * L22;
+  c6[3] = L10 * L10 + L11 * L11 + L12 * L12;
+  c6[4] = L10 * L20 + L11 * L21 + L12 * L22;
+  c6[5] = L20 * L20 + L21 * L21 + L22 * L22;
+}
+
+__device__ __forceinline__ void cov2d_ewa(const float t[3], float fx, float fy, float tanfovx, float tanfovy,
+                                          const float c6[6], const float* V, float abc[3]) {
+  float limx = GS_FOV_GUARD * tanfovx, limy = GS_FOV_GUARD * tanfovy;
+  float txtz = t[0] / t[2], tytz = t[1] / t[2];
+  float tx = fminf(limx, fmaxf(-limx, txtz)) * t[2];
+  float ty = fminf(limy, fmaxf(-limy, tytz)) * t[2];
+  float tz = t[2];
+  float J00 = fx / tz, J02 = -(fx * tx) / (tz * tz);
+  float J11 = fy / tz, J12 = -(fy * ty) / (tz * tz);
+  float T00 = J00 * V[0] + J02 * V[2];
+  float T01 = J00 * V[4] + J02 * V[6];
+  float T02 = J00 * V[8] + J02 * V[10];
+  float T10 = J11 * V[1] + J12 * V[2];
+  float T11 = J11 * V[5] + J12 * V[6];
+  float T12 = J11 * V[9] + J12 * V[10];
+  float c0 = c6[0], c1 = c6[1], c2 = c6[2], c3 = c6[3], c4 = c6[4], c5 = c6[5];
+  float U00 = c0 * T00 + c1 * T01 + c2 * T02;
+  float U01 = c1 * T00 + c3 * T01 + c4 * T02;
+  float U02 = c2 * T00 + c4 * T01 + c5 * T02;
+  float U10 = c0 * T10 + c1 * T11 + c2 * T12;
+  float U11 = c1 * T10 + c3 * T11 + c4 * T12;
+  float U12 = c2 * T10 + c4 * T11 + c5 * T12;
+  abc[0] = T00 * U00 + T01 * U01 + T02 * U02;
+  abc[1] = T00 * U10 + T01 * U11 + T02 * U12;
+  abc[2] = T10 * U10 + T11 * U11 + T12 * U12;
+}
+
+// s points at this Gaussian's staged "rest" row: s[3*(k-1)+c] is coefficient k, channel c.
+__device__ __forceinline__ void sh_to_rgb(int deg, const float p[3], const float campos[3], const float dc[3],
+                                          const float* s, float rgb[3], uint32_t& clamp_mask) {
+  float dx = p[0] - campos[0], dy = p[1] - campos[1], dz = p[2] - campos[2];
+  float len = sqrtf(dx * dx + dy * dy + dz * dz);
+  float x = dx / len, y = dy / len, z = dz / len;
+  clamp_mask = 0;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float res = GS_SH_C0 * dc[c];
+    if (deg > 0) {
+      res = res - GS_SH_C1 * y * s[0 + c] + GS_SH_C1 * z * s[3 + c] - GS_SH_C1 * x * s[6 + c];
+      if (deg > 1) {
+        float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        res = res + GS_SH_C2_0 * xy * s[9 + c] + GS_SH_C2_1 * yz * s[12 + c] +
+              GS_SH_C2_2 * (2.0f * zz - xx - yy) * s[15 + c] + GS_SH_C2_3 * xz * s[18 + c] +
+              GS_SH_C2_4 * (xx - yy) * s[21 + c];
+        if (deg > 2) {
+          res = res + GS_SH_C3_0 * y * (3.0f * xx - yy) * s[24 + c] + GS_SH_C3_1 * xy * z * s[27 + c] +
+                GS_SH_C3_2 * y * (4.0f * zz - xx - yy) * s[30 + c] +
+                GS_SH_C3_3 * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * s[33 + c] +
+                GS_SH_C3_4 * x * (4.0f * zz - xx - yy) * s[36 + c] + GS_SH_C3_5 * z * (xx - yy) * s[39 + c] +
+                GS_SH_C3_6 * x * (xx - 3.0f * yy) * s[42 + c];
+        }
+      }
+    }
+    res = res + 0.5f;
+    if (res < 0.0f) clamp_mask |= (1u << c);
+    rgb[c] = fmaxf(res, 0.0f);
+  }
+}
+
+__global__ void __launch_bounds__(PP_THREADS)
+preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreprocessArgs a) {
+  extern __shared__ float s_sh[];
+  const int tid = threadIdx.x;
+  const int row0 = blockIdx.x * PP_THREADS;
+  const int i = row0 + tid;
+  const int rows = min(PP_THREADS, a.N - row0);
+
+  // ---- stage the SH "rest" rows of this block: coalesced global reads, odd-pitch smem ----
+  if (a.rest_width > 0 && a.in.colors_precomp == nullptr) {
+    const int stride = a.in.sh_rest_stride;
+    const float* base = a.in.sh_rest + (size_t)row0 * stride;
+    const int total = (rows - 1) * stride + a.rest_width;  // never read past the last row
+    int row = tid / stride, col = tid % stride;
+    const int drow = PP_THREADS / stride, dcol = PP_THREADS % stride;
+    for (int f = tid; f < total; f += PP_THREADS) {
+      if (col < a.rest_width) s_sh[row * a.rest_pitch + col] = __ldg(base + f);
+      row += drow;
+      col += dcol;
+      if (col >= stride) { col -= stride; ++row; }
+    }
+  }
+  __syncthreads();
+  if (i >= a.N) return;
+
+  GsGeom g;
+  g.q0 = make_float4(0.f, 0.f, 0.f, 0.f);
+  g.q1 = g.q0;
+  g.q2 = g.q0;
+  int rad_out = 0;
+  uint32_t tiles = 0, cmask = 0;
+  float depth = 0.f;
+
+  const float p[3] = {a.in.means3D[3 * i], a.in.means3D[3 * i + 1], a.in.means3D[3 * i + 2]};
+  const float* V = st.viewmatrix;
+  const float* M = st.projmatrix;
+  float pv[3];
+  pv[0] = V[0] * p[0] + V[4] * p[1] + V[8] * p[2] + V[12];
+  pv[1] = V[1] * p[0] + V[5] * p[1] + V[9] * p[2] + V[13];
+  pv[2] = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
+  bool ok = pv[2] > GS_NEAR_Z;
+  if (ok) {
+    float ph[4];
+    ph[0] = M[0] * p[0] + M[4] * p[1] + M[8] * p[2] + M[12];
+    ph[1] = M[1] * p[0] + M[5] * p[1] + M[9] * p[2] + M[13];
+    ph[2] = M[2] * p[0] + M[6] * p[1] + M[10] * p[2] + M[14];
+    ph[3] = M[3] * p[0] + M[7] * p[1] + M[11] * p[2] + M[15];
+    float pw = 1.0f / (ph[3] + GS_W_EPS);
+    float ndc_x = ph[0] * pw, ndc_y = ph[1] * pw;
+
+    float c6[6];
+    if (a.in.cov3D_precomp) {
+#pragma unroll
+      for (int c = 0; c < 6; ++c) c6[c] = a.in.cov3D_precomp[6 * (size_t)i + c];
+    } else {
+      float s[3] = {a.in.scales[3 * i], a.in.scales[3 * i + 1], a.in.scales[3 * i + 2]};
+      const float4 q4 = *reinterpret_cast<const float4*>(a.in.rotations + 4 * (size_t)i);
+      float q[4] = {q4.x, q4.y, q4.z, q4.w};
+      if (a.in.raw_params) {
+        s[0] = expf(s[0]);
+        s[1] = expf(s[1]);
+        s[2] = expf(s[2]);
+      }
+      cov3d_from_scale_rot(s, st.scale_modifier, q, c6);
+    }
+    float abc[3];
+    cov2d_ewa(pv, a.focal_x, a.focal_y, st.tanfovx, st.tanfovy, c6, V, abc);
+    float ca = abc[0] + GS_DILATION, cb = abc[1], cc = abc[2] + GS_DILATION;
+    float det = ca * cc - cb * cb;
+    ok = det > 0.0f;
+    if (ok) {
+      float det_inv = 1.0f / det;
+      float con_x = cc * det_inv, con_y = -cb * det_inv, con_z = ca * det_inv;
+      float mid = 0.5f * (ca + cc);
+      float disc = sqrtf(fmaxf(GS_LAMBDA_FLOOR, mid * mid - det));
+      float lambda1 = mid + disc, lambda2 = mid - disc;
+      float rad_f = ceilf(3.0f * sqrtf(fmaxf(lambda1, lambda2)));
+      float px = ((ndc_x + 1.0f) * (float)st.W - 1.0f) * 0.5f;
+      float py = ((ndc_y + 1.0f) * (float)st.H - 1.0f) * 0.5f;
+      ok = (rad_f < 1e9f) && (fabsf(px) < 1e9f) && (fabsf(py) < 1e9f);
+      if (ok) {
+        int rad = (int)rad_f;
+        int x0 = (int)((px - (float)rad) / (float)GS_TILE);
+        int y0 = (int)((py - (float)rad) / (float)GS_TILE);
+        int x1 = (int)((px + (float)rad + (float)(GS_TILE - 1)) / (float)GS_TILE);
+        int y1 = (int)((py + (float)rad + (float)(GS_TILE - 1)) / (float)GS_TILE);
+        x0 = min(a.gx, max(0, x0));
+        x1 = min(a.gx, max(0, x1));
+        y0 = min(a.gy, max(0, y0));
+        y1 = min(a.gy, max(0, y1));
+        int area = (x1 - x0) * (y1 - y0);
+        if (area > 0) {
+          float rgb[3];
+          if (a.in.colors_precomp) {
+            rgb[0] = a.in.colors_precomp[3 * (size_t)i];
+            rgb[1] = a.in.colors_precomp[3 * (size_t)i + 1];
+            rgb[2] = a.in.colors_precomp[3 * (size_t)i + 2];
+          } else {
+            const float* dcp = a.in.sh_dc + (size_t)i * a.in.sh_dc_stride;
+            const float dc[3] = {__ldg(dcp), __ldg(dcp + 1), __ldg(dcp + 2)};
+            sh_to_rgb(st.sh_degree, p, st.campos, dc, s_sh + tid * a.rest_pitch, rgb, cmask);
+          }
+          float opac = a.in.opacities[i];
+          if (a.in.raw_params) opac = 1.0f / (1.0f + expf(-opac));
+          g.q0 = make_float4(px, py, 0.5f * con_x, con_y);
+          g.q1 = make_float4(0.5f * con_z, opac, rgb[0], rgb[1]);
+          g.q2 = make_float4(rgb[2], pv[2], 0.f, 0.f);
+          rad_out = rad;
+          tiles = (uint32_t)area;
+          depth = pv[2];
+        }
+      }
+    }
+  }
+  a.geom[i] = g;
+  a.depths[i] = depth;
+  a.radii[i] = rad_out;
+  a.tiles_touched[i] = tiles;
+  a.clamped[i] = (uint8_t)cmask;
+}
+
+cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, int N, GsGeom* geom, float* depths,
+                                 int* radii, uint32_t* tiles_touched, uint8_t* clamped, cudaStream_t stream) {
+  if (N == 0) return cudaSuccess;
+  PreprocessArgs a;
+  a.in = in;
+  a.N = N;
+  a.geom = geom;
+  a.depths = depths;
+  a.radii = radii;
+  a.tiles_touched = tiles_touched;
+  a.clamped = clamped;
+  a.focal_x = (float)st.W / (2.0f * st.tanfovx);
+  a.focal_y = (float)st.H / (2.0f * st.tanfovy);
+  a.gx = (st.W + GS_TILE - 1) / GS_TILE;
+  a.gy = (st.H + GS_TILE - 1) / GS_TILE;
+  const int kact = (st.sh_degree + 1) * (st.sh_degree + 1);
+  a.rest_width = in.colors_precomp ? 0 : 3 * (kact - 1);
+  a.rest_pitch = a.rest_width | 1;
+  size_t smem = (size_t)PP_THREADS * a.rest_pitch * sizeof(float);
+  if (a.rest_width == 0) smem = 0;
+  const int blocks = (N + PP_THREADS - 1) / PP_THREADS;
+  preprocess_kernel<<<blocks, PP_THREADS, smem, stream>>>(st, a);
+  return cudaGetLastError();
+}

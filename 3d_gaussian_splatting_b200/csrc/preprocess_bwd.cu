@@ -1,0 +1,389 @@
+// preprocess_bwd.cu — K4b: backward of the per-Gaussian preprocess.
+// conic -> cov2D -> (cov3D, view-space mean); mean2D -> mean3D; SH backward; cov3D ->
+// (scale, quaternion) through the reference's parametrisation (q normalised inside,
+// src/utils/general_utils.cpp:14-19; L = R diag(s), Sigma = L L^T, gaussian_model.cpp:18-28).
+// One thread per Gaussian; SH rows are staged through shared memory in both directions so the
+// 180-byte-per-Gaussian reads and gradient writes are coalesced.  With raw_params the
+// activation Jacobians (exp, sigmoid) are applied here too.
+#include "gs_common.cuh"
+
+#define PB_THREADS 256
+
+struct PreBwdArgs {
+  gs_gaussians in;
+  gs_gradients out;
+  int N;
+  const int* radii;
+  const uint8_t* clamped;
+  const float4* grad_geom;
+  float focal_x, focal_y;
+  int rest_width_act;  // 3*((deg+1)^2-1)
+  int rest_width_max;  // 3*((maxdeg+1)^2-1)
+  int pitch;           // odd, >= rest_width_max
+};
+
+__global__ void __launch_bounds__(PB_THREADS)
+preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a) {
+  extern __shared__ float s_sh[];
+  const int tid = threadIdx.x;
+  const int row0 = blockIdx.x * PB_THREADS;
+  const int i = row0 + tid;
+  const int rows = min(PB_THREADS, a.N - row0);
+  const bool use_sh = a.in.colors_precomp == nullptr;
+
+  if (use_sh && a.rest_width_act > 0) {
+    const int stride = a.in.sh_rest_stride;
+    const float* base = a.in.sh_rest + (size_t)row0 * stride;
+    const int total = (rows - 1) * stride + a.rest_width_act;
+    int row = tid / stride, col = tid % stride;
+    const int drow = PB_THREADS / stride, dcol = PB_THREADS % stride;
+    for (int f = tid; f < total; f += PB_THREADS) {
+      if (col < a.rest_width_act) s_sh[row * a.pitch + col] = __ldg(base + f);
+      row += drow;
+      col += dcol;
+      if (col >= stride) { col -= stride; ++row; }
+    }
+  }
+  __syncthreads();
+
+  float gm[3] = {0.f, 0.f, 0.f}, gs[3] = {0.f, 0.f, 0.f}, gq[4] = {0.f, 0.f, 0.f, 0.f};
+  float gcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float gdc[3] = {0.f, 0.f, 0.f}, gcol[3] = {0.f, 0.f, 0.f};
+  float g2x = 0.f, g2y = 0.f, gop = 0.f;
+  float basis[15], gr[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < 15; ++k) basis[k] = 0.f;
+  float* srow = s_sh + tid * a.pitch;
+  bool visible = false;
+
+  if (i < a.N) visible = a.radii[i] > 0;
+  if (visible) {
+    const float4 G0 = a.grad_geom[3 * (size_t)i], G1 = a.grad_geom[3 * (size_t)i + 1];
+    const float G2x = a.grad_geom[3 * (size_t)i + 2].x;
+    g2x = G0.x;
+    g2y = G0.y;
+    const float gA = G0.z, gB = G0.w, gC = G1.x;
+    gop = G1.y;
+    gcol[0] = G1.z;
+    gcol[1] = G1.w;
+    gcol[2] = G2x;
+    const float p[3] = {a.in.means3D[3 * i], a.in.means3D[3 * i + 1], a.in.means3D[3 * i + 2]};
+    const float* V = st.viewmatrix;
+    const float* M = st.projmatrix;
+    float t[3];
+    t[0] = V[0] * p[0] + V[4] * p[1] + V[8] * p[2] + V[12];
+    t[1] = V[1] * p[0] + V[5] * p[1] + V[9] * p[2] + V[13];
+    t[2] = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
+    // ---- recompute cov3D ----
+    float c6[6], qn[4] = {1.f, 0.f, 0.f, 0.f}, qlen = 1.f, R[9], sm[3] = {0.f, 0.f, 0.f}, sact[3] = {0.f, 0.f, 0.f};
+    const bool own_cov = a.in.cov3D_precomp == nullptr;
+    if (!own_cov) {
+#pragma unroll
+      for (int c = 0; c < 6; ++c) c6[c] = a.in.cov3D_precomp[6 * (size_t)i + c];
+    } else {
+      const float4 q4 = *reinterpret_cast<const float4*>(a.in.rotations + 4 * (size_t)i);
+      const float q[4] = {q4.x, q4.y, q4.z, q4.w};
+      qlen = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) qn[c] = q[c] / qlen;
+      const float r = qn[0], x = qn[1], y = qn[2], z = qn[3];
+      R[0] = 1.f - 2.f * (y * y + z * z); R[1] = 2.f * (x * y - r * z); R[2] = 2.f * (x * z + r * y);
+      R[3] = 2.f * (x * y + r * z); R[4] = 1.f - 2.f * (x * x + z * z); R[5] = 2.f * (y * z - r * x);
+      R[6] = 2.f * (x * z - r * y); R[7] = 2.f * (y * z + r * x); R[8] = 1.f - 2.f * (x * x + y * y);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float sv = a.in.scales[3 * i + c];
+        if (a.in.raw_params) sv = expf(sv);
+        sact[c] = sv;
+        sm[c] = st.scale_modifier * sv;
+      }
+      float L[9];
+#pragma unroll
+      for (int r2 = 0; r2 < 3; ++r2)
+#pragma unroll
+        for (int c2 = 0; c2 < 3; ++c2) L[3 * r2 + c2] = R[3 * r2 + c2] * sm[c2];
+      c6[0] = L[0] * L[0] + L[1] * L[1] + L[2] * L[2];
+      c6[1] = L[0] * L[3] + L[1] * L[4] + L[2] * L[5];
+      c6[2] = L[0] * L[6] + L[1] * L[7] + L[2] * L[8];
+      c6[3] = L[3] * L[3] + L[4] * L[4] + L[5] * L[5];
+      c6[4] = L[3] * L[6] + L[4] * L[7] + L[5] * L[8];
+      c6[5] = L[6] * L[6] + L[7] * L[7] + L[8] * L[8];
+    }
+    // ---- recompute EWA ----
+    const float limx = GS_FOV_GUARD * st.tanfovx, limy = GS_FOV_GUARD * st.tanfovy;
+    const float txtz = t[0] / t[2], tytz = t[1] / t[2];
+    const bool x_free = !(txtz < -limx || txtz > limx), y_free = !(tytz < -limy || tytz > limy);
+    const float tx = fminf(limx, fmaxf(-limx, txtz)) * t[2];
+    const float ty = fminf(limy, fmaxf(-limy, tytz)) * t[2];
+    const float tz = t[2];
+    const float fx = a.focal_x, fy = a.focal_y;
+    const float J00 = fx / tz, J02 = -(fx * tx) / (tz * tz);
+    const float J11 = fy / tz, J12 = -(fy * ty) / (tz * tz);
+    const float W0[3] = {V[0], V[4], V[8]}, W1[3] = {V[1], V[5], V[9]}, W2[3] = {V[2], V[6], V[10]};
+    float T0[3], T1[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      T0[c] = J00 * W0[c] + J02 * W2[c];
+      T1[c] = J11 * W1[c] + J12 * W2[c];
+    }
+    const float S[3][3] = {{c6[0], c6[1], c6[2]}, {c6[1], c6[3], c6[4]}, {c6[2], c6[4], c6[5]}};
+    float U0[3], U1[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      U0[c] = S[c][0] * T0[0] + S[c][1] * T0[1] + S[c][2] * T0[2];
+      U1[c] = S[c][0] * T1[0] + S[c][1] * T1[1] + S[c][2] * T1[2];
+    }
+    const float ca = T0[0] * U0[0] + T0[1] * U0[1] + T0[2] * U0[2] + GS_DILATION;
+    const float cb = T0[0] * U1[0] + T0[1] * U1[1] + T0[2] * U1[2];
+    const float cc = T1[0] * U1[0] + T1[1] * U1[1] + T1[2] * U1[2] + GS_DILATION;
+    const float det = ca * cc - cb * cb;
+    // ---- conic -> cov2D ----
+    const float d2 = 1.0f / (det * det);
+    const float ga = d2 * (-cc * cc * gA + cb * cc * gB - cb * cb * gC);
+    const float gb = d2 * (2.f * cb * cc * gA - (ca * cc + cb * cb) * gB + 2.f * ca * cb * gC);
+    const float gc = d2 * (-cb * cb * gA + ca * cb * gB - ca * ca * gC);
+    // ---- cov2D -> cov3D ----
+    gcov[0] = T0[0] * T0[0] * ga + T0[0] * T1[0] * gb + T1[0] * T1[0] * gc;
+    gcov[3] = T0[1] * T0[1] * ga + T0[1] * T1[1] * gb + T1[1] * T1[1] * gc;
+    gcov[5] = T0[2] * T0[2] * ga + T0[2] * T1[2] * gb + T1[2] * T1[2] * gc;
+    gcov[1] = 2.f * T0[0] * T0[1] * ga + (T0[0] * T1[1] + T0[1] * T1[0]) * gb + 2.f * T1[0] * T1[1] * gc;
+    gcov[2] = 2.f * T0[0] * T0[2] * ga + (T0[0] * T1[2] + T0[2] * T1[0]) * gb + 2.f * T1[0] * T1[2] * gc;
+    gcov[4] = 2.f * T0[1] * T0[2] * ga + (T0[1] * T1[2] + T0[2] * T1[1]) * gb + 2.f * T1[1] * T1[2] * gc;
+    // ---- cov2D -> T -> J -> t ----
+    float gT0[3], gT1[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      gT0[k] = 2.f * ga * U0[k] + gb * U1[k];
+      gT1[k] = gb * U0[k] + 2.f * gc * U1[k];
+    }
+    const float gJ00 = gT0[0] * W0[0] + gT0[1] * W0[1] + gT0[2] * W0[2];
+    const float gJ02 = gT0[0] * W2[0] + gT0[1] * W2[1] + gT0[2] * W2[2];
+    const float gJ11 = gT1[0] * W1[0] + gT1[1] * W1[1] + gT1[2] * W1[2];
+    const float gJ12 = gT1[0] * W2[0] + gT1[1] * W2[1] + gT1[2] * W2[2];
+    const float tz2 = 1.0f / (tz * tz), tz3 = tz2 / tz;
+    const float gtx = x_free ? -fx * tz2 * gJ02 : 0.f;
+    const float gty = y_free ? -fy * tz2 * gJ12 : 0.f;
+    const float kx = x_free ? 2.f : 1.f, ky = y_free ? 2.f : 1.f;
+    const float gtz = -fx * tz2 * gJ00 - fy * tz2 * gJ11 + kx * fx * tx * tz3 * gJ02 + ky * fy * ty * tz3 * gJ12;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) gm[c] = W0[c] * gtx + W1[c] * gty + W2[c] * gtz;
+    // ---- mean2D -> mean3D ----
+    float ph[4];
+#pragma unroll
+    for (int r2 = 0; r2 < 4; ++r2) ph[r2] = M[r2] * p[0] + M[4 + r2] * p[1] + M[8 + r2] * p[2] + M[12 + r2];
+    const float pw = 1.0f / (ph[3] + GS_W_EPS);
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const float dndcx = M[4 * j + 0] * pw - M[4 * j + 3] * ph[0] * pw * pw;
+      const float dndcy = M[4 * j + 1] * pw - M[4 * j + 3] * ph[1] * pw * pw;
+      gm[j] += g2x * dndcx + g2y * dndcy;
+    }
+    // ---- SH backward (row staged in smem is overwritten by its own gradient) ----
+    if (use_sh) {
+      const int deg = st.sh_degree;
+      const uint32_t cm = a.clamped[i];
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) gr[ch] = ((cm >> ch) & 1u) ? 0.f : gcol[ch];
+      const float dvx = p[0] - st.campos[0], dvy = p[1] - st.campos[1], dvz = p[2] - st.campos[2];
+      const float len = sqrtf(dvx * dvx + dvy * dvy + dvz * dvz);
+      const float x = dvx / len, y = dvy / len, z = dvz / len;
+      float ddx = 0.f, ddy = 0.f, ddz = 0.f;
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) gdc[ch] = GS_SH_C0 * gr[ch];
+      if (deg > 0) {
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        basis[0] = -GS_SH_C1 * y; basis[1] = GS_SH_C1 * z; basis[2] = -GS_SH_C1 * x;
+        if (deg > 1) {
+          basis[3] = GS_SH_C2_0 * xy; basis[4] = GS_SH_C2_1 * yz; basis[5] = GS_SH_C2_2 * (2.f * zz - xx - yy);
+          basis[6] = GS_SH_C2_3 * xz; basis[7] = GS_SH_C2_4 * (xx - yy);
+        }
+        if (deg > 2) {
+          basis[8] = GS_SH_C3_0 * y * (3.f * xx - yy);
+          basis[9] = GS_SH_C3_1 * xy * z;
+          basis[10] = GS_SH_C3_2 * y * (4.f * zz - xx - yy);
+          basis[11] = GS_SH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+          basis[12] = GS_SH_C3_4 * x * (4.f * zz - xx - yy);
+          basis[13] = GS_SH_C3_5 * z * (xx - yy);
+          basis[14] = GS_SH_C3_6 * x * (xx - 3.f * yy);
+        }
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+          const float g = gr[ch];
+          const float s1 = srow[0 + ch], s2 = srow[3 + ch], s3 = srow[6 + ch];
+          float ax = -GS_SH_C1 * s3, ay = -GS_SH_C1 * s1, az = GS_SH_C1 * s2;
+          if (deg > 1) {
+            const float s4 = srow[9 + ch], s5 = srow[12 + ch], s6 = srow[15 + ch], s7 = srow[18 + ch],
+                        s8 = srow[21 + ch];
+            ax += GS_SH_C2_0 * y * s4 + GS_SH_C2_2 * -2.f * x * s6 + GS_SH_C2_3 * z * s7 + GS_SH_C2_4 * 2.f * x * s8;
+            ay += GS_SH_C2_0 * x * s4 + GS_SH_C2_1 * z * s5 + GS_SH_C2_2 * -2.f * y * s6 + GS_SH_C2_4 * -2.f * y * s8;
+            az += GS_SH_C2_1 * y * s5 + GS_SH_C2_2 * 4.f * z * s6 + GS_SH_C2_3 * x * s7;
+            if (deg > 2) {
+              const float s9 = srow[24 + ch], s10 = srow[27 + ch], s11 = srow[30 + ch], s12 = srow[33 + ch],
+                          s13 = srow[36 + ch], s14 = srow[39 + ch], s15 = srow[42 + ch];
+              ax += GS_SH_C3_0 * 6.f * xy * s9 + GS_SH_C3_1 * yz * s10 + GS_SH_C3_2 * -2.f * xy * s11 +
+                    GS_SH_C3_3 * -6.f * xz * s12 + GS_SH_C3_4 * (4.f * zz - 3.f * xx - yy) * s13 +
+                    GS_SH_C3_5 * 2.f * xz * s14 + GS_SH_C3_6 * (3.f * xx - 3.f * yy) * s15;
+              ay += GS_SH_C3_0 * (3.f * xx - 3.f * yy) * s9 + GS_SH_C3_1 * xz * s10 +
+                    GS_SH_C3_2 * (4.f * zz - xx - 3.f * yy) * s11 + GS_SH_C3_3 * -6.f * yz * s12 +
+                    GS_SH_C3_4 * -2.f * xy * s13 + GS_SH_C3_5 * -2.f * yz * s14 + GS_SH_C3_6 * -6.f * xy * s15;
+              az += GS_SH_C3_1 * xy * s10 + GS_SH_C3_2 * 8.f * yz * s11 +
+                    GS_SH_C3_3 * (6.f * zz - 3.f * xx - 3.f * yy) * s12 + GS_SH_C3_4 * 8.f * xz * s13 +
+                    GS_SH_C3_5 * (xx - yy) * s14;
+            }
+          }
+          ddx += ax * g;
+          ddy += ay * g;
+          ddz += az * g;
+        }
+        const float dot = x * ddx + y * ddy + z * ddz;
+        gm[0] += (ddx - x * dot) / len;
+        gm[1] += (ddy - y * dot) / len;
+        gm[2] += (ddz - z * dot) / len;
+      }
+    }
+    // ---- cov3D -> scale, quaternion ----
+    if (own_cov) {
+      const float GS[3][3] = {{gcov[0], 0.5f * gcov[1], 0.5f * gcov[2]},
+                              {0.5f * gcov[1], gcov[3], 0.5f * gcov[4]},
+                              {0.5f * gcov[2], 0.5f * gcov[4], gcov[5]}};
+      float gL[9], gR[9];
+#pragma unroll
+      for (int a2 = 0; a2 < 3; ++a2)
+#pragma unroll
+        for (int b2 = 0; b2 < 3; ++b2) {
+          float acc = 0.f;
+#pragma unroll
+          for (int k = 0; k < 3; ++k) acc += GS[a2][k] * (R[3 * k + b2] * sm[b2]);
+          gL[3 * a2 + b2] = 2.f * acc;
+        }
+#pragma unroll
+      for (int b2 = 0; b2 < 3; ++b2) {
+        float acc = 0.f;
+#pragma unroll
+        for (int a2 = 0; a2 < 3; ++a2) acc += gL[3 * a2 + b2] * R[3 * a2 + b2];
+        gs[b2] = st.scale_modifier * acc;
+        if (a.in.raw_params) gs[b2] *= sact[b2];  // d exp(raw)/d raw = exp(raw)
+      }
+#pragma unroll
+      for (int a2 = 0; a2 < 3; ++a2)
+#pragma unroll
+        for (int b2 = 0; b2 < 3; ++b2) gR[3 * a2 + b2] = gL[3 * a2 + b2] * sm[b2];
+      const float r = qn[0], x = qn[1], y = qn[2], z = qn[3];
+      float gn[4];
+      gn[0] = 2.f * (-z * gR[1] + y * gR[2] + z * gR[3] - x * gR[5] - y * gR[6] + x * gR[7]);
+      gn[1] = 2.f * (y * gR[1] + z * gR[2] + y * gR[3] - 2.f * x * gR[4] - r * gR[5] + z * gR[6] + r * gR[7] -
+                     2.f * x * gR[8]);
+      gn[2] = 2.f * (-2.f * y * gR[0] + x * gR[1] + r * gR[2] + x * gR[3] + z * gR[5] - r * gR[6] + z * gR[7] -
+                     2.f * y * gR[8]);
+      gn[3] = 2.f * (-2.f * z * gR[0] - r * gR[1] + x * gR[2] + r * gR[3] - 2.f * z * gR[4] + y * gR[5] +
+                     x * gR[6] + y * gR[7]);
+      const float dotq = qn[0] * gn[0] + qn[1] * gn[1] + qn[2] * gn[2] + qn[3] * gn[3];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) gq[k] = (gn[k] - qn[k] * dotq) / qlen;
+    }
+    if (a.in.raw_params) {
+      const float o = 1.0f / (1.0f + expf(-a.in.opacities[i]));
+      gop *= o * (1.0f - o);
+    }
+  }
+
+  // ---- outputs ----
+  const bool acc = a.out.accumulate != 0;
+  if (i < a.N) {
+    if (a.out.dL_dmeans3D) {
+      float* o = a.out.dL_dmeans3D + 3 * (size_t)i;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o[c] = acc ? o[c] + gm[c] : gm[c];
+    }
+    if (a.out.dL_dscales) {
+      float* o = a.out.dL_dscales + 3 * (size_t)i;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o[c] = acc ? o[c] + gs[c] : gs[c];
+    }
+    if (a.out.dL_drotations) {
+      float4* o = reinterpret_cast<float4*>(a.out.dL_drotations + 4 * (size_t)i);
+      float4 v = make_float4(gq[0], gq[1], gq[2], gq[3]);
+      if (acc) { const float4 u = *o; v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w; }
+      *o = v;
+    }
+    if (a.out.dL_dopacities) {
+      float* o = a.out.dL_dopacities + i;
+      *o = acc ? *o + gop : gop;
+    }
+    if (a.out.dL_dmeans2D) {
+      float2* o = reinterpret_cast<float2*>(a.out.dL_dmeans2D + 2 * (size_t)i);
+      float2 v = make_float2(g2x, g2y);
+      if (acc) { const float2 u = *o; v.x += u.x; v.y += u.y; }
+      *o = v;
+    }
+    if (a.out.dL_dcov3D) {
+      float* o = a.out.dL_dcov3D + 6 * (size_t)i;
+#pragma unroll
+      for (int c = 0; c < 6; ++c) o[c] = acc ? o[c] + gcov[c] : gcov[c];
+    }
+    if (a.out.dL_dcolors) {
+      float* o = a.out.dL_dcolors + 3 * (size_t)i;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o[c] = acc ? o[c] + gcol[c] : gcol[c];
+    }
+    if (use_sh && a.out.dL_dsh_dc) {
+      float* o = a.out.dL_dsh_dc + (size_t)i * a.out.sh_dc_stride;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o[c] = acc ? o[c] + gdc[c] : gdc[c];
+    }
+    // this thread's smem row <- SH gradient of the "rest" coefficients (zeros when inactive)
+    if (use_sh && a.out.dL_dsh_rest && a.rest_width_max > 0) {
+      const int kmax = a.rest_width_max / 3;
+#pragma unroll
+      for (int k = 0; k < 15; ++k)
+        if (k < kmax) {
+#pragma unroll
+          for (int ch = 0; ch < 3; ++ch) srow[3 * k + ch] = basis[k] * gr[ch];
+        }
+    }
+  }
+  if (!(use_sh && a.out.dL_dsh_rest && a.rest_width_max > 0)) return;
+  __syncthreads();
+  {
+    const int stride = a.out.sh_rest_stride;
+    float* base = a.out.dL_dsh_rest + (size_t)row0 * stride;
+    const int width = acc ? a.rest_width_act : a.rest_width_max;  // accumulate: inactive rows add 0
+    if (width == 0) return;
+    const int total = (rows - 1) * stride + width;
+    int row = tid / stride, col = tid % stride;
+    const int drow = PB_THREADS / stride, dcol = PB_THREADS % stride;
+    for (int f = tid; f < total; f += PB_THREADS) {
+      if (col < width) {
+        const float v = s_sh[row * a.pitch + col];
+        base[f] = acc ? base[f] + v : v;
+      }
+      row += drow;
+      col += dcol;
+      if (col >= stride) { col -= stride; ++row; }
+    }
+  }
+}
+
+cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussians& in, const gs_gradients& out, int N,
+                                          const int* radii, const uint8_t* clamped, const float4* grad_geom,
+                                          cudaStream_t stream) {
+  if (N == 0) return cudaSuccess;
+  PreBwdArgs a;
+  a.in = in;
+  a.out = out;
+  a.N = N;
+  a.radii = radii;
+  a.clamped = clamped;
+  a.grad_geom = grad_geom;
+  a.focal_x = (float)st.W / (2.0f * st.tanfovx);
+  a.focal_y = (float)st.H / (2.0f * st.tanfovy);
+  const int kact = (st.sh_degree + 1) * (st.sh_degree + 1);
+  const int kmax = (st.max_sh_degree + 1) * (st.max_sh_degree + 1);
+  a.rest_width_act = in.colors_precomp ? 0 : 3 * (kact - 1);
+  a.rest_width_max = in.colors_precomp ? 0 : 3 * (kmax - 1);
+  a.pitch = a.rest_width_max | 1;
+  const size_t smem = a.rest_width_max > 0 ? (size_t)PB_THREADS * a.pitch * sizeof(float) : 0;
+  const int blocks = (N + PB_THREADS - 1) / PB_THREADS;
+  preprocess_backward_kernel<<<blocks, PB_THREADS, smem, stream>>>(st, a);
+  return cudaGetLastError();
+}

@@ -1,0 +1,62 @@
+/*
+ * oracle/orc_optim.c — TEST INFRASTRUCTURE (see orc_common.h header).
+ * Stage K5: Adam update and densification statistics, plus the L1 photometric
+ * loss used by the train step.
+ *   Adam: the reference builds six torch::optim::Adam with only `lr` set
+ *         (src/scene/gaussian_model.cpp:323-345) => libtorch defaults beta=(0.9,0.999),
+ *         eps=1e-8, no weight decay, no amsgrad.  The update order restated here is
+ *         libtorch's Adam::step: m = m*b1 + g*(1-b1); v = v*b2 + g*g*(1-b2);
+ *         denom = sqrt(v)/sqrt(1-b2^t) + eps; p -= (lr/(1-b1^t)) * m / denom, with the bias
+ *         corrections evaluated in double and applied as fp32 scalars.
+ *         Pinned against torch.optim.Adam on CPU in tests/test_oracle_optim.py.
+ *   Stats: fields max_radii2D_, xyz_gradient_accum_, denom_ (src/scene/gaussian_model.h:18-20).
+ */
+#include "orc_common.h"
+
+void orc_adam_step(size_t n, float *p, const float *g, float *m, float *v, double lr, double beta1,
+                   double beta2, double eps, long long step) {
+  const double bc1 = 1.0 - pow(beta1, (double)step);
+  const double bc2 = 1.0 - pow(beta2, (double)step);
+  const float b1 = (float)beta1, b2 = (float)beta2;
+  const float omb1 = (float)(1.0 - beta1), omb2 = (float)(1.0 - beta2);
+  const float bc2_sqrt = (float)sqrt(bc2);
+  const float step_size = (float)(lr / bc1);
+  const float epsf = (float)eps;
+#pragma omp parallel for schedule(static)
+  for (size_t i = 0; i < n; ++i) {
+    const float gi = g[i];
+    const float mi = m[i] * b1 + gi * omb1;
+    const float vi = v[i] * b2 + (gi * gi) * omb2;
+    const float denom = sqrtf(vi) / bc2_sqrt + epsf;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] = p[i] - step_size * (mi / denom);
+  }
+}
+
+void orc_densify_stats(int N, const int *radii, const float *dL_dmean2D, int *max_radii2D, float *xyz_grad_accum,
+                       float *denom) {
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < N; ++i) {
+    if (radii[i] > 0) {
+      if (radii[i] > max_radii2D[i]) max_radii2D[i] = radii[i];
+      const float gx = dL_dmean2D[2 * i], gy = dL_dmean2D[2 * i + 1];
+      xyz_grad_accum[i] += sqrtf(gx * gx + gy * gy);
+      denom[i] += 1.0f;
+    }
+  }
+}
+
+/* L1 loss = mean |img - gt| over 3*H*W; dL/dimg = sign(img - gt) / (3*H*W).
+ * (lambda_dssim_ of src/arguments/params.h:62 weights the D-SSIM term, a "next" row.) */
+double orc_l1_loss(size_t n, const real *img, const real *gt, real *dL_dimg) {
+  double acc = 0;
+  const real inv = RC(1) / RC(n);
+#pragma omp parallel for schedule(static) reduction(+ : acc)
+  for (size_t i = 0; i < n; ++i) {
+    const real d = img[i] - gt[i];
+    acc += (double)R_FABS(d);
+    if (dL_dimg) dL_dimg[i] = d > 0 ? inv : (d < 0 ? -inv : RC(0));
+  }
+  return acc / (double)n;
+}
