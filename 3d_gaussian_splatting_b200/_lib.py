@@ -81,8 +81,8 @@ def _load() -> C.CDLL:
     lib.gs_destroy.restype = None
     lib.gs_forward.argtypes = [vp, C.POINTER(GsSettings), i, C.POINTER(GsGaussians), vp, vp, vp]
     lib.gs_backward.argtypes = [vp, C.POINTER(GsSettings), i, C.POINTER(GsGaussians), vp, C.POINTER(GsGradients), vp]
-    lib.gs_adam_densify_step.argtypes = [vp, i, vp * 6, vp * 6, vp * 6, vp * 6, i * 6, f * 6, C.c_longlong * 6,
-                                         f, f, f, vp, vp, vp, vp, vp, i, vp]
+    lib.gs_adam_densify_step.argtypes = [vp, i, vp * 6, vp * 6, vp * 6, vp * 6, i * 6, d * 6, C.c_longlong * 6,
+                                         d, d, d, vp, vp, vp, vp, vp, i, vp]
     lib.gs_loss.argtypes = [vp, i, i, vp, vp, f, vp, vp, vp]
     lib.gs_debug_size.argtypes = [vp, i]
     lib.gs_debug_size.restype = C.c_longlong

@@ -29,7 +29,7 @@ cudaError_t gs_launch_blend_backward(const GsDims&, const uint2*, const uint32_t
 cudaError_t gs_launch_preprocess_backward(const gs_settings&, const gs_gaussians&, const gs_gradients&, int,
                                           const int*, const uint8_t*, const float4*, cudaStream_t);
 cudaError_t gs_launch_adam(int, float* const[6], float* const[6], float* const[6], float* const[6], const int[6],
-                           const float[6], const long long[6], float, float, float, const int*, const float*, int*,
+                           const double[6], const long long[6], double, double, double, const int*, const float*, int*,
                            float*, float*, int, cudaStream_t);
 cudaError_t gs_launch_l1_loss(size_t, const float*, const float*, float, float*, double*, float*, cudaStream_t);
 
@@ -381,8 +381,8 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
 }
 
 int gs_adam_densify_step(gs_ctx* c, int N, float* const params[6], float* const grads[6], float* const exp_avg[6],
-                         float* const exp_avg_sq[6], const int widths[6], const float lr[6], const long long step[6],
-                         float beta1, float beta2, float eps, const int* radii, const float* dL_dmeans2D,
+                         float* const exp_avg_sq[6], const int widths[6], const double lr[6], const long long step[6],
+                         double beta1, double beta2, double eps, const int* radii, const float* dL_dmeans2D,
                          int* max_radii2D, float* xyz_grad_accum, float* denom, int zero_grads, void* stream_) {
   if (!c || N < 0 || !params || !grads || !exp_avg || !exp_avg_sq || !widths || !lr || !step) {
     gs_set_error(c, "gs_adam_densify_step: null argument");

@@ -106,8 +106,8 @@ __global__ void __launch_bounds__(AD_THREADS) adam_stats_kernel(const __grid_con
 }
 
 cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6], float* const exp_avg[6],
-                           float* const exp_avg_sq[6], const int widths[6], const float lr[6],
-                           const long long step[6], float beta1, float beta2, float eps, const int* radii,
+                           float* const exp_avg_sq[6], const int widths[6], const double lr[6],
+                           const long long step[6], double beta1, double beta2, double eps, const int* radii,
                            const float* dL_dmeans2D, int* max_radii2D, float* xyz_grad_accum, float* denom,
                            int zero_grads, cudaStream_t stream) {
   AdamArgs a;
@@ -122,9 +122,9 @@ cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6],
     g.block_start = blocks;
     g.vec_ok = ((((uintptr_t)g.p | (uintptr_t)g.g | (uintptr_t)g.m | (uintptr_t)g.v) & 15) == 0);
     // libtorch evaluates the bias corrections in double and applies them as fp32 scalars
-    const double bc1 = 1.0 - pow((double)beta1, (double)step[s]);
-    const double bc2 = 1.0 - pow((double)beta2, (double)step[s]);
-    g.step_size = (float)((double)lr[s] / bc1);
+    const double bc1 = 1.0 - pow(beta1, (double)step[s]);
+    const double bc2 = 1.0 - pow(beta2, (double)step[s]);
+    g.step_size = (float)(lr[s] / bc1);
     g.bc2_sqrt = (float)sqrt(bc2);
     blocks += (int)((g.n + AD_FLOATS_PER_BLOCK - 1) / AD_FLOATS_PER_BLOCK);
   }
@@ -132,11 +132,11 @@ cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6],
   const bool stats = radii && dL_dmeans2D && max_radii2D && xyz_grad_accum && denom;
   if (stats) blocks += (N + AD_THREADS - 1) / AD_THREADS;
   a.total_blocks = blocks;
-  a.b1 = beta1;
-  a.b2 = beta2;
-  a.omb1 = (float)(1.0 - (double)beta1);
-  a.omb2 = (float)(1.0 - (double)beta2);
-  a.eps = eps;
+  a.b1 = (float)beta1;
+  a.b2 = (float)beta2;
+  a.omb1 = (float)(1.0 - beta1);
+  a.omb2 = (float)(1.0 - beta2);
+  a.eps = (float)eps;
   a.zero_grads = zero_grads;
   a.N = N;
   a.radii = radii;

@@ -1,0 +1,196 @@
+"""Host-side mirror of the reference's GaussianModel (src/scene/gaussian_model.{h,cpp}) and of
+the loop body the reference's train() is missing (src/utils/train_utils.cpp:128-145).
+
+Same member names and semantics as the reference: raw parameters xyz_/features_dc_/
+features_rest_/scaling_ (log)/rotation_ (w,x,y,z)/opacity_ (logit), statistics max_radii2D_/
+xyz_gradient_accum_/denom_, getters applying exp / normalise / sigmoid / cat, setup() with six
+Adam groups, update_learning_rate(), oneup_SH_degree().  Differences, all following the
+*intent* recorded in SURVEY.md §5.1: xyz_gradient_accum is (N,1) (defect 1), the xyz schedule
+decays over position_lr_max_steps (defect 2), spatial_lr_scale defaults to 1 (defect 3), and
+the six libtorch Adam instances are ONE fused CUDA launch (gs_adam_densify_step) with six
+segments and six step counters.  torch is used for device memory only.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from .camera import get_expon_lr_func
+from .rasterizer import GaussianRasterizationSettings, Rasterizer
+
+
+@dataclass
+class OptimizationParams:
+    """Defaults of the reference's OptimizationParams (src/arguments/params.h:52-68)."""
+    iterations: int = 30_000
+    position_lr_init: float = 0.00016
+    position_lr_final: float = 0.0000016
+    position_lr_delay_mult: float = 0.01
+    position_lr_max_steps: int = 30_000
+    feature_lr: float = 0.0025
+    opacity_lr: float = 0.05
+    scaling_lr: float = 0.005
+    rotation_lr: float = 0.001
+    percent_dense: float = 0.01
+    lambda_dssim: float = 0.2
+    densification_interval: int = 100
+    opacity_reset_interval: int = 3000
+    densify_from_iter: int = 500
+    densify_until_iter: int = 15_000
+    densify_grad_threshold: float = 0.0002
+    random_background: bool = False
+
+
+@dataclass
+class PipelineParams:
+    """src/arguments/params.h:93-97"""
+    convert_SHs_python: bool = False
+    compute_cov3D_python: bool = False
+    debug: bool = False
+
+
+class GaussianModel:
+    GROUPS = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")  # order of setup(), gaussian_model.cpp:323-345
+
+    def __init__(self, sh_degree: int, device: int = 0):
+        self.max_sh_degree = int(sh_degree)
+        self.active_sh_degree = 0
+        self.device = torch.device("cuda", device)
+        self.spatial_lr_scale = 1.0
+        self.percent_dense = 0.01
+        e = lambda *s: torch.empty(*s, device=self.device)
+        self.xyz_ = e(0, 3); self.features_dc_ = e(0, 1, 3); self.features_rest_ = e(0, 0, 3)
+        self.scaling_ = e(0, 3); self.rotation_ = e(0, 4); self.opacity_ = e(0, 1)
+        self.max_radii2D_ = torch.empty(0, dtype=torch.int32, device=self.device)
+        self.xyz_gradient_accum_ = e(0, 1); self.denom_ = e(0, 1)
+        self._opt_ready = False
+
+    # ---- construction from a synthetic scene (replaces create_from_pcd / Scene loading) ----
+    def load_scene(self, scene, active_sh_degree=None):
+        d = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).to(self.device)
+        self.xyz_ = d(scene.xyz); self.features_dc_ = d(scene.features_dc); self.features_rest_ = d(scene.features_rest)
+        self.scaling_ = d(scene.log_scales); self.rotation_ = d(scene.raw_rotations); self.opacity_ = d(scene.opacity_logits)
+        self.max_sh_degree = scene.max_sh_degree
+        self.active_sh_degree = self.max_sh_degree if active_sh_degree is None else int(active_sh_degree)
+        N = self.xyz_.shape[0]
+        self.max_radii2D_ = torch.zeros(N, dtype=torch.int32, device=self.device)
+        return self
+
+    @property
+    def N(self):
+        return int(self.xyz_.shape[0])
+
+    # ---- getters (src/scene/gaussian_model.cpp:270-304) ----
+    def get_xyz(self): return self.xyz_
+    def get_scaling(self): return torch.exp(self.scaling_)
+    def get_rotation(self): return torch.nn.functional.normalize(self.rotation_, dim=1)
+    def get_opacity(self): return torch.sigmoid(self.opacity_)
+    def get_features(self): return torch.cat((self.features_dc_, self.features_rest_), dim=1)
+
+    def oneup_SH_degree(self):
+        """src/scene/gaussian_model.cpp:307-313"""
+        if self.active_sh_degree < self.max_sh_degree:
+            self.active_sh_degree += 1
+
+    # ---- optimiser (src/scene/gaussian_model.cpp:316-361) ----
+    def params(self):
+        return [self.xyz_, self.features_dc_, self.features_rest_, self.opacity_, self.scaling_, self.rotation_]
+
+    def setup(self, opt: OptimizationParams):
+        N = self.N
+        self.percent_dense = opt.percent_dense
+        self.xyz_gradient_accum_ = torch.zeros((N, 1), device=self.device)
+        self.denom_ = torch.zeros((N, 1), device=self.device)
+        self.widths = [int(p.numel() // max(N, 1)) for p in self.params()]
+        self.lr = [opt.position_lr_init * self.spatial_lr_scale, opt.feature_lr, opt.feature_lr / 20.0,
+                   opt.opacity_lr, opt.scaling_lr, opt.rotation_lr]
+        self.exp_avg = [torch.zeros_like(p) for p in self.params()]
+        self.exp_avg_sq = [torch.zeros_like(p) for p in self.params()]
+        self.grads = [torch.zeros_like(p) for p in self.params()]
+        self.grad_means2D = torch.zeros((N, 2), device=self.device)
+        self.step_count = [0] * 6
+        self.xyz_scheduler_args = get_expon_lr_func(opt.position_lr_init * self.spatial_lr_scale,
+                                                    opt.position_lr_final * self.spatial_lr_scale, 0,
+                                                    opt.position_lr_delay_mult, opt.position_lr_max_steps)
+        self._opt_ready = True
+
+    def update_learning_rate(self, iteration: int) -> float:
+        """src/scene/gaussian_model.cpp:355-361"""
+        self.lr[0] = self.xyz_scheduler_args(iteration)
+        return self.lr[0]
+
+    def grad_sinks(self):
+        g = self.grads
+        return dict(means3D=g[0], sh_dc=g[1], sh_rest=g[2], opacities=g[3], scales=g[4], rotations=g[5],
+                    means2D=self.grad_means2D)
+
+
+def render(viewpoint_camera, pc: GaussianModel, pipe: PipelineParams, bg_color, rast: Rasterizer,
+           scaling_modifier: float = 1.0, fused_activations: bool = True):
+    """The missing render(viewpoint_cam, gaussians, pipe, background) call.  Returns
+    dict(render=(3,H,W), radii=(N) int32, visibility_filter=radii>0).
+    fused_activations=True feeds the RAW parameters (activations fused in the kernels);
+    False reproduces the getter chain of the reference (exp / normalise / sigmoid / cat)."""
+    st = GaussianRasterizationSettings.from_camera(viewpoint_camera, bg_color, pc.active_sh_degree, pc.max_sh_degree,
+                                                   scaling_modifier, pipe.debug)
+    if fused_activations:
+        color, radii = rast.forward(st, pc.xyz_, pc.scaling_, pc.rotation_, pc.opacity_, sh_dc=pc.features_dc_,
+                                    sh_rest=pc.features_rest_, raw_params=True)
+    else:
+        color, radii = rast.forward(st, pc.get_xyz(), pc.get_scaling(), pc.get_rotation(), pc.get_opacity(),
+                                    shs=pc.get_features())
+    return dict(render=color, radii=radii, visibility_filter=radii > 0)
+
+
+class Trainer:
+    """One training iteration = the loop body missing at src/utils/train_utils.cpp:138-145:
+    render -> loss -> backward -> densification stats -> optimizer step, all on the caller's
+    stream; only the ground-truth image comes from the host and only the loss goes back."""
+
+    def __init__(self, gaussians: GaussianModel, opt: OptimizationParams, pipe: PipelineParams | None = None,
+                 bg=(0.0, 0.0, 0.0), lambda_dssim: float | None = None):
+        self.g, self.opt, self.pipe = gaussians, opt, pipe or PipelineParams()
+        self.bg = tuple(bg)
+        self.rast = Rasterizer(gaussians.device.index or 0)
+        if not gaussians._opt_ready:
+            gaussians.setup(opt)
+        self.lambda_dssim = opt.lambda_dssim if lambda_dssim is None else lambda_dssim
+        self.iteration = 0
+        self._gt_dev = None
+        self._loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def forward_backward(self, cam, gt_dev: torch.Tensor, accumulate: bool = False):
+        """render + loss + backward for one view with the gradients left in the model's sinks."""
+        out = render(cam, self.g, self.pipe, self.bg, self.rast)
+        loss, dL = self.rast.loss(out["render"], gt_dev, self.lambda_dssim)
+        self.rast.backward(dL, grads=self.g.grad_sinks(), accumulate=accumulate)
+        return loss, out
+
+    def optimizer_step(self, radii):
+        g = self.g
+        g.step_count = [s + 1 for s in g.step_count]
+        self.rast.adam_densify_step(g.N, g.params(), g.grads, g.exp_avg, g.exp_avg_sq, g.widths, g.lr, g.step_count,
+                                    radii=radii, dL_dmeans2D=g.grad_means2D, max_radii2D=g.max_radii2D_,
+                                    xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_)
+
+    def train_step_device(self, cam, gt_dev: torch.Tensor):
+        """Device-resident step: ground truth already in HBM; returns the loss as a device tensor."""
+        self.iteration += 1
+        self.g.update_learning_rate(self.iteration)
+        if self.iteration % 1000 == 0:
+            self.g.oneup_SH_degree()
+        loss, out = self.forward_backward(cam, gt_dev)
+        self.optimizer_step(out["radii"])
+        return loss
+
+    def train_step(self, cam, gt_host: torch.Tensor) -> float:
+        """End-to-end step with HOST buffers: pinned ground-truth image H2D, loss D2H."""
+        if self._gt_dev is None or self._gt_dev.shape != gt_host.shape:
+            self._gt_dev = torch.empty(gt_host.shape, dtype=torch.float32, device=self.g.device)
+        self._gt_dev.copy_(gt_host, non_blocking=True)
+        loss = self.train_step_device(cam, self._gt_dev)
+        self._loss_host.copy_(loss, non_blocking=True)
+        torch.cuda.current_stream(self.g.device).synchronize()
+        return float(self._loss_host[0])

@@ -216,7 +216,7 @@ class Rasterizer:
         stream = torch.cuda.current_stream(self.device).cuda_stream
         check(self._ctx, lib.gs_adam_densify_step(
             self._ctx, int(N), arr(params), arr(grads), arr(exp_avg), arr(exp_avg_sq), (C.c_int * 6)(*widths),
-            (C.c_float * 6)(*[float(x) for x in lr]), (C.c_longlong * 6)(*[int(s) for s in step]), float(beta1),
+            (C.c_double * 6)(*[float(x) for x in lr]), (C.c_longlong * 6)(*[int(s) for s in step]), float(beta1),
             float(beta2), float(eps), _ptr(radii), _ptr(dL_dmeans2D), _ptr(max_radii2D), _ptr(xyz_grad_accum),
             _ptr(denom), int(zero_grads), C.c_void_p(stream)))
 

@@ -1,0 +1,407 @@
+#!/usr/bin/env python
+"""bench.py — the headline benchmark of BASELINE.json on B200.
+
+A "step" is ONE training iteration of the reference's (missing) loop body on one camera view
+per rank: render (K1-K3) -> L1 loss -> backward (K4a, K4b) -> fused Adam + densification stats
+(K5), on the synthetic 1.6M-Gaussian / 1246x825 / SH3 scene (BASELINE.json configs[2], the
+configuration the metric is quoted on).  metric = views/s (= train it/s at N=1).  With N>1 each
+rank renders its own camera (camera sharding, replicated Gaussians) and the per-Gaussian
+gradients are combined by ONE NCCL all-reduce before the identical Adam step on every rank.
+
+Printed JSON keys follow the driver contract; see DESIGN.md "Measurement" for the definitions
+of roofline / cpu_baseline / e2e / gpu_launches.
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "train_views_per_s"
+UNIT = "views/s"
+DEFAULT_CONFIG = "cfg2_1p6m_1246x825_sh3"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default=DEFAULT_CONFIG)
+    ap.add_argument("--views", type=int, default=8, help="distinct camera views cycled per rank")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--N", type=int, default=None, help="override the Gaussian count (debugging only)")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+# ---- clocks sampler (B200_PROFILING.md recipe) -------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            c = [x.strip() for x in r.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- algorithmic bytes ---------------------------------------------------
+def stage_bytes(N, N_vis, D, D_eff, P, T, K):
+    tile_bits = max(1, int(np.ceil(np.log2(max(T, 2)))))
+    passes = int(np.ceil((32 + tile_bits) / 8))
+    return {
+        "preprocess": (44 + 12 * K) * N + 48 * N_vis + 8 * (N - N_vis),
+        "scan_duplicate": 8 * N + 20 * N_vis + 12 * D,
+        "sort": (8 + 24 * passes) * D,
+        "ranges": 8 * D + 8 * T,
+        "blend_fwd": 40 * D_eff + 20 * P,
+        "blend_bwd": 40 * D_eff + 20 * P + 36 * N_vis,
+        "preprocess_bwd": (44 + 12 * K) * N_vis + 36 * N_vis + 4 * N + (44 + 12 * K) * N,
+        "adam_stats": 28 * (11 + 3 * K) * N + 36 * N_vis,
+        "loss": 36 * P,
+    }
+
+
+# ---- CPU leg: the oracle port timed on the host cores ------------------------------------------
+class CpuStep:
+    """One full train step (render, L1, backward, Adam + stats) of the CPU oracle on the same scene.
+    oracle/ is the checker; this is the one place bench.py executes it (cpu_baseline / --impl reference)."""
+
+    def __init__(self, scene, cams, deg, views):
+        from oracle.oracle_lib import Oracle, RasterSettings
+        self.o = Oracle()
+        self.RS = RasterSettings
+        self.scene, self.cams, self.deg = scene, cams, deg
+        self.raw = [scene.xyz.copy(), scene.features_dc.copy(), scene.features_rest.copy(),
+                    scene.opacity_logits.copy(), scene.log_scales.copy(), scene.raw_rotations.copy()]
+        self.m = [np.zeros_like(p) for p in self.raw]
+        self.v = [np.zeros_like(p) for p in self.raw]
+        self.lr = [1.6e-4, 2.5e-3, 2.5e-3 / 20, 0.05, 5e-3, 1e-3]
+        N = scene.N
+        self.maxr = np.zeros(N, np.int32); self.acc = np.zeros(N, np.float32); self.den = np.zeros(N, np.float32)
+        self.step = 0
+        self.gts = {}
+        self.views = views
+        self.cores = os.cpu_count() or 1
+
+    def settings(self, cam):
+        return self.RS(cam.image_height, cam.image_width, cam.tanfovx, cam.tanfovy, (0.0, 0.0, 0.0), 1.0,
+                       cam.world_view_transform.reshape(-1), cam.full_proj_transform.reshape(-1), cam.camera_center,
+                       self.deg, self.deg)
+
+    def activated(self):
+        xyz, dc, rest, opl, ls, rq = self.raw
+        sc = np.exp(ls); rot = rq / np.linalg.norm(rq, axis=1, keepdims=True); op = 1.0 / (1.0 + np.exp(-opl))
+        return sc.astype(np.float32), rot.astype(np.float32), op.astype(np.float32), \
+            np.ascontiguousarray(np.concatenate([dc, rest], axis=1))
+
+    def run(self, gt=None):
+        o = self.o
+        cam = self.cams[self.step % self.views]
+        s = self.settings(cam)
+        xyz = self.raw[0]
+        sc, rot, op, shs = self.activated()
+        pre, b, fwd = o.forward(s, xyz, sc, rot, op, shs)
+        if gt is None:
+            gt = np.zeros_like(fwd["out_color"])
+        loss, dL = o.l1_loss(fwd["out_color"], gt)
+        g = o.backward(s, xyz, sc, rot, shs, pre, b, fwd, dL)
+        # activation Jacobians of the getters (gaussian_model.cpp:54-59)
+        g_ls = g["dL_dscales"] * sc
+        g_op = (g["dL_dopacities"].reshape(-1, 1) * op * (1 - op)).astype(np.float32)
+        qn = np.linalg.norm(self.raw[5], axis=1, keepdims=True)
+        g_rq = ((g["dL_drotations"] - rot * (rot * g["dL_drotations"]).sum(1, keepdims=True)) / qn).astype(np.float32)
+        grads = [g["dL_dmeans3D"], np.ascontiguousarray(g["dL_dshs"][:, :1]), np.ascontiguousarray(g["dL_dshs"][:, 1:]),
+                 g_op, g_ls.astype(np.float32), g_rq]
+        self.step += 1
+        for k in range(6):
+            if self.raw[k].size:
+                o.adam_step(self.raw[k], np.ascontiguousarray(grads[k], dtype=np.float32), self.m[k], self.v[k],
+                            self.lr[k], 0.9, 0.999, 1e-8, self.step)
+        o.densify_stats(pre["radii"], g["dL_dmeans2D"], self.maxr, self.acc, self.den)
+        return loss
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference has no implementation of this path, so the CPU
+    arm is the oracle port on all host cores, one full step of the same workload per step."""
+    if rank != 0:
+        return
+    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
+    scene, cams, deg = syn.make_config(args.config, n_cameras=max(args.views, 1), N=args.N)
+    cpu = CpuStep(scene, cams, deg, args.views)
+    steps, warm = max(1, min(args.steps, 6)), max(0, min(args.warmup, 1))
+    for _ in range(warm):
+        cpu.run()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu.run()
+    dt = (time.perf_counter() - t0) / steps
+    val = 1.0 / dt
+    cam = cams[0]
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.config, "N": scene.N, "W": cam.image_width, "H": cam.image_height,
+                   "sh_degree": deg, "views_per_rank_per_step": 1, "loss": "L1",
+                   "note": "reference repo has no render path; CPU arm = this repo's oracle port (OpenMP)"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cpu.cores, "kind": "port",
+                         "sample": f"{steps} full train steps of the same workload (steps capped at 6)"},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }), flush=True)
+
+
+# ---- GPU arm -----------------------------------------------------------------------------------
+OWN_KERNELS_PER_STEP = 9   # preprocess, duplicate_with_keys, identify_tile_ranges, blend_forward, l1_loss,
+                           # loss_finalize, blend_backward, preprocess_backward, adam_stats
+LIB_KERNELS_PER_STEP = 10  # CUB DeviceScan (2) + DeviceRadixSort onesweep (histogram, scan, 6 passes)
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    pkg = importlib.import_module("3d_gaussian_splatting_b200")
+    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
+    gm = importlib.import_module("3d_gaussian_splatting_b200.gaussian_model")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    scene, cams, deg = syn.make_config(args.config, n_cameras=max(args.views * world, 1), N=args.N)
+    my_cams = [cams[rank + world * k] for k in range(args.views)]
+    H, W = my_cams[0].image_height, my_cams[0].image_width
+    P, T, K, N = H * W, ((H + 15) // 16) * ((W + 15) // 16), (deg + 1) ** 2, scene.N
+
+    model = gm.GaussianModel(deg, local_rank).load_scene(scene)
+    opt = gm.OptimizationParams()
+    trainer = gm.Trainer(model, opt, bg=(0.0, 0.0, 0.0), lambda_dssim=0.0)
+    g = model
+    # one contiguous gradient slab (a single all-reduce per step when world > 1)
+    sizes = [p.numel() for p in g.params()]
+    offs = np.cumsum([0] + [(s + 3) // 4 * 4 for s in sizes])
+    slab = torch.zeros(int(offs[-1]), device=dev)
+    g.grads = [slab[int(offs[k]):int(offs[k]) + sizes[k]].view_as(p) for k, p in enumerate(g.params())]
+
+    # ground truth = render of the scene with SH perturbed by N(0, 0.05^2)  
+    rng = np.random.Generator(np.random.Philox(99))
+    gt_model = gm.GaussianModel(deg, local_rank).load_scene(scene)
+    gt_model.features_dc_ += torch.from_numpy((0.05 * rng.standard_normal(scene.features_dc.shape)).astype(np.float32)).to(dev)
+    gts_dev, gts_host = [], []
+    for cam in my_cams:
+        out = gm.render(cam, gt_model, gm.PipelineParams(), (0.0, 0.0, 0.0), trainer.rast)
+        gts_dev.append(out["render"].clone())
+        gts_host.append(out["render"].cpu().pin_memory())
+    del gt_model
+    torch.cuda.synchronize()
+
+    def step_device(i):
+        cam, gt = my_cams[i % args.views], gts_dev[i % args.views]
+        trainer.iteration += 1
+        g.update_learning_rate(trainer.iteration)
+        loss, out = trainer.forward_backward(cam, gt)
+        if world > 1:
+            dist.all_reduce(slab)
+        trainer.optimizer_step(out["radii"])
+        return loss
+
+    def step_e2e(i):
+        cam = my_cams[i % args.views]
+        if trainer._gt_dev is None:
+            trainer._gt_dev = torch.empty_like(gts_dev[0])
+        trainer._gt_dev.copy_(gts_host[i % args.views], non_blocking=True)
+        trainer.iteration += 1
+        g.update_learning_rate(trainer.iteration)
+        loss, out = trainer.forward_backward(cam, trainer._gt_dev)
+        if world > 1:
+            dist.all_reduce(slab)
+        trainer.optimizer_step(out["radii"])
+        trainer._loss_host.copy_(loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(trainer._loss_host[0])
+
+    def timed(fn, steps, warmup, sampler=None):
+        for i in range(warmup):
+            fn(i)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(warmup + i)
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        clocks = sampler.stop() if sampler else None
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), clocks
+
+    warm = max(args.warmup, 3)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    total_ms, clocks = timed(step_device, args.steps, warm, sampler)
+    ms_per_step = total_ms / args.steps
+    value = world * 1.0 / (ms_per_step * 1e-3)
+    e2e_ms, _ = timed(step_e2e, args.steps, warm)
+    e2e_value = world * 1.0 / (e2e_ms / args.steps * 1e-3)
+
+    # ---- per-stage device times (CUDA events recorded by the library around each stage) ----
+    trainer.rast.set_profiling(True)
+    acc = {}
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+    extra = {"loss": [], "adam_stats": []}
+    for i in range(8):
+        cam, gt = my_cams[i % args.views], gts_dev[i % args.views]
+        out = gm.render(cam, g, trainer.pipe, trainer.bg, trainer.rast)
+        ev[0].record(); loss, dL = trainer.rast.loss(out["render"], gt, 0.0); ev[1].record()
+        trainer.rast.backward(dL, grads=g.grad_sinks())
+        ev[2].record(); trainer.optimizer_step(out["radii"]); ev[3].record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            for k, v in trainer.rast.stage_ms().items():
+                acc.setdefault(k, []).append(v)
+            extra["loss"].append(ev[0].elapsed_time(ev[1])); extra["adam_stats"].append(ev[2].elapsed_time(ev[3]))
+    trainer.rast.set_profiling(False)
+    stage_ms = {k: float(np.median(v)) for k, v in acc.items()}
+    stage_ms.update({k: float(np.median(v)) for k, v in extra.items()})
+    radii = out["radii"]
+    N_vis = int((radii > 0).sum().item())
+    D = int(trainer.rast.debug_get("NUM_RENDERED")[0])
+    ncon = torch.from_numpy(trainer.rast.debug_get("N_CONTRIB").astype(np.int64)).reshape(H, W)
+    pad = torch.zeros(((H + 15) // 16 * 16, (W + 15) // 16 * 16), dtype=torch.int64)
+    pad[:H, :W] = ncon
+    D_eff = int(pad.reshape(pad.shape[0] // 16, 16, pad.shape[1] // 16, 16).amax(dim=(1, 3)).sum().item())
+    interactions = int(ncon.sum().item())
+    by = stage_bytes(N, N_vis, D, D_eff, P, T, K)
+    peak, peak_kind = peaks()
+    dom = max(stage_ms, key=lambda k: stage_ms[k])
+    ach = by[dom] / (stage_ms[dom] * 1e-3) / 1e9
+    step_bytes = sum(by.values())
+    stages = {k: {"ms": round(stage_ms[k], 4), "alg_GB": round(by[k] / 1e9, 4),
+                  "GBps": round(by[k] / (stage_ms[k] * 1e-3) / 1e9, 1) if stage_ms[k] > 0 else None,
+                  "frac_hbm": round(by[k] / (stage_ms[k] * 1e-3) / 1e9 / peak, 4) if stage_ms[k] > 0 else None}
+              for k in stage_ms}
+    fwd_bwd_ms = sum(stage_ms[k] for k in ("preprocess", "scan_duplicate", "sort", "ranges", "blend_fwd",
+                                           "blend_bwd", "preprocess_bwd"))
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = CpuStep(scene, cams, deg, args.views)
+        gt_np = gts_host[0].numpy()
+        cpu.run(gt_np)  # warm-up (page faults, OpenMP pool)
+        t0 = time.perf_counter()
+        nrep = 2
+        for _ in range(nrep):
+            cpu.run(gt_np)
+        dt = (time.perf_counter() - t0) / nrep
+        cpu_baseline = {"value": 1.0 / dt, "unit": UNIT, "cores": cpu.cores, "kind": "port",
+                        "sample": f"{nrep} full train steps of the same workload after 1 warm-up ({dt:.2f} s/step)"}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.config, "N": N, "W": W, "H": H, "sh_degree": deg, "tiles": T,
+                       "views_per_rank_per_step": 1, "loss": "L1", "N_vis": N_vis, "D": D, "D_eff": D_eff,
+                       "pixel_gaussian_interactions": interactions,
+                       "l2_policy": "inputs larger than L2 (params+Adam state 1.13 GB per step vs 126 MB L2)",
+                       "parallelism": f"camera-sharded dp{world}, one NCCL all-reduce of {slab.numel() * 4 / 1e6:.0f} MB grads per step"
+                       if world > 1 else "single GPU"},
+            "raster_fwd_bwd_ms": fwd_bwd_ms, "train_it_per_s_per_gpu": 1e3 / ms_per_step,
+            "stages": stages,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+                         "frac": ach / peak, "traffic": None, "peak_kind": peak_kind,
+                         "step_frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
+            "cpu_baseline": cpu_baseline,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
+                    "h2d_bytes_per_step": int(gts_host[0].numel() * 4 + 172), "d2h_bytes_per_step": 4},
+            "gpu_launches": OWN_KERNELS_PER_STEP * args.steps,
+            "library_launches": LIB_KERNELS_PER_STEP * args.steps,
+            "clocks": clocks,
+        }), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -138,15 +138,15 @@ GS_API int gs_backward(gs_ctx *ctx, const gs_settings *settings, int N, const gs
  * The reference builds six torch::optim::Adam with only `lr` set
  * (src/scene/gaussian_model.cpp:323-345: xyz, f_dc, f_rest, opacity, scaling, rotation) =>
  * libtorch defaults beta=(0.9,0.999), eps=1e-8, no weight decay, no amsgrad, six independent
- * step counters.  One launch updates all six segments (segment s has N*widths[s] floats).
+ * step counters (hyper-parameters are double, as in torch::optim::AdamOptions).  One launch updates all six segments (segment s has N*widths[s] floats).
  * Statistics on Gaussians with radii > 0 (fields at src/scene/gaussian_model.h:18-20):
  *   max_radii2D = max(max_radii2D, radii); xyz_grad_accum += |dL_dmeans2D.xy|; denom += 1.
  * radii / dL_dmeans2D / the three stat buffers may be NULL to skip the statistics.
  * zero_grads != 0 re-zeroes the gradient buffers in the same pass. */
 GS_API int gs_adam_densify_step(gs_ctx *ctx, int N, float *const params[6], float *const grads[6],
                                 float *const exp_avg[6], float *const exp_avg_sq[6], const int widths[6],
-                                const float lr[6], const long long step[6], float beta1, float beta2,
-                                float eps, const int *radii, const float *dL_dmeans2D, int *max_radii2D,
+                                const double lr[6], const long long step[6], double beta1, double beta2,
+                                double eps, const int *radii, const float *dL_dmeans2D, int *max_radii2D,
                                 float *xyz_grad_accum, float *denom, int zero_grads, void *stream);
 
 /* ---- photometric loss ----------------------------------------------------------------------
