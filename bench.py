@@ -230,7 +230,8 @@ def run_ours(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=dev)
 
     scene, cams, deg = syn.make_config(args.config, n_cameras=max(args.views * world, 1), N=args.N)
-    my_cams = [cams[rank + world * k] for k in range(args.views)]
+    par = importlib.import_module("3d_gaussian_splatting_b200.parallel")
+    my_cams = par.shard_cameras(cams, rank, world)[:args.views]
     H, W = my_cams[0].image_height, my_cams[0].image_width
     P, T, K, N = H * W, ((H + 15) // 16) * ((W + 15) // 16), (deg + 1) ** 2, scene.N
 
@@ -239,10 +240,9 @@ def run_ours(args, rank, world, local_rank):
     trainer = gm.Trainer(model, opt, bg=(0.0, 0.0, 0.0), lambda_dssim=0.0)
     g = model
     # one contiguous gradient slab (a single all-reduce per step when world > 1)
-    sizes = [p.numel() for p in g.params()]
-    offs = np.cumsum([0] + [(s + 3) // 4 * 4 for s in sizes])
-    slab = torch.zeros(int(offs[-1]), device=dev)
-    g.grads = [slab[int(offs[k]):int(offs[k]) + sizes[k]].view_as(p) for k, p in enumerate(g.params())]
+    gslab = par.GradientSlab(g.params())
+    slab = gslab.flat
+    g.grads = gslab.views
 
     # ground truth = render of the scene with SH perturbed by N(0, 0.05^2)  
     rng = np.random.Generator(np.random.Philox(99))
@@ -262,7 +262,7 @@ def run_ours(args, rank, world, local_rank):
         g.update_learning_rate(trainer.iteration)
         loss, out = trainer.forward_backward(cam, gt)
         if world > 1:
-            dist.all_reduce(slab)
+            gslab.all_reduce()
         trainer.optimizer_step(out["radii"])
         return loss
 
@@ -275,7 +275,7 @@ def run_ours(args, rank, world, local_rank):
         g.update_learning_rate(trainer.iteration)
         loss, out = trainer.forward_backward(cam, trainer._gt_dev)
         if world > 1:
-            dist.all_reduce(slab)
+            gslab.all_reduce()
         trainer.optimizer_step(out["radii"])
         trainer._loss_host.copy_(loss, non_blocking=True)
         torch.cuda.current_stream().synchronize()

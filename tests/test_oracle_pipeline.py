@@ -1,0 +1,206 @@
+"""The oracle checked against independent evidence (the reference pins nothing downstream of
+cov3D): structural invariants, central finite differences on the float64 build,
+and a tiny float64 PyTorch-autograd restatement of the whole render path."""
+import numpy as np
+import pytest
+
+from helpers import cammod, oracle_settings, small_scene, syn
+from oracle.oracle_lib import RasterSettings
+
+torch = pytest.importorskip("torch")
+
+
+def test_invariants(oracle):
+    """keys sorted; ranges partition the key array; sum(tiles_touched) = #keys; T in (0,1];
+    radii = 0 <=> culled; n_contrib <= tile list length."""
+    scene, cam = small_scene(N=5000, H=100, W=140, deg=2, seed=4, scale_boost=0.6, focal=90.0, eye=(0.2, 0.1, 1.6))
+    sc, rot, op, shs = scene.activated()
+    s = oracle_settings(cam, 2, 2)
+    pre, b, fwd = oracle.forward(s, scene.xyz, sc, rot, op, shs)
+    D = b["D"]
+    assert D == int(pre["tiles_touched"].sum()) and D > 0
+    assert (np.diff(b["keys"].astype(np.uint64)) >= 0).all()
+    assert ((pre["radii"] > 0) == (pre["tiles_touched"] > 0)).all()
+    assert 0 < (pre["radii"] > 0).mean() < 1          # some culled, some visible
+    tile_of = (b["keys"] >> np.uint64(32)).astype(np.int64)
+    r = b["ranges"].astype(np.int64)
+    covered = 0
+    for t in range(r.shape[0]):
+        lo, hi = r[t]
+        assert hi >= lo
+        if hi > lo:
+            assert (tile_of[lo:hi] == t).all()
+            covered += hi - lo
+    assert covered == D
+    # stable: equal keys keep ascending Gaussian ids
+    same = b["keys"][1:] == b["keys"][:-1]
+    assert (b["values"][1:][same] > b["values"][:-1][same]).all()
+    assert (fwd["final_T"] > 0).all() and (fwd["final_T"] <= 1).all()
+    gx = (s.W + 15) // 16
+    for (y, x) in [(0, 0), (50, 70), (99, 139)]:
+        t = (y // 16) * gx + x // 16
+        assert fwd["n_contrib"][y, x] <= r[t, 1] - r[t, 0]
+    assert fwd["D_eff"] <= D and fwd["interactions"] <= fwd["sum_contrib"]
+
+
+def _fd_setup(oracle64, N=160, boost=0.9):
+    scene = syn.make_scene(N, 3, seed=7)
+    scene.log_scales += np.float32(boost)
+    cam = cammod.look_at_camera((0.5, 0.3, 3.0), (0, 0, 0), (0, 1, 0), 60.0, 48, 64)
+    sc, _, op, shs = [a.astype(np.float64) for a in scene.activated()]
+    rot = scene.raw_rotations.astype(np.float64)   # un-normalised: exercises the normalisation Jacobian
+    xyz = scene.xyz.astype(np.float64)
+    s = RasterSettings(48, 64, cam.tanfovx, cam.tanfovy, (0.3, 0.1, 0.7), 1.0,
+                       cam.world_view_transform.reshape(-1).astype(np.float64),
+                       cam.full_proj_transform.reshape(-1).astype(np.float64),
+                       cam.camera_center.astype(np.float64), 3, 3)
+    return s, dict(means3D=xyz, scales=sc, rotations=rot, opacities=op, shs=shs)
+
+
+def test_gradients_finite_differences(oracle64):
+    """Every input gradient of the oracle against central differences of L = <dL, image> (float64)."""
+    o = oracle64
+    s, P = _fd_setup(o)
+    rng = np.random.default_rng(1)
+    dL = rng.standard_normal((3, s.H, s.W))
+
+    def loss():
+        pre, b, fwd = o.forward(s, P["means3D"], P["scales"], P["rotations"], P["opacities"], P["shs"])
+        return float((fwd["out_color"] * dL).sum()), (pre, b, fwd)
+
+    _, (pre, b, fwd) = loss()
+    g = o.backward(s, P["means3D"], P["scales"], P["rotations"], P["shs"], pre, b, fwd, dL)
+    keymap = dict(means3D="dL_dmeans3D", scales="dL_dscales", rotations="dL_drotations", opacities="dL_dopacities",
+                  shs="dL_dshs")
+    eps = 1e-6
+    for name, arr in P.items():
+        flat, ga = arr.reshape(-1), g[keymap[name]].reshape(-1)
+        scale = np.abs(ga).max()
+        assert scale > 0
+        nz = np.flatnonzero(np.abs(ga) > 1e-3 * scale)
+        idxs = rng.choice(nz, size=min(25, nz.size), replace=False)
+        bad = 0
+        for i in idxs:
+            old = flat[i]
+            flat[i] = old + eps; lp, _ = loss()
+            flat[i] = old - eps; lm, _ = loss()
+            flat[i] = old
+            fd = (lp - lm) / (2 * eps)
+            if abs(fd - ga[i]) > 1e-4 * abs(ga[i]) + 1e-6 * scale:
+                bad += 1
+        # a finite step may cross one of the renderer's discontinuities (alpha < 1/255, radius ceil) once
+        assert bad <= 1, f"{name}: {bad} of {len(idxs)} finite-difference checks failed"
+
+
+def _torch_render(s, xyz, scales, rot, op, shs, pre, b):
+    """Differentiable float64 restatement in PyTorch: same math, vectorised over pixels, with the
+    discrete structure (tile membership, depth order) taken from the oracle's binning."""
+    H, W = s.H, s.W
+    V = torch.tensor(np.asarray(s.viewmatrix, np.float64)).reshape(4, 4).T      # row-major V
+    M = torch.tensor(np.asarray(s.projmatrix, np.float64)).reshape(4, 4).T
+    cam = torch.tensor(np.asarray(s.campos, np.float64))
+    N = xyz.shape[0]
+    ones = torch.ones(N, 1, dtype=torch.float64)
+    ph = torch.cat([xyz, ones], 1) @ M.T
+    pw = 1.0 / (ph[:, 3] + 1e-7)
+    px = ((ph[:, 0] * pw + 1) * W - 1) * 0.5
+    py = ((ph[:, 1] * pw + 1) * H - 1) * 0.5
+    t = torch.cat([xyz, ones], 1) @ V.T
+    q = rot / rot.norm(dim=1, keepdim=True)
+    r_, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r_ * z), 2 * (x * z + r_ * y),
+                     2 * (x * y + r_ * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r_ * x),
+                     2 * (x * z - r_ * y), 2 * (y * z + r_ * x), 1 - 2 * (x * x + y * y)], 1).reshape(N, 3, 3)
+    L = R * (s.scale_modifier * scales)[:, None, :]
+    Sig = L @ L.transpose(1, 2)
+    fx, fy = W / (2 * s.tanfovx), H / (2 * s.tanfovy)
+    limx, limy = 1.3 * s.tanfovx, 1.3 * s.tanfovy
+    tz = t[:, 2]
+    tx = torch.clamp(t[:, 0] / tz, -limx, limx) * tz
+    ty = torch.clamp(t[:, 1] / tz, -limy, limy) * tz
+    J = torch.zeros(N, 2, 3, dtype=torch.float64)
+    J[:, 0, 0] = fx / tz; J[:, 0, 2] = -fx * tx / tz ** 2
+    J[:, 1, 1] = fy / tz; J[:, 1, 2] = -fy * ty / tz ** 2
+    T = J @ V[:3, :3]
+    cov = T @ Sig @ T.transpose(1, 2)
+    a, bb, c = cov[:, 0, 0] + 0.3, cov[:, 0, 1], cov[:, 1, 1] + 0.3
+    det = a * c - bb * bb
+    A, B, Cc = c / det, -bb / det, a / det
+    # SH -> RGB
+    d = xyz - cam
+    d = d / d.norm(dim=1, keepdim=True)
+    x, y, z = d[:, 0:1], d[:, 1:2], d[:, 2:3]
+    xx, yy, zz, xy, yz, xz = x * x, y * y, z * z, x * y, y * z, x * z
+    C1 = 0.4886025119029199
+    C2 = [1.0925484305920792, -1.0925484305920792, 0.31539156525252005, -1.0925484305920792, 0.5462742152960396]
+    C3 = [-0.5900435899266435, 2.890611442640554, -0.4570457994644658, 0.3731763325901154, -0.4570457994644658,
+          1.445305721320277, -0.5900435899266435]
+    basis = [0.28209479177387814 * torch.ones_like(x), -C1 * y, C1 * z, -C1 * x,
+             C2[0] * xy, C2[1] * yz, C2[2] * (2 * zz - xx - yy), C2[3] * xz, C2[4] * (xx - yy),
+             C3[0] * y * (3 * xx - yy), C3[1] * xy * z, C3[2] * y * (4 * zz - xx - yy),
+             C3[3] * z * (2 * zz - 3 * xx - 3 * yy), C3[4] * x * (4 * zz - xx - yy), C3[5] * z * (xx - yy),
+             C3[6] * x * (xx - 3 * yy)]
+    nact = (s.sh_degree + 1) ** 2
+    rgb = sum(basis[k] * shs[:, k, :] for k in range(nact)) + 0.5
+    rgb = torch.clamp_min(rgb, 0.0)
+    # per-tile compositing
+    gx = (W + 15) // 16
+    out = torch.zeros(3, H, W, dtype=torch.float64)
+    bg = torch.tensor(s.bg, dtype=torch.float64)
+    vals = torch.from_numpy(b["values"].astype(np.int64))
+    for tile, (lo, hi) in enumerate(b["ranges"].astype(np.int64)):
+        ty0, tx0 = (tile // gx) * 16, (tile % gx) * 16
+        ys = torch.arange(ty0, min(ty0 + 16, H), dtype=torch.float64)
+        xs = torch.arange(tx0, min(tx0 + 16, W), dtype=torch.float64)
+        PY, PX = torch.meshgrid(ys, xs, indexing="ij")
+        ids = vals[lo:hi]
+        if ids.numel() == 0:
+            out[:, ty0:ty0 + 16, tx0:tx0 + 16] = bg[:, None, None]
+            continue
+        dx = px[ids][:, None, None] - PX[None]
+        dy = py[ids][:, None, None] - PY[None]
+        power = -0.5 * (A[ids][:, None, None] * dx * dx + Cc[ids][:, None, None] * dy * dy) - B[ids][:, None, None] * dx * dy
+        alpha = torch.clamp_max(op[ids].reshape(-1, 1, 1) * torch.exp(power), 0.99)
+        keep = (power <= 0) & (alpha >= 1.0 / 255.0)
+        alpha = torch.where(keep, alpha, torch.zeros_like(alpha))
+        Tex = torch.cumprod(torch.cat([torch.ones_like(alpha[:1]), 1 - alpha[:-1]], 0), 0)   # T before each entry
+        test_T = Tex * (1 - alpha)
+        stop = (keep & (test_T < 1e-4)).to(torch.int64).cumsum(0) > 0      # this entry and everything after it
+        w = torch.where(stop, torch.zeros_like(alpha), alpha * Tex)
+        Tfin = 1 - w.sum(0)                                               # sum(alpha_i T_i) telescopes to 1 - T_final
+        col = (w[:, None] * rgb[ids][:, :, None, None]).sum(0) + Tfin[None] * bg[:, None, None]
+        out[:, ty0:ty0 + 16, tx0:tx0 + 16] = col
+    return out
+
+
+def test_torch_autograd_cross_oracle(oracle64):
+    """Image and all gradients of the C oracle (float64 build) vs the PyTorch restatement."""
+    o = oracle64
+    s, P = _fd_setup(o, N=120, boost=0.8)
+    pre, b, fwd = o.forward(s, P["means3D"], P["scales"], P["rotations"], P["opacities"], P["shs"])
+    assert (pre["radii"] > 0).all()
+    rng = np.random.default_rng(3)
+    dL = rng.standard_normal((3, s.H, s.W))
+    g = o.backward(s, P["means3D"], P["scales"], P["rotations"], P["shs"], pre, b, fwd, dL)
+    tp = {k: torch.tensor(v, dtype=torch.float64, requires_grad=True) for k, v in P.items()}
+    img = _torch_render(s, tp["means3D"], tp["scales"], tp["rotations"], tp["opacities"], tp["shs"], pre, b)
+    assert np.abs(img.detach().numpy() - fwd["out_color"]).max() < 1e-9
+    (img * torch.tensor(dL)).sum().backward()
+    keymap = dict(means3D="dL_dmeans3D", scales="dL_dscales", rotations="dL_drotations", opacities="dL_dopacities",
+                  shs="dL_dshs")
+    for k, kk in keymap.items():
+        ref = tp[k].grad.numpy().reshape(g[kk].shape)
+        err = np.abs(g[kk] - ref).max() / np.abs(ref).max()
+        assert err < 1e-8, f"{k}: {err}"
+
+
+def test_f32_and_f64_oracles_agree(oracle, oracle64):
+    """The fp32 oracle (specified exp polynomial, explicit FMAs) against the fp64 build (libm)."""
+    scene, cam = small_scene(N=1500, H=64, W=96, deg=3, seed=11, scale_boost=0.5)
+    sc, rot, op, shs = scene.activated()
+    s = oracle_settings(cam, 3, 3, bg=(0.1, 0.2, 0.3))
+    _, _, f32 = oracle.forward(s, scene.xyz, sc, rot, op, shs)
+    _, _, f64 = oracle64.forward(s, scene.xyz, sc, rot, op, shs)
+    diff = np.abs(f32["out_color"] - f64["out_color"])
+    # a handful of pixels may sit on a skip threshold (alpha = 1/255) and flip between precisions
+    assert np.quantile(diff, 0.999) < 2e-5 and (diff > 1e-3).mean() < 1e-3
