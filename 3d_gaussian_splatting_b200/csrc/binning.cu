@@ -77,6 +77,49 @@ identify_tile_ranges_kernel(uint32_t D, const uint64_t* __restrict__ keys, uint2
   if (i == D - 1) ranges[cur].y = D;
 }
 
+// ---- tile scheduling order: longest lists first --------------------------------------------------
+// Per-tile work is extremely skewed (mean ~300 processed entries, max several thousand), and the
+// blend kernels run one block per tile, so launching the heavy tiles first (longest-processing-time
+// order) removes the tail.  Counting sort by a 7-bit log-scale bucket of the list length; one block.
+#define ORDER_BUCKETS 128
+__device__ __forceinline__ int length_bucket(uint32_t len) {
+  if (len < 4) return (int)len;
+  const int msb = 31 - __clz(len);                      // >= 2
+  const int sub = (int)((len >> (msb - 2)) & 3u);       // next two bits
+  return min(ORDER_BUCKETS - 1, 4 * (msb - 1) + sub);   // monotone in len
+}
+__global__ void __launch_bounds__(1024)
+order_tiles_kernel(int ntiles, const uint2* __restrict__ ranges, uint32_t* __restrict__ tile_order) {
+  __shared__ uint32_t s_count[ORDER_BUCKETS];
+  __shared__ uint32_t s_start[ORDER_BUCKETS];
+  for (int b = threadIdx.x; b < ORDER_BUCKETS; b += blockDim.x) s_count[b] = 0;
+  __syncthreads();
+  for (int t = threadIdx.x; t < ntiles; t += blockDim.x) {
+    const uint2 r = ranges[t];
+    atomicAdd(&s_count[length_bucket(r.y - r.x)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t acc = 0;
+    for (int b = ORDER_BUCKETS - 1; b >= 0; --b) {  // descending: heaviest bucket first
+      s_start[b] = acc;
+      acc += s_count[b];
+    }
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < ntiles; t += blockDim.x) {
+    const uint2 r = ranges[t];
+    const uint32_t pos = atomicAdd(&s_start[length_bucket(r.y - r.x)], 1u);
+    tile_order[pos] = (uint32_t)t;
+  }
+}
+
+cudaError_t gs_launch_order_tiles(int ntiles, const uint2* ranges, uint32_t* tile_order, cudaStream_t stream) {
+  if (ntiles == 0) return cudaSuccess;
+  order_tiles_kernel<<<1, 1024, 0, stream>>>(ntiles, ranges, tile_order);
+  return cudaGetLastError();
+}
+
 // ---- host-side launchers ---------------------------------------------------------------------
 size_t gs_scan_temp_bytes(int N) {
   size_t bytes = 0;

@@ -1,152 +1,212 @@
-// blend_bwd.cu — K4a: backward alpha compositing.  Same tiling as K3; each
-// pixel walks its tile list back-to-front from its last contributor, recomputing alpha and
-// transmittance.  Per-Gaussian partial gradients are reduced across the warp with shuffles and
-// leave the SM as three 16-byte vector reductions (red.global.add.v4.f32) per (warp, Gaussian).
+// blend_bwd.cu — K4a: backward alpha compositing, segmented.
+//
+// Per-tile work is extremely skewed (mean ~300 processed list entries, max several thousand), and a
+// pixel's walk through its tile list is sequential, so "one block per tile" is bound by the heaviest
+// tile.  Instead the forward leaves a per-pixel checkpoint (T, C.rgb) at every GS_SEG-entry boundary
+// and a list of (tile, segment) work items; here every work item is independent: a block restarts
+// from the checkpoint and replays its GS_SEG entries FRONT-TO-BACK with exactly the forward's
+// arithmetic (so T and the prefix colour C are the forward's bits), and gets the colour behind the
+// current Gaussian from the final pixel colour:  Cb = out - C_prefix_after  (includes bg * T_final).
+//     dL/dalpha_i = sum_ch dL/dC_ch * (c_ch * T_i - Cb_ch / (1 - alpha_i))
+// Persistent 64-thread blocks pull work items from an atomic cursor; every thread owns a 2x2 pixel
+// quad, so a segment needs only two cross-lane reductions per Gaussian: per-thread partial sums of
+// the 9 gradient components are reduced with a halving butterfly (8 values in 4+2+1+1+1 shuffles,
+// the 9th in 5) and leave the SM as ONE predicated red.global.add.f32 (9 lanes, 9 consecutive floats).
 //
 // Gradient record per Gaussian (48 B, pre-zeroed):
-//   g0 = { dL/dmean2D.x, dL/dmean2D.y, dL/dA, dL/dB }   (mean2D gradient in NDC units: x0.5W/0.5H)
-//   g1 = { dL/dC, dL/dopacity, dL/dr, dL/dg }
-//   g2 = { dL/db, -, -, - }
+//   { dL/dmean2D.x, dL/dmean2D.y, dL/dA, dL/dB } { dL/dC, dL/dopacity, dL/dr, dL/dg } { dL/db, -, -, - }
+// (mean2D gradient in NDC units, x0.5W / x0.5H).  Skip decisions use the specified numerics of
+// gs_common.cuh and are identical to the forward's and the oracle's.
 #include "gs_common.cuh"
 
-#define BB_THREADS 256
-
-__device__ __forceinline__ float warp_sum(float v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
+#define BB_THREADS 64
+#define BB_PER_THREAD (GS_SEG / BB_THREADS)
 
 __global__ void __launch_bounds__(BB_THREADS)
 blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                       const GsGeom* __restrict__ geom, float bg0, float bg1, float bg2,
-                      const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
-                      const float* __restrict__ dL_dpixels, float4* __restrict__ grad_geom) {
-  __shared__ float4 s_q0[BB_THREADS];
-  __shared__ float4 s_q1[BB_THREADS];
-  __shared__ float s_b[BB_THREADS];
-  __shared__ uint32_t s_id[BB_THREADS];
+                      const float4* __restrict__ final_state, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
+                      const float4* __restrict__ ckpt, const uint2* __restrict__ work_items,
+                      const uint32_t* __restrict__ work_count, uint32_t* __restrict__ work_cursor,
+                      const uint32_t* __restrict__ tile_last, float* __restrict__ grad_geom) {
+  __shared__ float4 s_q0[GS_SEG];
+  __shared__ float4 s_q1[GS_SEG];
+  __shared__ float s_b[GS_SEG];
+  __shared__ uint32_t s_id[GS_SEG];
+  __shared__ uint32_t s_work;
 
-  const int tile = blockIdx.x;
-  const int tx = tile % d.gx, ty = tile / d.gx;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int px = tx * GS_TILE + (warp & 1) * 8 + (lane & 7);
-  const int py = ty * GS_TILE + (warp >> 1) * 4 + (lane >> 3);
-  const bool inside = px < d.W && py < d.H;
-  const float pixx = (float)px, pixy = (float)py;
-  const size_t pix = (size_t)py * d.W + px;
+  const int tid = threadIdx.x, lane = tid & 31;
   const size_t plane = (size_t)d.H * d.W;
-
-  const uint2 range = ranges[tile];
-  const int total = (int)(range.y - range.x);
-  const int rounds = (total + BB_THREADS - 1) / BB_THREADS;
-
-  const float T_final = inside ? final_T[pix] : 0.f;
-  float T = T_final;
-  const int last_contributor = inside ? (int)n_contrib[pix] : 0;
-  float dLp0 = 0.f, dLp1 = 0.f, dLp2 = 0.f;
-  if (inside) {
-    dLp0 = dL_dpixels[pix];
-    dLp1 = dL_dpixels[plane + pix];
-    dLp2 = dL_dpixels[2 * plane + pix];
-  }
-  const float bg_dot = bg0 * dLp0 + bg1 * dLp1 + bg2 * dLp2;
-  float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_alpha = 0.f;
   const float ddelx_dx = 0.5f * (float)d.W, ddely_dy = 0.5f * (float)d.H;
+  const uint32_t nwork = *work_count;
 
-  // the whole warp can start at the largest last_contributor among its lanes
-  int warp_last = last_contributor;
+  for (;;) {
+    __syncthreads();
+    if (tid == 0) s_work = atomicAdd(work_cursor, 1u);
+    __syncthreads();
+    const uint32_t w = s_work;
+    if (w >= nwork) break;
+    const uint2 item = work_items[w];
+    const int tile = (int)item.x;
+    const int seg = (int)item.y;
+    const int k0 = seg << GS_SEG_SHIFT;                                  // first list entry of the segment
+    const int n = min(GS_SEG, (int)tile_last[tile] - k0);                // entries in it
+    const uint2 range = ranges[tile];
+    const int tx = tile % d.gx, ty = tile / d.gx;
+    const int qx = 2 * (tid & 7), qy = 2 * (tid >> 3);
+    const int x0 = tx * GS_TILE + qx, y0 = ty * GS_TILE + qy;
+
+    // gather the segment's records (coalesced ids, L2-resident 48-B records)
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
-
-  int contributor = total;  // index (0-based) of the entry about to be processed is contributor-1
-  int todo = total;
-  for (int r = 0; r < rounds; ++r, todo -= BB_THREADS) {
-    __syncthreads();
-    const int k = r * BB_THREADS + tid;  // position counted from the back
-    if (k < total) {
-      const uint32_t id = __ldg(point_list + range.y - 1 - k);
-      const float4* gp = reinterpret_cast<const float4*>(geom + id);
-      s_id[tid] = id;
-      s_q0[tid] = __ldg(gp);
-      s_q1[tid] = __ldg(gp + 1);
-      s_b[tid] = __ldg(reinterpret_cast<const float*>(gp + 2));
+    for (int u = 0; u < BB_PER_THREAD; ++u) {
+      const int j = tid + u * BB_THREADS;
+      if (j < n) {
+        const uint32_t id = __ldg(point_list + range.x + (uint32_t)(k0 + j));
+        const float4* gp = reinterpret_cast<const float4*>(geom + id);
+        s_id[j] = id;
+        s_q0[j] = __ldg(gp);
+        s_q1[j] = __ldg(gp + 1);
+        s_b[j] = __ldg(reinterpret_cast<const float*>(gp + 2));
+      }
     }
+    // per-pixel state
+    float pixx[4], pixy[4], T[4], C0[4], C1[4], C2[4], O0[4], O1[4], O2[4], dL0[4], dL1[4], dL2[4];
+    int last[4];
+    const float4* ck = ckpt + ((size_t)(range.x >> GS_SEG_SHIFT) + (size_t)tile + (size_t)seg) * GS_TILE_PIX;
+    int my_last = 0;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const int px = x0 + (p & 1), py = y0 + (p >> 1);
+      const bool inside = px < d.W && py < d.H;
+      pixx[p] = (float)px;
+      pixy[p] = (float)py;
+      const size_t pix = (size_t)py * d.W + px;
+      last[p] = inside ? (int)n_contrib[pix] : 0;
+      const bool active = last[p] > k0;  // this pixel still had contributors in this segment
+      dL0[p] = active ? dL_dpixels[pix] : 0.f;
+      dL1[p] = active ? dL_dpixels[plane + pix] : 0.f;
+      dL2[p] = active ? dL_dpixels[2 * plane + pix] : 0.f;
+      const float4 fs = active ? final_state[pix] : make_float4(0.f, 0.f, 0.f, 0.f);
+      O0[p] = fmaf(fs.x, bg0, fs.y);  // final pixel colour incl. background, as the forward wrote it
+      O1[p] = fmaf(fs.x, bg1, fs.z);
+      O2[p] = fmaf(fs.x, bg2, fs.w);
+      float4 st = make_float4(1.f, 0.f, 0.f, 0.f);
+      if (active && seg > 0) st = ck[(qy + (p >> 1)) * GS_TILE + qx + (p & 1)];
+      T[p] = st.x;
+      C0[p] = st.y;
+      C1[p] = st.z;
+      C2[p] = st.w;
+      if (!active) last[p] = 0;
+      my_last = max(my_last, last[p]);
+    }
+    int warp_last = my_last;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
     __syncthreads();
-    const int n = min(BB_THREADS, todo);
-    for (int j = 0; j < n; ++j) {
-      --contributor;
-      if (contributor >= warp_last) continue;  // warp-uniform
+    const int jend = min(n, warp_last - k0);  // this warp only needs entries k < warp_last
+
+    for (int j = 0; j < jend; ++j) {
+      const int k = k0 + j;
       const float4 q0 = s_q0[j];
       const float4 q1 = s_q1[j];
-      const float dx = q0.x - pixx, dy = q0.y - pixy;
-      const float power = gs_power(q0.z, q0.w, q1.x, dx, dy);
-      float G = 0.f;
-      float alpha = 0.f;
-      bool valid = (contributor < last_contributor) && !(power > 0.0f);
-      if (valid) {
-        alpha = gs_alpha(q1.y, power, G);
-        valid = !(alpha < GS_ALPHA_MIN);
+      const float cb = s_b[j];
+      float a_mx = 0.f, a_my = 0.f, a_A = 0.f, a_B = 0.f, a_C = 0.f, a_o = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f;
+      bool any = false;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const float dx = q0.x - pixx[p], dy = q0.y - pixy[p];
+        const float power = gs_power(q0.z, q0.w, q1.x, dx, dy);
+        if (k < last[p] && !(power > 0.0f)) {
+          float G;
+          const float alpha = gs_alpha(q1.y, power, G);
+          if (!(alpha < GS_ALPHA_MIN)) {
+            any = true;
+            const float one_m = 1.0f - alpha;
+            const float Ti = T[p];
+            const float wgt = alpha * Ti;
+            C0[p] = fmaf(q1.z, wgt, C0[p]);   // same FMAs as the forward: prefix colour incl. this Gaussian
+            C1[p] = fmaf(q1.w, wgt, C1[p]);
+            C2[p] = fmaf(cb, wgt, C2[p]);
+            T[p] = Ti * one_m;
+            const float inv = __fdividef(1.0f, one_m);
+            a_r = fmaf(wgt, dL0[p], a_r);
+            a_g = fmaf(wgt, dL1[p], a_g);
+            a_b = fmaf(wgt, dL2[p], a_b);
+            float dL_dalpha = (q1.z * Ti - (O0[p] - C0[p]) * inv) * dL0[p];
+            dL_dalpha = fmaf(q1.w * Ti - (O1[p] - C1[p]) * inv, dL1[p], dL_dalpha);
+            dL_dalpha = fmaf(cb * Ti - (O2[p] - C2[p]) * inv, dL2[p], dL_dalpha);
+            a_o = fmaf(G, dL_dalpha, a_o);
+            const float wg = q1.y * dL_dalpha * G;  // dL/dG * G
+            const float wdx = wg * dx, wdy = wg * dy;
+            a_mx += wdx;               // sum w dx
+            a_my += wdy;               // sum w dy
+            a_A = fmaf(wdx, dx, a_A);  // sum w dx^2
+            a_B = fmaf(wdx, dy, a_B);  // sum w dx dy
+            a_C = fmaf(wdy, dy, a_C);  // sum w dy^2
+          }
+        }
       }
-      if (__ballot_sync(0xffffffffu, valid) == 0u) continue;
-
-      float v_mx = 0.f, v_my = 0.f, v_A = 0.f, v_B = 0.f, v_C = 0.f, v_o = 0.f, v_r = 0.f, v_g = 0.f, v_b = 0.f;
-      if (valid) {
-        const float cb = s_b[j];
-        T = T / (1.0f - alpha);
-        const float dchannel_dcolor = alpha * T;
-        acc0 = last_alpha * lc0 + (1.0f - last_alpha) * acc0;
-        acc1 = last_alpha * lc1 + (1.0f - last_alpha) * acc1;
-        acc2 = last_alpha * lc2 + (1.0f - last_alpha) * acc2;
-        lc0 = q1.z;
-        lc1 = q1.w;
-        lc2 = cb;
-        float dL_dalpha = (q1.z - acc0) * dLp0 + (q1.w - acc1) * dLp1 + (cb - acc2) * dLp2;
-        v_r = dchannel_dcolor * dLp0;
-        v_g = dchannel_dcolor * dLp1;
-        v_b = dchannel_dcolor * dLp2;
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
-        const float dL_dG = q1.y * dL_dalpha;
-        const float gdx = G * dx, gdy = G * dy;
-        const float A = 2.0f * q0.z, B = q0.w, C = 2.0f * q1.x;
-        const float dG_ddelx = -gdx * A - gdy * B;
-        const float dG_ddely = -gdy * C - gdx * B;
-        v_mx = dL_dG * dG_ddelx * ddelx_dx;
-        v_my = dL_dG * dG_ddely * ddely_dy;
-        v_A = -0.5f * gdx * dx * dL_dG;
-        v_B = -gdx * dy * dL_dG;
-        v_C = -0.5f * gdy * dy * dL_dG;
-        v_o = G * dL_dalpha;
+      if (__ballot_sync(0xffffffffu, any) == 0u) continue;
+      // moments -> gradient components (A = 2*hA, C = 2*hC)
+      const float A = 2.0f * q0.z, B = q0.w, C = 2.0f * q1.x;
+      float v[8];
+      v[0] = -(A * a_mx + B * a_my) * ddelx_dx;  // dL/dmean2D.x
+      v[1] = -(C * a_my + B * a_mx) * ddely_dy;  // dL/dmean2D.y
+      v[2] = -0.5f * a_A;                        // dL/dA
+      v[3] = -a_B;                               // dL/dB
+      v[4] = -0.5f * a_C;                        // dL/dC
+      v[5] = a_o;                                // dL/dopacity
+      v[6] = a_r;
+      v[7] = a_g;
+      float v8 = a_b;
+      // halving butterfly: 8 values -> each quad of lanes ends up owning the total of one value
+      const bool up16 = lane & 16, up8 = lane & 8, up4 = lane & 4;
+      float w4[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float send = up16 ? v[i] : v[i + 4];
+        const float keep = up16 ? v[i + 4] : v[i];
+        w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
       }
-      v_mx = warp_sum(v_mx);
-      v_my = warp_sum(v_my);
-      v_A = warp_sum(v_A);
-      v_B = warp_sum(v_B);
-      v_C = warp_sum(v_C);
-      v_o = warp_sum(v_o);
-      v_r = warp_sum(v_r);
-      v_g = warp_sum(v_g);
-      v_b = warp_sum(v_b);
-      if (lane < 3) {
-        float4* dst = grad_geom + 3 * (size_t)s_id[j] + lane;
-        float4 v;
-        if (lane == 0) v = make_float4(v_mx, v_my, v_A, v_B);
-        else if (lane == 1) v = make_float4(v_C, v_o, v_r, v_g);
-        else v = make_float4(v_b, 0.f, 0.f, 0.f);
-        atomicAdd(dst, v);
+      float w2[2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const float send = up8 ? w4[i] : w4[i + 2];
+        const float keep = up8 ? w4[i + 2] : w4[i];
+        w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
       }
+      float w1;
+      {
+        const float send = up4 ? w2[0] : w2[1];
+        const float keep = up4 ? w2[1] : w2[0];
+        w1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+      }
+      w1 += __shfl_xor_sync(0xffffffffu, w1, 2);
+      w1 += __shfl_xor_sync(0xffffffffu, w1, 1);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, o);
+      // lane L (L % 4 == 0) owns value index 4*bit4 + 2*bit3 + bit2; lane 1 carries the ninth
+      const int idx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+      float* dst = grad_geom + 12 * (size_t)s_id[j];
+      const bool ninth = lane == 1;
+      if ((lane & 3) == 0 || ninth) atomicAdd(dst + (ninth ? 8 : idx), ninth ? v8 : w1);
     }
   }
 }
 
 cudaError_t gs_launch_blend_backward(const GsDims& d, const uint2* ranges, const uint32_t* point_list,
-                                     const GsGeom* geom, const float bg[3], const float* final_T,
-                                     const uint32_t* n_contrib, const float* dL_dpixels, float4* grad_geom,
-                                     cudaStream_t stream) {
+                                     const GsGeom* geom, const float bg[3], const float4* final_state,
+                                     const uint32_t* n_contrib,
+                                     const float* dL_dpixels, const float4* ckpt, const uint2* work_items,
+                                     const uint32_t* work_count, uint32_t* work_cursor, const uint32_t* tile_last,
+                                     float4* grad_geom, int num_sms, cudaStream_t stream) {
   if (d.ntiles == 0) return cudaSuccess;
-  blend_backward_kernel<<<d.ntiles, BB_THREADS, 0, stream>>>(d, ranges, point_list, geom, bg[0], bg[1], bg[2],
-                                                            final_T, n_contrib, dL_dpixels, grad_geom);
+  cudaError_t e = cudaMemsetAsync(work_cursor, 0, sizeof(uint32_t), stream);
+  if (e != cudaSuccess) return e;
+  const int blocks = num_sms * 10;  // persistent: 95 regs x 64 threads -> 10 blocks per SM
+  blend_backward_kernel<<<blocks, BB_THREADS, 0, stream>>>(d, ranges, point_list, geom, bg[0], bg[1], bg[2],
+                                                          final_state, n_contrib,
+                                                          dL_dpixels, ckpt, work_items, work_count, work_cursor,
+                                                          tile_last, reinterpret_cast<float*>(grad_geom));
   return cudaGetLastError();
 }

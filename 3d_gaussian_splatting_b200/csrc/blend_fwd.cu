@@ -1,90 +1,132 @@
-// blend_fwd.cu — K3: forward alpha compositing, one 256-thread block per
-// 16x16 tile.  Each warp owns an 8x4 pixel sub-block (tight footprint => whole-warp rejects
-// are common for small splats).  Gaussian records (48 B AoS) are gathered in sorted order into
-// shared memory 256 at a time and broadcast-read by all pixels.
-// Skip decisions (power > 0, alpha < 1/255) use the specified numerics in gs_common.cuh and
-// are bit-identical to the oracle's; colour accumulation uses FMAs (smooth differences only).
+// blend_fwd.cu — K3: forward alpha compositing.
+//
+// One 256-thread block per 16x16 tile (one pixel per thread: the per-tile critical path is the
+// number of list entries a pixel walks, so a tile gets the maximum parallelism); each warp owns an
+// 8x4 pixel sub-block.  Tiles are launched heaviest-first (tile_order, binning.cu) because per-tile
+// work is extremely skewed.  Gaussian records (48 B AoS) are gathered in sorted order 256 at a time
+// into shared memory and broadcast-read; entries are evaluated four at a time (power/alpha of four
+// entries are independent, only the short transmittance chain is sequential) so one warp keeps
+// several FMA/MUFU operations in flight.  The block stops once every pixel has terminated.
+//
+// For the segmented backward (blend_bwd.cu) the kernel also leaves, per tile:
+//   * a checkpoint (T, C.rgb) of every live pixel at each GS_SEG-entry boundary of the tile list,
+//   * the work items (tile, segment) for segment < ceil(max_pixel(n_contrib) / GS_SEG).
+// Skip decisions (power > 0, alpha < 1/255) use the specified numerics in gs_common.cuh and are
+// bit-identical to the oracle's; colour accumulation uses FMAs (smooth differences only).
 #include "gs_common.cuh"
 
 #define BF_THREADS 256
 
 __global__ void __launch_bounds__(BF_THREADS)
-blend_forward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
-                     const GsGeom* __restrict__ geom, float bg0, float bg1, float bg2, float* __restrict__ out_color,
-                     float* __restrict__ final_T, uint32_t* __restrict__ n_contrib) {
+blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
+                     const uint32_t* __restrict__ point_list, const GsGeom* __restrict__ geom, float bg0, float bg1,
+                     float bg2, float* __restrict__ out_color, float4* __restrict__ final_state,
+                     uint32_t* __restrict__ n_contrib, float4* __restrict__ ckpt, uint2* __restrict__ work_items,
+                     uint32_t* __restrict__ work_count, uint32_t* __restrict__ tile_last) {
   __shared__ float4 s_q0[BF_THREADS];
   __shared__ float4 s_q1[BF_THREADS];
   __shared__ float s_b[BF_THREADS];
+  __shared__ uint32_t s_wlast[BF_THREADS / 32];
 
-  const int tile = blockIdx.x;
+  const int tile = (int)tile_order[blockIdx.x];
   const int tx = tile % d.gx, ty = tile / d.gx;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int px = tx * GS_TILE + (warp & 1) * 8 + (lane & 7);
-  const int py = ty * GS_TILE + (warp >> 1) * 4 + (lane >> 3);
+  const int lx = (warp & 1) * 8 + (lane & 7), ly = (warp >> 1) * 4 + (lane >> 3);
+  const int px = tx * GS_TILE + lx, py = ty * GS_TILE + ly;
   const bool inside = px < d.W && py < d.H;
   const float pixx = (float)px, pixy = (float)py;
 
   const uint2 range = ranges[tile];
-  int todo = (int)(range.y - range.x);
-  const int rounds = (todo + BF_THREADS - 1) / BF_THREADS;
+  const int total = (int)(range.y - range.x);
+  float4* my_ckpt = ckpt + ((size_t)(range.x >> GS_SEG_SHIFT) + (size_t)tile) * GS_TILE_PIX + (ly * GS_TILE + lx);
 
   bool done = !inside;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
-  uint32_t contributor = 0, last_contributor = 0;
+  uint32_t last_contributor = 0;
 
-  for (int r = 0; r < rounds; ++r, todo -= BF_THREADS) {
-    if (__syncthreads_count(done) == BF_THREADS) break;
-    const uint32_t idx = range.x + r * BF_THREADS + tid;
-    if (idx < range.y) {
-      const uint32_t id = __ldg(point_list + idx);
+  for (int lo = 0; lo < total; lo += BF_THREADS) {
+    if (__syncthreads_and(done)) break;
+    const int n = min(BF_THREADS, total - lo);
+    if (tid < n) {
+      const uint32_t id = __ldg(point_list + range.x + lo + tid);
       const float4* gp = reinterpret_cast<const float4*>(geom + id);
-      const float4 q0 = __ldg(gp), q1 = __ldg(gp + 1);
-      const float b = __ldg(reinterpret_cast<const float*>(gp + 2));
-      s_q0[tid] = q0;
-      s_q1[tid] = q1;
-      s_b[tid] = b;
+      s_q0[tid] = __ldg(gp);
+      s_q1[tid] = __ldg(gp + 1);
+      s_b[tid] = __ldg(reinterpret_cast<const float*>(gp + 2));
     }
     __syncthreads();
-    const int n = min(BF_THREADS, todo);
-    for (int j = 0; !done && j < n; ++j) {
-      ++contributor;
-      const float4 q0 = s_q0[j];
-      const float4 q1 = s_q1[j];
-      const float dx = q0.x - pixx, dy = q0.y - pixy;
-      const float power = gs_power(q0.z, q0.w, q1.x, dx, dy);
-      if (power > 0.0f) continue;
-      float G;
-      const float alpha = gs_alpha(q1.y, power, G);
-      if (alpha < GS_ALPHA_MIN) continue;
-      const float test_T = T * (1.0f - alpha);
-      if (test_T < GS_T_MIN) {
-        done = true;
-        continue;
+    for (int j0 = 0; j0 < n && !done; j0 += 4) {
+      // segment boundary: checkpoint the state in front of entry lo + j0
+      if (((lo + j0) & (GS_SEG - 1)) == 0 && (lo + j0) > 0)
+        my_ckpt[(size_t)((lo + j0) >> GS_SEG_SHIFT) * GS_TILE_PIX] = make_float4(T, C0, C1, C2);
+      float alpha[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = min(j0 + u, n - 1);
+        const float4 q0 = s_q0[j];
+        const float hC = s_q1[j].x, op = s_q1[j].y;
+        const float dx = q0.x - pixx, dy = q0.y - pixy;
+        const float power = gs_power(q0.z, q0.w, hC, dx, dy);
+        float G;
+        const float a = gs_alpha(op, power, G);
+        alpha[u] = (j0 + u < n && !(power > 0.0f) && !(a < GS_ALPHA_MIN)) ? a : 0.0f;
       }
-      const float w = alpha * T;
-      C0 = fmaf(q1.z, w, C0);
-      C1 = fmaf(q1.w, w, C1);
-      C2 = fmaf(s_b[j], w, C2);
-      T = test_T;
-      last_contributor = contributor;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (alpha[u] != 0.0f && !done) {
+          const float test_T = T * (1.0f - alpha[u]);
+          if (test_T < GS_T_MIN) {
+            done = true;
+          } else {
+            const int j = j0 + u;
+            const float w = alpha[u] * T;
+            C0 = fmaf(s_q1[j].z, w, C0);
+            C1 = fmaf(s_q1[j].w, w, C1);
+            C2 = fmaf(s_b[j], w, C2);
+            T = test_T;
+            last_contributor = (uint32_t)(lo + j + 1);
+          }
+        }
+      }
     }
   }
   if (inside) {
     const size_t pix = (size_t)py * d.W + px;
     const size_t plane = (size_t)d.H * d.W;
-    final_T[pix] = T;
+    final_state[pix] = make_float4(T, C0, C1, C2);  // out = C + T * bg; the backward rebuilds it from here
     n_contrib[pix] = last_contributor;
     out_color[pix] = fmaf(T, bg0, C0);
     out_color[plane + pix] = fmaf(T, bg1, C1);
     out_color[2 * plane + pix] = fmaf(T, bg2, C2);
   }
+  // ---- work items of the segmented backward: (tile, s) for s < ceil(tile_last / GS_SEG) ----
+  uint32_t wl = last_contributor;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wl = max(wl, __shfl_xor_sync(0xffffffffu, wl, o));
+  if (lane == 0) s_wlast[warp] = wl;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t tl = lane < BF_THREADS / 32 ? s_wlast[lane] : 0u;
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) tl = max(tl, __shfl_xor_sync(0xffffffffu, tl, o));
+    tl = __shfl_sync(0xffffffffu, tl, 0);
+    const uint32_t nseg = (tl + GS_SEG - 1) >> GS_SEG_SHIFT;
+    uint32_t pos = 0;
+    if (lane == 0 && nseg > 0) pos = atomicAdd(work_count, nseg);
+    pos = __shfl_sync(0xffffffffu, pos, 0);
+    for (uint32_t s = lane; s < nseg; s += 32) work_items[pos + s] = make_uint2((uint32_t)tile, s);
+    if (lane == 0) tile_last[tile] = tl;
+  }
 }
 
-cudaError_t gs_launch_blend_forward(const GsDims& d, const uint2* ranges, const uint32_t* point_list,
-                                    const GsGeom* geom, const float bg[3], float* out_color, float* final_T,
-                                    uint32_t* n_contrib, cudaStream_t stream) {
+cudaError_t gs_launch_blend_forward(const GsDims& d, const uint32_t* tile_order, const uint2* ranges,
+                                    const uint32_t* point_list, const GsGeom* geom, const float bg[3],
+                                    float* out_color, float4* final_state, uint32_t* n_contrib, float4* ckpt,
+                                    uint2* work_items, uint32_t* work_count, uint32_t* tile_last,
+                                    cudaStream_t stream) {
   if (d.ntiles == 0) return cudaSuccess;
-  blend_forward_kernel<<<d.ntiles, BF_THREADS, 0, stream>>>(d, ranges, point_list, geom, bg[0], bg[1], bg[2],
-                                                           out_color, final_T, n_contrib);
+  blend_forward_kernel<<<d.ntiles, BF_THREADS, 0, stream>>>(d, tile_order, ranges, point_list, geom, bg[0], bg[1],
+                                                           bg[2], out_color, final_state, n_contrib, ckpt, work_items,
+                                                           work_count, tile_last);
   return cudaGetLastError();
 }

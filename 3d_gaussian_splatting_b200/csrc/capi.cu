@@ -22,10 +22,13 @@ size_t gs_sort_temp_bytes(uint32_t D, int end_bit);
 cudaError_t gs_launch_sort(void*, size_t, const uint64_t*, uint64_t*, const uint32_t*, uint32_t*, uint32_t, int,
                            cudaStream_t);
 cudaError_t gs_launch_ranges(uint32_t, const uint64_t*, uint2*, int, cudaStream_t);
-cudaError_t gs_launch_blend_forward(const GsDims&, const uint2*, const uint32_t*, const GsGeom*, const float[3],
-                                    float*, float*, uint32_t*, cudaStream_t);
+cudaError_t gs_launch_order_tiles(int, const uint2*, uint32_t*, cudaStream_t);
+cudaError_t gs_launch_blend_forward(const GsDims&, const uint32_t*, const uint2*, const uint32_t*, const GsGeom*,
+                                    const float[3], float*, float4*, uint32_t*, float4*, uint2*, uint32_t*, uint32_t*,
+                                    cudaStream_t);
 cudaError_t gs_launch_blend_backward(const GsDims&, const uint2*, const uint32_t*, const GsGeom*, const float[3],
-                                     const float*, const uint32_t*, const float*, float4*, cudaStream_t);
+                                     const float4*, const uint32_t*, const float*, const float4*, const uint2*,
+                                     const uint32_t*, uint32_t*, const uint32_t*, float4*, int, cudaStream_t);
 cudaError_t gs_launch_preprocess_backward(const gs_settings&, const gs_gaussians&, const gs_gradients&, int,
                                           const int*, const uint8_t*, const float4*, cudaStream_t);
 cudaError_t gs_launch_adam(int, float* const[6], float* const[6], float* const[6], float* const[6], const int[6],
@@ -47,7 +50,10 @@ struct gs_ctx {
   // per-duplicate
   DevBuf keys_a, keys_b, vals_a, vals_b;
   // per-tile / per-pixel
-  DevBuf ranges, final_T, n_contrib;
+  DevBuf ranges, final_state, n_contrib, tile_order, tile_last;
+  // segmented backward: per-segment pixel checkpoints, (tile, segment) work list, {work_count, work_cursor}
+  DevBuf ckpt, work_items, counters;
+  int num_sms = 148;
   DevBuf scan_tmp, sort_tmp, loss_acc;
   uint32_t* d_host_pinned = nullptr;  // D readback
   // state of the last forward
@@ -152,6 +158,7 @@ int gs_create(gs_ctx** out, int device) {
   gs_ctx* c = new (std::nothrow) gs_ctx();
   if (!c) return GS_ENOMEM;
   c->device = device;
+  c->num_sms = prop.multiProcessorCount;
   if (cudaSetDevice(device) != cudaSuccess || cudaMallocHost((void**)&c->d_host_pinned, 64) != cudaSuccess) {
     gs_set_error(nullptr, "cudaSetDevice/cudaMallocHost failed: %s", cudaGetErrorString(cudaGetLastError()));
     delete c;
@@ -166,7 +173,8 @@ void gs_destroy(gs_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   DevBuf* bufs[] = {&c->geom,   &c->depths, &c->radii,  &c->tiles,   &c->offsets,   &c->clamped,  &c->grad_geom,
-                    &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_T,  &c->n_contrib,
+                    &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_state,  &c->n_contrib,
+                    &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters,
                     &c->scan_tmp, &c->sort_tmp, &c->loss_acc};
   for (DevBuf* b : bufs)
     if (b->ptr) cudaFree(b->ptr);
@@ -261,7 +269,10 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->offsets, Nn * 4);
   GS_ENSURE(c, c->clamped, Nn);
   GS_ENSURE(c, c->ranges, (size_t)d.ntiles * sizeof(uint2));
-  GS_ENSURE(c, c->final_T, P * 4);
+  GS_ENSURE(c, c->final_state, P * 16);
+  GS_ENSURE(c, c->tile_order, (size_t)d.ntiles * 4);
+  GS_ENSURE(c, c->tile_last, (size_t)d.ntiles * 4);
+  GS_ENSURE(c, c->counters, 64);
   GS_ENSURE(c, c->n_contrib, P * 4);
   const size_t scan_bytes = gs_scan_temp_bytes(N > 0 ? N : 1);
   GS_ENSURE(c, c->scan_tmp, scan_bytes);
@@ -318,12 +329,21 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
     StageTimer t(c, 3, stream);
     GS_CUDA_CHECK(c, gs_launch_ranges((uint32_t)D, (const uint64_t*)c->keys_b.ptr, (uint2*)c->ranges.ptr, d.ntiles,
                                       stream));
+    GS_CUDA_CHECK(c, gs_launch_order_tiles(d.ntiles, (const uint2*)c->ranges.ptr, (uint32_t*)c->tile_order.ptr,
+                                           stream));
   }
+  // segment bookkeeping of the backward: at most D/GS_SEG + ntiles segments over all tiles
+  const size_t max_segs = (size_t)(D >> GS_SEG_SHIFT) + (size_t)d.ntiles;
+  GS_ENSURE(c, c->work_items, max_segs * sizeof(uint2));
+  GS_ENSURE(c, c->ckpt, max_segs * GS_TILE_PIX * sizeof(float4));
   {
     StageTimer t(c, 4, stream);
-    GS_CUDA_CHECK(c, gs_launch_blend_forward(d, (const uint2*)c->ranges.ptr, (const uint32_t*)c->vals_b.ptr,
-                                             (const GsGeom*)c->geom.ptr, st->bg, out_color, (float*)c->final_T.ptr,
-                                             (uint32_t*)c->n_contrib.ptr, stream));
+    GS_CUDA_CHECK(c, cudaMemsetAsync(c->counters.ptr, 0, 8, stream));
+    GS_CUDA_CHECK(c, gs_launch_blend_forward(d, (const uint32_t*)c->tile_order.ptr, (const uint2*)c->ranges.ptr,
+                                             (const uint32_t*)c->vals_b.ptr, (const GsGeom*)c->geom.ptr, st->bg,
+                                             out_color, (float4*)c->final_state.ptr, (uint32_t*)c->n_contrib.ptr,
+                                             (float4*)c->ckpt.ptr, (uint2*)c->work_items.ptr,
+                                             (uint32_t*)c->counters.ptr, (uint32_t*)c->tile_last.ptr, stream));
   }
   if (radii && N > 0)
     GS_CUDA_CHECK(c, cudaMemcpyAsync(radii, c->radii.ptr, (size_t)N * 4, cudaMemcpyDeviceToDevice, stream));
@@ -362,9 +382,12 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
     StageTimer t(c, 5, stream);
     GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
     GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, (const uint32_t*)c->vals_b.ptr,
-                                              (const GsGeom*)c->geom.ptr, st->bg, (const float*)c->final_T.ptr,
+                                              (const GsGeom*)c->geom.ptr, st->bg, (const float4*)c->final_state.ptr,
                                               (const uint32_t*)c->n_contrib.ptr, dL_dout_color,
-                                              (float4*)c->grad_geom.ptr, stream));
+                                              (const float4*)c->ckpt.ptr, (const uint2*)c->work_items.ptr,
+                                              (const uint32_t*)c->counters.ptr, (uint32_t*)c->counters.ptr + 1,
+                                              (const uint32_t*)c->tile_last.ptr, (float4*)c->grad_geom.ptr,
+                                              c->num_sms, stream));
   }
   {
     StageTimer t(c, 6, stream);
@@ -479,7 +502,13 @@ int gs_debug_get(gs_ctx* c, int what, void* host_dst, size_t bytes) {
     case GS_DBG_KEYS_SORTED: src = c->keys_b.ptr; break;
     case GS_DBG_POINT_LIST: src = c->vals_b.ptr; break;
     case GS_DBG_RANGES: src = c->ranges.ptr; break;
-    case GS_DBG_FINAL_T: src = c->final_T.ptr; break;
+    case GS_DBG_FINAL_T: {  // .x of the per-pixel final state {T, C.r, C.g, C.b}
+      const size_t P = (size_t)c->H * c->W;
+      std::vector<float> fs(P * 4);
+      GS_CUDA_CHECK(c, cudaMemcpy(fs.data(), c->final_state.ptr, P * 16, cudaMemcpyDeviceToHost));
+      for (size_t i = 0; i < P; ++i) ((float*)host_dst)[i] = fs[4 * i];
+      return GS_OK;
+    }
     case GS_DBG_N_CONTRIB: src = c->n_contrib.ptr; break;
     case GS_DBG_KEYS_UNSORTED: src = c->keys_a.ptr; break;
     case GS_DBG_VALUES_UNSORTED: src = c->vals_a.ptr; break;
