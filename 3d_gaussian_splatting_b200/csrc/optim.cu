@@ -1,15 +1,19 @@
 // optim.cu — K5: fused Adam over the six parameter groups of
 // GaussianModel::setup (src/scene/gaussian_model.cpp:323-345) + densification statistics
 // (fields at src/scene/gaussian_model.h:18-20), and the L1 photometric loss.
-// Adam follows libtorch's Adam::step order with its defaults (only lr is set by the reference):
-//   m = m*b1 + g*(1-b1); v = v*b2 + g*g*(1-b2); denom = sqrt(v)/sqrt(1-b2^t) + eps;
-//   p -= lr/(1-b1^t) * m/denom.
-// Purely HBM-bound: 28 B per parameter float (+4 B when the gradient is re-zeroed); 16-byte
-// vector accesses, 4 independent vectors per thread in flight, no shared memory.
+// Adam follows libtorch's Adam::step with its defaults (only lr is set by the reference), in the
+// arithmetic of libtorch's CUDA elementwise kernels (the reference keeps its tensors on kCUDA):
+//   m = fma(1-b1, g, m*b1);  v = fma((1-b2)*g, g, v*b2);
+//   denom = sqrt(v) * (1/sqrt(1-b2^t)) + eps;  p = fma(-lr/(1-b1^t), m/denom, p)
+// with IEEE sqrt and division -- the same specified numerics as oracle/orc_optim.c, so the
+// result is bit-identical to the oracle.
+// Purely HBM-bound: 28 B per parameter float (+4 B when the gradient is re-zeroed); streaming
+// 16-byte accesses (evict-first: nothing here is reused within the step), 8 independent vector
+// loads per thread in flight at <= 64 registers so four 256-thread blocks stay resident per SM.
 #include "gs_common.cuh"
 
 #define AD_THREADS 256
-#define AD_VEC_PER_THREAD 4
+#define AD_VEC_PER_THREAD 2
 #define AD_FLOATS_PER_BLOCK (AD_THREADS * AD_VEC_PER_THREAD * 4)
 
 struct AdamSeg {
@@ -20,7 +24,7 @@ struct AdamSeg {
   size_t n;         // floats in this segment
   int block_start;  // first block of this segment
   int vec_ok;       // all four pointers 16-byte aligned
-  float step_size, bc2_sqrt;
+  float neg_step, inv_bc2_sqrt;
 };
 struct AdamArgs {
   AdamSeg seg[6];
@@ -35,16 +39,17 @@ struct AdamArgs {
   float* denom;
 };
 
-__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, const AdamArgs& a, const AdamSeg& s) {
-  const float mi = __fadd_rn(__fmul_rn(m, a.b1), __fmul_rn(g, a.omb1));
-  const float vi = __fadd_rn(__fmul_rn(v, a.b2), __fmul_rn(__fmul_rn(g, g), a.omb2));
-  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), s.bc2_sqrt), a.eps);
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float b1, float b2, float omb1,
+                                         float omb2, float eps, float neg_step, float inv_bc2_sqrt) {
+  const float mi = __fmaf_rn(omb1, g, __fmul_rn(m, b1));
+  const float vi = __fmaf_rn(__fmul_rn(omb2, g), g, __fmul_rn(v, b2));
+  const float denom = __fadd_rn(__fmul_rn(__fsqrt_rn(vi), inv_bc2_sqrt), eps);
   m = mi;
   v = vi;
-  p = __fsub_rn(p, __fmul_rn(s.step_size, __fdiv_rn(mi, denom)));
+  p = __fmaf_rn(neg_step, __fdiv_rn(mi, denom), p);
 }
 
-__global__ void __launch_bounds__(AD_THREADS) adam_stats_kernel(const __grid_constant__ AdamArgs a) {
+__global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_constant__ AdamArgs a) {
   const int b = blockIdx.x;
   if (b >= a.stats_block_start) {
     // ---- densification statistics, one thread per Gaussian ----
@@ -65,38 +70,39 @@ __global__ void __launch_bounds__(AD_THREADS) adam_stats_kernel(const __grid_con
   for (int k = 1; k < 6; ++k)
     if (b >= a.seg[k].block_start) si = k;
   const AdamSeg& s = a.seg[si];
+  const float b1 = a.b1, b2 = a.b2, omb1 = a.omb1, omb2 = a.omb2, eps = a.eps;
+  const float neg_step = s.neg_step, inv_bc2_sqrt = s.inv_bc2_sqrt;
   const size_t base = (size_t)(b - s.block_start) * AD_FLOATS_PER_BLOCK;
   if (s.vec_ok && base + AD_FLOATS_PER_BLOCK <= s.n) {
     float4 p[AD_VEC_PER_THREAD], g[AD_VEC_PER_THREAD], m[AD_VEC_PER_THREAD], v[AD_VEC_PER_THREAD];
     const size_t v0 = base / 4 + threadIdx.x;
+    float4* __restrict__ pp = reinterpret_cast<float4*>(s.p) + v0;
+    float4* __restrict__ gp = reinterpret_cast<float4*>(s.g) + v0;
+    float4* __restrict__ mp = reinterpret_cast<float4*>(s.m) + v0;
+    float4* __restrict__ vp = reinterpret_cast<float4*>(s.v) + v0;
 #pragma unroll
     for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
-      const size_t idx = v0 + (size_t)k * AD_THREADS;
-      p[k] = reinterpret_cast<const float4*>(s.p)[idx];
-      g[k] = reinterpret_cast<const float4*>(s.g)[idx];
-      m[k] = reinterpret_cast<const float4*>(s.m)[idx];
-      v[k] = reinterpret_cast<const float4*>(s.v)[idx];
+      g[k] = __ldcs(gp + k * AD_THREADS);
+      m[k] = __ldcs(mp + k * AD_THREADS);
+      v[k] = __ldcs(vp + k * AD_THREADS);
+      p[k] = __ldcs(pp + k * AD_THREADS);
     }
 #pragma unroll
     for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
-      adam_one(p[k].x, g[k].x, m[k].x, v[k].x, a, s);
-      adam_one(p[k].y, g[k].y, m[k].y, v[k].y, a, s);
-      adam_one(p[k].z, g[k].z, m[k].z, v[k].z, a, s);
-      adam_one(p[k].w, g[k].w, m[k].w, v[k].w, a, s);
-    }
-#pragma unroll
-    for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
-      const size_t idx = v0 + (size_t)k * AD_THREADS;
-      reinterpret_cast<float4*>(s.p)[idx] = p[k];
-      reinterpret_cast<float4*>(s.m)[idx] = m[k];
-      reinterpret_cast<float4*>(s.v)[idx] = v[k];
-      if (a.zero_grads) reinterpret_cast<float4*>(s.g)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+      adam_one(p[k].x, g[k].x, m[k].x, v[k].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      adam_one(p[k].y, g[k].y, m[k].y, v[k].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      adam_one(p[k].z, g[k].z, m[k].z, v[k].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      adam_one(p[k].w, g[k].w, m[k].w, v[k].w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      __stcs(mp + k * AD_THREADS, m[k]);
+      __stcs(vp + k * AD_THREADS, v[k]);
+      __stcs(pp + k * AD_THREADS, p[k]);
+      if (a.zero_grads) __stcs(gp + k * AD_THREADS, make_float4(0.f, 0.f, 0.f, 0.f));
     }
   } else {
     // ragged tail / unaligned segment: scalar, still coalesced
     for (size_t idx = base + threadIdx.x; idx < s.n && idx < base + AD_FLOATS_PER_BLOCK; idx += AD_THREADS) {
       float p = s.p[idx], m = s.m[idx], v = s.v[idx];
-      adam_one(p, s.g[idx], m, v, a, s);
+      adam_one(p, s.g[idx], m, v, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
       s.p[idx] = p;
       s.m[idx] = m;
       s.v[idx] = v;
@@ -124,8 +130,8 @@ cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6],
     // libtorch evaluates the bias corrections in double and applies them as fp32 scalars
     const double bc1 = 1.0 - pow(beta1, (double)step[s]);
     const double bc2 = 1.0 - pow(beta2, (double)step[s]);
-    g.step_size = (float)(lr[s] / bc1);
-    g.bc2_sqrt = (float)sqrt(bc2);
+    g.neg_step = (float)(-(lr[s] / bc1));
+    g.inv_bc2_sqrt = 1.0f / (float)sqrt(bc2);
     blocks += (int)((g.n + AD_FLOATS_PER_BLOCK - 1) / AD_FLOATS_PER_BLOCK);
   }
   a.stats_block_start = blocks;

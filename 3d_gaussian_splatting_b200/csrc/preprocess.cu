@@ -8,11 +8,15 @@
 // (src/utils/general_utils.cpp:12-40), L = R*diag(mod*s) (:88-99), Sigma = L*L^T packed
 // [xx,xy,xz,yy,yz,zz] (src/scene/gaussian_model.cpp:18-28).
 //
-// Memory: xyz/scale/rot/opacity are read straight from the reference's row-major (N,C)
-// tensors (a warp covers a contiguous span; L1 absorbs the stride-C pattern).  The SH rows
-// (up to 180 B per Gaussian) are staged through shared memory with fully coalesced loads and
-// an odd row pitch so the per-thread row reads are bank-conflict free.
+// Memory, measured path (preprocess_bulk_kernel): the reference's row-major (N,C) tensors are
+// consumed as they are -- each 128-row block pulls its xyz / scale / rotation / opacity / SH-dc /
+// SH-rest slices into shared memory with TMA bulk copies on one mbarrier (the AoS -> thread-row
+// transposition happens there; 45- and 3-float row pitches are odd, hence bank-conflict free),
+// and the 48-B geometry records, depths, radii, tile counts and clamp masks leave as bulk stores.
+// Generic fallback (preprocess_kernel: strided / unaligned tensors, precomputed cov3D or colours,
+// ragged tail): direct loads, SH rows staged through shared memory with coalesced loops.
 #include "gs_common.cuh"
+#include "tma_bulk.cuh"
 
 #define PP_THREADS 256
 
@@ -113,31 +117,19 @@ __device__ __forceinline__ void sh_to_rgb(int deg, const float p[3], const float
   }
 }
 
-__global__ void __launch_bounds__(PP_THREADS)
-preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreprocessArgs a) {
-  extern __shared__ float s_sh[];
-  const int tid = threadIdx.x;
-  const int row0 = blockIdx.x * PP_THREADS;
-  const int i = row0 + tid;
-  const int rows = min(PP_THREADS, a.N - row0);
+struct PpOut {
+  GsGeom g;
+  float depth;
+  int radius;
+  uint32_t tiles, cmask;
+};
 
-  // ---- stage the SH "rest" rows of this block: coalesced global reads, odd-pitch smem ----
-  if (a.rest_width > 0 && a.in.colors_precomp == nullptr) {
-    const int stride = a.in.sh_rest_stride;
-    const float* base = a.in.sh_rest + (size_t)row0 * stride;
-    const int total = (rows - 1) * stride + a.rest_width;  // never read past the last row
-    int row = tid / stride, col = tid % stride;
-    const int drow = PP_THREADS / stride, dcol = PP_THREADS % stride;
-    for (int f = tid; f < total; f += PP_THREADS) {
-      if (col < a.rest_width) s_sh[row * a.rest_pitch + col] = __ldg(base + f);
-      row += drow;
-      col += dcol;
-      if (col >= stride) { col -= stride; ++row; }
-    }
-  }
-  __syncthreads();
-  if (i >= a.N) return;
-
+// One Gaussian.  p / scl / q4 / opac_in as stored by the caller (raw when a.in.raw_params); cov_pre, col_pre:
+// precomputed cov3D / colour rows or nullptr; dcp: the three SH dc floats; srow: the staged SH "rest" row.
+__device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const PreprocessArgs& a, const float p[3],
+                                            const float scl[3], const float4 q4, const float opac_in,
+                                            const float* cov_pre, const float* col_pre, const float* dcp,
+                                            const float* srow) {
   GsGeom g;
   g.q0 = make_float4(0.f, 0.f, 0.f, 0.f);
   g.q1 = g.q0;
@@ -146,7 +138,6 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
   uint32_t tiles = 0, cmask = 0;
   float depth = 0.f;
 
-  const float p[3] = {a.in.means3D[3 * i], a.in.means3D[3 * i + 1], a.in.means3D[3 * i + 2]};
   const float* V = st.viewmatrix;
   const float* M = st.projmatrix;
   float pv[3];
@@ -164,12 +155,11 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
     float ndc_x = ph[0] * pw, ndc_y = ph[1] * pw;
 
     float c6[6];
-    if (a.in.cov3D_precomp) {
+    if (cov_pre) {
 #pragma unroll
-      for (int c = 0; c < 6; ++c) c6[c] = a.in.cov3D_precomp[6 * (size_t)i + c];
+      for (int c = 0; c < 6; ++c) c6[c] = cov_pre[c];
     } else {
-      float s[3] = {a.in.scales[3 * i], a.in.scales[3 * i + 1], a.in.scales[3 * i + 2]};
-      const float4 q4 = *reinterpret_cast<const float4*>(a.in.rotations + 4 * (size_t)i);
+      float s[3] = {scl[0], scl[1], scl[2]};
       float q[4] = {q4.x, q4.y, q4.z, q4.w};
       if (a.in.raw_params) {
         s[0] = expf(s[0]);
@@ -206,16 +196,15 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
         int area = (x1 - x0) * (y1 - y0);
         if (area > 0) {
           float rgb[3];
-          if (a.in.colors_precomp) {
-            rgb[0] = a.in.colors_precomp[3 * (size_t)i];
-            rgb[1] = a.in.colors_precomp[3 * (size_t)i + 1];
-            rgb[2] = a.in.colors_precomp[3 * (size_t)i + 2];
+          if (col_pre) {
+            rgb[0] = col_pre[0];
+            rgb[1] = col_pre[1];
+            rgb[2] = col_pre[2];
           } else {
-            const float* dcp = a.in.sh_dc + (size_t)i * a.in.sh_dc_stride;
-            const float dc[3] = {__ldg(dcp), __ldg(dcp + 1), __ldg(dcp + 2)};
-            sh_to_rgb(st.sh_degree, p, st.campos, dc, s_sh + tid * a.rest_pitch, rgb, cmask);
+            const float dc[3] = {dcp[0], dcp[1], dcp[2]};
+            sh_to_rgb(st.sh_degree, p, st.campos, dc, srow, rgb, cmask);
           }
-          float opac = a.in.opacities[i];
+          float opac = opac_in;
           if (a.in.raw_params) opac = 1.0f / (1.0f + expf(-opac));
           g.q0 = make_float4(px, py, 0.5f * con_x, con_y);
           g.q1 = make_float4(0.5f * con_z, opac, rgb[0], rgb[1]);
@@ -227,12 +216,126 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
       }
     }
   }
-  a.geom[i] = g;
-  a.depths[i] = depth;
-  a.radii[i] = rad_out;
-  a.tiles_touched[i] = tiles;
-  a.clamped[i] = (uint8_t)cmask;
+  PpOut o;
+  o.g = g;
+  o.depth = depth;
+  o.radius = rad_out;
+  o.tiles = tiles;
+  o.cmask = cmask;
+  return o;
 }
+
+__global__ void __launch_bounds__(PP_THREADS)
+preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreprocessArgs a, const int first) {
+  extern __shared__ float s_sh[];
+  const int tid = threadIdx.x;
+  const int row0 = first + blockIdx.x * PP_THREADS;
+  const int i = row0 + tid;
+  const int rows = min(PP_THREADS, a.N - row0);
+
+  // ---- stage the SH "rest" rows of this block: coalesced global reads, odd-pitch smem ----
+  if (a.rest_width > 0 && a.in.colors_precomp == nullptr) {
+    const int stride = a.in.sh_rest_stride;
+    const float* base = a.in.sh_rest + (size_t)row0 * stride;
+    const int total = (rows - 1) * stride + a.rest_width;  // never read past the last row
+    int row = tid / stride, col = tid % stride;
+    const int drow = PP_THREADS / stride, dcol = PP_THREADS % stride;
+    for (int f = tid; f < total; f += PP_THREADS) {
+      if (col < a.rest_width) s_sh[row * a.rest_pitch + col] = __ldg(base + f);
+      row += drow;
+      col += dcol;
+      if (col >= stride) { col -= stride; ++row; }
+    }
+  }
+  __syncthreads();
+  if (i >= a.N) return;
+
+  const float p[3] = {a.in.means3D[3 * i], a.in.means3D[3 * i + 1], a.in.means3D[3 * i + 2]};
+  const float* cov_pre = a.in.cov3D_precomp ? a.in.cov3D_precomp + 6 * (size_t)i : nullptr;
+  const float* col_pre = a.in.colors_precomp ? a.in.colors_precomp + 3 * (size_t)i : nullptr;
+  float scl[3] = {0.f, 0.f, 0.f};
+  float4 q4 = make_float4(1.f, 0.f, 0.f, 0.f);
+  if (!cov_pre) {
+    scl[0] = a.in.scales[3 * i];
+    scl[1] = a.in.scales[3 * i + 1];
+    scl[2] = a.in.scales[3 * i + 2];
+    q4 = *reinterpret_cast<const float4*>(a.in.rotations + 4 * (size_t)i);
+  }
+  const float* dcp = col_pre ? nullptr : a.in.sh_dc + (size_t)i * a.in.sh_dc_stride;
+  const PpOut o = pp_compute(st, a, p, scl, q4, a.in.opacities[i], cov_pre, col_pre, dcp, s_sh + tid * a.rest_pitch);
+  a.geom[i] = o.g;
+  a.depths[i] = o.depth;
+  a.radii[i] = o.radius;
+  a.tiles_touched[i] = o.tiles;
+  a.clamped[i] = (uint8_t)o.cmask;
+}
+
+// ---- TMA-staged path ---------------------------------------------------------------------------
+#define PPB_ROWS 128
+#define PPB_OFF_SH 0                               // rows x 45 floats
+#define PPB_OFF_XYZ (PPB_OFF_SH + PPB_ROWS * 45)   // rows x 3
+#define PPB_OFF_SCL (PPB_OFF_XYZ + PPB_ROWS * 3)   // rows x 3
+#define PPB_OFF_ROT (PPB_OFF_SCL + PPB_ROWS * 3)   // rows x 4
+#define PPB_OFF_OP (PPB_OFF_ROT + PPB_ROWS * 4)    // rows x 1
+#define PPB_OFF_DC (PPB_OFF_OP + PPB_ROWS)         // rows x 3
+#define PPB_OFF_GEOM (PPB_OFF_DC + PPB_ROWS * 3)   // rows x 12 (out)
+#define PPB_OFF_DEPTH (PPB_OFF_GEOM + PPB_ROWS * 12)
+#define PPB_OFF_RADII (PPB_OFF_DEPTH + PPB_ROWS)
+#define PPB_OFF_TILES (PPB_OFF_RADII + PPB_ROWS)
+#define PPB_OFF_CLAMP (PPB_OFF_TILES + PPB_ROWS)   // rows x 1 byte
+#define PPB_FLOATS (PPB_OFF_CLAMP + PPB_ROWS / 4)
+#define PPB_SMEM_BYTES (PPB_FLOATS * 4 + 16)
+
+__global__ void __launch_bounds__(PPB_ROWS)
+preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreprocessArgs a) {
+  extern __shared__ __align__(128) float s_buf[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_buf + PPB_FLOATS);
+  const int tid = threadIdx.x;
+  const size_t row0 = (size_t)blockIdx.x * PPB_ROWS;
+  const int W = a.in.sh_rest_stride;  // dense rows (0 when the model has no higher-order SH)
+
+  if (tid == 0) {
+    tma::mbar_init(bar, 1);
+    tma::fence_mbar_init();
+    const uint32_t sh_bytes = a.rest_width > 0 ? (uint32_t)(PPB_ROWS * W * 4) : 0u;
+    tma::mbar_arrive_expect_tx(bar, sh_bytes + PPB_ROWS * (12u + 12u + 16u + 4u + 12u));
+    tma::load(s_buf + PPB_OFF_XYZ, a.in.means3D + 3 * row0, PPB_ROWS * 12u, bar);
+    tma::load(s_buf + PPB_OFF_SCL, a.in.scales + 3 * row0, PPB_ROWS * 12u, bar);
+    tma::load(s_buf + PPB_OFF_ROT, a.in.rotations + 4 * row0, PPB_ROWS * 16u, bar);
+    tma::load(s_buf + PPB_OFF_OP, a.in.opacities + row0, PPB_ROWS * 4u, bar);
+    tma::load(s_buf + PPB_OFF_DC, a.in.sh_dc + 3 * row0, PPB_ROWS * 12u, bar);
+    if (sh_bytes) tma::load(s_buf + PPB_OFF_SH, a.in.sh_rest + row0 * W, sh_bytes, bar);
+  }
+  __syncthreads();
+  tma::mbar_wait(bar, 0);
+
+  const float p[3] = {s_buf[PPB_OFF_XYZ + 3 * tid], s_buf[PPB_OFF_XYZ + 3 * tid + 1], s_buf[PPB_OFF_XYZ + 3 * tid + 2]};
+  const float scl[3] = {s_buf[PPB_OFF_SCL + 3 * tid], s_buf[PPB_OFF_SCL + 3 * tid + 1], s_buf[PPB_OFF_SCL + 3 * tid + 2]};
+  const float4 q4 = reinterpret_cast<const float4*>(s_buf + PPB_OFF_ROT)[tid];
+  const PpOut o = pp_compute(st, a, p, scl, q4, s_buf[PPB_OFF_OP + tid], nullptr, nullptr, s_buf + PPB_OFF_DC + 3 * tid,
+                             s_buf + PPB_OFF_SH + tid * W);
+  float4* sg = reinterpret_cast<float4*>(s_buf + PPB_OFF_GEOM) + 3 * tid;
+  sg[0] = o.g.q0;
+  sg[1] = o.g.q1;
+  sg[2] = o.g.q2;
+  s_buf[PPB_OFF_DEPTH + tid] = o.depth;
+  reinterpret_cast<int*>(s_buf)[PPB_OFF_RADII + tid] = o.radius;
+  reinterpret_cast<uint32_t*>(s_buf)[PPB_OFF_TILES + tid] = o.tiles;
+  reinterpret_cast<uint8_t*>(s_buf + PPB_OFF_CLAMP)[tid] = (uint8_t)o.cmask;
+  tma::fence_proxy_async_smem();
+  __syncthreads();
+  if (tid == 0) {
+    tma::store(a.geom + row0, s_buf + PPB_OFF_GEOM, PPB_ROWS * 48u);
+    tma::store(a.depths + row0, s_buf + PPB_OFF_DEPTH, PPB_ROWS * 4u);
+    tma::store(a.radii + row0, s_buf + PPB_OFF_RADII, PPB_ROWS * 4u);
+    tma::store(a.tiles_touched + row0, s_buf + PPB_OFF_TILES, PPB_ROWS * 4u);
+    tma::store(a.clamped + row0, s_buf + PPB_OFF_CLAMP, PPB_ROWS);
+    tma::commit_group();
+    tma::wait_group_read0();
+  }
+}
+
+static bool pp_aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 
 cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, int N, GsGeom* geom, float* depths,
                                  int* radii, uint32_t* tiles_touched, uint8_t* clamped, cudaStream_t stream) {
@@ -254,7 +357,29 @@ cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, 
   a.rest_pitch = a.rest_width | 1;
   size_t smem = (size_t)PP_THREADS * a.rest_pitch * sizeof(float);
   if (a.rest_width == 0) smem = 0;
-  const int blocks = (N + PP_THREADS - 1) / PP_THREADS;
-  preprocess_kernel<<<blocks, PP_THREADS, smem, stream>>>(st, a);
+  const int kmax = (st.max_sh_degree + 1) * (st.max_sh_degree + 1);
+  const int Wmax = 3 * (kmax - 1);
+  const bool dense = !in.colors_precomp && !in.cov3D_precomp && in.sh_dc_stride == 3 &&
+                     (Wmax == 0 || in.sh_rest_stride == Wmax) && (a.rest_width == 0 || in.sh_rest_stride <= 45) &&
+                     pp_aligned16(in.means3D) && pp_aligned16(in.scales) && pp_aligned16(in.rotations) &&
+                     pp_aligned16(in.opacities) && pp_aligned16(in.sh_dc) &&
+                     (a.rest_width == 0 || pp_aligned16(in.sh_rest));
+  int first = 0;
+  if (dense && N >= PPB_ROWS) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t e =
+          cudaFuncSetAttribute(preprocess_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PPB_SMEM_BYTES);
+      if (e != cudaSuccess) return e;
+      attr_set = true;
+    }
+    const int blocks = N / PPB_ROWS;
+    preprocess_bulk_kernel<<<blocks, PPB_ROWS, PPB_SMEM_BYTES, stream>>>(st, a);
+    first = blocks * PPB_ROWS;
+  }
+  if (first < N) {
+    const int blocks = (N - first + PP_THREADS - 1) / PP_THREADS;
+    preprocess_kernel<<<blocks, PP_THREADS, smem, stream>>>(st, a, first);
+  }
   return cudaGetLastError();
 }

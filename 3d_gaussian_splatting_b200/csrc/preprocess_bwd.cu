@@ -2,10 +2,17 @@
 // conic -> cov2D -> (cov3D, view-space mean); mean2D -> mean3D; SH backward; cov3D ->
 // (scale, quaternion) through the reference's parametrisation (q normalised inside,
 // src/utils/general_utils.cpp:14-19; L = R diag(s), Sigma = L L^T, gaussian_model.cpp:18-28).
-// One thread per Gaussian; SH rows are staged through shared memory in both directions so the
-// 180-byte-per-Gaussian reads and gradient writes are coalesced.  With raw_params the
-// activation Jacobians (exp, sigmoid) are applied here too.
+// One thread per Gaussian.  Two kernels share the math (pb_compute):
+//  * preprocess_backward_bulk_kernel — the measured path: every per-Gaussian input slice of a
+//    128-row block (xyz, scales, rotations, opacities, the 48-B blend-gradient records, the 180-B
+//    SH rows) arrives by TMA bulk copy on one mbarrier while the threads already work, the
+//    gradients are written in place into the same shared-memory slices and leave as bulk stores
+//    (or bulk fp32 reduce-adds when accumulating across views).  No strided LDG/STG, no index math.
+//  * preprocess_backward_kernel — generic fallback (precomputed cov3D / colours, strided or
+//    unaligned tensors, ragged tail): SH rows staged through shared memory with coalesced loops.
+// With raw_params the activation Jacobians (exp, sigmoid, normalise) are applied here too.
 #include "gs_common.cuh"
+#include "tma_bulk.cuh"
 
 #define PB_THREADS 256
 
@@ -22,52 +29,47 @@ struct PreBwdArgs {
   int pitch;           // odd, >= rest_width_max
 };
 
-__global__ void __launch_bounds__(PB_THREADS)
-preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a) {
-  extern __shared__ float s_sh[];
-  const int tid = threadIdx.x;
-  const int row0 = blockIdx.x * PB_THREADS;
-  const int i = row0 + tid;
-  const int rows = min(PB_THREADS, a.N - row0);
-  const bool use_sh = a.in.colors_precomp == nullptr;
+struct PbOut {
+  float gm[3], gs[3], gq[4], gcov[6], gdc[3], gcol[3], gr[3], basis[15];
+  float g2x, g2y, gop;
+};
 
-  if (use_sh && a.rest_width_act > 0) {
-    const int stride = a.in.sh_rest_stride;
-    const float* base = a.in.sh_rest + (size_t)row0 * stride;
-    const int total = (rows - 1) * stride + a.rest_width_act;
-    int row = tid / stride, col = tid % stride;
-    const int drow = PB_THREADS / stride, dcol = PB_THREADS % stride;
-    for (int f = tid; f < total; f += PB_THREADS) {
-      if (col < a.rest_width_act) s_sh[row * a.pitch + col] = __ldg(base + f);
-      row += drow;
-      col += dcol;
-      if (col >= stride) { col -= stride; ++row; }
-    }
-  }
-  __syncthreads();
-
-  float gm[3] = {0.f, 0.f, 0.f}, gs[3] = {0.f, 0.f, 0.f}, gq[4] = {0.f, 0.f, 0.f, 0.f};
-  float gcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  float gdc[3] = {0.f, 0.f, 0.f}, gcol[3] = {0.f, 0.f, 0.f};
-  float g2x = 0.f, g2y = 0.f, gop = 0.f;
-  float basis[15], gr[3] = {0.f, 0.f, 0.f};
+__device__ __forceinline__ void pb_zero(PbOut& o) {
 #pragma unroll
-  for (int k = 0; k < 15; ++k) basis[k] = 0.f;
-  float* srow = s_sh + tid * a.pitch;
-  bool visible = false;
+  for (int k = 0; k < 3; ++k) o.gm[k] = o.gs[k] = o.gdc[k] = o.gcol[k] = o.gr[k] = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) o.gq[k] = 0.f;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) o.gcov[k] = 0.f;
+#pragma unroll
+  for (int k = 0; k < 15; ++k) o.basis[k] = 0.f;
+  o.g2x = o.g2y = o.gop = 0.f;
+}
 
-  if (i < a.N) visible = a.radii[i] > 0;
-  if (visible) {
-    const float4 G0 = a.grad_geom[3 * (size_t)i], G1 = a.grad_geom[3 * (size_t)i + 1];
-    const float G2x = a.grad_geom[3 * (size_t)i + 2].x;
-    g2x = G0.x;
-    g2y = G0.y;
+// Backward of one visible Gaussian.  p: mean; q4/scl/opac_in: rotation, scale, opacity as stored by the
+// caller (raw when a.in.raw_params); cov_pre: precomputed cov3D row or nullptr; G0/G1/G2x: the blend
+// gradient record; cm: colour clamp mask; srow: this Gaussian's staged SH "rest" row.
+__device__ __forceinline__ void pb_compute(const gs_settings& st, const PreBwdArgs& a, const float p[3], const float4 q4,
+                                           const float scl[3], const float opac_in, const float* cov_pre,
+                                           const float4 G0, const float4 G1, const float G2x, const uint32_t cm,
+                                           const float* srow, const bool use_sh, PbOut& o) {
+  float* gm = o.gm;
+  float* gs = o.gs;
+  float* gq = o.gq;
+  float* gcov = o.gcov;
+  float* gdc = o.gdc;
+  float* gcol = o.gcol;
+  float* gr = o.gr;
+  float* basis = o.basis;
+  {
+    o.g2x = G0.x;
+    o.g2y = G0.y;
+    const float g2x = G0.x, g2y = G0.y;
     const float gA = G0.z, gB = G0.w, gC = G1.x;
-    gop = G1.y;
+    float gop = G1.y;
     gcol[0] = G1.z;
     gcol[1] = G1.w;
     gcol[2] = G2x;
-    const float p[3] = {a.in.means3D[3 * i], a.in.means3D[3 * i + 1], a.in.means3D[3 * i + 2]};
     const float* V = st.viewmatrix;
     const float* M = st.projmatrix;
     float t[3];
@@ -76,12 +78,11 @@ preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_
     t[2] = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
     // ---- recompute cov3D ----
     float c6[6], qn[4] = {1.f, 0.f, 0.f, 0.f}, qlen = 1.f, R[9], sm[3] = {0.f, 0.f, 0.f}, sact[3] = {0.f, 0.f, 0.f};
-    const bool own_cov = a.in.cov3D_precomp == nullptr;
+    const bool own_cov = cov_pre == nullptr;
     if (!own_cov) {
 #pragma unroll
-      for (int c = 0; c < 6; ++c) c6[c] = a.in.cov3D_precomp[6 * (size_t)i + c];
+      for (int c = 0; c < 6; ++c) c6[c] = cov_pre[c];
     } else {
-      const float4 q4 = *reinterpret_cast<const float4*>(a.in.rotations + 4 * (size_t)i);
       const float q[4] = {q4.x, q4.y, q4.z, q4.w};
       qlen = sqrtf(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
 #pragma unroll
@@ -92,7 +93,7 @@ preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_
       R[6] = 2.f * (x * z - r * y); R[7] = 2.f * (y * z + r * x); R[8] = 1.f - 2.f * (x * x + y * y);
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        float sv = a.in.scales[3 * i + c];
+        float sv = scl[c];
         if (a.in.raw_params) sv = expf(sv);
         sact[c] = sv;
         sm[c] = st.scale_modifier * sv;
@@ -181,7 +182,6 @@ preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_
     // ---- SH backward (row staged in smem is overwritten by its own gradient) ----
     if (use_sh) {
       const int deg = st.sh_degree;
-      const uint32_t cm = a.clamped[i];
 #pragma unroll
       for (int ch = 0; ch < 3; ++ch) gr[ch] = ((cm >> ch) & 1u) ? 0.f : gcol[ch];
       const float dvx = p[0] - st.campos[0], dvy = p[1] - st.campos[1], dvz = p[2] - st.campos[2];
@@ -282,10 +282,69 @@ preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_
       for (int k = 0; k < 4; ++k) gq[k] = (gn[k] - qn[k] * dotq) / qlen;
     }
     if (a.in.raw_params) {
-      const float o = 1.0f / (1.0f + expf(-a.in.opacities[i]));
-      gop *= o * (1.0f - o);
+      const float sg = 1.0f / (1.0f + expf(-opac_in));
+      gop *= sg * (1.0f - sg);
+    }
+    o.gop = gop;
+  }
+}
+
+
+__global__ void __launch_bounds__(PB_THREADS)
+preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a, const int first) {
+  extern __shared__ float s_sh[];
+  const int tid = threadIdx.x;
+  const int row0 = first + blockIdx.x * PB_THREADS;
+  const int i = row0 + tid;
+  const int rows = min(PB_THREADS, a.N - row0);
+  const bool use_sh = a.in.colors_precomp == nullptr;
+
+  if (use_sh && a.rest_width_act > 0) {
+    const int stride = a.in.sh_rest_stride;
+    const float* base = a.in.sh_rest + (size_t)row0 * stride;
+    const int total = (rows - 1) * stride + a.rest_width_act;
+    int row = tid / stride, col = tid % stride;
+    const int drow = PB_THREADS / stride, dcol = PB_THREADS % stride;
+    for (int f = tid; f < total; f += PB_THREADS) {
+      if (col < a.rest_width_act) s_sh[row * a.pitch + col] = __ldg(base + f);
+      row += drow;
+      col += dcol;
+      if (col >= stride) { col -= stride; ++row; }
     }
   }
+  __syncthreads();
+
+  PbOut o;
+  pb_zero(o);
+  float* srow = s_sh + tid * a.pitch;
+  bool visible = false;
+  if (i < a.N) visible = a.radii[i] > 0;
+  if (visible) {
+    const float4 G0 = a.grad_geom[3 * (size_t)i], G1 = a.grad_geom[3 * (size_t)i + 1];
+    const float G2x = a.grad_geom[3 * (size_t)i + 2].x;
+    const float p[3] = {a.in.means3D[3 * i], a.in.means3D[3 * i + 1], a.in.means3D[3 * i + 2]};
+    const float* cov_pre = a.in.cov3D_precomp ? a.in.cov3D_precomp + 6 * (size_t)i : nullptr;
+    float4 q4 = make_float4(1.f, 0.f, 0.f, 0.f);
+    float scl[3] = {0.f, 0.f, 0.f};
+    if (!cov_pre) {
+      q4 = *reinterpret_cast<const float4*>(a.in.rotations + 4 * (size_t)i);
+      scl[0] = a.in.scales[3 * i];
+      scl[1] = a.in.scales[3 * i + 1];
+      scl[2] = a.in.scales[3 * i + 2];
+    }
+    const float opac_in = a.in.raw_params ? a.in.opacities[i] : 0.f;
+    const uint32_t cm = use_sh ? a.clamped[i] : 0u;
+    pb_compute(st, a, p, q4, scl, opac_in, cov_pre, G0, G1, G2x, cm, srow, use_sh, o);
+  }
+  const float* gm = o.gm;
+  const float* gs = o.gs;
+  const float* gq = o.gq;
+  const float* gcov = o.gcov;
+  const float* gdc = o.gdc;
+  const float* gcol = o.gcol;
+  const float* gr = o.gr;
+  const float* basis = o.basis;
+  const float g2x = o.g2x, g2y = o.g2y, gop = o.gop;
 
   // ---- outputs ----
   const bool acc = a.out.accumulate != 0;
@@ -364,6 +423,106 @@ preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_
   }
 }
 
+// ---- TMA-staged path ---------------------------------------------------------------------------
+#define PBB_ROWS 128
+// shared-memory slices of one block (floats); every slice offset and size is a multiple of 16 B
+#define PBB_OFF_SH 0                               // rows x 45 (SH rest in, dSH rest out)
+#define PBB_OFF_XYZ (PBB_OFF_SH + PBB_ROWS * 45)   // rows x 3  (means in, dmeans3D out)
+#define PBB_OFF_SCL (PBB_OFF_XYZ + PBB_ROWS * 3)   // rows x 3
+#define PBB_OFF_ROT (PBB_OFF_SCL + PBB_ROWS * 3)   // rows x 4
+#define PBB_OFF_OP (PBB_OFF_ROT + PBB_ROWS * 4)    // rows x 1
+#define PBB_OFF_GG (PBB_OFF_OP + PBB_ROWS)         // rows x 12 (blend gradient records in)
+#define PBB_OFF_M2D (PBB_OFF_GG + PBB_ROWS * 12)   // rows x 2  (dmeans2D out)
+#define PBB_OFF_DC (PBB_OFF_M2D + PBB_ROWS * 2)    // rows x 3  (dSH dc out)
+#define PBB_FLOATS (PBB_OFF_DC + PBB_ROWS * 3)
+#define PBB_SMEM_BYTES (PBB_FLOATS * 4 + 16)
+
+__global__ void __launch_bounds__(PBB_ROWS)
+preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a) {
+  extern __shared__ __align__(128) float s_buf[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_buf + PBB_FLOATS);
+  const int tid = threadIdx.x;
+  const size_t row0 = (size_t)blockIdx.x * PBB_ROWS;
+  const size_t i = row0 + tid;
+  const int W = a.rest_width_max;  // == sh_rest_stride (dense rows), 0..45
+  const bool load_sh = a.rest_width_act > 0;
+
+  if (tid == 0) {
+    tma::mbar_init(bar, 1);
+    tma::fence_mbar_init();
+    const uint32_t sh_bytes = load_sh ? (uint32_t)(PBB_ROWS * W * 4) : 0u;
+    const uint32_t op_bytes = a.in.raw_params ? PBB_ROWS * 4u : 0u;
+    tma::mbar_arrive_expect_tx(bar, sh_bytes + op_bytes + PBB_ROWS * (12u + 12u + 16u + 48u));
+    tma::load(s_buf + PBB_OFF_GG, a.grad_geom + 3 * row0, PBB_ROWS * 48u, bar);
+    tma::load(s_buf + PBB_OFF_XYZ, a.in.means3D + 3 * row0, PBB_ROWS * 12u, bar);
+    tma::load(s_buf + PBB_OFF_SCL, a.in.scales + 3 * row0, PBB_ROWS * 12u, bar);
+    tma::load(s_buf + PBB_OFF_ROT, a.in.rotations + 4 * row0, PBB_ROWS * 16u, bar);
+    if (op_bytes) tma::load(s_buf + PBB_OFF_OP, a.in.opacities + row0, op_bytes, bar);
+    if (sh_bytes) tma::load(s_buf + PBB_OFF_SH, a.in.sh_rest + row0 * W, sh_bytes, bar);
+  }
+  const bool visible = a.radii[i] > 0;
+  const uint32_t cm = a.clamped[i];
+  __syncthreads();  // barrier initialised before anyone polls it
+  tma::mbar_wait(bar, 0);
+
+  PbOut o;
+  pb_zero(o);
+  float* srow = s_buf + PBB_OFF_SH + tid * W;
+  if (visible) {
+    const float4* gg = reinterpret_cast<const float4*>(s_buf + PBB_OFF_GG) + 3 * tid;
+    const float4 G0 = gg[0], G1 = gg[1];
+    const float G2x = s_buf[PBB_OFF_GG + 12 * tid + 8];
+    const float p[3] = {s_buf[PBB_OFF_XYZ + 3 * tid], s_buf[PBB_OFF_XYZ + 3 * tid + 1], s_buf[PBB_OFF_XYZ + 3 * tid + 2]};
+    const float scl[3] = {s_buf[PBB_OFF_SCL + 3 * tid], s_buf[PBB_OFF_SCL + 3 * tid + 1], s_buf[PBB_OFF_SCL + 3 * tid + 2]};
+    const float4 q4 = reinterpret_cast<const float4*>(s_buf + PBB_OFF_ROT)[tid];
+    const float opac_in = a.in.raw_params ? s_buf[PBB_OFF_OP + tid] : 0.f;
+    pb_compute(st, a, p, q4, scl, opac_in, nullptr, G0, G1, G2x, cm, srow, true, o);
+  }
+  // gradients overwrite the input slices in place (each thread touches only its own rows)
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    s_buf[PBB_OFF_XYZ + 3 * tid + c] = o.gm[c];
+    s_buf[PBB_OFF_SCL + 3 * tid + c] = o.gs[c];
+    s_buf[PBB_OFF_DC + 3 * tid + c] = o.gdc[c];
+  }
+  reinterpret_cast<float4*>(s_buf + PBB_OFF_ROT)[tid] = make_float4(o.gq[0], o.gq[1], o.gq[2], o.gq[3]);
+  s_buf[PBB_OFF_OP + tid] = o.gop;
+  reinterpret_cast<float2*>(s_buf + PBB_OFF_M2D)[tid] = make_float2(o.g2x, o.g2y);
+  {
+    const int kmax = W / 3;
+#pragma unroll
+    for (int k = 0; k < 15; ++k)
+      if (k < kmax) {
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) srow[3 * k + ch] = o.basis[k] * o.gr[ch];
+      }
+  }
+  tma::fence_proxy_async_smem();
+  __syncthreads();
+  if (tid == 0) {
+    const bool acc = a.out.accumulate != 0;
+#define PBB_OUT(gptr, soff, bytes)                                          \
+  do {                                                                      \
+    if (gptr) {                                                             \
+      if (acc) tma::reduce_add_f32((gptr), s_buf + (soff), (bytes));        \
+      else tma::store((gptr), s_buf + (soff), (bytes));                     \
+    }                                                                       \
+  } while (0)
+    PBB_OUT(a.out.dL_dmeans3D ? a.out.dL_dmeans3D + 3 * row0 : nullptr, PBB_OFF_XYZ, PBB_ROWS * 12u);
+    PBB_OUT(a.out.dL_dscales ? a.out.dL_dscales + 3 * row0 : nullptr, PBB_OFF_SCL, PBB_ROWS * 12u);
+    PBB_OUT(a.out.dL_drotations ? a.out.dL_drotations + 4 * row0 : nullptr, PBB_OFF_ROT, PBB_ROWS * 16u);
+    PBB_OUT(a.out.dL_dopacities ? a.out.dL_dopacities + row0 : nullptr, PBB_OFF_OP, PBB_ROWS * 4u);
+    PBB_OUT(a.out.dL_dmeans2D ? a.out.dL_dmeans2D + 2 * row0 : nullptr, PBB_OFF_M2D, PBB_ROWS * 8u);
+    PBB_OUT(a.out.dL_dsh_dc ? a.out.dL_dsh_dc + 3 * row0 : nullptr, PBB_OFF_DC, PBB_ROWS * 12u);
+    if (W > 0) PBB_OUT(a.out.dL_dsh_rest ? a.out.dL_dsh_rest + row0 * W : nullptr, PBB_OFF_SH, (uint32_t)(PBB_ROWS * W * 4));
+#undef PBB_OUT
+    tma::commit_group();
+    tma::wait_group_read0();  // shared memory must stay alive until the copies have read it
+  }
+}
+
+static bool aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
+
 cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussians& in, const gs_gradients& out, int N,
                                           const int* radii, const uint8_t* clamped, const float4* grad_geom,
                                           cudaStream_t stream) {
@@ -382,8 +541,34 @@ cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussi
   a.rest_width_act = in.colors_precomp ? 0 : 3 * (kact - 1);
   a.rest_width_max = in.colors_precomp ? 0 : 3 * (kmax - 1);
   a.pitch = a.rest_width_max | 1;
-  const size_t smem = a.rest_width_max > 0 ? (size_t)PB_THREADS * a.pitch * sizeof(float) : 0;
-  const int blocks = (N + PB_THREADS - 1) / PB_THREADS;
-  preprocess_backward_kernel<<<blocks, PB_THREADS, smem, stream>>>(st, a);
+
+  // TMA-staged path: dense, 16-byte aligned reference tensors (the GaussianModel layout) and the SH path
+  const int W = a.rest_width_max;
+  const bool dense = !in.colors_precomp && !in.cov3D_precomp && !out.dL_dcov3D && !out.dL_dcolors &&
+                     (W == 0 || (in.sh_rest_stride == W && (!out.dL_dsh_rest || out.sh_rest_stride == W))) &&
+                     (!out.dL_dsh_dc || out.sh_dc_stride == 3) && (W * 4 * PBB_ROWS) % 16 == 0 &&
+                     aligned16(in.means3D) && aligned16(in.scales) && aligned16(in.rotations) &&
+                     aligned16(in.opacities) && (W == 0 || aligned16(in.sh_rest)) && aligned16(out.dL_dmeans3D) &&
+                     aligned16(out.dL_dscales) && aligned16(out.dL_drotations) && aligned16(out.dL_dopacities) &&
+                     aligned16(out.dL_dmeans2D) && aligned16(out.dL_dsh_dc) && aligned16(out.dL_dsh_rest) &&
+                     aligned16(grad_geom);
+  int first = 0;
+  if (dense && N >= PBB_ROWS) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t e = cudaFuncSetAttribute(preprocess_backward_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           PBB_SMEM_BYTES);
+      if (e != cudaSuccess) return e;
+      attr_set = true;
+    }
+    const int blocks = N / PBB_ROWS;
+    preprocess_backward_bulk_kernel<<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a);
+    first = blocks * PBB_ROWS;
+  }
+  if (first < N) {
+    const size_t smem = a.rest_width_max > 0 ? (size_t)PB_THREADS * a.pitch * sizeof(float) : 0;
+    const int blocks = (N - first + PB_THREADS - 1) / PB_THREADS;
+    preprocess_backward_kernel<<<blocks, PB_THREADS, smem, stream>>>(st, a, first);
+  }
   return cudaGetLastError();
 }

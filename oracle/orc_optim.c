@@ -5,10 +5,16 @@
  *   Adam: the reference builds six torch::optim::Adam with only `lr` set
  *         (src/scene/gaussian_model.cpp:323-345) => libtorch defaults beta=(0.9,0.999),
  *         eps=1e-8, no weight decay, no amsgrad.  The update order restated here is
- *         libtorch's Adam::step: m = m*b1 + g*(1-b1); v = v*b2 + g*g*(1-b2);
- *         denom = sqrt(v)/sqrt(1-b2^t) + eps; p -= (lr/(1-b1^t)) * m / denom, with the bias
- *         corrections evaluated in double and applied as fp32 scalars.
- *         Pinned against torch.optim.Adam on CPU in tests/test_oracle_optim.py.
+ *         libtorch's Adam::step: m.mul_(b1).add_(g, 1-b1); v.mul_(b2).addcmul_(g, g, 1-b2);
+ *         denom = (sqrt(v) / sqrt(1-b2^t)).add_(eps); p.addcdiv_(m, denom, -lr/(1-b1^t)), with
+ *         the bias corrections evaluated in double and applied as fp32 scalars.
+ *         SPECIFIED NUMERICS (shared by definition with csrc/optim.cu): the reference keeps its
+ *         tensors on torch::kCUDA (src/scene/gaussian_model.cpp:319-320), where libtorch's
+ *         elementwise kernels (a) contract `a + alpha*b` into one FMA, (b) evaluate addcmul as
+ *         fma(alpha*b, c, a), (c) divide by a host scalar by multiplying with its fp32 reciprocal
+ *         and (d) evaluate addcdiv as fma(alpha, b/c, a) with an IEEE division.  Each line below is
+ *         one such kernel; sqrt and the division are correctly rounded.
+ *         Pinned against torch.optim.Adam on CPU in tests/test_oracle_optim.py (<= 2 ulp of p).
  *   Stats: fields max_radii2D_, xyz_gradient_accum_, denom_ (src/scene/gaussian_model.h:18-20).
  */
 #include "orc_common.h"
@@ -19,18 +25,18 @@ void orc_adam_step(size_t n, float *p, const float *g, float *m, float *v, doubl
   const double bc2 = 1.0 - pow(beta2, (double)step);
   const float b1 = (float)beta1, b2 = (float)beta2;
   const float omb1 = (float)(1.0 - beta1), omb2 = (float)(1.0 - beta2);
-  const float bc2_sqrt = (float)sqrt(bc2);
-  const float step_size = (float)(lr / bc1);
+  const float inv_bc2_sqrt = 1.0f / (float)sqrt(bc2);
+  const float neg_step = (float)(-(lr / bc1));
   const float epsf = (float)eps;
 #pragma omp parallel for schedule(static)
   for (size_t i = 0; i < n; ++i) {
     const float gi = g[i];
-    const float mi = m[i] * b1 + gi * omb1;
-    const float vi = v[i] * b2 + (gi * gi) * omb2;
-    const float denom = sqrtf(vi) / bc2_sqrt + epsf;
+    const float mi = fmaf(omb1, gi, m[i] * b1);
+    const float vi = fmaf(omb2 * gi, gi, v[i] * b2);
+    const float denom = sqrtf(vi) * inv_bc2_sqrt + epsf;
     m[i] = mi;
     v[i] = vi;
-    p[i] = p[i] - step_size * (mi / denom);
+    p[i] = fmaf(neg_step, mi / denom, p[i]);
   }
 }
 
