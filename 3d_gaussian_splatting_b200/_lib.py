@@ -13,12 +13,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libgsplat_b200.so")
 
 GS_OK, GS_EINVAL, GS_ENOMEM, GS_ECUDA, GS_EOVERFLOW, GS_ESTATE = 0, -1, -2, -3, -4, -5
-GS_NUM_STAGES = 7
-STAGE_NAMES = ("preprocess", "scan_duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")
+GS_NUM_STAGES = 8
+STAGE_NAMES = ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")
 
-DBG = dict(MEANS2D=0, DEPTHS=1, CONIC_OPACITY=2, RGB=3, CLAMPED=4, TILES_TOUCHED=5, POINT_OFFSETS=6,
+DBG = dict(MEANS2D=0, DEPTHS=1, CONIC_OPACITY=2, RGB=3, CLAMPED=4, TILES_TOUCHED=5, DEPTH_ORDER=6,
            KEYS_SORTED=7, POINT_LIST=8, RANGES=9, FINAL_T=10, N_CONTRIB=11, DL_DMEAN2D=12, DL_DCONIC=13,
-           DL_DOPACITY=14, DL_DCOLOR=15, NUM_RENDERED=16, KEYS_UNSORTED=17, VALUES_UNSORTED=18)
+           DL_DOPACITY=14, DL_DCOLOR=15, NUM_RENDERED=16)
 
 
 class GsSettings(C.Structure):

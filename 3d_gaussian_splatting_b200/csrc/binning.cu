@@ -1,80 +1,260 @@
-// binning.cu — K2: inclusive scan of tiles_touched,
-// duplicateWithKeys (key = tile_id << 32 | fp32 bits of the view depth, value = Gaussian id),
-// stable radix sort restricted to the significant bits, identifyTileRanges.
-// All outputs are integers and bit-exact against the oracle.
-#include <cub/cub.cuh>
-
+// binning.cu — K2: from per-Gaussian tile rectangles to per-tile,
+// depth-ordered point lists.  The sorted list is, bit for bit, the one a stable sort of the 64-bit
+// keys (tile_id << 32 | fp32 bits of the view depth) over the duplicates emitted in Gaussian order
+// produces (the oracle's definition) -- but the 64-bit keys are never materialised:
+//
+//   1. depth sort    argsort of the N Gaussians by depth bits (stable LSD radix, 4 passes over N pairs)
+//   2. duplicate     the Gaussians emit their (tile id, Gaussian id) pairs IN DEPTH ORDER
+//                    (offsets = exclusive scan of the rectangle areas along that order; K1 leaves an 8-B
+//                    rectangle record per Gaussian so this stage gathers 8 B per Gaussian, nothing else)
+//   3. tile sort     stable LSD radix sort of the D pairs by tile id only: ceil(log2(T) / 8) passes of
+//                    6 B pairs (u16 tile ids) instead of 6 passes of 12 B pairs
+//   4. ranges        per-tile binary search in the sorted tile ids
+//
+// Because both sorts are stable, the order inside a tile is (depth, Gaussian id) ascending = the
+// oracle's.  Every element count that depends on the data (D) is read from device memory by the
+// kernels, which run on fixed persistent grids: the stage needs no host round-trip by itself.
+// HBM traffic per duplicate: 6 (emit) + passes * (2 + 6 + 6) B  vs  12 + 8 + 6 * 24 + 8 B for the
+// one-level 64-bit sort.
 #include "gs_common.cuh"
+#include "radix_sort.cuh"
 
-// ---- K2a: duplicateWithKeys ------------------------------------------------------------------
-// One thread per Gaussian for small rectangles; rectangles wider than a warp's worth of tiles are
-// emitted cooperatively by the whole warp so one huge splat does not serialise a thread.
-__global__ void __launch_bounds__(256)
-duplicate_with_keys_kernel(int N, const GsGeom* __restrict__ geom, const float* __restrict__ depths,
-                           const int* __restrict__ radii, const uint32_t* __restrict__ offsets,
-                           uint64_t* __restrict__ keys, uint32_t* __restrict__ values, int gx, int gy) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const int lane = threadIdx.x & 31;
-  int rad = 0;
-  uint32_t off = 0, dbits = 0;
-  int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
-  if (i < N) {
-    rad = radii[i];
-    if (rad > 0) {
-      off = (i == 0) ? 0u : offsets[i - 1];
-      const float4 q0 = geom[i].q0;
-      const float px = q0.x, py = q0.y;
-      x0 = min(gx, max(0, (int)__fdiv_rn(__fsub_rn(px, (float)rad), (float)GS_TILE)));
-      y0 = min(gy, max(0, (int)__fdiv_rn(__fsub_rn(py, (float)rad), (float)GS_TILE)));
-      x1 = min(gx, max(0, (int)__fdiv_rn(__fadd_rn(__fadd_rn(px, (float)rad), (float)(GS_TILE - 1)), (float)GS_TILE)));
-      y1 = min(gy, max(0, (int)__fdiv_rn(__fadd_rn(__fadd_rn(py, (float)rad), (float)(GS_TILE - 1)), (float)GS_TILE)));
-      dbits = __float_as_uint(depths[i]);
-    }
+// ---- 1. depth sort ----------------------------------------------------------------------------
+cudaError_t gs_launch_depth_sort(int N, const uint32_t* depth_bits, uint32_t* k0, uint32_t* k1, uint32_t* v0,
+                                 uint32_t* v1, uint32_t* counts, int grid, cudaStream_t stream) {
+  if (N == 0) return cudaSuccess;
+  // result (Gaussian ids in depth order) lands in v1
+  radix_pass<uint32_t>(depth_bits, k0, nullptr, v0, (uint32_t)N, nullptr, 0, counts, grid, stream);
+  radix_pass<uint32_t>(k0, k1, v0, v1, (uint32_t)N, nullptr, 8, counts, grid, stream);
+  radix_pass<uint32_t>(k1, k0, v1, v0, (uint32_t)N, nullptr, 16, counts, grid, stream);
+  return radix_pass<uint32_t>(k0, nullptr, v0, v1, (uint32_t)N, nullptr, 24, counts, grid, stream);
+}
+
+// ---- 2. scan of tiles_touched along the depth order + duplicate ---------------------------------
+#define DUP_THREADS 256
+#define DUP_ITEMS 4
+#define DUP_BLOCK (DUP_THREADS * DUP_ITEMS)
+
+__device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_t* s_warp, uint32_t& block_total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
   }
-  const int area = (x1 - x0) * (y1 - y0);
-  const bool big = area > 64;
-  if (rad > 0 && !big) {
-    for (int y = y0; y < y1; ++y)
-      for (int x = x0; x < x1; ++x) {
-        keys[off] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | dbits;
-        values[off] = (uint32_t)i;
-        ++off;
-      }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  uint32_t off = 0, tot = 0;
+#pragma unroll
+  for (int w = 0; w < DUP_THREADS / 32; ++w) {
+    const uint32_t t = s_warp[w];
+    off += (w < warp) ? t : 0u;
+    tot += t;
   }
-  // warp-cooperative emission of the big rectangles
-  unsigned big_mask = __ballot_sync(0xffffffffu, big);
-  while (big_mask) {
-    const int src = __ffs(big_mask) - 1;
-    big_mask &= big_mask - 1;
-    const int bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
-    const int bx1 = __shfl_sync(0xffffffffu, x1, src), by1 = __shfl_sync(0xffffffffu, y1, src);
-    const uint32_t boff = __shfl_sync(0xffffffffu, off, src), bd = __shfl_sync(0xffffffffu, dbits, src);
-    const int bi = __shfl_sync(0xffffffffu, i, src);
-    const int w = bx1 - bx0, total = w * (by1 - by0);
-    for (int k = lane; k < total; k += 32) {
-      const int y = by0 + k / w, x = bx0 + k % w;
-      keys[boff + k] = ((uint64_t)(uint32_t)(y * gx + x) << 32) | bd;
-      values[boff + k] = (uint32_t)bi;
-    }
+  block_total = tot;
+  return off + incl - v;
+}
+
+__device__ __forceinline__ uint32_t rect_area(uint2 r) {
+  return ((r.y & 0xFFFFu) - (r.x & 0xFFFFu)) * ((r.y >> 16) - (r.x >> 16));
+}
+
+__global__ void __launch_bounds__(DUP_THREADS)
+dup_block_sums_kernel(int N, const uint32_t* __restrict__ order, const uint2* __restrict__ rects,
+                      uint32_t* __restrict__ block_sums) {
+  __shared__ uint32_t s_warp[DUP_THREADS / 32];
+  uint32_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < DUP_ITEMS; ++k) {
+    const int r = blockIdx.x * DUP_BLOCK + k * DUP_THREADS + threadIdx.x;
+    if (r < N) sum += rect_area(rects[order[r]]);
+  }
+  uint32_t tot;
+  block_exclusive_scan_256(sum, s_warp, tot);
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
+}
+
+// one block: exclusive scan of the block sums in place; the grand total D goes to *total (64-bit, so
+// a wrapped 32-bit scan is detectable) and to *total32 for the kernels that index with it
+__global__ void __launch_bounds__(1024)
+dup_scan_sums_kernel(int nb, uint32_t* __restrict__ block_sums, unsigned long long* __restrict__ total,
+                     uint32_t* __restrict__ total32) {
+  __shared__ unsigned long long s_warp[32];
+  const int per = (nb + 1023) / 1024;
+  const int lo = min(nb, (int)threadIdx.x * per), hi = min(nb, lo + per);
+  unsigned long long sum = 0;
+  for (int i = lo; i < hi; ++i) sum += block_sums[i];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned long long incl = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  unsigned long long off = 0, tot = 0;
+  for (int w = 0; w < 32; ++w) {
+    const unsigned long long t = s_warp[w];
+    off += (w < warp) ? t : 0ull;
+    tot += t;
+  }
+  unsigned long long run = off + incl - sum;
+  for (int i = lo; i < hi; ++i) {
+    const uint32_t t = block_sums[i];
+    block_sums[i] = (uint32_t)run;
+    run += t;
+  }
+  if (threadIdx.x == 0) {
+    *total = tot;
+    *total32 = tot > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)tot;
   }
 }
 
-// ---- K2c: identifyTileRanges -------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-identify_tile_ranges_kernel(uint32_t D, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= D) return;
-  const uint32_t cur = (uint32_t)(keys[i] >> 32);
-  if (i == 0) {
-    ranges[cur].x = 0;
-  } else {
-    const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
-    if (cur != prev) {
-      ranges[prev].y = i;
-      ranges[cur].x = i;
+// A block expands 1024 consecutive ranks of the depth order.  Thread t first scans the tile counts of
+// ranks 4t .. 4t+3; then the block's output slots [0, total) are dealt round-robin to the threads: slot j
+// finds its owner by binary search in the shared prefix array and derives its tile from the owner's
+// rectangle, so both output arrays are written fully coalesced whatever the rectangle sizes are (no
+// per-thread loops over big splats).  cap: capacity of the pair buffers (pairs past it are dropped and
+// *overflow is raised -- only possible when the caller fixed the capacity in advance).
+template <typename KeyT>
+__global__ void __launch_bounds__(DUP_THREADS)
+duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint2* __restrict__ rects,
+                           const uint32_t* __restrict__ block_base, KeyT* __restrict__ tile_ids,
+                           uint32_t* __restrict__ values, int gx, uint32_t cap, uint32_t* __restrict__ overflow) {
+  __shared__ uint32_t s_warp[DUP_THREADS / 32];
+  __shared__ uint32_t s_off[DUP_BLOCK];
+  __shared__ uint32_t s_id[DUP_BLOCK];
+  __shared__ uint2 s_rect[DUP_BLOCK];
+  const int r0 = blockIdx.x * DUP_BLOCK + threadIdx.x * DUP_ITEMS;
+  uint32_t cnt[DUP_ITEMS];
+  uint32_t sum = 0;
+#pragma unroll
+  for (int k = 0; k < DUP_ITEMS; ++k) {
+    uint32_t id = 0;
+    uint2 rc = make_uint2(0u, 0u);
+    if (r0 + k < N) {
+      id = order[r0 + k];
+      rc = rects[id];
     }
+    s_id[threadIdx.x * DUP_ITEMS + k] = id;
+    s_rect[threadIdx.x * DUP_ITEMS + k] = rc;
+    cnt[k] = rect_area(rc);
+    sum += cnt[k];
   }
-  if (i == D - 1) ranges[cur].y = D;
+  uint32_t total;
+  uint32_t off = block_exclusive_scan_256(sum, s_warp, total);
+#pragma unroll
+  for (int k = 0; k < DUP_ITEMS; ++k) {
+    s_off[threadIdx.x * DUP_ITEMS + k] = off;
+    off += cnt[k];
+  }
+  __syncthreads();
+  const uint32_t base = block_base[blockIdx.x];
+  uint32_t limit = total;
+  if ((unsigned long long)base + total > cap) {
+    limit = base < cap ? cap - base : 0u;
+    if (threadIdx.x == 0) *overflow = 1u;
+  }
+  for (uint32_t j = threadIdx.x; j < limit; j += DUP_THREADS) {
+    // owner = last entry with s_off <= j (entries with zero tiles share an offset with their successor and are
+    // skipped because the search returns the LAST such entry)
+    int lo = 0, hi = DUP_BLOCK - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (s_off[mid] <= j) lo = mid;
+      else hi = mid - 1;
+    }
+    const uint2 rc = s_rect[lo];
+    const uint32_t k = j - s_off[lo];
+    const uint32_t x0 = rc.x & 0xFFFFu, y0 = rc.x >> 16, w = (rc.y & 0xFFFFu) - x0;
+    const uint32_t row = k / w, col = k - row * w;
+    tile_ids[base + j] = (KeyT)((y0 + row) * (uint32_t)gx + x0 + col);
+    values[base + j] = s_id[lo];
+  }
+}
+
+int gs_dup_num_blocks(int N) { return (N + DUP_BLOCK - 1) / DUP_BLOCK; }
+
+cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint2* rects, uint32_t* block_sums,
+                               unsigned long long* total, uint32_t* total32, cudaStream_t stream) {
+  if (N == 0) return cudaMemsetAsync(total, 0, 8, stream);
+  const int nb = gs_dup_num_blocks(N);
+  dup_block_sums_kernel<<<nb, DUP_THREADS, 0, stream>>>(N, order, rects, block_sums);
+  dup_scan_sums_kernel<<<1, 1024, 0, stream>>>(nb, block_sums, total, total32);
+  return cudaGetLastError();
+}
+
+cudaError_t gs_launch_duplicate(int N, const uint32_t* order, const uint2* rects, const uint32_t* block_base,
+                                void* tile_ids, int key_bytes, uint32_t* values, int gx, uint32_t cap,
+                                uint32_t* overflow, cudaStream_t stream) {
+  if (N == 0) return cudaSuccess;
+  const int nb = gs_dup_num_blocks(N);
+  if (key_bytes == 2)
+    duplicate_with_keys_kernel<uint16_t><<<nb, DUP_THREADS, 0, stream>>>(N, order, rects, block_base, (uint16_t*)tile_ids,
+                                                                        values, gx, cap, overflow);
+  else
+    duplicate_with_keys_kernel<uint32_t><<<nb, DUP_THREADS, 0, stream>>>(N, order, rects, block_base, (uint32_t*)tile_ids,
+                                                                        values, gx, cap, overflow);
+  return cudaGetLastError();
+}
+
+// ---- 3. tile sort -------------------------------------------------------------------------------
+// Sorts the D pairs by tile id.  Buffers a = input; the result is in `a` after an even number of
+// passes and in `b` after an odd number (returned through *result_in_b).
+cudaError_t gs_launch_tile_sort(const uint32_t* D_dev, int tile_bits, int key_bytes, void* keys_a, void* keys_b,
+                                uint32_t* vals_a, uint32_t* vals_b, uint32_t* counts, int grid, int* result_in_b,
+                                cudaStream_t stream) {
+  const int passes = (tile_bits + 7) / 8;
+  bool in_a = true;
+  for (int p = 0; p < passes; ++p) {
+    if (key_bytes == 2) {
+      uint16_t* ki = (uint16_t*)(in_a ? keys_a : keys_b);
+      uint16_t* ko = (uint16_t*)(in_a ? keys_b : keys_a);
+      radix_pass<uint16_t>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
+    } else {
+      uint32_t* ki = (uint32_t*)(in_a ? keys_a : keys_b);
+      uint32_t* ko = (uint32_t*)(in_a ? keys_b : keys_a);
+      radix_pass<uint32_t>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
+    }
+    in_a = !in_a;
+  }
+  *result_in_b = in_a ? 0 : 1;
+  return cudaGetLastError();
+}
+
+// ---- 4. tile ranges -----------------------------------------------------------------------------
+template <typename KeyT>
+__device__ __forceinline__ uint32_t lower_bound_tile(const KeyT* __restrict__ keys, uint32_t n, uint32_t t) {
+  uint32_t lo = 0, hi = n;
+  while (lo < hi) {
+    const uint32_t mid = lo + ((hi - lo) >> 1);
+    if ((uint32_t)keys[mid] < t) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+identify_tile_ranges_kernel(const uint32_t* __restrict__ D_dev, const KeyT* __restrict__ keys, int ntiles,
+                            uint2* __restrict__ ranges) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ntiles) return;
+  const uint32_t n = *D_dev;
+  const uint32_t a = lower_bound_tile(keys, n, (uint32_t)t);
+  const uint32_t b = lower_bound_tile(keys, n, (uint32_t)t + 1u);
+  ranges[t] = a == b ? make_uint2(0u, 0u) : make_uint2(a, b);  // empty tiles read (0,0), as in the oracle
+}
+
+cudaError_t gs_launch_ranges(const uint32_t* D_dev, const void* keys, int key_bytes, uint2* ranges, int ntiles,
+                             cudaStream_t stream) {
+  if (ntiles == 0) return cudaSuccess;
+  if (key_bytes == 2)
+    identify_tile_ranges_kernel<uint16_t><<<(ntiles + 255) / 256, 256, 0, stream>>>(D_dev, (const uint16_t*)keys, ntiles, ranges);
+  else
+    identify_tile_ranges_kernel<uint32_t><<<(ntiles + 255) / 256, 256, 0, stream>>>(D_dev, (const uint32_t*)keys, ntiles, ranges);
+  return cudaGetLastError();
 }
 
 // ---- tile scheduling order: longest lists first --------------------------------------------------
@@ -117,46 +297,5 @@ order_tiles_kernel(int ntiles, const uint2* __restrict__ ranges, uint32_t* __res
 cudaError_t gs_launch_order_tiles(int ntiles, const uint2* ranges, uint32_t* tile_order, cudaStream_t stream) {
   if (ntiles == 0) return cudaSuccess;
   order_tiles_kernel<<<1, 1024, 0, stream>>>(ntiles, ranges, tile_order);
-  return cudaGetLastError();
-}
-
-// ---- host-side launchers ---------------------------------------------------------------------
-size_t gs_scan_temp_bytes(int N) {
-  size_t bytes = 0;
-  cub::DeviceScan::InclusiveSum(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, N);
-  return bytes;
-}
-cudaError_t gs_launch_scan(void* temp, size_t temp_bytes, const uint32_t* tiles_touched, uint32_t* offsets, int N,
-                           cudaStream_t stream) {
-  return cub::DeviceScan::InclusiveSum(temp, temp_bytes, tiles_touched, offsets, N, stream);
-}
-
-cudaError_t gs_launch_duplicate(int N, const GsGeom* geom, const float* depths, const int* radii,
-                                const uint32_t* offsets, uint64_t* keys, uint32_t* values, int gx, int gy,
-                                cudaStream_t stream) {
-  if (N == 0) return cudaSuccess;
-  duplicate_with_keys_kernel<<<(N + 255) / 256, 256, 0, stream>>>(N, geom, depths, radii, offsets, keys, values,
-                                                                  gx, gy);
-  return cudaGetLastError();
-}
-
-size_t gs_sort_temp_bytes(uint32_t D, int end_bit) {
-  size_t bytes = 0;
-  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
-                                  (const uint32_t*)nullptr, (uint32_t*)nullptr, (int)D, 0, end_bit);
-  return bytes;
-}
-cudaError_t gs_launch_sort(void* temp, size_t temp_bytes, const uint64_t* keys_in, uint64_t* keys_out,
-                           const uint32_t* vals_in, uint32_t* vals_out, uint32_t D, int end_bit,
-                           cudaStream_t stream) {
-  if (D == 0) return cudaSuccess;
-  return cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, vals_in, vals_out, (int)D, 0, end_bit,
-                                         stream);
-}
-
-cudaError_t gs_launch_ranges(uint32_t D, const uint64_t* keys, uint2* ranges, int ntiles, cudaStream_t stream) {
-  cudaError_t e = cudaMemsetAsync(ranges, 0, (size_t)ntiles * sizeof(uint2), stream);
-  if (e != cudaSuccess || D == 0) return e;
-  identify_tile_ranges_kernel<<<(D + 255) / 256, 256, 0, stream>>>(D, keys, ranges);
   return cudaGetLastError();
 }

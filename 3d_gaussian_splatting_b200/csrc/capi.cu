@@ -13,15 +13,17 @@
 
 // ---- launchers implemented in the other translation units ----
 cudaError_t gs_launch_preprocess(const gs_settings&, const gs_gaussians&, int, GsGeom*, float*, int*, uint32_t*,
-                                 uint8_t*, cudaStream_t);
-size_t gs_scan_temp_bytes(int N);
-cudaError_t gs_launch_scan(void*, size_t, const uint32_t*, uint32_t*, int, cudaStream_t);
-cudaError_t gs_launch_duplicate(int, const GsGeom*, const float*, const int*, const uint32_t*, uint64_t*, uint32_t*,
-                                int, int, cudaStream_t);
-size_t gs_sort_temp_bytes(uint32_t D, int end_bit);
-cudaError_t gs_launch_sort(void*, size_t, const uint64_t*, uint64_t*, const uint32_t*, uint32_t*, uint32_t, int,
-                           cudaStream_t);
-cudaError_t gs_launch_ranges(uint32_t, const uint64_t*, uint2*, int, cudaStream_t);
+                                 uint2*, uint8_t*, cudaStream_t);
+cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, int,
+                                 cudaStream_t);
+int gs_dup_num_blocks(int N);
+cudaError_t gs_launch_dup_scan(int, const uint32_t*, const uint2*, uint32_t*, unsigned long long*, uint32_t*,
+                               cudaStream_t);
+cudaError_t gs_launch_duplicate(int, const uint32_t*, const uint2*, const uint32_t*, void*, int, uint32_t*, int,
+                                uint32_t, uint32_t*, cudaStream_t);
+cudaError_t gs_launch_tile_sort(const uint32_t*, int, int, void*, void*, uint32_t*, uint32_t*, uint32_t*, int, int*,
+                                cudaStream_t);
+cudaError_t gs_launch_ranges(const uint32_t*, const void*, int, uint2*, int, cudaStream_t);
 cudaError_t gs_launch_order_tiles(int, const uint2*, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_blend_forward(const GsDims&, const uint32_t*, const uint2*, const uint32_t*, const GsGeom*,
                                     const float[3], float*, float4*, uint32_t*, float4*, uint2*, uint32_t*, uint32_t*,
@@ -46,20 +48,26 @@ struct gs_ctx {
   int device = 0;
   std::string err;
   // per-Gaussian
-  DevBuf geom, depths, radii, tiles, offsets, clamped, grad_geom;
-  // per-duplicate
+  DevBuf geom, depths, radii, tiles, rects, clamped, grad_geom;
+  DevBuf sort_k0, sort_k1, sort_v0, sort_v1, dup_sums;  // depth argsort ping-pong (order = sort_v1), scan partials
+  // per-duplicate: tile ids (u16, u32 beyond 65536 tiles) and Gaussian ids, ping-pong
   DevBuf keys_a, keys_b, vals_a, vals_b;
+  DevBuf radix_counts;
+  int radix_grid = 296;
+  int key_bytes = 2;
+  const void* sorted_tiles = nullptr;    // tile ids of the sorted list
+  const uint32_t* point_list = nullptr;  // Gaussian ids of the sorted list
   // per-tile / per-pixel
   DevBuf ranges, final_state, n_contrib, tile_order, tile_last;
   // segmented backward: per-segment pixel checkpoints, (tile, segment) work list, {work_count, work_cursor}
   DevBuf ckpt, work_items, counters;
   int num_sms = 148;
-  DevBuf scan_tmp, sort_tmp, loss_acc;
+  DevBuf loss_acc;
   uint32_t* d_host_pinned = nullptr;  // D readback
   // state of the last forward
   int N = -1, H = 0, W = 0, ntiles = 0;
   uint64_t D = 0;
-  bool have_forward = false, have_backward = false, kept_unsorted = false;
+  bool have_forward = false, have_backward = false;
   // profiling
   bool profiling = false;
   cudaEvent_t ev[2 * GS_NUM_STAGES] = {};
@@ -159,6 +167,7 @@ int gs_create(gs_ctx** out, int device) {
   if (!c) return GS_ENOMEM;
   c->device = device;
   c->num_sms = prop.multiProcessorCount;
+  c->radix_grid = 4 * c->num_sms < 608 ? 4 * c->num_sms : 608;  // RS_MAX_GRID
   if (cudaSetDevice(device) != cudaSuccess || cudaMallocHost((void**)&c->d_host_pinned, 64) != cudaSuccess) {
     gs_set_error(nullptr, "cudaSetDevice/cudaMallocHost failed: %s", cudaGetErrorString(cudaGetLastError()));
     delete c;
@@ -172,10 +181,10 @@ int gs_create(gs_ctx** out, int device) {
 void gs_destroy(gs_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  DevBuf* bufs[] = {&c->geom,   &c->depths, &c->radii,  &c->tiles,   &c->offsets,   &c->clamped,  &c->grad_geom,
+  DevBuf* bufs[] = {&c->geom,   &c->depths, &c->radii,  &c->tiles,   &c->rects, &c->clamped,   &c->grad_geom, &c->sort_k0,
+                    &c->sort_k1, &c->sort_v0, &c->sort_v1, &c->dup_sums, &c->radix_counts,
                     &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_state,  &c->n_contrib,
-                    &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters,
-                    &c->scan_tmp, &c->sort_tmp, &c->loss_acc};
+                    &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters, &c->loss_acc};
   for (DevBuf* b : bufs)
     if (b->ptr) cudaFree(b->ptr);
   if (c->d_host_pinned) cudaFreeHost(c->d_host_pinned);
@@ -266,69 +275,85 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->depths, Nn * 4);
   GS_ENSURE(c, c->radii, Nn * 4);
   GS_ENSURE(c, c->tiles, Nn * 4);
-  GS_ENSURE(c, c->offsets, Nn * 4);
+  GS_ENSURE(c, c->rects, Nn * 8);
   GS_ENSURE(c, c->clamped, Nn);
+  GS_ENSURE(c, c->sort_k0, Nn * 4);
+  GS_ENSURE(c, c->sort_k1, Nn * 4);
+  GS_ENSURE(c, c->sort_v0, Nn * 4);
+  GS_ENSURE(c, c->sort_v1, Nn * 4);
+  GS_ENSURE(c, c->dup_sums, (size_t)(gs_dup_num_blocks(N > 0 ? N : 1) + 1) * 4);
+  GS_ENSURE(c, c->radix_counts, (size_t)256 * (c->radix_grid + 1) * 4);
   GS_ENSURE(c, c->ranges, (size_t)d.ntiles * sizeof(uint2));
   GS_ENSURE(c, c->final_state, P * 16);
   GS_ENSURE(c, c->tile_order, (size_t)d.ntiles * 4);
   GS_ENSURE(c, c->tile_last, (size_t)d.ntiles * 4);
   GS_ENSURE(c, c->counters, 64);
   GS_ENSURE(c, c->n_contrib, P * 4);
-  const size_t scan_bytes = gs_scan_temp_bytes(N > 0 ? N : 1);
-  GS_ENSURE(c, c->scan_tmp, scan_bytes);
+  // device counters: [0] backward work items, [1] backward cursor, bytes 8..15 D (u64), [4] D (u32), [5] overflow
+  uint32_t* cnt = (uint32_t*)c->counters.ptr;
+  unsigned long long* D64_dev = (unsigned long long*)(cnt + 2);
+  uint32_t* D_dev = cnt + 4;
+  uint32_t* overflow_dev = cnt + 5;
+  c->key_bytes = d.ntiles <= 65536 ? 2 : 4;
+  int tile_bits = 1;
+  while ((1u << tile_bits) < (uint32_t)d.ntiles) ++tile_bits;
 
   uint64_t D = 0;
+  GS_CUDA_CHECK(c, cudaMemsetAsync(c->counters.ptr, 0, 64, stream));
   if (N > 0) {
     {
       StageTimer t(c, 0, stream);
       GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
-                                            (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint8_t*)c->clamped.ptr,
-                                            stream));
+                                            (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint2*)c->rects.ptr,
+                                            (uint8_t*)c->clamped.ptr, stream));
     }
     {
       StageTimer t(c, 1, stream);
-      GS_CUDA_CHECK(c, gs_launch_scan(c->scan_tmp.ptr, scan_bytes, (const uint32_t*)c->tiles.ptr,
-                                      (uint32_t*)c->offsets.ptr, N, stream));
-      // the one host synchronisation of the forward: number of (Gaussian, tile) duplicates
-      GS_CUDA_CHECK(c, cudaMemcpyAsync(c->d_host_pinned, (uint32_t*)c->offsets.ptr + (N - 1), 4,
-                                       cudaMemcpyDeviceToHost, stream));
-      GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
-      D = *c->d_host_pinned;
-      // a 32-bit inclusive scan wraps silently: detect it with a 64-bit bound (each Gaussian touches at most
-      // ntiles tiles), falling back to an exact check only when the bound allows overflow
-      if ((uint64_t)N * (uint64_t)d.ntiles > 0xFFFFFFFFull && D > 0xF0000000ull) {
-        gs_set_error(c, "duplicate list too long for 32-bit indices");
-        return GS_EOVERFLOW;
-      }
-      const size_t Dn = (size_t)(D > 0 ? D : 1);
-      GS_ENSURE(c, c->keys_a, Dn * 8);
-      GS_ENSURE(c, c->keys_b, Dn * 8);
-      GS_ENSURE(c, c->vals_a, Dn * 4);
-      GS_ENSURE(c, c->vals_b, Dn * 4);
-      if (D > 0)
-        GS_CUDA_CHECK(c, gs_launch_duplicate(N, (const GsGeom*)c->geom.ptr, (const float*)c->depths.ptr,
-                                             (const int*)c->radii.ptr, (const uint32_t*)c->offsets.ptr,
-                                             (uint64_t*)c->keys_a.ptr, (uint32_t*)c->vals_a.ptr, d.gx, d.gy, stream));
+      GS_CUDA_CHECK(c, gs_launch_depth_sort(N, (const uint32_t*)c->depths.ptr, (uint32_t*)c->sort_k0.ptr,
+                                            (uint32_t*)c->sort_k1.ptr, (uint32_t*)c->sort_v0.ptr,
+                                            (uint32_t*)c->sort_v1.ptr, (uint32_t*)c->radix_counts.ptr, c->radix_grid,
+                                            stream));
     }
     {
       StageTimer t(c, 2, stream);
-      int tile_bits = 1;
-      while ((1u << tile_bits) < (uint32_t)d.ntiles) ++tile_bits;
-      const int end_bit = 32 + tile_bits;
-      const size_t sort_bytes = gs_sort_temp_bytes((uint32_t)D, end_bit);
-      GS_ENSURE(c, c->sort_tmp, sort_bytes > 0 ? sort_bytes : 1);
-      GS_CUDA_CHECK(c, gs_launch_sort(c->sort_tmp.ptr, sort_bytes, (const uint64_t*)c->keys_a.ptr,
-                                      (uint64_t*)c->keys_b.ptr, (const uint32_t*)c->vals_a.ptr,
-                                      (uint32_t*)c->vals_b.ptr, (uint32_t)D, end_bit, stream));
+      GS_CUDA_CHECK(c, gs_launch_dup_scan(N, (const uint32_t*)c->sort_v1.ptr, (const uint2*)c->rects.ptr,
+                                          (uint32_t*)c->dup_sums.ptr, D64_dev, D_dev, stream));
+      // the one host synchronisation of the forward: number of (Gaussian, tile) duplicates, to size the lists
+      GS_CUDA_CHECK(c, cudaMemcpyAsync(c->d_host_pinned, D64_dev, 8, cudaMemcpyDeviceToHost, stream));
+      GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
+      D = *(const unsigned long long*)c->d_host_pinned;
+      if (D > 0xFFFFFFF0ull) {
+        gs_set_error(c, "duplicate list too long for 32-bit indices (%llu pairs)", (unsigned long long)D);
+        return GS_EOVERFLOW;
+      }
+      const size_t Dn = (size_t)(D > 0 ? D : 1);
+      GS_ENSURE(c, c->keys_a, Dn * c->key_bytes);
+      GS_ENSURE(c, c->keys_b, Dn * c->key_bytes);
+      GS_ENSURE(c, c->vals_a, Dn * 4);
+      GS_ENSURE(c, c->vals_b, Dn * 4);
+      if (D > 0)
+        GS_CUDA_CHECK(c, gs_launch_duplicate(N, (const uint32_t*)c->sort_v1.ptr, (const uint2*)c->rects.ptr,
+                                             (const uint32_t*)c->dup_sums.ptr, c->keys_a.ptr, c->key_bytes,
+                                             (uint32_t*)c->vals_a.ptr, d.gx, (uint32_t)D, overflow_dev, stream));
+    }
+    {
+      StageTimer t(c, 3, stream);
+      int in_b = 0;
+      GS_CUDA_CHECK(c, gs_launch_tile_sort(D_dev, tile_bits, c->key_bytes, c->keys_a.ptr, c->keys_b.ptr,
+                                           (uint32_t*)c->vals_a.ptr, (uint32_t*)c->vals_b.ptr,
+                                           (uint32_t*)c->radix_counts.ptr, c->radix_grid, &in_b, stream));
+      c->sorted_tiles = in_b ? c->keys_b.ptr : c->keys_a.ptr;
+      c->point_list = (const uint32_t*)(in_b ? c->vals_b.ptr : c->vals_a.ptr);
     }
   } else {
-    GS_ENSURE(c, c->keys_b, 8);
-    GS_ENSURE(c, c->vals_b, 4);
+    GS_ENSURE(c, c->keys_a, 8);
+    GS_ENSURE(c, c->vals_a, 4);
+    c->sorted_tiles = c->keys_a.ptr;
+    c->point_list = (const uint32_t*)c->vals_a.ptr;
   }
   {
-    StageTimer t(c, 3, stream);
-    GS_CUDA_CHECK(c, gs_launch_ranges((uint32_t)D, (const uint64_t*)c->keys_b.ptr, (uint2*)c->ranges.ptr, d.ntiles,
-                                      stream));
+    StageTimer t(c, 4, stream);
+    GS_CUDA_CHECK(c, gs_launch_ranges(D_dev, c->sorted_tiles, c->key_bytes, (uint2*)c->ranges.ptr, d.ntiles, stream));
     GS_CUDA_CHECK(c, gs_launch_order_tiles(d.ntiles, (const uint2*)c->ranges.ptr, (uint32_t*)c->tile_order.ptr,
                                            stream));
   }
@@ -337,10 +362,9 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->work_items, max_segs * sizeof(uint2));
   GS_ENSURE(c, c->ckpt, max_segs * GS_TILE_PIX * sizeof(float4));
   {
-    StageTimer t(c, 4, stream);
-    GS_CUDA_CHECK(c, cudaMemsetAsync(c->counters.ptr, 0, 8, stream));
+    StageTimer t(c, 5, stream);
     GS_CUDA_CHECK(c, gs_launch_blend_forward(d, (const uint32_t*)c->tile_order.ptr, (const uint2*)c->ranges.ptr,
-                                             (const uint32_t*)c->vals_b.ptr, (const GsGeom*)c->geom.ptr, st->bg,
+                                             c->point_list, (const GsGeom*)c->geom.ptr, st->bg,
                                              out_color, (float4*)c->final_state.ptr, (uint32_t*)c->n_contrib.ptr,
                                              (float4*)c->ckpt.ptr, (uint2*)c->work_items.ptr,
                                              (uint32_t*)c->counters.ptr, (uint32_t*)c->tile_last.ptr, stream));
@@ -356,7 +380,6 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   c->W = d.W;
   c->ntiles = d.ntiles;
   c->D = D;
-  c->kept_unsorted = true;  // keys_a/vals_a are not reused until the next forward
   c->have_forward = true;
   return GS_OK;
 }
@@ -379,9 +402,9 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
   const GsDims d = gs_dims(*st);
   GS_ENSURE(c, c->grad_geom, (size_t)N * 48);
   {
-    StageTimer t(c, 5, stream);
+    StageTimer t(c, 6, stream);
     GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
-    GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, (const uint32_t*)c->vals_b.ptr,
+    GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, c->point_list,
                                               (const GsGeom*)c->geom.ptr, st->bg, (const float4*)c->final_state.ptr,
                                               (const uint32_t*)c->n_contrib.ptr, dL_dout_color,
                                               (const float4*)c->ckpt.ptr, (const uint2*)c->work_items.ptr,
@@ -390,7 +413,7 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
                                               c->num_sms, stream));
   }
   {
-    StageTimer t(c, 6, stream);
+    StageTimer t(c, 7, stream);
     GS_CUDA_CHECK(c, gs_launch_preprocess_backward(*st, *in, *grads, N, (const int*)c->radii.ptr,
                                                    (const uint8_t*)c->clamped.ptr, (const float4*)c->grad_geom.ptr,
                                                    stream));
@@ -456,7 +479,7 @@ static long long dbg_size(gs_ctx* c, int what) {
     case GS_DBG_RGB: return N * 12;
     case GS_DBG_CLAMPED: return N;
     case GS_DBG_TILES_TOUCHED: return N * 4;
-    case GS_DBG_POINT_OFFSETS: return N * 4;
+    case GS_DBG_DEPTH_ORDER: return N * 4;
     case GS_DBG_KEYS_SORTED: return D * 8;
     case GS_DBG_POINT_LIST: return D * 4;
     case GS_DBG_RANGES: return T * 8;
@@ -467,8 +490,6 @@ static long long dbg_size(gs_ctx* c, int what) {
     case GS_DBG_DL_DOPACITY: return c->have_backward ? N * 4 : GS_ESTATE;
     case GS_DBG_DL_DCOLOR: return c->have_backward ? N * 12 : GS_ESTATE;
     case GS_DBG_NUM_RENDERED: return 8;
-    case GS_DBG_KEYS_UNSORTED: return c->kept_unsorted ? D * 8 : GS_ESTATE;
-    case GS_DBG_VALUES_UNSORTED: return c->kept_unsorted ? D * 4 : GS_ESTATE;
     default: return GS_EINVAL;
   }
 }
@@ -498,9 +519,23 @@ int gs_debug_get(gs_ctx* c, int what, void* host_dst, size_t bytes) {
     case GS_DBG_DEPTHS: src = c->depths.ptr; break;
     case GS_DBG_CLAMPED: src = c->clamped.ptr; break;
     case GS_DBG_TILES_TOUCHED: src = c->tiles.ptr; break;
-    case GS_DBG_POINT_OFFSETS: src = c->offsets.ptr; break;
-    case GS_DBG_KEYS_SORTED: src = c->keys_b.ptr; break;
-    case GS_DBG_POINT_LIST: src = c->vals_b.ptr; break;
+    case GS_DBG_DEPTH_ORDER: src = c->sort_v1.ptr; break;
+    case GS_DBG_KEYS_SORTED: {
+      // the 64-bit keys (tile << 32 | depth bits) are implied by the two-level sort: rebuild them on the host
+      const size_t D = (size_t)c->D;
+      std::vector<uint32_t> ids(D), dep(N);
+      std::vector<uint8_t> tk(D * (size_t)c->key_bytes);
+      GS_CUDA_CHECK(c, cudaMemcpy(ids.data(), c->point_list, D * 4, cudaMemcpyDeviceToHost));
+      GS_CUDA_CHECK(c, cudaMemcpy(tk.data(), c->sorted_tiles, tk.size(), cudaMemcpyDeviceToHost));
+      GS_CUDA_CHECK(c, cudaMemcpy(dep.data(), c->depths.ptr, N * 4, cudaMemcpyDeviceToHost));
+      uint64_t* o = (uint64_t*)host_dst;
+      for (size_t i = 0; i < D; ++i) {
+        const uint32_t tile = c->key_bytes == 2 ? ((const uint16_t*)tk.data())[i] : ((const uint32_t*)tk.data())[i];
+        o[i] = ((uint64_t)tile << 32) | dep[ids[i]];
+      }
+      return GS_OK;
+    }
+    case GS_DBG_POINT_LIST: src = c->point_list; break;
     case GS_DBG_RANGES: src = c->ranges.ptr; break;
     case GS_DBG_FINAL_T: {  // .x of the per-pixel final state {T, C.r, C.g, C.b}
       const size_t P = (size_t)c->H * c->W;
@@ -510,8 +545,6 @@ int gs_debug_get(gs_ctx* c, int what, void* host_dst, size_t bytes) {
       return GS_OK;
     }
     case GS_DBG_N_CONTRIB: src = c->n_contrib.ptr; break;
-    case GS_DBG_KEYS_UNSORTED: src = c->keys_a.ptr; break;
-    case GS_DBG_VALUES_UNSORTED: src = c->vals_a.ptr; break;
     case GS_DBG_NUM_RENDERED: {
       const uint64_t D = c->D;
       memcpy(host_dst, &D, 8);

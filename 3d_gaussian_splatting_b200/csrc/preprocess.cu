@@ -27,6 +27,7 @@ struct PreprocessArgs {
   float* depths;
   int* radii;
   uint32_t* tiles_touched;
+  uint2* rects;  // tile rectangle {x0 | y0 << 16, x1 | y1 << 16}; (0,0) when culled
   uint8_t* clamped;
   float focal_x, focal_y;
   int gx, gy;
@@ -122,6 +123,7 @@ struct PpOut {
   float depth;
   int radius;
   uint32_t tiles, cmask;
+  uint2 rect;
 };
 
 // One Gaussian.  p / scl / q4 / opac_in as stored by the caller (raw when a.in.raw_params); cov_pre, col_pre:
@@ -136,6 +138,7 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
   g.q2 = g.q0;
   int rad_out = 0;
   uint32_t tiles = 0, cmask = 0;
+  uint2 rect = make_uint2(0u, 0u);
   float depth = 0.f;
 
   const float* V = st.viewmatrix;
@@ -211,6 +214,7 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
           g.q2 = make_float4(rgb[2], pv[2], 0.f, 0.f);
           rad_out = rad;
           tiles = (uint32_t)area;
+          rect = make_uint2((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)x1 | ((uint32_t)y1 << 16));
           depth = pv[2];
         }
       }
@@ -222,6 +226,7 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
   o.radius = rad_out;
   o.tiles = tiles;
   o.cmask = cmask;
+  o.rect = rect;
   return o;
 }
 
@@ -267,6 +272,7 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
   a.depths[i] = o.depth;
   a.radii[i] = o.radius;
   a.tiles_touched[i] = o.tiles;
+  a.rects[i] = o.rect;
   a.clamped[i] = (uint8_t)o.cmask;
 }
 
@@ -282,7 +288,8 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
 #define PPB_OFF_DEPTH (PPB_OFF_GEOM + PPB_ROWS * 12)
 #define PPB_OFF_RADII (PPB_OFF_DEPTH + PPB_ROWS)
 #define PPB_OFF_TILES (PPB_OFF_RADII + PPB_ROWS)
-#define PPB_OFF_CLAMP (PPB_OFF_TILES + PPB_ROWS)   // rows x 1 byte
+#define PPB_OFF_RECT (PPB_OFF_TILES + PPB_ROWS)    // rows x 2
+#define PPB_OFF_CLAMP (PPB_OFF_RECT + PPB_ROWS * 2) // rows x 1 byte
 #define PPB_FLOATS (PPB_OFF_CLAMP + PPB_ROWS / 4)
 #define PPB_SMEM_BYTES (PPB_FLOATS * 4 + 16)
 
@@ -321,6 +328,7 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
   s_buf[PPB_OFF_DEPTH + tid] = o.depth;
   reinterpret_cast<int*>(s_buf)[PPB_OFF_RADII + tid] = o.radius;
   reinterpret_cast<uint32_t*>(s_buf)[PPB_OFF_TILES + tid] = o.tiles;
+  reinterpret_cast<uint2*>(s_buf + PPB_OFF_RECT)[tid] = o.rect;
   reinterpret_cast<uint8_t*>(s_buf + PPB_OFF_CLAMP)[tid] = (uint8_t)o.cmask;
   tma::fence_proxy_async_smem();
   __syncthreads();
@@ -329,6 +337,7 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
     tma::store(a.depths + row0, s_buf + PPB_OFF_DEPTH, PPB_ROWS * 4u);
     tma::store(a.radii + row0, s_buf + PPB_OFF_RADII, PPB_ROWS * 4u);
     tma::store(a.tiles_touched + row0, s_buf + PPB_OFF_TILES, PPB_ROWS * 4u);
+    tma::store(a.rects + row0, s_buf + PPB_OFF_RECT, PPB_ROWS * 8u);
     tma::store(a.clamped + row0, s_buf + PPB_OFF_CLAMP, PPB_ROWS);
     tma::commit_group();
     tma::wait_group_read0();
@@ -338,7 +347,8 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
 static bool pp_aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 
 cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, int N, GsGeom* geom, float* depths,
-                                 int* radii, uint32_t* tiles_touched, uint8_t* clamped, cudaStream_t stream) {
+                                 int* radii, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped,
+                                 cudaStream_t stream) {
   if (N == 0) return cudaSuccess;
   PreprocessArgs a;
   a.in = in;
@@ -347,6 +357,7 @@ cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, 
   a.depths = depths;
   a.radii = radii;
   a.tiles_touched = tiles_touched;
+  a.rects = rects;
   a.clamped = clamped;
   a.focal_x = (float)st.W / (2.0f * st.tanfovx);
   a.focal_y = (float)st.H / (2.0f * st.tanfovy);

@@ -232,10 +232,10 @@ class Rasterizer:
 
     # ---- parity harness / profiling -------------------------------------------------------------
     _DBG_DTYPES = dict(MEANS2D=np.float32, DEPTHS=np.float32, CONIC_OPACITY=np.float32, RGB=np.float32,
-                       CLAMPED=np.uint8, TILES_TOUCHED=np.uint32, POINT_OFFSETS=np.uint32, KEYS_SORTED=np.uint64,
+                       CLAMPED=np.uint8, TILES_TOUCHED=np.uint32, DEPTH_ORDER=np.uint32, KEYS_SORTED=np.uint64,
                        POINT_LIST=np.uint32, RANGES=np.uint32, FINAL_T=np.float32, N_CONTRIB=np.uint32,
                        DL_DMEAN2D=np.float32, DL_DCONIC=np.float32, DL_DOPACITY=np.float32, DL_DCOLOR=np.float32,
-                       NUM_RENDERED=np.uint64, KEYS_UNSORTED=np.uint64, VALUES_UNSORTED=np.uint32)
+                       NUM_RENDERED=np.uint64)
 
     def debug_get(self, name: str) -> np.ndarray:
         what = _lib.DBG[name]

@@ -106,12 +106,16 @@ class ClockSampler:
 # ---- algorithmic bytes ---------------------------------------------------
 def stage_bytes(N, N_vis, D, D_eff, P, T, K):
     tile_bits = max(1, int(np.ceil(np.log2(max(T, 2)))))
-    passes = int(np.ceil((32 + tile_bits) / 8))
+    passes = int(np.ceil(tile_bits / 8))
+    kb = 2 if T <= 65536 else 4
     return {
         "preprocess": (44 + 12 * K) * N + 48 * N_vis + 8 * (N - N_vis),
-        "scan_duplicate": 8 * N + 20 * N_vis + 12 * D,
-        "sort": (8 + 24 * passes) * D,
-        "ranges": 8 * D + 8 * T,
+        # two-level sort: argsort of N depth keys, 4 passes of (hist 4 + read 8 + write 8) B
+        "depth_sort": 4 * 20 * N - 8 * N,
+        # scan along the depth order (order + tiles_touched, twice) + rectangle (means2D 8, radius 4) + (tile, id) pairs
+        "scan_duplicate": 16 * N + 12 * N_vis + (kb + 4) * D,
+        "sort": passes * (kb + 2 * (kb + 4)) * D,
+        "ranges": 8 * T,
         "blend_fwd": 40 * D_eff + 20 * P,
         "blend_bwd": 40 * D_eff + 20 * P + 36 * N_vis,
         "preprocess_bwd": (44 + 12 * K) * N_vis + 36 * N_vis + 4 * N + (44 + 12 * K) * N,
@@ -212,9 +216,10 @@ def run_reference(args, rank, world):
 
 
 # ---- GPU arm -----------------------------------------------------------------------------------
-OWN_KERNELS_PER_STEP = 9   # preprocess, duplicate_with_keys, identify_tile_ranges, blend_forward, l1_loss,
-                           # loss_finalize, blend_backward, preprocess_backward, adam_stats
-LIB_KERNELS_PER_STEP = 10  # CUB DeviceScan (2) + DeviceRadixSort onesweep (histogram, scan, 6 passes)
+# preprocess, depth sort 4 x (hist, scan, scatter), dup block sums + scan + duplicate, tile sort 2 x 3, tile
+# ranges, tile order, blend_forward, l1_loss + finalize, blend_backward, preprocess_backward, adam_stats
+OWN_KERNELS_PER_STEP = 1 + 12 + 3 + 6 + 2 + 1 + 2 + 1 + 1 + 1
+LIB_KERNELS_PER_STEP = 0   # no library kernels on the path (the radix sort and scans are this repo's own)
 
 
 def run_ours(args, rank, world, local_rank):
@@ -349,7 +354,7 @@ def run_ours(args, rank, world, local_rank):
                   "GBps": round(by[k] / (stage_ms[k] * 1e-3) / 1e9, 1) if stage_ms[k] > 0 else None,
                   "frac_hbm": round(by[k] / (stage_ms[k] * 1e-3) / 1e9 / peak, 4) if stage_ms[k] > 0 else None}
               for k in stage_ms}
-    fwd_bwd_ms = sum(stage_ms[k] for k in ("preprocess", "scan_duplicate", "sort", "ranges", "blend_fwd",
+    fwd_bwd_ms = sum(stage_ms[k] for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd",
                                            "blend_bwd", "preprocess_bwd"))
 
     cpu_baseline = None

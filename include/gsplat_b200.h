@@ -167,8 +167,8 @@ enum {
   GS_DBG_RGB = 3,           /* (N,3) f32 */
   GS_DBG_CLAMPED = 4,       /* (N) u8, bit c set when channel c was clamped at 0 */
   GS_DBG_TILES_TOUCHED = 5, /* (N) u32 */
-  GS_DBG_POINT_OFFSETS = 6, /* (N) u32 inclusive scan */
-  GS_DBG_KEYS_SORTED = 7,   /* (D) u64 */
+  GS_DBG_DEPTH_ORDER = 6,   /* (N) u32 Gaussian ids in (depth bits, id) order: the first level of the sort */
+  GS_DBG_KEYS_SORTED = 7,   /* (D) u64 tile << 32 | depth bits, rebuilt from the sorted (tile, id) pairs */
   GS_DBG_POINT_LIST = 8,    /* (D) u32 */
   GS_DBG_RANGES = 9,        /* (T,2) u32 */
   GS_DBG_FINAL_T = 10,      /* (H,W) f32 */
@@ -177,18 +177,16 @@ enum {
   GS_DBG_DL_DCONIC = 13,    /* (N,3) f32 d/d(A,B,C), after gs_backward */
   GS_DBG_DL_DOPACITY = 14,  /* (N) f32 w.r.t. the ACTIVATED opacity, after gs_backward */
   GS_DBG_DL_DCOLOR = 15,    /* (N,3) f32, after gs_backward */
-  GS_DBG_NUM_RENDERED = 16, /* 1 x u64: D */
-  GS_DBG_KEYS_UNSORTED = 17,/* (D) u64 (only kept when settings.debug != 0) */
-  GS_DBG_VALUES_UNSORTED = 18
+  GS_DBG_NUM_RENDERED = 16  /* 1 x u64: D */
 };
 GS_API long long gs_debug_size(gs_ctx *ctx, int what);
 GS_API int gs_debug_get(gs_ctx *ctx, int what, void *host_dst, size_t bytes);
 
 /* Per-stage device time of the last forward/backward in milliseconds (CUDA events recorded
- * only when gs_set_profiling(ctx,1)); order: preprocess, scan+duplicate, sort, ranges, blend,
- * blend_bwd, preprocess_bwd.  The role of the CUDA-event timers the reference says it lacks
+ * only when gs_set_profiling(ctx,1)); order: preprocess, depth sort, scan+duplicate, tile sort,
+ * ranges, blend, blend_bwd, preprocess_bwd.  The role of the CUDA-event timers the reference says it lacks
  * (src/utils/train_utils.cpp:119-121). */
-#define GS_NUM_STAGES 7
+#define GS_NUM_STAGES 8
 GS_API int gs_set_profiling(gs_ctx *ctx, int enabled);
 GS_API int gs_get_stage_ms(gs_ctx *ctx, float ms[GS_NUM_STAGES]);
 
