@@ -56,19 +56,31 @@ __device__ __forceinline__ uint32_t block_exclusive_scan_256(uint32_t v, uint32_
   return off + incl - v;
 }
 
-__device__ __forceinline__ uint32_t rect_area(uint2 r) {
+// per-Gaussian record written by K1: {x0 | y0 << 16, x1 | y1 << 16, alive mask lo, hi}; the 64-bit mask (bit =
+// row-major index inside the rectangle) is only meaningful for rectangles of <= 64 tiles, larger ones keep all
+__device__ __forceinline__ uint32_t rect_area(uint4 r) {
   return ((r.y & 0xFFFFu) - (r.x & 0xFFFFu)) * ((r.y >> 16) - (r.x >> 16));
+}
+__device__ __forceinline__ uint32_t rect_alive(uint4 r) {
+  const uint32_t area = rect_area(r);
+  return area > GS_CULL_MAX_TILES ? area : (uint32_t)(__popc(r.z) + __popc(r.w));
+}
+// index (inside the rectangle) of the k-th alive tile
+__device__ __forceinline__ uint32_t rect_kth_alive(uint4 r, uint32_t k) {
+  if (rect_area(r) > GS_CULL_MAX_TILES) return k;
+  const uint32_t c = (uint32_t)__popc(r.z);
+  return k < c ? __fns(r.z, 0, (int)k + 1) : 32u + __fns(r.w, 0, (int)(k - c) + 1);
 }
 
 __global__ void __launch_bounds__(DUP_THREADS)
-dup_block_sums_kernel(int N, const uint32_t* __restrict__ order, const uint2* __restrict__ rects,
+dup_block_sums_kernel(int N, const uint32_t* __restrict__ order, const uint4* __restrict__ rects,
                       uint32_t* __restrict__ block_sums) {
   __shared__ uint32_t s_warp[DUP_THREADS / 32];
   uint32_t sum = 0;
 #pragma unroll
   for (int k = 0; k < DUP_ITEMS; ++k) {
     const int r = blockIdx.x * DUP_BLOCK + k * DUP_THREADS + threadIdx.x;
-    if (r < N) sum += rect_area(rects[order[r]]);
+    if (r < N) sum += rect_alive(__ldg(rects + order[r]));
   }
   uint32_t tot;
   block_exclusive_scan_256(sum, s_warp, tot);
@@ -115,32 +127,32 @@ dup_scan_sums_kernel(int nb, uint32_t* __restrict__ block_sums, unsigned long lo
 // A block expands 1024 consecutive ranks of the depth order.  Thread t first scans the tile counts of
 // ranks 4t .. 4t+3; then the block's output slots [0, total) are dealt round-robin to the threads: slot j
 // finds its owner by binary search in the shared prefix array and derives its tile from the owner's
-// rectangle, so both output arrays are written fully coalesced whatever the rectangle sizes are (no
+// rectangle and alive-tile mask (exact tile culling, gs_common.cuh), so both output arrays are written fully coalesced whatever the rectangle sizes are (no
 // per-thread loops over big splats).  cap: capacity of the pair buffers (pairs past it are dropped and
 // *overflow is raised -- only possible when the caller fixed the capacity in advance).
 template <typename KeyT>
 __global__ void __launch_bounds__(DUP_THREADS)
-duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint2* __restrict__ rects,
+duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint4* __restrict__ rects,
                            const uint32_t* __restrict__ block_base, KeyT* __restrict__ tile_ids,
                            uint32_t* __restrict__ values, int gx, uint32_t cap, uint32_t* __restrict__ overflow) {
   __shared__ uint32_t s_warp[DUP_THREADS / 32];
   __shared__ uint32_t s_off[DUP_BLOCK];
   __shared__ uint32_t s_id[DUP_BLOCK];
-  __shared__ uint2 s_rect[DUP_BLOCK];
+  __shared__ uint4 s_rect[DUP_BLOCK];
   const int r0 = blockIdx.x * DUP_BLOCK + threadIdx.x * DUP_ITEMS;
   uint32_t cnt[DUP_ITEMS];
   uint32_t sum = 0;
 #pragma unroll
   for (int k = 0; k < DUP_ITEMS; ++k) {
     uint32_t id = 0;
-    uint2 rc = make_uint2(0u, 0u);
+    uint4 rc = make_uint4(0u, 0u, 0u, 0u);
     if (r0 + k < N) {
       id = order[r0 + k];
-      rc = rects[id];
+      rc = __ldg(rects + id);
     }
     s_id[threadIdx.x * DUP_ITEMS + k] = id;
     s_rect[threadIdx.x * DUP_ITEMS + k] = rc;
-    cnt[k] = rect_area(rc);
+    cnt[k] = rect_alive(rc);
     sum += cnt[k];
   }
   uint32_t total;
@@ -166,8 +178,8 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
       if (s_off[mid] <= j) lo = mid;
       else hi = mid - 1;
     }
-    const uint2 rc = s_rect[lo];
-    const uint32_t k = j - s_off[lo];
+    const uint4 rc = s_rect[lo];
+    const uint32_t k = rect_kth_alive(rc, j - s_off[lo]);
     const uint32_t x0 = rc.x & 0xFFFFu, y0 = rc.x >> 16, w = (rc.y & 0xFFFFu) - x0;
     const uint32_t row = k / w, col = k - row * w;
     tile_ids[base + j] = (KeyT)((y0 + row) * (uint32_t)gx + x0 + col);
@@ -177,7 +189,7 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
 
 int gs_dup_num_blocks(int N) { return (N + DUP_BLOCK - 1) / DUP_BLOCK; }
 
-cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint2* rects, uint32_t* block_sums,
+cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint4* rects, uint32_t* block_sums,
                                unsigned long long* total, uint32_t* total32, cudaStream_t stream) {
   if (N == 0) return cudaMemsetAsync(total, 0, 8, stream);
   const int nb = gs_dup_num_blocks(N);
@@ -186,7 +198,7 @@ cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint2* rects,
   return cudaGetLastError();
 }
 
-cudaError_t gs_launch_duplicate(int N, const uint32_t* order, const uint2* rects, const uint32_t* block_base,
+cudaError_t gs_launch_duplicate(int N, const uint32_t* order, const uint4* rects, const uint32_t* block_base,
                                 void* tile_ids, int key_bytes, uint32_t* values, int gx, uint32_t cap,
                                 uint32_t* overflow, cudaStream_t stream) {
   if (N == 0) return cudaSuccess;

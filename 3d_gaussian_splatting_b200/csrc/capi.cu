@@ -13,13 +13,13 @@
 
 // ---- launchers implemented in the other translation units ----
 cudaError_t gs_launch_preprocess(const gs_settings&, const gs_gaussians&, int, GsGeom*, float*, int*, uint32_t*,
-                                 uint2*, uint8_t*, cudaStream_t);
+                                 uint4*, uint8_t*, cudaStream_t);
 cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, int,
                                  cudaStream_t);
 int gs_dup_num_blocks(int N);
-cudaError_t gs_launch_dup_scan(int, const uint32_t*, const uint2*, uint32_t*, unsigned long long*, uint32_t*,
+cudaError_t gs_launch_dup_scan(int, const uint32_t*, const uint4*, uint32_t*, unsigned long long*, uint32_t*,
                                cudaStream_t);
-cudaError_t gs_launch_duplicate(int, const uint32_t*, const uint2*, const uint32_t*, void*, int, uint32_t*, int,
+cudaError_t gs_launch_duplicate(int, const uint32_t*, const uint4*, const uint32_t*, void*, int, uint32_t*, int,
                                 uint32_t, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_tile_sort(const uint32_t*, int, int, void*, void*, uint32_t*, uint32_t*, uint32_t*, int, int*,
                                 cudaStream_t);
@@ -275,7 +275,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->depths, Nn * 4);
   GS_ENSURE(c, c->radii, Nn * 4);
   GS_ENSURE(c, c->tiles, Nn * 4);
-  GS_ENSURE(c, c->rects, Nn * 8);
+  GS_ENSURE(c, c->rects, Nn * 16);
   GS_ENSURE(c, c->clamped, Nn);
   GS_ENSURE(c, c->sort_k0, Nn * 4);
   GS_ENSURE(c, c->sort_k1, Nn * 4);
@@ -304,7 +304,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
     {
       StageTimer t(c, 0, stream);
       GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
-                                            (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint2*)c->rects.ptr,
+                                            (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint4*)c->rects.ptr,
                                             (uint8_t*)c->clamped.ptr, stream));
     }
     {
@@ -316,7 +316,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
     }
     {
       StageTimer t(c, 2, stream);
-      GS_CUDA_CHECK(c, gs_launch_dup_scan(N, (const uint32_t*)c->sort_v1.ptr, (const uint2*)c->rects.ptr,
+      GS_CUDA_CHECK(c, gs_launch_dup_scan(N, (const uint32_t*)c->sort_v1.ptr, (const uint4*)c->rects.ptr,
                                           (uint32_t*)c->dup_sums.ptr, D64_dev, D_dev, stream));
       // the one host synchronisation of the forward: number of (Gaussian, tile) duplicates, to size the lists
       GS_CUDA_CHECK(c, cudaMemcpyAsync(c->d_host_pinned, D64_dev, 8, cudaMemcpyDeviceToHost, stream));
@@ -332,7 +332,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
       GS_ENSURE(c, c->vals_a, Dn * 4);
       GS_ENSURE(c, c->vals_b, Dn * 4);
       if (D > 0)
-        GS_CUDA_CHECK(c, gs_launch_duplicate(N, (const uint32_t*)c->sort_v1.ptr, (const uint2*)c->rects.ptr,
+        GS_CUDA_CHECK(c, gs_launch_duplicate(N, (const uint32_t*)c->sort_v1.ptr, (const uint4*)c->rects.ptr,
                                              (const uint32_t*)c->dup_sums.ptr, c->keys_a.ptr, c->key_bytes,
                                              (uint32_t*)c->vals_a.ptr, d.gx, (uint32_t)D, overflow_dev, stream));
     }

@@ -27,7 +27,7 @@ struct PreprocessArgs {
   float* depths;
   int* radii;
   uint32_t* tiles_touched;
-  uint2* rects;  // tile rectangle {x0 | y0 << 16, x1 | y1 << 16}; (0,0) when culled
+  uint4* rects;  // {x0 | y0 << 16, x1 | y1 << 16, alive-tile mask lo, hi}; zeros when culled (mask unused when area > 64)
   uint8_t* clamped;
   float focal_x, focal_y;
   int gx, gy;
@@ -123,7 +123,7 @@ struct PpOut {
   float depth;
   int radius;
   uint32_t tiles, cmask;
-  uint2 rect;
+  uint4 rect;
 };
 
 // One Gaussian.  p / scl / q4 / opac_in as stored by the caller (raw when a.in.raw_params); cov_pre, col_pre:
@@ -138,7 +138,7 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
   g.q2 = g.q0;
   int rad_out = 0;
   uint32_t tiles = 0, cmask = 0;
-  uint2 rect = make_uint2(0u, 0u);
+  uint4 rect = make_uint4(0u, 0u, 0u, 0u);
   float depth = 0.f;
 
   const float* V = st.viewmatrix;
@@ -209,12 +209,27 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
           }
           float opac = opac_in;
           if (a.in.raw_params) opac = 1.0f / (1.0f + expf(-opac));
+          // exact tile culling (gs_common.cuh): which tiles of the rectangle can receive alpha >= 1/255
+          uint32_t mlo = 0xFFFFFFFFu, mhi = 0xFFFFFFFFu;
+          if (area <= GS_CULL_MAX_TILES) {
+            const GsCull cs = gs_cull_setup(0.5f * con_x, con_y, 0.5f * con_z, opac);
+            mlo = mhi = 0u;
+            int bit = 0;
+            for (int ty = y0; ty < y1; ++ty)
+              for (int tx = x0; tx < x1; ++tx, ++bit)
+                if (gs_tile_alive(cs, px, py, tx, ty)) {
+                  if (bit < 32) mlo |= 1u << bit;
+                  else mhi |= 1u << (bit - 32);
+                }
+            area = __popc(mlo) + __popc(mhi);
+          }
           g.q0 = make_float4(px, py, 0.5f * con_x, con_y);
           g.q1 = make_float4(0.5f * con_z, opac, rgb[0], rgb[1]);
           g.q2 = make_float4(rgb[2], pv[2], 0.f, 0.f);
           rad_out = rad;
           tiles = (uint32_t)area;
-          rect = make_uint2((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)x1 | ((uint32_t)y1 << 16));
+          rect = make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)x1 | ((uint32_t)y1 << 16),
+                            mlo, mhi);
           depth = pv[2];
         }
       }
@@ -288,8 +303,8 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
 #define PPB_OFF_DEPTH (PPB_OFF_GEOM + PPB_ROWS * 12)
 #define PPB_OFF_RADII (PPB_OFF_DEPTH + PPB_ROWS)
 #define PPB_OFF_TILES (PPB_OFF_RADII + PPB_ROWS)
-#define PPB_OFF_RECT (PPB_OFF_TILES + PPB_ROWS)    // rows x 2
-#define PPB_OFF_CLAMP (PPB_OFF_RECT + PPB_ROWS * 2) // rows x 1 byte
+#define PPB_OFF_RECT (PPB_OFF_TILES + PPB_ROWS)    // rows x 4
+#define PPB_OFF_CLAMP (PPB_OFF_RECT + PPB_ROWS * 4) // rows x 1 byte
 #define PPB_FLOATS (PPB_OFF_CLAMP + PPB_ROWS / 4)
 #define PPB_SMEM_BYTES (PPB_FLOATS * 4 + 16)
 
@@ -328,7 +343,7 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
   s_buf[PPB_OFF_DEPTH + tid] = o.depth;
   reinterpret_cast<int*>(s_buf)[PPB_OFF_RADII + tid] = o.radius;
   reinterpret_cast<uint32_t*>(s_buf)[PPB_OFF_TILES + tid] = o.tiles;
-  reinterpret_cast<uint2*>(s_buf + PPB_OFF_RECT)[tid] = o.rect;
+  reinterpret_cast<uint4*>(s_buf + PPB_OFF_RECT)[tid] = o.rect;
   reinterpret_cast<uint8_t*>(s_buf + PPB_OFF_CLAMP)[tid] = (uint8_t)o.cmask;
   tma::fence_proxy_async_smem();
   __syncthreads();
@@ -337,7 +352,7 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
     tma::store(a.depths + row0, s_buf + PPB_OFF_DEPTH, PPB_ROWS * 4u);
     tma::store(a.radii + row0, s_buf + PPB_OFF_RADII, PPB_ROWS * 4u);
     tma::store(a.tiles_touched + row0, s_buf + PPB_OFF_TILES, PPB_ROWS * 4u);
-    tma::store(a.rects + row0, s_buf + PPB_OFF_RECT, PPB_ROWS * 8u);
+    tma::store(a.rects + row0, s_buf + PPB_OFF_RECT, PPB_ROWS * 16u);
     tma::store(a.clamped + row0, s_buf + PPB_OFF_CLAMP, PPB_ROWS);
     tma::commit_group();
     tma::wait_group_read0();
@@ -347,7 +362,7 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
 static bool pp_aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 
 cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, int N, GsGeom* geom, float* depths,
-                                 int* radii, uint32_t* tiles_touched, uint2* rects, uint8_t* clamped,
+                                 int* radii, uint32_t* tiles_touched, uint4* rects, uint8_t* clamped,
                                  cudaStream_t stream) {
   if (N == 0) return cudaSuccess;
   PreprocessArgs a;

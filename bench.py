@@ -109,11 +109,11 @@ def stage_bytes(N, N_vis, D, D_eff, P, T, K):
     passes = int(np.ceil(tile_bits / 8))
     kb = 2 if T <= 65536 else 4
     return {
-        "preprocess": (44 + 12 * K) * N + 48 * N_vis + 8 * (N - N_vis),
+        "preprocess": (44 + 12 * K) * N + 48 * N_vis + 8 * (N - N_vis) + 16 * N,   # + 16-B rectangle/alive-mask record
         # two-level sort: argsort of N depth keys, 4 passes of (hist 4 + read 8 + write 8) B
         "depth_sort": 4 * 20 * N - 8 * N,
-        # scan along the depth order (order + tiles_touched, twice) + rectangle (means2D 8, radius 4) + (tile, id) pairs
-        "scan_duplicate": 16 * N + 12 * N_vis + (kb + 4) * D,
+        # scan along the depth order: order id (4) + 16-B rectangle record, read twice; (tile, id) pairs written once
+        "scan_duplicate": 2 * 20 * N + (kb + 4) * D,
         "sort": passes * (kb + 2 * (kb + 4)) * D,
         "ranges": 8 * T,
         "blend_fwd": 40 * D_eff + 20 * P,

@@ -74,6 +74,10 @@ class Oracle:
         self.lib.orc_expon_lr.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, C.c_int, C.c_int]
         self.lib.orc_focal2fov.argtypes = [C.c_double, C.c_double]
 
+    def set_tile_cull(self, enabled: bool):
+        """Exact tile culling on/off (orc_common.h); on by default -- off only to prove it is conservative."""
+        self.lib.orc_set_tile_cull(C.c_int(1 if enabled else 0))
+
     # ---- helpers -------------------------------------------------------------------
     def arr(self, a, dtype=None):
         return np.ascontiguousarray(a, dtype=self.dt if dtype is None else dtype)
@@ -134,8 +138,8 @@ class Oracle:
         D = int(self.lib.orc_scan_tiles(C.c_int(N), self.p(pre["tiles_touched"]), self.p(offsets)))
         keys = np.zeros(max(D, 1), np.uint64); values = np.zeros(max(D, 1), np.uint32)
         self.lib.orc_duplicate_with_keys(C.c_int(s.H), C.c_int(s.W), C.c_int(N), self.p(pre["means2D"]),
-                                         self.p(pre["depths"]), self.p(pre["radii"]), self.p(offsets),
-                                         self.p(keys), self.p(values))
+                                         self.p(pre["depths"]), self.p(pre["radii"]), self.p(pre["conic_opacity"]),
+                                         self.p(offsets), self.p(keys), self.p(values))
         keys_unsorted = keys.copy(); values_unsorted = values.copy()
         self.lib.orc_sort_pairs(C.c_uint64(D), self.p(keys), self.p(values))
         ranges = np.zeros((gx * gy, 2), np.uint32)

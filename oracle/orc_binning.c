@@ -38,7 +38,8 @@ uint64_t orc_scan_tiles(int N, const uint32_t *tiles_touched, uint32_t *point_of
 /* duplicateWithKeys: Gaussian i writes its keys at [offsets[i-1], offsets[i]) in row-major
  * tile order (y outer, x inner). */
 void orc_duplicate_with_keys(int H, int W, int N, const real *means2D, const real *depths, const int *radii,
-                             const uint32_t *point_offsets, uint64_t *keys, uint32_t *values) {
+                             const real *conic_opacity, const uint32_t *point_offsets, uint64_t *keys,
+                             uint32_t *values) {
   const int gx = orc_grid_x(W), gy = orc_grid_y(H);
 #pragma omp parallel for schedule(static)
   for (int i = 0; i < N; ++i) {
@@ -47,8 +48,12 @@ void orc_duplicate_with_keys(int H, int W, int N, const real *means2D, const rea
     int x0, y0, x1, y1;
     tile_rect(means2D[2 * i], means2D[2 * i + 1], radii[i], gx, gy, &x0, &y0, &x1, &y1);
     uint32_t dbits = f32_bits((float)depths[i]);
+    const int cull = orc_tile_cull_enabled && (x1 - x0) * (y1 - y0) <= ORC_CULL_MAX_TILES;
+    const real *co = conic_opacity + 4 * (size_t)i;
+    const orc_cull cs = orc_cull_setup(RC(0.5) * co[0], co[1], RC(0.5) * co[2], co[3]);
     for (int y = y0; y < y1; ++y)
       for (int x = x0; x < x1; ++x) {
+        if (cull && !orc_tile_alive(&cs, means2D[2 * i], means2D[2 * i + 1], x, y)) continue;
         uint64_t key = (uint64_t)(uint32_t)(y * gx + x);
         key = (key << 32) | dbits;
         keys[off] = key;

@@ -145,6 +145,82 @@ static inline real orc_power(real hA, real B, real hC, real dx, real dy) {
   return -q;
 }
 
+/*
+ * Exact tile culling (specified numerics, shared by definition with csrc/gs_common.cuh gs_cull_*).
+ * A Gaussian enters the list of a tile of its 3-sigma rectangle only if it can pass the blend's
+ * alpha >= 1/255 test somewhere in that tile: alpha_max = opacity * exp(-q_min) >= 1/255, i.e.
+ *     q_min <= ln(255 * opacity) + margin,
+ * where q_min is the minimum of q(d) = hA dx^2 + B dx dy + hC dy^2 (= -power) over the continuous box
+ * spanned by the tile's 16x16 pixel centres (d = mean - pixel).  The box minimum is 0 when the mean
+ * lies inside, otherwise the smallest of the four edge minima (1-D quadratics, clamped).  The margin
+ * of 0.01 in the exponent (1% in alpha) keeps the test conservative against rounding (and against the
+ * ~1e-7 error of the specified logarithm below), so dropping a pair never changes the image:
+ * tests/test_oracle_pipeline.py checks image and gradient equality with the cull off.
+ * Per Gaussian: thr = orc_log(255 o) + margin, rA = 1/(2 hA), rC = 1/(2 hC); per tile: no division, no
+ * transcendental.  Rectangles of more than ORC_CULL_MAX_TILES tiles are not culled (their mask would not
+ * fit 64 bits).  radii (and hence visibility) are NOT affected: they keep the 3-sigma definition.
+ */
+#define ORC_CULL_MARGIN RC(0.01)
+#define ORC_CULL_MAX_TILES 64
+extern int orc_tile_cull_enabled;
+#ifdef ORC_DOUBLE
+static inline real orc_log(real x) { return x > 0 ? log(x) : -HUGE_VAL; }
+#else
+/* ln(x) for normal x > 0: x = 2^e * m, m in [sqrt(1/2), sqrt(2)); ln m = 2 atanh(s), s = (m-1)/(m+1) */
+static inline real orc_log(real x) {
+  if (!(x > 0.0f)) return -HUGE_VALF;
+  uint32_t bits;
+  memcpy(&bits, &x, 4);
+  int32_t e = (int32_t)(bits >> 23) - 127;
+  bits = (bits & 0x007FFFFFu) | 0x3F800000u;
+  float m;
+  memcpy(&m, &bits, 4);
+  if (m > 1.41421356f) {
+    m = m * 0.5f;
+    e += 1;
+  }
+  const float s = (m - 1.0f) / (m + 1.0f);
+  const float s2 = s * s;
+  float p = fmaf(s2, 0.14285714285714285f, 0.2f);
+  p = fmaf(s2, p, 0.33333333333333333f);
+  p = fmaf(s2, p, 1.0f);
+  return fmaf((float)e, 0.69314718055994531f, 2.0f * s * p);
+}
+#endif
+typedef struct {
+  real hA, B, hC, rA, rC, thr;
+} orc_cull;
+static inline orc_cull orc_cull_setup(real hA, real B, real hC, real opacity) {
+  orc_cull c;
+  c.hA = hA;
+  c.B = B;
+  c.hC = hC;
+  c.rA = RC(1) / (RC(2) * hA);
+  c.rC = RC(1) / (RC(2) * hC);
+  c.thr = orc_log(RC(255) * opacity) + ORC_CULL_MARGIN;
+  return c;
+}
+static inline real orc_edge_min(real a, real b, real c, real rc, real e, real lo, real hi) {
+  /* q on the edge u = e, v in [lo,hi]:  a e^2 + b e v + c v^2, minimised at v = -(b e) / (2 c) */
+  const real be = b * e;
+  real v = -(be * rc);
+  v = v < lo ? lo : (v > hi ? hi : v);
+  return (a * e) * e + be * v + (c * v) * v;
+}
+static inline int orc_tile_alive(const orc_cull *c, real px, real py, int tx, int ty) {
+  const real dxl = px - RC(tx * ORC_TILE + ORC_TILE - 1), dxh = px - RC(tx * ORC_TILE);
+  const real dyl = py - RC(ty * ORC_TILE + ORC_TILE - 1), dyh = py - RC(ty * ORC_TILE);
+  real qmin = RC(0);
+  if (!(dxl <= RC(0) && dxh >= RC(0) && dyl <= RC(0) && dyh >= RC(0))) {
+    const real q1 = orc_edge_min(c->hA, c->B, c->hC, c->rC, dxl, dyl, dyh);
+    const real q2 = orc_edge_min(c->hA, c->B, c->hC, c->rC, dxh, dyl, dyh);
+    const real q3 = orc_edge_min(c->hC, c->B, c->hA, c->rA, dyl, dxl, dxh);
+    const real q4 = orc_edge_min(c->hC, c->B, c->hA, c->rA, dyh, dxl, dxh);
+    qmin = R_FMIN(R_FMIN(q1, q2), R_FMIN(q3, q4));
+  }
+  return !(qmin > c->thr); /* NaN => alive */
+}
+
 static inline int orc_grid_x(int W) { return (W + ORC_TILE - 1) / ORC_TILE; }
 static inline int orc_grid_y(int H) { return (H + ORC_TILE - 1) / ORC_TILE; }
 

@@ -97,9 +97,13 @@ void orc_sh_to_rgb_one(int deg, const real *pos, const real *campos, const real 
  * tensors are addressable without a copy.  colors_precomp / cov3D_precomp are the
  * PipelineParams::convert_SHs_python_/compute_cov3D_python_ branches (src/arguments/params.h:95-96).
  * Outputs: means2D (N,2), depths (N), cov3D (N,6), conic_opacity (N,4), rgb (N,3),
- * clamped (N,3) u8, radii (N) i32, tiles_touched (N) u32.  Culled Gaussians get radii = 0,
+ * clamped (N,3) u8, radii (N) i32, tiles_touched (N) u32 (tiles of the 3-sigma rectangle that
+ * survive the exact tile cull of orc_common.h).  Culled Gaussians get radii = 0,
  * tiles_touched = 0 and zeros elsewhere.
  */
+int orc_tile_cull_enabled = 1;
+void orc_set_tile_cull(int enabled) { orc_tile_cull_enabled = enabled; }
+
 void orc_preprocess(const orc_settings *st, int N, const real *means3D, const real *scales,
                     const real *rotations, const real *opacities, const real *sh_dc, int dc_stride,
                     const real *sh_rest, int rest_stride, const real *colors_precomp,
@@ -164,6 +168,14 @@ void orc_preprocess(const orc_settings *st, int N, const real *means3D, const re
     y1 = y1 < 0 ? 0 : (y1 > gy ? gy : y1);
     int area = (x1 - x0) * (y1 - y0);
     if (area <= 0) continue;
+    /* exact tile culling (orc_common.h): tiles_touched counts the tiles that can receive alpha >= 1/255 */
+    int alive = area;
+    if (orc_tile_cull_enabled && area <= ORC_CULL_MAX_TILES) {
+      const orc_cull cs = orc_cull_setup(RC(0.5) * con_x, con_y, RC(0.5) * con_z, opacities[i]);
+      alive = 0;
+      for (int ty = y0; ty < y1; ++ty)
+        for (int tx = x0; tx < x1; ++tx) alive += orc_tile_alive(&cs, px, py, tx, ty);
+    }
 
     if (colors_precomp) {
       for (int ch = 0; ch < 3; ++ch) rgb[3 * i + ch] = colors_precomp[3 * i + ch];
@@ -180,6 +192,6 @@ void orc_preprocess(const orc_settings *st, int N, const real *means3D, const re
     conic_opacity[4 * i + 1] = con_y;
     conic_opacity[4 * i + 2] = con_z;
     conic_opacity[4 * i + 3] = opacities[i];
-    tiles_touched[i] = (uint32_t)area;
+    tiles_touched[i] = (uint32_t)alive;
   }
 }
