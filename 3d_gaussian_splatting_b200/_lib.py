@@ -57,6 +57,7 @@ EXPORTS = (
     "gs_version", "gs_create", "gs_destroy", "gs_last_error", "gs_forward", "gs_backward",
     "gs_adam_densify_step", "gs_loss", "gs_debug_size", "gs_debug_get", "gs_set_profiling", "gs_get_stage_ms",
     "gs_focal2fov", "gs_get_world2view2", "gs_get_projection_matrix", "gs_camera_settings", "gs_expon_lr",
+    "gs_set_duplicate_capacity", "gs_set_overflow_mirror", "gs_overflow_guard", "gs_get_forward_status",
 )
 
 
@@ -82,7 +83,12 @@ def _load() -> C.CDLL:
     lib.gs_forward.argtypes = [vp, C.POINTER(GsSettings), i, C.POINTER(GsGaussians), vp, vp, vp]
     lib.gs_backward.argtypes = [vp, C.POINTER(GsSettings), i, C.POINTER(GsGaussians), vp, C.POINTER(GsGradients), vp]
     lib.gs_adam_densify_step.argtypes = [vp, i, vp * 6, vp * 6, vp * 6, vp * 6, i * 6, d * 6, C.c_longlong * 6,
-                                         d, d, d, vp, vp, vp, vp, vp, i, vp]
+                                         d, d, d, vp, vp, vp, vp, vp, i, vp, vp]
+    lib.gs_set_duplicate_capacity.argtypes = [vp, C.c_ulonglong]
+    lib.gs_set_overflow_mirror.argtypes = [vp, vp]
+    lib.gs_overflow_guard.argtypes = [vp]
+    lib.gs_overflow_guard.restype = vp
+    lib.gs_get_forward_status.argtypes = [vp, C.POINTER(C.c_ulonglong), C.POINTER(i)]
     lib.gs_loss.argtypes = [vp, i, i, vp, vp, f, vp, vp, vp]
     lib.gs_debug_size.argtypes = [vp, i]
     lib.gs_debug_size.restype = C.c_longlong

@@ -88,10 +88,13 @@ dup_block_sums_kernel(int N, const uint32_t* __restrict__ order, const uint4* __
 }
 
 // one block: exclusive scan of the block sums in place; the grand total D goes to *total (64-bit, so
-// a wrapped 32-bit scan is detectable) and to *total32 for the kernels that index with it
+// a wrapped 32-bit scan is detectable) and, clamped to the capacity of the pair buffers, to *total32 for
+// the kernels that index with it.  D > cap raises the overflow flag and the float guards (the step is
+// then invalid: the Adam kernel skips its update when it sees the guard, see optim.cu).
 __global__ void __launch_bounds__(1024)
 dup_scan_sums_kernel(int nb, uint32_t* __restrict__ block_sums, unsigned long long* __restrict__ total,
-                     uint32_t* __restrict__ total32) {
+                     uint32_t* __restrict__ total32, unsigned long long cap, uint32_t* __restrict__ overflow,
+                     float* __restrict__ guard, float* __restrict__ mirror) {
   __shared__ unsigned long long s_warp[32];
   const int per = (nb + 1023) / 1024;
   const int lo = min(nb, (int)threadIdx.x * per), hi = min(nb, lo + per);
@@ -120,7 +123,12 @@ dup_scan_sums_kernel(int nb, uint32_t* __restrict__ block_sums, unsigned long lo
   }
   if (threadIdx.x == 0) {
     *total = tot;
-    *total32 = tot > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)tot;
+    *total32 = (uint32_t)(tot > cap ? cap : tot);
+    if (tot > cap) {
+      *overflow = 1u;
+      *guard = 1.0f;
+      if (mirror) *mirror = 1.0f;
+    }
   }
 }
 
@@ -166,8 +174,7 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
   const uint32_t base = block_base[blockIdx.x];
   uint32_t limit = total;
   if ((unsigned long long)base + total > cap) {
-    limit = base < cap ? cap - base : 0u;
-    if (threadIdx.x == 0) *overflow = 1u;
+    limit = base < cap ? cap - base : 0u;  // (the scan kernel has raised the overflow flag)
   }
   for (uint32_t j = threadIdx.x; j < limit; j += DUP_THREADS) {
     // owner = last entry with s_off <= j (entries with zero tiles share an offset with their successor and are
@@ -190,11 +197,12 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
 int gs_dup_num_blocks(int N) { return (N + DUP_BLOCK - 1) / DUP_BLOCK; }
 
 cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint4* rects, uint32_t* block_sums,
-                               unsigned long long* total, uint32_t* total32, cudaStream_t stream) {
+                               unsigned long long* total, uint32_t* total32, unsigned long long cap,
+                               uint32_t* overflow, float* guard, float* mirror, cudaStream_t stream) {
   if (N == 0) return cudaMemsetAsync(total, 0, 8, stream);
   const int nb = gs_dup_num_blocks(N);
   dup_block_sums_kernel<<<nb, DUP_THREADS, 0, stream>>>(N, order, rects, block_sums);
-  dup_scan_sums_kernel<<<1, 1024, 0, stream>>>(nb, block_sums, total, total32);
+  dup_scan_sums_kernel<<<1, 1024, 0, stream>>>(nb, block_sums, total, total32, cap, overflow, guard, mirror);
   return cudaGetLastError();
 }
 

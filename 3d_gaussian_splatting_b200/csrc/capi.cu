@@ -18,7 +18,7 @@ cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uin
                                  cudaStream_t);
 int gs_dup_num_blocks(int N);
 cudaError_t gs_launch_dup_scan(int, const uint32_t*, const uint4*, uint32_t*, unsigned long long*, uint32_t*,
-                               cudaStream_t);
+                               unsigned long long, uint32_t*, float*, float*, cudaStream_t);
 cudaError_t gs_launch_duplicate(int, const uint32_t*, const uint4*, const uint32_t*, void*, int, uint32_t*, int,
                                 uint32_t, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_tile_sort(const uint32_t*, int, int, void*, void*, uint32_t*, uint32_t*, uint32_t*, int, int*,
@@ -35,7 +35,7 @@ cudaError_t gs_launch_preprocess_backward(const gs_settings&, const gs_gaussians
                                           const int*, const uint8_t*, const float4*, cudaStream_t);
 cudaError_t gs_launch_adam(int, float* const[6], float* const[6], float* const[6], float* const[6], const int[6],
                            const double[6], const long long[6], double, double, double, const int*, const float*, int*,
-                           float*, float*, int, cudaStream_t);
+                           float*, float*, int, const float*, cudaStream_t);
 cudaError_t gs_launch_l1_loss(size_t, const float*, const float*, float, float*, double*, float*, cudaStream_t);
 
 // ---- context ----------------------------------------------------------------------------------
@@ -63,7 +63,10 @@ struct gs_ctx {
   DevBuf ckpt, work_items, counters;
   int num_sms = 148;
   DevBuf loss_acc;
-  uint32_t* d_host_pinned = nullptr;  // D readback
+  uint32_t* d_host_pinned = nullptr;  // readback: bytes 0..7 D (u64), 8..11 overflow flag
+  uint64_t dup_cap_fixed = 0;         // > 0: caller-fixed pair capacity, no host synchronisation in gs_forward
+  float* overflow_mirror = nullptr;   // optional caller-owned device float raised to 1.0 on overflow
+  bool D_pending = false;             // D of the last forward not yet read back
   // state of the last forward
   int N = -1, H = 0, W = 0, ntiles = 0;
   uint64_t D = 0;
@@ -289,11 +292,14 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->tile_last, (size_t)d.ntiles * 4);
   GS_ENSURE(c, c->counters, 64);
   GS_ENSURE(c, c->n_contrib, P * 4);
-  // device counters: [0] backward work items, [1] backward cursor, bytes 8..15 D (u64), [4] D (u32), [5] overflow
+  // device counters: [0] backward work items, [1] backward cursor, bytes 8..15 D (u64), [4] D (u32, clamped to the
+  // capacity), [5] overflow flag, [6] overflow guard (float)
   uint32_t* cnt = (uint32_t*)c->counters.ptr;
   unsigned long long* D64_dev = (unsigned long long*)(cnt + 2);
   uint32_t* D_dev = cnt + 4;
   uint32_t* overflow_dev = cnt + 5;
+  float* guard_dev = (float*)(cnt + 6);  // 1.0f when this forward overflowed its pair capacity
+  c->D_pending = false;
   c->key_bytes = d.ntiles <= 65536 ? 2 : 4;
   int tile_bits = 1;
   while ((1u << tile_bits) < (uint32_t)d.ntiles) ++tile_bits;
@@ -316,15 +322,26 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
     }
     {
       StageTimer t(c, 2, stream);
+      const bool async_mode = c->dup_cap_fixed > 0;
+      const unsigned long long cap = async_mode ? c->dup_cap_fixed : 0xFFFFFFF0ull;
       GS_CUDA_CHECK(c, gs_launch_dup_scan(N, (const uint32_t*)c->sort_v1.ptr, (const uint4*)c->rects.ptr,
-                                          (uint32_t*)c->dup_sums.ptr, D64_dev, D_dev, stream));
-      // the one host synchronisation of the forward: number of (Gaussian, tile) duplicates, to size the lists
+                                          (uint32_t*)c->dup_sums.ptr, D64_dev, D_dev, cap, overflow_dev, guard_dev,
+                                          c->overflow_mirror, stream));
       GS_CUDA_CHECK(c, cudaMemcpyAsync(c->d_host_pinned, D64_dev, 8, cudaMemcpyDeviceToHost, stream));
-      GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
-      D = *(const unsigned long long*)c->d_host_pinned;
-      if (D > 0xFFFFFFF0ull) {
-        gs_set_error(c, "duplicate list too long for 32-bit indices (%llu pairs)", (unsigned long long)D);
-        return GS_EOVERFLOW;
+      GS_CUDA_CHECK(c, cudaMemcpyAsync(c->d_host_pinned + 2, overflow_dev, 4, cudaMemcpyDeviceToHost, stream));
+      if (async_mode) {
+        // caller-fixed capacity: nothing to wait for; an overflow poisons the step (guard) and is reported by
+        // gs_get_forward_status once the caller has synchronised
+        D = cap;
+        c->D_pending = true;
+      } else {
+        // the one host synchronisation of the forward: number of (Gaussian, tile) duplicates, to size the lists
+        GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
+        D = *(const unsigned long long*)c->d_host_pinned;
+        if (D > 0xFFFFFFF0ull) {
+          gs_set_error(c, "duplicate list too long for 32-bit indices (%llu pairs)", (unsigned long long)D);
+          return GS_EOVERFLOW;
+        }
       }
       const size_t Dn = (size_t)(D > 0 ? D : 1);
       GS_ENSURE(c, c->keys_a, Dn * c->key_bytes);
@@ -348,6 +365,8 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   } else {
     GS_ENSURE(c, c->keys_a, 8);
     GS_ENSURE(c, c->vals_a, 4);
+    *(unsigned long long*)c->d_host_pinned = 0ull;
+    c->d_host_pinned[2] = 0u;
     c->sorted_tiles = c->keys_a.ptr;
     c->point_list = (const uint32_t*)c->vals_a.ptr;
   }
@@ -429,7 +448,8 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
 int gs_adam_densify_step(gs_ctx* c, int N, float* const params[6], float* const grads[6], float* const exp_avg[6],
                          float* const exp_avg_sq[6], const int widths[6], const double lr[6], const long long step[6],
                          double beta1, double beta2, double eps, const int* radii, const float* dL_dmeans2D,
-                         int* max_radii2D, float* xyz_grad_accum, float* denom, int zero_grads, void* stream_) {
+                         int* max_radii2D, float* xyz_grad_accum, float* denom, int zero_grads,
+                         const float* skip_guard, void* stream_) {
   if (!c || N < 0 || !params || !grads || !exp_avg || !exp_avg_sq || !widths || !lr || !step) {
     gs_set_error(c, "gs_adam_densify_step: null argument");
     return GS_EINVAL;
@@ -446,8 +466,44 @@ int gs_adam_densify_step(gs_ctx* c, int N, float* const params[6], float* const 
   }
   GS_CUDA_CHECK(c, cudaSetDevice(c->device));
   GS_CUDA_CHECK(c, gs_launch_adam(N, params, grads, exp_avg, exp_avg_sq, widths, lr, step, beta1, beta2, eps, radii,
-                                  dL_dmeans2D, max_radii2D, xyz_grad_accum, denom, zero_grads,
+                                  dL_dmeans2D, max_radii2D, xyz_grad_accum, denom, zero_grads, skip_guard,
                                   (cudaStream_t)stream_));
+  return GS_OK;
+}
+
+int gs_set_duplicate_capacity(gs_ctx* c, unsigned long long pairs) {
+  if (!c) return GS_EINVAL;
+  if (pairs > 0xFFFFFFF0ull) {
+    gs_set_error(c, "capacity of %llu pairs exceeds 32-bit indexing", pairs);
+    return GS_EINVAL;
+  }
+  c->dup_cap_fixed = pairs;
+  return GS_OK;
+}
+
+int gs_set_overflow_mirror(gs_ctx* c, float* device_float) {
+  if (!c) return GS_EINVAL;
+  c->overflow_mirror = device_float;
+  return GS_OK;
+}
+
+const float* gs_overflow_guard(gs_ctx* c) {
+  if (!c) return nullptr;
+  cudaSetDevice(c->device);
+  if (ensure(c, c->counters, 64) != GS_OK) return nullptr;
+  return (const float*)((uint32_t*)c->counters.ptr + 6);
+}
+
+int gs_get_forward_status(gs_ctx* c, unsigned long long* num_duplicates, int* overflow) {
+  if (!c) return GS_EINVAL;
+  if (!c->have_forward) {
+    gs_set_error(c, "gs_get_forward_status: no forward has run on this context");
+    return GS_ESTATE;
+  }
+  // the values were copied to pinned memory on the forward's stream: the caller has synchronised it
+  const unsigned long long D = *(const unsigned long long*)c->d_host_pinned;
+  if (num_duplicates) *num_duplicates = D;
+  if (overflow) *overflow = c->N > 0 ? (int)c->d_host_pinned[2] : 0;
   return GS_OK;
 }
 
@@ -471,6 +527,13 @@ int gs_loss(gs_ctx* c, int H, int W, const float* image, const float* gt, float 
 // ---- parity harness ---------------------------------------------------------------------------
 static long long dbg_size(gs_ctx* c, int what) {
   if (!c->have_forward) return GS_ESTATE;
+  if (c->D_pending) {  // capacity mode: the forward did not wait for D
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    const unsigned long long D = *(const unsigned long long*)c->d_host_pinned;
+    c->D = D < c->dup_cap_fixed ? D : c->dup_cap_fixed;
+    c->D_pending = false;
+  }
   const long long N = c->N, D = (long long)c->D, T = c->ntiles, P = (long long)c->H * c->W;
   switch (what) {
     case GS_DBG_MEANS2D: return N * 8;

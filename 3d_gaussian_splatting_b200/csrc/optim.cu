@@ -31,6 +31,7 @@ struct AdamArgs {
   int stats_block_start, total_blocks;
   float b1, b2, omb1, omb2, eps;
   int zero_grads;
+  const float* skip_guard;  // device float; non-zero => the step is invalid (pair-capacity overflow), do nothing
   int N;
   const int* radii;
   const float* dL_dmeans2D;
@@ -50,6 +51,7 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
 }
 
 __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_constant__ AdamArgs a) {
+  if (a.skip_guard && __ldg(a.skip_guard) != 0.0f) return;
   const int b = blockIdx.x;
   if (b >= a.stats_block_start) {
     // ---- densification statistics, one thread per Gaussian ----
@@ -115,7 +117,7 @@ cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6],
                            float* const exp_avg_sq[6], const int widths[6], const double lr[6],
                            const long long step[6], double beta1, double beta2, double eps, const int* radii,
                            const float* dL_dmeans2D, int* max_radii2D, float* xyz_grad_accum, float* denom,
-                           int zero_grads, cudaStream_t stream) {
+                           int zero_grads, const float* skip_guard, cudaStream_t stream) {
   AdamArgs a;
   int blocks = 0;
   for (int s = 0; s < 6; ++s) {
@@ -144,6 +146,7 @@ cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6],
   a.omb2 = (float)(1.0 - beta2);
   a.eps = (float)eps;
   a.zero_grads = zero_grads;
+  a.skip_guard = skip_guard;
   a.N = N;
   a.radii = radii;
   a.dL_dmeans2D = dL_dmeans2D;

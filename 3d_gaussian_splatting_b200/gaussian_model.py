@@ -133,8 +133,12 @@ def render(viewpoint_camera, pc: GaussianModel, pipe: PipelineParams, bg_color, 
     dict(render=(3,H,W), radii=(N) int32, visibility_filter=radii>0).
     fused_activations=True feeds the RAW parameters (activations fused in the kernels);
     False reproduces the getter chain of the reference (exp / normalise / sigmoid / cat)."""
-    st = GaussianRasterizationSettings.from_camera(viewpoint_camera, bg_color, pc.active_sh_degree, pc.max_sh_degree,
-                                                   scaling_modifier, pipe.debug)
+    key = (tuple(bg_color), pc.active_sh_degree, pc.max_sh_degree, scaling_modifier, pipe.debug)
+    cache = viewpoint_camera.__dict__.setdefault("_raster_settings", {})
+    st = cache.get(key)
+    if st is None:   # raster settings of a camera are fixed (src/scene/camera.cpp:56-71): build them once
+        st = cache[key] = GaussianRasterizationSettings.from_camera(
+            viewpoint_camera, bg_color, pc.active_sh_degree, pc.max_sh_degree, scaling_modifier, pipe.debug)
     if fused_activations:
         color, radii = rast.forward(st, pc.xyz_, pc.scaling_, pc.rotation_, pc.opacity_, sh_dc=pc.features_dc_,
                                     sh_rest=pc.features_rest_, raw_params=True)
@@ -160,11 +164,52 @@ class Trainer:
         self.iteration = 0
         self._gt_dev = None
         self._loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+        # capacity mode (no host round-trip inside the forward): enabled by reserve_pairs()
+        self.pair_capacity = 0
+        self.grad_sync = None           # multi-GPU: callable run between backward and the optimiser step (all-reduce)
+        self._copy_stream = None
+        self._gt_ready = None
+        self._guard_tensor = None
+        self.skip_guard = None          # device float the Adam step honours (all-reduced slab tail when multi-GPU)
+        self.retries = 0
 
-    def forward_backward(self, cam, gt_dev: torch.Tensor, accumulate: bool = False):
-        """render + loss + backward for one view with the gradients left in the model's sinks."""
+    def reserve_pairs(self, pairs: int, guard: torch.Tensor | None = None):
+        """Fix the (tile, Gaussian) pair capacity so that forwards run without synchronising the host.  An
+        iteration whose forward overflows is skipped on the device (Adam guard) and repeated by train_step
+        with twice the capacity.  guard: caller-owned device float raised on overflow (the gradient slab's
+        guard element when the gradients are all-reduced); default: the context's own flag."""
+        self.pair_capacity = int(pairs)
+        self.rast.set_duplicate_capacity(self.pair_capacity)
+        self._guard_tensor = guard
+        if guard is not None:
+            self.rast.set_overflow_mirror(guard)
+            self.skip_guard = guard.data_ptr()
+        else:
+            self.skip_guard = self.rast.overflow_guard_ptr()
+
+    def forward_backward(self, cam, gt_dev: torch.Tensor, accumulate: bool = False, gt_host=None):
+        """render + loss + backward for one view with the gradients left in the model's sinks.
+        gt_host: pinned host image to copy into gt_dev first.  The image is not needed before the loss, so the
+        copy is issued on a side stream AFTER the render has been enqueued and runs underneath it; the compute
+        stream only waits for it in front of the loss kernel."""
+        if self._guard_tensor is not None and not accumulate:
+            self._guard_tensor.zero_()   # caller-owned guard: lowered at the start of every iteration
         out = render(cam, self.g, self.pipe, self.bg, self.rast)
+        if gt_host is not None:
+            main = torch.cuda.current_stream(self.g.device)
+            if self._copy_stream is None:
+                self._copy_stream = torch.cuda.Stream(device=self.g.device)
+                self._gt_ready = torch.cuda.Event()
+                self._gt_free = torch.cuda.Event()
+                self._gt_free.record(main)
+            self._copy_stream.wait_event(self._gt_free)   # the previous iteration's loss kernel has read gt_dev
+            with torch.cuda.stream(self._copy_stream):
+                gt_dev.copy_(gt_host, non_blocking=True)
+                self._gt_ready.record(self._copy_stream)
+            main.wait_event(self._gt_ready)
         loss, dL = self.rast.loss(out["render"], gt_dev, self.lambda_dssim)
+        if gt_host is not None:
+            self._gt_free.record(torch.cuda.current_stream(self.g.device))
         self.rast.backward(dL, grads=self.g.grad_sinks(), accumulate=accumulate)
         return loss, out
 
@@ -173,24 +218,44 @@ class Trainer:
         g.step_count = [s + 1 for s in g.step_count]
         self.rast.adam_densify_step(g.N, g.params(), g.grads, g.exp_avg, g.exp_avg_sq, g.widths, g.lr, g.step_count,
                                     radii=radii, dL_dmeans2D=g.grad_means2D, max_radii2D=g.max_radii2D_,
-                                    xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_)
+                                    xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_,
+                                    skip_guard=self.skip_guard if self.pair_capacity else None)
 
-    def train_step_device(self, cam, gt_dev: torch.Tensor):
+    def check_overflow(self) -> bool:
+        """After the step's stream synchronisation: did the last forward overflow the fixed capacity?  If so the
+        device skipped the optimiser step; roll the host-side counters back and double the capacity."""
+        if not self.pair_capacity:
+            return False
+        D, overflow = self.rast.forward_status()
+        if overflow:
+            self.g.step_count = [s - 1 for s in self.g.step_count]
+            self.iteration -= 1
+            self.retries += 1
+            self.pair_capacity = max(2 * self.pair_capacity, int(1.25 * D))
+            self.rast.set_duplicate_capacity(self.pair_capacity)
+        return overflow
+
+    def train_step_device(self, cam, gt_dev: torch.Tensor, gt_host=None):
         """Device-resident step: ground truth already in HBM; returns the loss as a device tensor."""
         self.iteration += 1
         self.g.update_learning_rate(self.iteration)
         if self.iteration % 1000 == 0:
             self.g.oneup_SH_degree()
-        loss, out = self.forward_backward(cam, gt_dev)
+        loss, out = self.forward_backward(cam, gt_dev, gt_host=gt_host)
+        if self.grad_sync is not None:
+            self.grad_sync()
         self.optimizer_step(out["radii"])
         return loss
 
     def train_step(self, cam, gt_host: torch.Tensor) -> float:
-        """End-to-end step with HOST buffers: pinned ground-truth image H2D, loss D2H."""
+        """End-to-end step with HOST buffers: pinned ground-truth image H2D (overlapped with the render, see
+        forward_backward), loss D2H."""
+        dev = self.g.device
         if self._gt_dev is None or self._gt_dev.shape != gt_host.shape:
-            self._gt_dev = torch.empty(gt_host.shape, dtype=torch.float32, device=self.g.device)
-        self._gt_dev.copy_(gt_host, non_blocking=True)
-        loss = self.train_step_device(cam, self._gt_dev)
-        self._loss_host.copy_(loss, non_blocking=True)
-        torch.cuda.current_stream(self.g.device).synchronize()
-        return float(self._loss_host[0])
+            self._gt_dev = torch.empty(gt_host.shape, dtype=torch.float32, device=dev)
+        while True:
+            loss = self.train_step_device(cam, self._gt_dev, gt_host=gt_host)
+            self._loss_host.copy_(loss, non_blocking=True)
+            torch.cuda.current_stream(self.g.device).synchronize()
+            if not self.check_overflow():   # capacity mode only: an overflowed iteration was skipped on the device
+                return float(self._loss_host[0])

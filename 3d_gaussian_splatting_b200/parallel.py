@@ -32,7 +32,12 @@ class GradientSlab:
             self.offsets.append(off)
             off += (s + 3) // 4 * 4
         dev = params[0].device if len(params) else "cpu"
+        # 4 trailing floats; [0] is the step guard: a rank whose forward overflowed its fixed pair capacity raises it
+        # to 1, the all-reduce spreads it, and the fused Adam step of EVERY rank then skips the iteration
+        self.guard_offset = off
+        off += 4
         self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.guard = self.flat[self.guard_offset:self.guard_offset + 1]
         self.views = [self.flat[o:o + s].view_as(p) for o, s, p in zip(self.offsets, self.sizes, params)]
 
     def zero_(self):

@@ -37,6 +37,9 @@ class GaussianRasterizationSettings:
     debug: bool = False         # PipelineParams::debug_ (src/arguments/params.h:97)
 
     def to_c(self) -> GsSettings:
+        cached = self.__dict__.get("_c")
+        if cached is not None:      # settings objects are immutable in practice; the ctypes struct is built once
+            return cached
         st = GsSettings()
         st.H, st.W = int(self.image_height), int(self.image_width)
         st.tanfovx, st.tanfovy = float(self.tanfovx), float(self.tanfovy)
@@ -52,6 +55,7 @@ class GaussianRasterizationSettings:
         st.scale_modifier = float(self.scale_modifier)
         st.sh_degree, st.max_sh_degree = int(self.sh_degree), int(self.max_sh_degree)
         st.prefiltered, st.debug = int(self.prefiltered), int(self.debug)
+        self.__dict__["_c"] = st
         return st
 
     @staticmethod
@@ -205,12 +209,34 @@ class Rasterizer:
                                          C.c_void_p(stream)))
         return grads
 
+    # ---- running without the host round-trip ---------------------------------------------------
+    def set_duplicate_capacity(self, pairs: int):
+        """pairs > 0: fixed (tile, Gaussian) pair capacity, gs_forward never waits for the host; 0: synchronous."""
+        check(self._ctx, lib.gs_set_duplicate_capacity(self._ctx, int(pairs)))
+
+    def set_overflow_mirror(self, t: Optional[torch.Tensor]):
+        """A caller-owned device float (e.g. the tail element of the all-reduced gradient slab) that the forward
+        raises to 1.0 when it overflows the fixed capacity."""
+        check(self._ctx, lib.gs_set_overflow_mirror(self._ctx, None if t is None else C.c_void_p(t.data_ptr())))
+
+    def overflow_guard_ptr(self) -> int:
+        return int(lib.gs_overflow_guard(self._ctx) or 0)
+
+    def forward_status(self):
+        """(D, overflow) of the last forward; the caller must have synchronised the stream it ran on."""
+        D, ov = C.c_ulonglong(0), C.c_int(0)
+        check(self._ctx, lib.gs_get_forward_status(self._ctx, C.byref(D), C.byref(ov)))
+        return int(D.value), bool(ov.value)
+
     # ---- optimiser / loss ---------------------------------------------------------------------
     def adam_densify_step(self, N, params, grads, exp_avg, exp_avg_sq, widths, lr, step, beta1=0.9, beta2=0.999,
                           eps=1e-8, radii=None, dL_dmeans2D=None, max_radii2D=None, xyz_grad_accum=None,
-                          denom=None, zero_grads=False):
+                          denom=None, zero_grads=False, skip_guard=None):
         """Fused Adam over the six parameter groups of GaussianModel::setup
-        (src/scene/gaussian_model.cpp:323-345) + densification statistics."""
+        (src/scene/gaussian_model.cpp:323-345) + densification statistics.  skip_guard: device float
+        (tensor or raw pointer); non-zero at execution time turns the call into a no-op."""
+        if isinstance(skip_guard, torch.Tensor):
+            skip_guard = skip_guard.data_ptr()
         VP6 = C.c_void_p * 6
         arr = lambda ts: VP6(*[None if t is None else t.data_ptr() for t in ts])
         stream = torch.cuda.current_stream(self.device).cuda_stream
@@ -218,7 +244,7 @@ class Rasterizer:
             self._ctx, int(N), arr(params), arr(grads), arr(exp_avg), arr(exp_avg_sq), (C.c_int * 6)(*widths),
             (C.c_double * 6)(*[float(x) for x in lr]), (C.c_longlong * 6)(*[int(s) for s in step]), float(beta1),
             float(beta2), float(eps), _ptr(radii), _ptr(dL_dmeans2D), _ptr(max_radii2D), _ptr(xyz_grad_accum),
-            _ptr(denom), int(zero_grads), C.c_void_p(stream)))
+            _ptr(denom), int(zero_grads), C.c_void_p(skip_guard) if skip_guard else None, C.c_void_p(stream)))
 
     def loss(self, image, gt, lambda_dssim=0.0, want_grad=True):
         """(1-lambda)*L1 + lambda*(1-SSIM); returns (loss 1-element device tensor, dL/dimage)."""

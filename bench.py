@@ -254,37 +254,27 @@ def run_ours(args, rank, world, local_rank):
     gt_model = gm.GaussianModel(deg, local_rank).load_scene(scene)
     gt_model.features_dc_ += torch.from_numpy((0.05 * rng.standard_normal(scene.features_dc.shape)).astype(np.float32)).to(dev)
     gts_dev, gts_host = [], []
+    max_pairs = 0
     for cam in my_cams:
         out = gm.render(cam, gt_model, gm.PipelineParams(), (0.0, 0.0, 0.0), trainer.rast)
         gts_dev.append(out["render"].clone())
         gts_host.append(out["render"].cpu().pin_memory())
+        max_pairs = max(max_pairs, trainer.rast.forward_status()[0])   # (synchronised by the .cpu() above)
     del gt_model
     torch.cuda.synchronize()
+    # fixed (tile, Gaussian) pair capacity: the forward then never waits for the host (include/gsplat_b200.h);
+    # an overflowing iteration would be skipped on the device and is reported below
+    trainer.reserve_pairs(int(1.3 * max_pairs) + 1024, guard=gslab.guard if world > 1 else None)
+
+    if world > 1:
+        trainer.grad_sync = gslab.all_reduce     # ONE NCCL all-reduce of the gradient slab per iteration
 
     def step_device(i):
-        cam, gt = my_cams[i % args.views], gts_dev[i % args.views]
-        trainer.iteration += 1
-        g.update_learning_rate(trainer.iteration)
-        loss, out = trainer.forward_backward(cam, gt)
-        if world > 1:
-            gslab.all_reduce()
-        trainer.optimizer_step(out["radii"])
-        return loss
+        return trainer.train_step_device(my_cams[i % args.views], gts_dev[i % args.views])
 
     def step_e2e(i):
-        cam = my_cams[i % args.views]
-        if trainer._gt_dev is None:
-            trainer._gt_dev = torch.empty_like(gts_dev[0])
-        trainer._gt_dev.copy_(gts_host[i % args.views], non_blocking=True)
-        trainer.iteration += 1
-        g.update_learning_rate(trainer.iteration)
-        loss, out = trainer.forward_backward(cam, trainer._gt_dev)
-        if world > 1:
-            gslab.all_reduce()
-        trainer.optimizer_step(out["radii"])
-        trainer._loss_host.copy_(loss, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return float(trainer._loss_host[0])
+        # the public call: pinned host image in, loss (python float) out
+        return trainer.train_step(my_cams[i % args.views], gts_host[i % args.views])
 
     def timed(fn, steps, warmup, sampler=None):
         for i in range(warmup):
@@ -313,6 +303,7 @@ def run_ours(args, rank, world, local_rank):
     warm = max(args.warmup, 3)
     sampler = ClockSampler(local_rank) if rank == 0 else None
     total_ms, clocks = timed(step_device, args.steps, warm, sampler)
+    assert not trainer.rast.forward_status()[1], "pair capacity overflow inside the timed region"
     ms_per_step = total_ms / args.steps
     value = world * 1.0 / (ms_per_step * 1e-3)
     e2e_ms, _ = timed(step_e2e, args.steps, warm)
@@ -389,6 +380,7 @@ def run_ours(args, rank, world, local_rank):
             "cpu_baseline": cpu_baseline,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                     "h2d_bytes_per_step": int(gts_host[0].numel() * 4 + 172), "d2h_bytes_per_step": 4},
+            "pair_capacity": trainer.pair_capacity, "capacity_retries": trainer.retries,
             "gpu_launches": OWN_KERNELS_PER_STEP * args.steps,
             "library_launches": LIB_KERNELS_PER_STEP * args.steps,
             "clocks": clocks,

@@ -142,12 +142,32 @@ GS_API int gs_backward(gs_ctx *ctx, const gs_settings *settings, int N, const gs
  * Statistics on Gaussians with radii > 0 (fields at src/scene/gaussian_model.h:18-20):
  *   max_radii2D = max(max_radii2D, radii); xyz_grad_accum += |dL_dmeans2D.xy|; denom += 1.
  * radii / dL_dmeans2D / the three stat buffers may be NULL to skip the statistics.
- * zero_grads != 0 re-zeroes the gradient buffers in the same pass. */
+ * zero_grads != 0 re-zeroes the gradient buffers in the same pass.
+ * skip_guard (nullable): device float; when it is non-zero at execution time the whole call is a
+ * no-op (parameters, moments, statistics and gradients untouched).  Pass gs_overflow_guard(ctx) --
+ * or, with several GPUs, the all-reduced copy of it -- so that a forward that overflowed its fixed
+ * pair capacity (gs_set_duplicate_capacity) cannot corrupt the model; the caller then grows the
+ * capacity and repeats the iteration. */
 GS_API int gs_adam_densify_step(gs_ctx *ctx, int N, float *const params[6], float *const grads[6],
                                 float *const exp_avg[6], float *const exp_avg_sq[6], const int widths[6],
                                 const double lr[6], const long long step[6], double beta1, double beta2,
                                 double eps, const int *radii, const float *dL_dmeans2D, int *max_radii2D,
-                                float *xyz_grad_accum, float *denom, int zero_grads, void *stream);
+                                float *xyz_grad_accum, float *denom, int zero_grads, const float *skip_guard,
+                                void *stream);
+
+/* ---- running without the host round-trip ----------------------------------------------------
+ * By default gs_forward synchronises the stream once, to size the (tile, Gaussian) pair lists from
+ * the data-dependent pair count D.  gs_set_duplicate_capacity(ctx, pairs > 0) fixes the capacity
+ * instead: gs_forward then enqueues everything without waiting (the kernels read D from device
+ * memory).  If D exceeds the capacity the lists are truncated, the forward's outputs are invalid,
+ * and the overflow is signalled (a) on the device through the float at gs_overflow_guard(ctx) (and
+ * the optional caller-owned mirror, e.g. one element of an all-reduced gradient slab) which
+ * gs_adam_densify_step honours, and (b) on the host through gs_get_forward_status once the caller
+ * has synchronised the stream.  pairs == 0 restores the synchronous behaviour. */
+GS_API int gs_set_duplicate_capacity(gs_ctx *ctx, unsigned long long pairs);
+GS_API int gs_set_overflow_mirror(gs_ctx *ctx, float *device_float);
+GS_API const float *gs_overflow_guard(gs_ctx *ctx);
+GS_API int gs_get_forward_status(gs_ctx *ctx, unsigned long long *num_duplicates, int *overflow);
 
 /* ---- photometric loss ----------------------------------------------------------------------
  * loss = (1 - lambda_dssim) * L1 + lambda_dssim * (1 - SSIM)   (lambda_dssim_ = 0.2 at
