@@ -33,6 +33,7 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
   __shared__ float4 s_q1[GS_SEG];
   __shared__ float s_b[GS_SEG];
   __shared__ uint32_t s_id[GS_SEG];
+  __shared__ uint32_t s_bits[BB_THREADS / 32][GS_SEG / 32];  // [pixel warp][32-entry word]: entries alive for it
   __shared__ uint32_t s_work;
 
   const int tid = threadIdx.x, lane = tid & 31;
@@ -57,16 +58,36 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
     const int x0 = tx * GS_TILE + qx, y0 = ty * GS_TILE + qy;
 
     // gather the segment's records (coalesced ids, L2-resident 48-B records)
+    // the loading thread also decides which of the two pixel warps (16x8 pixel boxes) its entry can reach with
+    // alpha >= 1/255 (gs_box_alive, the conservative test of the exact tile cull): a warp then walks only those
 #pragma unroll
     for (int u = 0; u < BB_PER_THREAD; ++u) {
       const int j = tid + u * BB_THREADS;
+      uint32_t alive = 0;
       if (j < n) {
         const uint32_t id = __ldg(point_list + range.x + (uint32_t)(k0 + j));
         const float4* gp = reinterpret_cast<const float4*>(geom + id);
+        const float4 q0 = __ldg(gp), q1 = __ldg(gp + 1), q2 = __ldg(gp + 2);
         s_id[j] = id;
-        s_q0[j] = __ldg(gp);
-        s_q1[j] = __ldg(gp + 1);
-        s_b[j] = __ldg(reinterpret_cast<const float*>(gp + 2));
+        s_q0[j] = q0;
+        s_q1[j] = q1;
+        s_b[j] = q2.x;
+        GsCull c;
+        c.hA = q0.z;
+        c.B = q0.w;
+        c.hC = q1.x;
+        c.rA = __frcp_rn(2.0f * q0.z);
+        c.rC = __frcp_rn(2.0f * q1.x);
+        c.thr = q2.z;
+        const float bx = (float)(tx * GS_TILE), by = (float)(ty * GS_TILE);
+#pragma unroll
+        for (int w = 0; w < BB_THREADS / 32; ++w)
+          if (gs_box_alive(c, q0.x, q0.y, bx, bx + 15.0f, by + (float)(8 * w), by + (float)(8 * w + 7))) alive |= 1u << w;
+      }
+#pragma unroll
+      for (int w = 0; w < BB_THREADS / 32; ++w) {
+        const uint32_t word = __ballot_sync(0xffffffffu, (alive >> w) & 1u);
+        if (lane == 0) s_bits[w][u * (BB_THREADS / 32) + (tid >> 5)] = word;
       }
     }
     // per-pixel state
@@ -105,7 +126,12 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
     __syncthreads();
     const int jend = min(n, warp_last - k0);  // this warp only needs entries k < warp_last
 
-    for (int j = 0; j < jend; ++j) {
+    for (int wd = 0; wd < GS_SEG / 32; ++wd) {
+     uint32_t word = s_bits[tid >> 5][wd];
+     if ((wd << 5) + 32 > jend) word &= (wd << 5) < jend ? (0xFFFFFFFFu >> (32 - (jend - (wd << 5)))) : 0u;
+     while (word) {
+      const int j = (wd << 5) + __ffs(word) - 1;
+      word &= word - 1;
       const int k = k0 + j;
       const float4 q0 = s_q0[j];
       const float4 q1 = s_q1[j];
@@ -190,6 +216,7 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
       float* dst = grad_geom + 12 * (size_t)s_id[j];
       const bool ninth = lane == 1;
       if ((lane & 3) == 0 || ninth) atomicAdd(dst + (ninth ? 8 : idx), ninth ? v8 : w1);
+     }
     }
   }
 }

@@ -7,6 +7,9 @@
 // into shared memory and broadcast-read; entries are evaluated four at a time (power/alpha of four
 // entries are independent, only the short transmittance chain is sequential) so one warp keeps
 // several FMA/MUFU operations in flight.  The block stops once every pixel has terminated.
+// Warp-level culling: while staging, every loading thread tests its entry against the eight 8x4 pixel boxes
+// of the tile (the conservative alpha-reach test of the exact tile cull, gs_common.cuh) and the block
+// publishes one bit list per pixel warp; a warp then walks only the entries that can touch its box.
 //
 // For the segmented backward (blend_bwd.cu) the kernel also leaves, per tile:
 //   * a checkpoint (T, C.rgb) of every live pixel at each GS_SEG-entry boundary of the tile list,
@@ -26,6 +29,7 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
   __shared__ float4 s_q0[BF_THREADS];
   __shared__ float4 s_q1[BF_THREADS];
   __shared__ float s_b[BF_THREADS];
+  __shared__ uint32_t s_bits[BF_THREADS / 32][BF_THREADS / 32];  // [pixel warp][32-entry word]: entries alive for it
   __shared__ uint32_t s_wlast[BF_THREADS / 32];
 
   const int tile = (int)tile_order[blockIdx.x];
@@ -47,44 +51,80 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
   for (int lo = 0; lo < total; lo += BF_THREADS) {
     if (__syncthreads_and(done)) break;
     const int n = min(BF_THREADS, total - lo);
+    // ---- stage 256 entries; the loading thread also decides, for each of the 8 pixel warps (8x4 pixel
+    //      boxes), whether its entry can reach alpha >= 1/255 anywhere in that box (gs_box_alive: the same
+    //      conservative test as the tile cull, so skipping a dead (warp, entry) pair never changes a pixel) ----
+    uint32_t alive8 = 0;
     if (tid < n) {
       const uint32_t id = __ldg(point_list + range.x + lo + tid);
       const float4* gp = reinterpret_cast<const float4*>(geom + id);
-      s_q0[tid] = __ldg(gp);
-      s_q1[tid] = __ldg(gp + 1);
-      s_b[tid] = __ldg(reinterpret_cast<const float*>(gp + 2));
+      const float4 q0 = __ldg(gp), q1 = __ldg(gp + 1), q2 = __ldg(gp + 2);
+      s_q0[tid] = q0;
+      s_q1[tid] = q1;
+      s_b[tid] = q2.x;
+      GsCull c;
+      c.hA = q0.z;
+      c.B = q0.w;
+      c.hC = q1.x;
+      c.rA = __frcp_rn(2.0f * q0.z);
+      c.rC = __frcp_rn(2.0f * q1.x);
+      c.thr = q2.z;
+      const float x0 = (float)(tx * GS_TILE), y0 = (float)(ty * GS_TILE);
+#pragma unroll
+      for (int w = 0; w < BF_THREADS / 32; ++w) {
+        const float bx = x0 + (float)((w & 1) * 8), by = y0 + (float)((w >> 1) * 4);
+        if (gs_box_alive(c, q0.x, q0.y, bx, bx + 7.0f, by, by + 3.0f)) alive8 |= 1u << w;
+      }
+    }
+#pragma unroll
+    for (int w = 0; w < BF_THREADS / 32; ++w) {
+      const uint32_t word = __ballot_sync(0xffffffffu, (alive8 >> w) & 1u);
+      if (lane == 0) s_bits[w][warp] = word;
     }
     __syncthreads();
-    for (int j0 = 0; j0 < n && !done; j0 += 4) {
-      // segment boundary: checkpoint the state in front of entry lo + j0
-      if (((lo + j0) & (GS_SEG - 1)) == 0 && (lo + j0) > 0)
-        my_ckpt[(size_t)((lo + j0) >> GS_SEG_SHIFT) * GS_TILE_PIX] = make_float4(T, C0, C1, C2);
-      float alpha[4];
+    // ---- this warp walks only its alive entries, in list order, 32-entry word by word ----
+    const int nwords = (n + 31) >> 5;
+    for (int wd = 0; wd < nwords && !__all_sync(0xffffffffu, done); ++wd) {
+      // segment boundary: checkpoint the state in front of entry lo + 32*wd
+      const int pos = lo + (wd << 5);
+      if ((pos & (GS_SEG - 1)) == 0 && pos > 0 && !done)
+        my_ckpt[(size_t)(pos >> GS_SEG_SHIFT) * GS_TILE_PIX] = make_float4(T, C0, C1, C2);
+      uint32_t word = s_bits[warp][wd];
+      while (word) {
+        // up to four alive entries at a time: their power / alpha are independent, only T is sequential
+        int jj[4];
+        float alpha[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int j = min(j0 + u, n - 1);
-        const float4 q0 = s_q0[j];
-        const float hC = s_q1[j].x, op = s_q1[j].y;
-        const float dx = q0.x - pixx, dy = q0.y - pixy;
-        const float power = gs_power(q0.z, q0.w, hC, dx, dy);
-        float G;
-        const float a = gs_alpha(op, power, G);
-        alpha[u] = (j0 + u < n && !(power > 0.0f) && !(a < GS_ALPHA_MIN)) ? a : 0.0f;
-      }
+        for (int u = 0; u < 4; ++u) {
+          jj[u] = word ? (wd << 5) + __ffs(word) - 1 : -1;
+          word &= word - 1;
+        }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        if (alpha[u] != 0.0f && !done) {
-          const float test_T = T * (1.0f - alpha[u]);
-          if (test_T < GS_T_MIN) {
-            done = true;
-          } else {
-            const int j = j0 + u;
-            const float w = alpha[u] * T;
-            C0 = fmaf(s_q1[j].z, w, C0);
-            C1 = fmaf(s_q1[j].w, w, C1);
-            C2 = fmaf(s_b[j], w, C2);
-            T = test_T;
-            last_contributor = (uint32_t)(lo + j + 1);
+        for (int u = 0; u < 4; ++u) {
+          const int j = max(jj[u], 0);
+          const float4 q0 = s_q0[j];
+          const float hC = s_q1[j].x, op = s_q1[j].y;
+          const float dx = q0.x - pixx, dy = q0.y - pixy;
+          const float power = gs_power(q0.z, q0.w, hC, dx, dy);
+          float G;
+          const float a = gs_alpha(op, power, G);
+          alpha[u] = (jj[u] >= 0 && !(power > 0.0f) && !(a < GS_ALPHA_MIN)) ? a : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (alpha[u] != 0.0f && !done) {
+            const float test_T = T * (1.0f - alpha[u]);
+            if (test_T < GS_T_MIN) {
+              done = true;
+            } else {
+              const int j = jj[u];
+              const float w = alpha[u] * T;
+              C0 = fmaf(s_q1[j].z, w, C0);
+              C1 = fmaf(s_q1[j].w, w, C1);
+              C2 = fmaf(s_b[j], w, C2);
+              T = test_T;
+              last_contributor = (uint32_t)(lo + j + 1);
+            }
           }
         }
       }

@@ -211,8 +211,8 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
           if (a.in.raw_params) opac = 1.0f / (1.0f + expf(-opac));
           // exact tile culling (gs_common.cuh): which tiles of the rectangle can receive alpha >= 1/255
           uint32_t mlo = 0xFFFFFFFFu, mhi = 0xFFFFFFFFu;
+          const GsCull cs = gs_cull_setup(0.5f * con_x, con_y, 0.5f * con_z, opac);
           if (area <= GS_CULL_MAX_TILES) {
-            const GsCull cs = gs_cull_setup(0.5f * con_x, con_y, 0.5f * con_z, opac);
             mlo = mhi = 0u;
             int bit = 0;
             for (int ty = y0; ty < y1; ++ty)
@@ -225,7 +225,7 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
           }
           g.q0 = make_float4(px, py, 0.5f * con_x, con_y);
           g.q1 = make_float4(0.5f * con_z, opac, rgb[0], rgb[1]);
-          g.q2 = make_float4(rgb[2], pv[2], 0.f, 0.f);
+          g.q2 = make_float4(rgb[2], pv[2], cs.thr, 0.f);
           rad_out = rad;
           tiles = (uint32_t)area;
           rect = make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)x1 | ((uint32_t)y1 << 16),
