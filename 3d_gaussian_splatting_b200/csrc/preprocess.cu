@@ -124,10 +124,14 @@ struct PpOut {
   int radius;
   uint32_t tiles, cmask;
   uint4 rect;
+  GsCull cs;  // cull parameters of a visible Gaussian (deferred, warp-cooperative cull of the bulk kernel)
 };
 
 // One Gaussian.  p / scl / q4 / opac_in as stored by the caller (raw when a.in.raw_params); cov_pre, col_pre:
 // precomputed cov3D / colour rows or nullptr; dcp: the three SH dc floats; srow: the staged SH "rest" row.
+// kInlineCull: evaluate the exact tile cull here, one thread looping over its rectangle (generic kernel); otherwise
+// tiles / rect mask are left as "all tiles" and the caller culls cooperatively (pp_warp_cull).
+template <bool kInlineCull>
 __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const PreprocessArgs& a, const float p[3],
                                             const float scl[3], const float4 q4, const float opac_in,
                                             const float* cov_pre, const float* col_pre, const float* dcp,
@@ -140,6 +144,8 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
   uint32_t tiles = 0, cmask = 0;
   uint4 rect = make_uint4(0u, 0u, 0u, 0u);
   float depth = 0.f;
+  GsCull cs_out;
+  cs_out.hA = cs_out.B = cs_out.hC = cs_out.rA = cs_out.rC = cs_out.thr = 0.f;
 
   const float* V = st.viewmatrix;
   const float* M = st.projmatrix;
@@ -212,7 +218,8 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
           // exact tile culling (gs_common.cuh): which tiles of the rectangle can receive alpha >= 1/255
           uint32_t mlo = 0xFFFFFFFFu, mhi = 0xFFFFFFFFu;
           const GsCull cs = gs_cull_setup(0.5f * con_x, con_y, 0.5f * con_z, opac);
-          if (area <= GS_CULL_MAX_TILES) {
+          cs_out = cs;
+          if (kInlineCull && area <= GS_CULL_MAX_TILES) {
             mlo = mhi = 0u;
             int bit = 0;
             for (int ty = y0; ty < y1; ++ty)
@@ -242,7 +249,76 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
   o.tiles = tiles;
   o.cmask = cmask;
   o.rect = rect;
+  o.cs = cs_out;
   return o;
+}
+
+// Exact tile cull of one warp's Gaussians, load-balanced: the candidate (Gaussian, tile) pairs of the 32 lanes are
+// flattened (exclusive scan of the rectangle areas), lane l tests candidates l, l+32, ...: it finds the owner by
+// binary search in the shared offsets, evaluates gs_tile_alive with the owner's parameters and ORs the result into
+// the owner's 64-bit mask.  Same decisions as the per-thread loop (same function, same inputs), without the
+// divergence of 32 different rectangle sizes.  sw: this warp's scratch (32 lanes x PP_CULL_WORDS words).
+#define PP_CULL_WORDS 15  // 14 used; odd pitch: conflict-free owner look-ups
+__device__ __forceinline__ void pp_warp_cull(PpOut& o, uint32_t* sw) {
+  const int lane = threadIdx.x & 31;
+  const int x0 = (int)(o.rect.x & 0xFFFFu), y0 = (int)(o.rect.x >> 16);
+  const int w = (int)(o.rect.y & 0xFFFFu) - x0, h = (int)(o.rect.y >> 16) - y0;
+  const int area = w * h;
+  const bool cand = area > 0 && area <= GS_CULL_MAX_TILES;
+  const int cnt = cand ? area : 0;
+  int incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  const int total = __shfl_sync(0xffffffffu, incl, 31);
+  uint32_t* me = sw + lane * PP_CULL_WORDS;
+  me[0] = (uint32_t)(incl - cnt);
+  me[1] = __float_as_uint(o.g.q0.x);
+  me[2] = __float_as_uint(o.g.q0.y);
+  me[3] = __float_as_uint(o.cs.hA);
+  me[4] = __float_as_uint(o.cs.B);
+  me[5] = __float_as_uint(o.cs.hC);
+  me[6] = __float_as_uint(o.cs.rA);
+  me[7] = __float_as_uint(o.cs.rC);
+  me[8] = __float_as_uint(o.cs.thr);
+  me[9] = (uint32_t)x0 | ((uint32_t)y0 << 16);
+  me[10] = (uint32_t)w;
+  me[11] = __float_as_uint(1.0f / (float)(w > 0 ? w : 1));
+  me[12] = 0u;
+  me[13] = 0u;
+  __syncwarp();
+  for (int c = lane; c < total; c += 32) {
+    int lo = 0, hi = 31;  // owner = last lane whose offset is <= c (lanes without candidates share their successor's)
+#pragma unroll
+    for (int it = 0; it < 5; ++it) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (sw[mid * PP_CULL_WORDS] <= (uint32_t)c) lo = mid;
+      else hi = mid - 1;
+    }
+    uint32_t* ow = sw + lo * PP_CULL_WORDS;
+    const int k = c - (int)ow[0];
+    const int ww = (int)ow[10];
+    const int row = __float2int_rd(((float)k + 0.5f) * __uint_as_float(ow[11]));  // exact for k, ww <= 64
+    const int col = k - row * ww;
+    GsCull cs;
+    cs.hA = __uint_as_float(ow[3]);
+    cs.B = __uint_as_float(ow[4]);
+    cs.hC = __uint_as_float(ow[5]);
+    cs.rA = __uint_as_float(ow[6]);
+    cs.rC = __uint_as_float(ow[7]);
+    cs.thr = __uint_as_float(ow[8]);
+    const int tx = (int)(ow[9] & 0xFFFFu) + col, ty = (int)(ow[9] >> 16) + row;
+    if (gs_tile_alive(cs, __uint_as_float(ow[1]), __uint_as_float(ow[2]), tx, ty)) atomicOr(&ow[12 + (k >> 5)], 1u << (k & 31));
+  }
+  __syncwarp();
+  if (cand) {
+    o.rect.z = me[12];
+    o.rect.w = me[13];
+    o.tiles = (uint32_t)(__popc(me[12]) + __popc(me[13]));
+  }
+  __syncwarp();
 }
 
 __global__ void __launch_bounds__(PP_THREADS)
@@ -282,7 +358,7 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
     q4 = *reinterpret_cast<const float4*>(a.in.rotations + 4 * (size_t)i);
   }
   const float* dcp = col_pre ? nullptr : a.in.sh_dc + (size_t)i * a.in.sh_dc_stride;
-  const PpOut o = pp_compute(st, a, p, scl, q4, a.in.opacities[i], cov_pre, col_pre, dcp, s_sh + tid * a.rest_pitch);
+  const PpOut o = pp_compute<true>(st, a, p, scl, q4, a.in.opacities[i], cov_pre, col_pre, dcp, s_sh + tid * a.rest_pitch);
   a.geom[i] = o.g;
   a.depths[i] = o.depth;
   a.radii[i] = o.radius;
@@ -334,8 +410,12 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
   const float p[3] = {s_buf[PPB_OFF_XYZ + 3 * tid], s_buf[PPB_OFF_XYZ + 3 * tid + 1], s_buf[PPB_OFF_XYZ + 3 * tid + 2]};
   const float scl[3] = {s_buf[PPB_OFF_SCL + 3 * tid], s_buf[PPB_OFF_SCL + 3 * tid + 1], s_buf[PPB_OFF_SCL + 3 * tid + 2]};
   const float4 q4 = reinterpret_cast<const float4*>(s_buf + PPB_OFF_ROT)[tid];
-  const PpOut o = pp_compute(st, a, p, scl, q4, s_buf[PPB_OFF_OP + tid], nullptr, nullptr, s_buf + PPB_OFF_DC + 3 * tid,
-                             s_buf + PPB_OFF_SH + tid * W);
+  PpOut o = pp_compute<false>(st, a, p, scl, q4, s_buf[PPB_OFF_OP + tid], nullptr, nullptr, s_buf + PPB_OFF_DC + 3 * tid,
+                              s_buf + PPB_OFF_SH + tid * W);
+  // the (not yet written) output slices serve as per-warp scratch of the cooperative tile cull
+  static_assert(4 * 32 * PP_CULL_WORDS <= PPB_OFF_CLAMP - PPB_OFF_GEOM, "cull scratch does not fit the output slices");
+  pp_warp_cull(o, reinterpret_cast<uint32_t*>(s_buf + PPB_OFF_GEOM) + (tid >> 5) * 32 * PP_CULL_WORDS);
+  __syncthreads();
   float4* sg = reinterpret_cast<float4*>(s_buf + PPB_OFF_GEOM) + 3 * tid;
   sg[0] = o.g.q0;
   sg[1] = o.g.q1;
