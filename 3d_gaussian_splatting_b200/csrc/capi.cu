@@ -37,6 +37,9 @@ cudaError_t gs_launch_adam(int, float* const[6], float* const[6], float* const[6
                            const double[6], const long long[6], double, double, double, const int*, const float*, int*,
                            float*, float*, int, const float*, cudaStream_t);
 cudaError_t gs_launch_l1_loss(size_t, const float*, const float*, float, float*, double*, float*, cudaStream_t);
+size_t gs_ssim_workspace_bytes(int H, int W);
+cudaError_t gs_launch_photometric_loss(int, int, const float*, const float*, float, float*, double*, float*, float*,
+                                       cudaStream_t);
 
 // ---- context ----------------------------------------------------------------------------------
 struct DevBuf {
@@ -62,7 +65,7 @@ struct gs_ctx {
   // segmented backward: per-segment pixel checkpoints, (tile, segment) work list, {work_count, work_cursor}
   DevBuf ckpt, work_items, counters;
   int num_sms = 148;
-  DevBuf loss_acc;
+  DevBuf loss_acc, ssim_work;
   uint32_t* d_host_pinned = nullptr;  // readback: bytes 0..7 D (u64), 8..11 overflow flag
   uint64_t dup_cap_fixed = 0;         // > 0: caller-fixed pair capacity, no host synchronisation in gs_forward
   float* overflow_mirror = nullptr;   // optional caller-owned device float raised to 1.0 on overflow
@@ -187,7 +190,7 @@ void gs_destroy(gs_ctx* c) {
   DevBuf* bufs[] = {&c->geom,   &c->depths, &c->radii,  &c->tiles,   &c->rects, &c->clamped,   &c->grad_geom, &c->sort_k0,
                     &c->sort_k1, &c->sort_v0, &c->sort_v1, &c->dup_sums, &c->radix_counts,
                     &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_state,  &c->n_contrib,
-                    &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters, &c->loss_acc};
+                    &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters, &c->loss_acc, &c->ssim_work};
   for (DevBuf* b : bufs)
     if (b->ptr) cudaFree(b->ptr);
   if (c->d_host_pinned) cudaFreeHost(c->d_host_pinned);
@@ -513,12 +516,19 @@ int gs_loss(gs_ctx* c, int H, int W, const float* image, const float* gt, float 
     gs_set_error(c, "gs_loss: bad argument");
     return GS_EINVAL;
   }
-  if (lambda_dssim != 0.0f) {
-    gs_set_error(c, "gs_loss: the D-SSIM term is not built yet (lambda_dssim must be 0)");
+  if (!(lambda_dssim >= 0.0f && lambda_dssim <= 1.0f)) {
+    gs_set_error(c, "gs_loss: lambda_dssim %g outside [0,1]", (double)lambda_dssim);
     return GS_EINVAL;
   }
   GS_CUDA_CHECK(c, cudaSetDevice(c->device));
   GS_ENSURE(c, c->loss_acc, 64);
+  if (lambda_dssim != 0.0f) {
+    GS_ENSURE(c, c->ssim_work, gs_ssim_workspace_bytes(H, W));
+    GS_CUDA_CHECK(c, gs_launch_photometric_loss(H, W, image, gt, lambda_dssim, (float*)c->ssim_work.ptr,
+                                                (double*)c->loss_acc.ptr, loss_out, dL_dimage,
+                                                (cudaStream_t)stream_));
+    return GS_OK;
+  }
   GS_CUDA_CHECK(c, gs_launch_l1_loss((size_t)3 * H * W, image, gt, 1.0f, dL_dimage, (double*)c->loss_acc.ptr,
                                      loss_out, (cudaStream_t)stream_));
   return GS_OK;

@@ -128,7 +128,7 @@ class GaussianModel:
 
 
 def render(viewpoint_camera, pc: GaussianModel, pipe: PipelineParams, bg_color, rast: Rasterizer,
-           scaling_modifier: float = 1.0, fused_activations: bool = True):
+           scaling_modifier: float = 1.0, fused_activations: bool = True, with_visibility: bool = True):
     """The missing render(viewpoint_cam, gaussians, pipe, background) call.  Returns
     dict(render=(3,H,W), radii=(N) int32, visibility_filter=radii>0).
     fused_activations=True feeds the RAW parameters (activations fused in the kernels);
@@ -145,7 +145,10 @@ def render(viewpoint_camera, pc: GaussianModel, pipe: PipelineParams, bg_color, 
     else:
         color, radii = rast.forward(st, pc.get_xyz(), pc.get_scaling(), pc.get_rotation(), pc.get_opacity(),
                                     shs=pc.get_features())
-    return dict(render=color, radii=radii, visibility_filter=radii > 0)
+    out = dict(render=color, radii=radii)
+    if with_visibility:   # one more elementwise kernel; the fused Adam/stats step derives it from radii itself
+        out["visibility_filter"] = radii > 0
+    return out
 
 
 class Trainer:
@@ -194,7 +197,7 @@ class Trainer:
         stream only waits for it in front of the loss kernel."""
         if self._guard_tensor is not None and not accumulate:
             self._guard_tensor.zero_()   # caller-owned guard: lowered at the start of every iteration
-        out = render(cam, self.g, self.pipe, self.bg, self.rast)
+        out = render(cam, self.g, self.pipe, self.bg, self.rast, with_visibility=False)
         if gt_host is not None:
             main = torch.cuda.current_stream(self.g.device)
             if self._copy_stream is None:

@@ -120,7 +120,9 @@ def stage_bytes(N, N_vis, D, D_eff, P, T, K):
         "blend_bwd": 40 * D_eff + 20 * P + 36 * N_vis,
         "preprocess_bwd": (44 + 12 * K) * N_vis + 36 * N_vis + 4 * N + (44 + 12 * K) * N,
         "adam_stats": 28 * (11 + 3 * K) * N + 36 * N_vis,
-        "loss": 36 * P,
+        # (1-lambda) L1 + lambda D-SSIM: fwd reads image + target, writes 3 partial maps; bwd reads them + both images,
+        # writes dL/dimage (12 B per pixel each)
+        "loss": 12 * P * (2 + 3 + 5 + 1),
     }
 
 
@@ -166,7 +168,7 @@ class CpuStep:
         pre, b, fwd = o.forward(s, xyz, sc, rot, op, shs)
         if gt is None:
             gt = np.zeros_like(fwd["out_color"])
-        loss, dL = o.l1_loss(fwd["out_color"], gt)
+        loss, dL, _, _ = o.photometric_loss(fwd["out_color"], gt, LAMBDA_DSSIM)
         g = o.backward(s, xyz, sc, rot, shs, pre, b, fwd, dL)
         # activation Jacobians of the getters (gaussian_model.cpp:54-59)
         g_ls = g["dL_dscales"] * sc
@@ -206,7 +208,7 @@ def run_reference(args, rank, world):
         "warmup": warm, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.config, "N": scene.N, "W": cam.image_width, "H": cam.image_height,
-                   "sh_degree": deg, "views_per_rank_per_step": 1, "loss": "L1",
+                   "sh_degree": deg, "views_per_rank_per_step": 1, "loss": LOSS_NAME,
                    "note": "reference repo has no render path; CPU arm = this repo's oracle port (OpenMP)"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cpu.cores, "kind": "port",
                          "sample": f"{steps} full train steps of the same workload (steps capped at 6)"},
@@ -217,8 +219,10 @@ def run_reference(args, rank, world):
 
 # ---- GPU arm -----------------------------------------------------------------------------------
 # preprocess, depth sort 4 x (hist, scan, scatter), dup block sums + scan + duplicate, tile sort 2 x 3, tile
-# ranges, tile order, blend_forward, l1_loss + finalize, blend_backward, preprocess_backward, adam_stats
-OWN_KERNELS_PER_STEP = 1 + 12 + 3 + 6 + 2 + 1 + 2 + 1 + 1 + 1
+# ranges, tile order, blend_forward, ssim forward + backward + finalize, blend_backward, preprocess_backward, adam_stats
+OWN_KERNELS_PER_STEP = 1 + 12 + 3 + 6 + 2 + 1 + 3 + 1 + 1 + 1
+LAMBDA_DSSIM = 0.2   # lambda_dssim_ default (src/arguments/params.h:62)
+LOSS_NAME = "0.8*L1 + 0.2*(1-SSIM)"
 LIB_KERNELS_PER_STEP = 0   # no library kernels on the path (the radix sort and scans are this repo's own)
 
 
@@ -242,7 +246,7 @@ def run_ours(args, rank, world, local_rank):
 
     model = gm.GaussianModel(deg, local_rank).load_scene(scene)
     opt = gm.OptimizationParams()
-    trainer = gm.Trainer(model, opt, bg=(0.0, 0.0, 0.0), lambda_dssim=0.0)
+    trainer = gm.Trainer(model, opt, bg=(0.0, 0.0, 0.0), lambda_dssim=LAMBDA_DSSIM)
     g = model
     # one contiguous gradient slab (a single all-reduce per step when world > 1)
     gslab = par.GradientSlab(g.params())
@@ -317,7 +321,7 @@ def run_ours(args, rank, world, local_rank):
     for i in range(8):
         cam, gt = my_cams[i % args.views], gts_dev[i % args.views]
         out = gm.render(cam, g, trainer.pipe, trainer.bg, trainer.rast)
-        ev[0].record(); loss, dL = trainer.rast.loss(out["render"], gt, 0.0); ev[1].record()
+        ev[0].record(); loss, dL = trainer.rast.loss(out["render"], gt, LAMBDA_DSSIM); ev[1].record()
         trainer.rast.backward(dL, grads=g.grad_sinks())
         ev[2].record(); trainer.optimizer_step(out["radii"]); ev[3].record()
         torch.cuda.synchronize()
@@ -367,7 +371,7 @@ def run_ours(args, rank, world, local_rank):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.config, "N": N, "W": W, "H": H, "sh_degree": deg, "tiles": T,
-                       "views_per_rank_per_step": 1, "loss": "L1", "N_vis": N_vis, "D": D, "D_eff": D_eff,
+                       "views_per_rank_per_step": 1, "loss": LOSS_NAME, "N_vis": N_vis, "D": D, "D_eff": D_eff,
                        "pixel_gaussian_interactions": interactions,
                        "l2_policy": "inputs larger than L2 (params+Adam state 1.13 GB per step vs 126 MB L2)",
                        "parallelism": f"camera-sharded dp{world}, one NCCL all-reduce of {slab.numel() * 4 / 1e6:.0f} MB grads per step"

@@ -69,6 +69,7 @@ class Oracle:
         self.Settings = _settings_type(self.real)
         self.lib.orc_scan_tiles.restype = C.c_uint64
         self.lib.orc_l1_loss.restype = C.c_double
+        self.lib.orc_photometric_loss.restype = C.c_double
         self.lib.orc_focal2fov.restype = C.c_double
         self.lib.orc_expon_lr.restype = C.c_float
         self.lib.orc_expon_lr.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, C.c_int, C.c_int]
@@ -216,6 +217,16 @@ class Oracle:
     def densify_stats(self, radii, dL_dmean2D, max_radii2D, accum, denom):
         self.lib.orc_densify_stats(C.c_int(radii.shape[0]), self.p(radii), self.p(dL_dmean2D),
                                    self.p(max_radii2D), self.p(accum), self.p(denom))
+
+    def photometric_loss(self, img, gt, lambda_dssim=0.2, want_grad=True):
+        """(1-lambda) L1 + lambda (1 - SSIM) (orc_ssim.c); returns (loss, dL/dimg or None, l1, ssim)."""
+        img = self.arr(img); gt = self.arr(gt)
+        _, H, W = img.shape
+        d = np.zeros_like(img) if want_grad else None
+        l1, ss = C.c_double(0), C.c_double(0)
+        loss = self.lib.orc_photometric_loss(C.c_int(H), C.c_int(W), self.p(img), self.p(gt), C.c_double(lambda_dssim),
+                                             self.p(d), C.byref(l1), C.byref(ss))
+        return float(loss), d, float(l1.value), float(ss.value)
 
     def l1_loss(self, img, gt):
         img = self.arr(img); gt = self.arr(gt)

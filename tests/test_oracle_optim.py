@@ -46,3 +46,31 @@ def test_l1_loss(oracle):
     loss, d = oracle.l1_loss(a, b)
     assert loss == pytest.approx(np.abs(a - b).mean(), rel=1e-6)
     np.testing.assert_allclose(d, np.sign(a - b) / a.size)
+
+
+def _torch_ssim_loss(img, gt, lam):
+    """The published trainer's loss: 11x11 Gaussian window (sigma 1.5), zero-padded conv2d per channel."""
+    import torch.nn.functional as F
+    g = torch.tensor([np.exp(-(i - 5) ** 2 / (2 * 1.5 ** 2)) for i in range(11)], dtype=torch.float64)
+    g = g / g.sum()
+    w = (g[:, None] * g[None, :]).expand(3, 1, 11, 11).contiguous()
+    conv = lambda t: F.conv2d(t[None], w, padding=5, groups=3)[0]
+    mu1, mu2 = conv(img), conv(gt)
+    s11, s22, s12 = conv(img * img) - mu1 * mu1, conv(gt * gt) - mu2 * mu2, conv(img * gt) - mu1 * mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    ssim = ((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1 * mu1 + mu2 * mu2 + C1) * (s11 + s22 + C2))
+    return (1 - lam) * (img - gt).abs().mean() + lam * (1 - ssim.mean())
+
+
+@pytest.mark.parametrize("H,W,lam", [(37, 53, 0.2), (16, 16, 1.0), (9, 70, 0.5)])
+def test_photometric_loss_matches_torch(oracle, H, W, lam):
+    """D-SSIM + L1 (lambda_dssim_, src/arguments/params.h:62) against a float64 torch conv2d/autograd restatement."""
+    rng = np.random.default_rng(H)
+    a = rng.random((3, H, W)).astype(np.float32); b = np.clip(a + 0.2 * rng.standard_normal((3, H, W)), 0, 1).astype(np.float32)
+    loss, d, l1, ss = oracle.photometric_loss(a, b, lam)
+    ta = torch.tensor(a, dtype=torch.float64, requires_grad=True); tb = torch.tensor(b, dtype=torch.float64)
+    ref = _torch_ssim_loss(ta, tb, lam)
+    ref.backward()
+    assert loss == pytest.approx(ref.item(), rel=1e-6)
+    np.testing.assert_allclose(d, ta.grad.numpy(), rtol=1e-4, atol=1e-9)
+    assert l1 == pytest.approx(np.abs(a.astype(np.float64) - b).mean(), rel=1e-6) and 0 < ss < 1

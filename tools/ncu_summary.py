@@ -49,19 +49,19 @@ def main():
                 d[short] = v
         stalls = []
         for h, i in idx.items():
-            if h.startswith(STALL_PREFIX) and h.endswith("_per_warp_active.pct") and "not_issued" not in h:
+            if h.startswith(STALL_PREFIX) and h.endswith("_per_issue_active.ratio") and "not_issued" not in h:
                 try:
-                    stalls.append((float(r[i].replace(",", "")), h[len(STALL_PREFIX):].replace("_per_warp_active.pct", "")))
+                    stalls.append((float(r[i].replace(",", "")), h[len(STALL_PREFIX):].replace("_per_issue_active.ratio", "")))
                 except ValueError:
                     pass
         stalls.sort(reverse=True)
-        d["stalls"] = " ".join(f"{n}:{v:.0f}" for v, n in stalls[:4])
+        d["stalls"] = " ".join(f"{n}:{v:.1f}" for v, n in stalls[:4])
         d["grid"] = r[idx["Grid Size"]] if "Grid Size" in idx else ""
         d["block"] = r[idx["Block Size"]] if "Block Size" in idx else ""
         lines.append((name, d))
     cols = ["dur_us", "dram_rd_MB", "dram_wr_MB", "dram_pct", "l2_pct", "l1_pct", "sm_pct", "issue_pct", "occ_pct", "regs",
             "inst_M", "l2_red_sect_M"]
-    txt = ["| kernel | grid | block | " + " | ".join(cols) + " | top stalls (% of warp-active) |", "|" + "---|" * (len(cols) + 4)]
+    txt = ["| kernel | grid | block | " + " | ".join(cols) + " | top stalls (warps stalled per issue) |", "|" + "---|" * (len(cols) + 4)]
     for name, d in lines:
         txt.append(f"| {name} | {d['grid']} | {d['block']} | " + " | ".join(
             (f"{d[c]:.1f}" if c in d else "-") for c in cols) + f" | {d['stalls']} |")
