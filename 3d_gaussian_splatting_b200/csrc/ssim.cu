@@ -3,7 +3,8 @@
 // reference (src/utils/train_utils.cpp:138-145).  SSIM: per channel, 11x11 Gaussian window (sigma 1.5),
 // zero-padded "same" convolution, C1 = 0.01^2, C2 = 0.03^2 -- the oracle's definition (oracle/orc_ssim.c).
 //
-// Two fused kernels over 32x16 pixel tiles of one channel (grid.z = 3):
+// Two fused kernels over 32x16 pixel tiles of one channel (grid.z = 3), 128 threads each producing 4 outputs per
+// pass so every staged value (and, in the forward, its three products) is reused from registers by 4 windows:
 //   ssim_forward_kernel   stages the 42x26 halo of image and target in shared memory, runs the separable
 //                         window over the five products (x, y, xx, yy, xy) -- rows, then columns -- evaluates the
 //                         SSIM map and its partial derivatives w.r.t. the windowed means (dmu1, de11, de12;
@@ -17,21 +18,42 @@
 #define SS_R 5
 #define SS_HX (SS_TX + 2 * SS_R)  // 42
 #define SS_HY (SS_TY + 2 * SS_R)  // 26
-#define SS_THREADS (SS_TX * SS_TY)
+#define SS_THREADS 128            // every thread produces 4 outputs of each pass (register-blocked window)
+#define SS_V 4
+#define SS_PITCH (SS_HX + 1)      // 43: with 4-wide column groups the 32 lanes of a warp hit 32 different banks
 
 struct SsimWindow {
   float g[2 * SS_R + 1];
 };
 
+// Column pass for one thread: 4 consecutive rows of column `col` from NP row-filtered planes.
+template <int NP>
+__device__ __forceinline__ void ssim_columns(const float (*s_h)[SS_HY][SS_TX], const SsimWindow& win, int row0, int col,
+                                             float out[NP][SS_V]) {
+#pragma unroll
+  for (int q = 0; q < NP; ++q) {
+    float v[SS_V + 2 * SS_R];
+#pragma unroll
+    for (int j = 0; j < SS_V + 2 * SS_R; ++j) v[j] = s_h[q][row0 + j][col];
+#pragma unroll
+    for (int u = 0; u < SS_V; ++u) {
+      float a = 0.f;
+#pragma unroll
+      for (int t = 0; t <= 2 * SS_R; ++t) a = fmaf(win.g[t], v[u + t], a);
+      out[q][u] = a;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(SS_THREADS)
 ssim_forward_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, SsimWindow win,
                     float* __restrict__ dmu, float* __restrict__ de11, float* __restrict__ de12,
-                    double* __restrict__ acc /* [0] sum |x-y|, [1] sum SSIM */) {
-  __shared__ float s_x[SS_HY][SS_HX + 1];
-  __shared__ float s_y[SS_HY][SS_HX + 1];
+                    float2* __restrict__ partial /* per block: {sum |x-y|, sum SSIM} */) {
+  __shared__ float s_x[SS_HY][SS_PITCH];
+  __shared__ float s_y[SS_HY][SS_PITCH];
   __shared__ float s_h[5][SS_HY][SS_TX];
   __shared__ float s_red[2][SS_THREADS / 32];
-  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * SS_TX + tx;
+  const int tid = threadIdx.x;
   const int x0 = blockIdx.x * SS_TX, y0 = blockIdx.y * SS_TY;
   const size_t plane = (size_t)H * W;
   const float* xp = img + blockIdx.z * plane;
@@ -45,53 +67,65 @@ ssim_forward_kernel(int H, int W, const float* __restrict__ img, const float* __
     s_y[r][c] = in ? __ldg(yp + (size_t)gy * W + gx) : 0.f;
   }
   __syncthreads();
-  // rows: 26 x 32 outputs, five products each
-  for (int k = tid; k < SS_HY * SS_TX; k += SS_THREADS) {
-    const int r = k / SS_TX, c = k - r * SS_TX;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+  // rows: 26 rows x 8 groups of 4 adjacent outputs; the 14 staged values (and their products) are reused by the 4
+  for (int k = tid; k < SS_HY * (SS_TX / SS_V); k += SS_THREADS) {
+    const int r = k / (SS_TX / SS_V), c = (k - r * (SS_TX / SS_V)) * SS_V;
+    float xv[SS_V + 2 * SS_R], yv[SS_V + 2 * SS_R];
 #pragma unroll
-    for (int t = 0; t <= 2 * SS_R; ++t) {
-      const float w = win.g[t], xv = s_x[r][c + t], yv = s_y[r][c + t];
-      a0 = fmaf(w, xv, a0);
-      a1 = fmaf(w, yv, a1);
-      a2 = fmaf(w, xv * xv, a2);
-      a3 = fmaf(w, yv * yv, a3);
-      a4 = fmaf(w, xv * yv, a4);
+    for (int j = 0; j < SS_V + 2 * SS_R; ++j) {
+      xv[j] = s_x[r][c + j];
+      yv[j] = s_y[r][c + j];
     }
-    s_h[0][r][c] = a0;
-    s_h[1][r][c] = a1;
-    s_h[2][r][c] = a2;
-    s_h[3][r][c] = a3;
-    s_h[4][r][c] = a4;
+    float acc[5][SS_V];
+#pragma unroll
+    for (int u = 0; u < SS_V; ++u) acc[0][u] = acc[1][u] = acc[2][u] = acc[3][u] = acc[4][u] = 0.f;
+#pragma unroll
+    for (int j = 0; j < SS_V + 2 * SS_R; ++j) {
+      const float xx = xv[j] * xv[j], yy = yv[j] * yv[j], xy = xv[j] * yv[j];
+#pragma unroll
+      for (int u = 0; u < SS_V; ++u) {
+        const int t = j - u;
+        if (t >= 0 && t <= 2 * SS_R) {
+          const float w = win.g[t];
+          acc[0][u] = fmaf(w, xv[j], acc[0][u]);
+          acc[1][u] = fmaf(w, yv[j], acc[1][u]);
+          acc[2][u] = fmaf(w, xx, acc[2][u]);
+          acc[3][u] = fmaf(w, yy, acc[3][u]);
+          acc[4][u] = fmaf(w, xy, acc[4][u]);
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 5; ++q)
+#pragma unroll
+      for (int u = 0; u < SS_V; ++u) s_h[q][r][c + u] = acc[q][u];
   }
   __syncthreads();
-  // columns + map
-  float m1 = 0.f, m2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
-#pragma unroll
-  for (int t = 0; t <= 2 * SS_R; ++t) {
-    const float w = win.g[t];
-    m1 = fmaf(w, s_h[0][ty + t][tx], m1);
-    m2 = fmaf(w, s_h[1][ty + t][tx], m2);
-    e11 = fmaf(w, s_h[2][ty + t][tx], e11);
-    e22 = fmaf(w, s_h[3][ty + t][tx], e22);
-    e12 = fmaf(w, s_h[4][ty + t][tx], e12);
-  }
-  const int gx = x0 + tx, gy = y0 + ty;
+  // columns + map: thread = column tx, rows 4*rg .. 4*rg+3
+  const int tx = tid & 31, row0 = (tid >> 5) * SS_V;
+  float m[5][SS_V];
+  ssim_columns<5>(s_h, win, row0, tx, m);
+  const int gx = x0 + tx;
   float l1 = 0.f, ss = 0.f;
-  if (gx < W && gy < H) {
-    const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-    const float s11 = e11 - m1 * m1, s22 = e22 - m2 * m2, s12 = e12 - m1 * m2;
-    const float A1 = 2.f * m1 * m2 + C1, A2 = 2.f * s12 + C2;
-    const float B1 = m1 * m1 + m2 * m2 + C1, B2 = s11 + s22 + C2;
-    const float inv = 1.0f / (B1 * B2);
-    const float S = A1 * A2 * inv;
-    const float dA1 = A2 * inv, dA2 = A1 * inv, dB1 = -S / B1, dB2 = -S / B2;
-    const size_t o = blockIdx.z * plane + (size_t)gy * W + gx;
-    dmu[o] = 2.f * (dA1 * m2 + dB1 * m1 - dB2 * m1 - dA2 * m2);
-    de11[o] = dB2;
-    de12[o] = 2.f * dA2;
-    ss = S;
-    l1 = fabsf(s_x[ty + SS_R][tx + SS_R] - s_y[ty + SS_R][tx + SS_R]);
+#pragma unroll
+  for (int u = 0; u < SS_V; ++u) {
+    const int gy = y0 + row0 + u;
+    if (gx < W && gy < H) {
+      const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+      const float m1 = m[0][u], m2 = m[1][u];
+      const float s11 = m[2][u] - m1 * m1, s22 = m[3][u] - m2 * m2, s12 = m[4][u] - m1 * m2;
+      const float A1 = 2.f * m1 * m2 + C1, A2 = 2.f * s12 + C2;
+      const float B1 = m1 * m1 + m2 * m2 + C1, B2 = s11 + s22 + C2;
+      const float inv = 1.0f / (B1 * B2);
+      const float S = A1 * A2 * inv;
+      const float dA1 = A2 * inv, dA2 = A1 * inv, dB1 = -S / B1, dB2 = -S / B2;
+      const size_t o = blockIdx.z * plane + (size_t)gy * W + gx;
+      dmu[o] = 2.f * (dA1 * m2 + dB1 * m1 - dB2 * m1 - dA2 * m2);
+      de11[o] = dB2;
+      de12[o] = 2.f * dA2;
+      ss += S;
+      l1 += fabsf(s_x[row0 + u + SS_R][tx + SS_R] - s_y[row0 + u + SS_R][tx + SS_R]);
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
@@ -103,10 +137,14 @@ ssim_forward_kernel(int H, int W, const float* __restrict__ img, const float* __
     s_red[1][tid >> 5] = ss;
   }
   __syncthreads();
-  if (tid < 2) {
-    float t = 0.f;
-    for (int k = 0; k < SS_THREADS / 32; ++k) t += s_red[tid][k];
-    atomicAdd(acc + tid, (double)t);
+  if (tid == 0) {
+    float t0 = 0.f, t1 = 0.f;
+    for (int k = 0; k < SS_THREADS / 32; ++k) {
+      t0 += s_red[0][k];
+      t1 += s_red[1][k];
+    }
+    // one partial per block, summed in double by the finalize kernel: deterministic, no same-address atomics
+    partial[(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = make_float2(t0, t1);
   }
 }
 
@@ -114,9 +152,9 @@ __global__ void __launch_bounds__(SS_THREADS)
 ssim_backward_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, SsimWindow win,
                      const float* __restrict__ dmu, const float* __restrict__ de11, const float* __restrict__ de12,
                      float k_ssim /* -lambda / n */, float k_l1 /* (1 - lambda) / n */, float* __restrict__ dL_dimg) {
-  __shared__ float s_in[3][SS_HY][SS_HX + 1];
+  __shared__ float s_in[3][SS_HY][SS_PITCH];
   __shared__ float s_h[3][SS_HY][SS_TX];
-  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * SS_TX + tx;
+  const int tid = threadIdx.x;
   const int x0 = blockIdx.x * SS_TX, y0 = blockIdx.y * SS_TY;
   const size_t plane = (size_t)H * W, base = blockIdx.z * plane;
   for (int k = tid; k < SS_HY * SS_HX; k += SS_THREADS) {
@@ -129,44 +167,76 @@ ssim_backward_kernel(int H, int W, const float* __restrict__ img, const float* _
     s_in[2][r][c] = in ? __ldg(de12 + o) : 0.f;
   }
   __syncthreads();
-  for (int k = tid; k < SS_HY * SS_TX; k += SS_THREADS) {
-    const int r = k / SS_TX, c = k - r * SS_TX;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+  for (int k = tid; k < SS_HY * (SS_TX / SS_V); k += SS_THREADS) {
+    const int r = k / (SS_TX / SS_V), c = (k - r * (SS_TX / SS_V)) * SS_V;
 #pragma unroll
-    for (int t = 0; t <= 2 * SS_R; ++t) {
-      const float w = win.g[t];
-      a0 = fmaf(w, s_in[0][r][c + t], a0);
-      a1 = fmaf(w, s_in[1][r][c + t], a1);
-      a2 = fmaf(w, s_in[2][r][c + t], a2);
+    for (int q = 0; q < 3; ++q) {
+      float v[SS_V + 2 * SS_R];
+#pragma unroll
+      for (int j = 0; j < SS_V + 2 * SS_R; ++j) v[j] = s_in[q][r][c + j];
+#pragma unroll
+      for (int u = 0; u < SS_V; ++u) {
+        float a = 0.f;
+#pragma unroll
+        for (int t = 0; t <= 2 * SS_R; ++t) a = fmaf(win.g[t], v[u + t], a);
+        s_h[q][r][c + u] = a;
+      }
     }
-    s_h[0][r][c] = a0;
-    s_h[1][r][c] = a1;
-    s_h[2][r][c] = a2;
   }
   __syncthreads();
-  const int gx = x0 + tx, gy = y0 + ty;
-  if (gx >= W || gy >= H) return;
-  float c0 = 0.f, c1 = 0.f, c2 = 0.f;
+  const int tx = tid & 31, row0 = (tid >> 5) * SS_V;
+  float cv[3][SS_V];
+  ssim_columns<3>(s_h, win, row0, tx, cv);
+  const int gx = x0 + tx;
+  if (gx >= W) return;
 #pragma unroll
-  for (int t = 0; t <= 2 * SS_R; ++t) {
-    const float w = win.g[t];
-    c0 = fmaf(w, s_h[0][ty + t][tx], c0);
-    c1 = fmaf(w, s_h[1][ty + t][tx], c1);
-    c2 = fmaf(w, s_h[2][ty + t][tx], c2);
+  for (int u = 0; u < SS_V; ++u) {
+    const int gy = y0 + row0 + u;
+    if (gy < H) {
+      const size_t o = base + (size_t)gy * W + gx;
+      const float x = __ldg(img + o), y = __ldg(gt + o);
+      const float dS = cv[0][u] + 2.f * x * cv[1][u] + y * cv[2][u];
+      const float d = x - y;
+      const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+      dL_dimg[o] = fmaf(k_ssim, dS, k_l1 * sg);
+    }
   }
-  const size_t o = base + (size_t)gy * W + gx;
-  const float x = __ldg(img + o), y = __ldg(gt + o);
-  const float dS = c0 + 2.f * x * c1 + y * c2;
-  const float d = x - y;
-  const float sg = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
-  dL_dimg[o] = fmaf(k_ssim, dS, k_l1 * sg);
 }
 
-__global__ void photometric_finalize_kernel(const double* acc, double inv_n, double lambda, float* loss_out) {
-  *loss_out = (float)((1.0 - lambda) * acc[0] * inv_n + lambda * (1.0 - acc[1] * inv_n));
+__global__ void __launch_bounds__(1024)
+photometric_finalize_kernel(const float2* __restrict__ partial, int nblocks, double inv_n, double lambda,
+                            float* __restrict__ loss_out) {
+  __shared__ double s_a[32], s_b[32];
+  double a = 0, b = 0;
+  for (int i = threadIdx.x; i < nblocks; i += 1024) {
+    const float2 p = partial[i];
+    a += (double)p.x;
+    b += (double)p.y;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    s_a[threadIdx.x >> 5] = a;
+    s_b[threadIdx.x >> 5] = b;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double ta = 0, tb = 0;
+    for (int k = 0; k < 32; ++k) {
+      ta += s_a[k];
+      tb += s_b[k];
+    }
+    *loss_out = (float)((1.0 - lambda) * ta * inv_n + lambda * (1.0 - tb * inv_n));
+  }
 }
 
-size_t gs_ssim_workspace_bytes(int H, int W) { return (size_t)9 * H * W * sizeof(float); }
+static int ssim_blocks(int H, int W) { return ((W + SS_TX - 1) / SS_TX) * ((H + SS_TY - 1) / SS_TY) * 3; }
+size_t gs_ssim_workspace_bytes(int H, int W) {
+  return (((size_t)9 * H * W + 3) & ~(size_t)3) * sizeof(float) + (size_t)ssim_blocks(H, W) * sizeof(float2);
+}
 
 cudaError_t gs_launch_photometric_loss(int H, int W, const float* img, const float* gt, float lambda, float* work,
                                        double* acc, float* loss_out, float* dL_dimg, cudaStream_t stream) {
@@ -182,13 +252,13 @@ cudaError_t gs_launch_photometric_loss(int H, int W, const float* img, const flo
   float* dmu = work;
   float* de11 = work + n;
   float* de12 = work + 2 * n;
-  cudaError_t e = cudaMemsetAsync(acc, 0, 2 * sizeof(double), stream);
-  if (e != cudaSuccess) return e;
-  const dim3 grid((W + SS_TX - 1) / SS_TX, (H + SS_TY - 1) / SS_TY, 3), block(SS_TX, SS_TY);
-  ssim_forward_kernel<<<grid, block, 0, stream>>>(H, W, img, gt, win, dmu, de11, de12, acc);
+  (void)acc;
+  float2* partial = reinterpret_cast<float2*>(work + ((3 * n + 3) & ~(size_t)3));
+  const dim3 grid((W + SS_TX - 1) / SS_TX, (H + SS_TY - 1) / SS_TY, 3), block(SS_THREADS);
+  ssim_forward_kernel<<<grid, block, 0, stream>>>(H, W, img, gt, win, dmu, de11, de12, partial);
   if (dL_dimg)
     ssim_backward_kernel<<<grid, block, 0, stream>>>(H, W, img, gt, win, dmu, de11, de12, -lambda / (float)n,
                                                      (1.0f - lambda) / (float)n, dL_dimg);
-  photometric_finalize_kernel<<<1, 1, 0, stream>>>(acc, 1.0 / (double)n, (double)lambda, loss_out);
+  photometric_finalize_kernel<<<1, 1024, 0, stream>>>(partial, ssim_blocks(H, W), 1.0 / (double)n, (double)lambda, loss_out);
   return cudaGetLastError();
 }
