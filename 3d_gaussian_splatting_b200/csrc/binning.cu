@@ -21,13 +21,17 @@
 
 // ---- 1. depth sort ----------------------------------------------------------------------------
 cudaError_t gs_launch_depth_sort(int N, const uint32_t* depth_bits, uint32_t* k0, uint32_t* k1, uint32_t* v0,
-                                 uint32_t* v1, uint32_t* counts, int grid, cudaStream_t stream) {
+                                 uint32_t* v1, uint32_t* counts, int grid_unused, cudaStream_t stream) {
   if (N == 0) return cudaSuccess;
+  (void)grid_unused;
+  // one 2048-pair tile per block when that fits the grid limit: the N-sized sort is latency-bound
+  int grid = (N + 2047) / 2048;
+  if (grid > RS_MAX_GRID) grid = RS_MAX_GRID;
   // result (Gaussian ids in depth order) lands in v1
-  radix_pass<uint32_t>(depth_bits, k0, nullptr, v0, (uint32_t)N, nullptr, 0, counts, grid, stream);
-  radix_pass<uint32_t>(k0, k1, v0, v1, (uint32_t)N, nullptr, 8, counts, grid, stream);
-  radix_pass<uint32_t>(k1, k0, v1, v0, (uint32_t)N, nullptr, 16, counts, grid, stream);
-  return radix_pass<uint32_t>(k0, nullptr, v0, v1, (uint32_t)N, nullptr, 24, counts, grid, stream);
+  radix_pass<uint32_t, 8>(depth_bits, k0, nullptr, v0, (uint32_t)N, nullptr, 0, counts, grid, stream);
+  radix_pass<uint32_t, 8>(k0, k1, v0, v1, (uint32_t)N, nullptr, 8, counts, grid, stream);
+  radix_pass<uint32_t, 8>(k1, k0, v1, v0, (uint32_t)N, nullptr, 16, counts, grid, stream);
+  return radix_pass<uint32_t, 8>(k0, nullptr, v0, v1, (uint32_t)N, nullptr, 24, counts, grid, stream);
 }
 
 // ---- 2. scan of tiles_touched along the depth order + duplicate ---------------------------------
@@ -232,11 +236,11 @@ cudaError_t gs_launch_tile_sort(const uint32_t* D_dev, int tile_bits, int key_by
     if (key_bytes == 2) {
       uint16_t* ki = (uint16_t*)(in_a ? keys_a : keys_b);
       uint16_t* ko = (uint16_t*)(in_a ? keys_b : keys_a);
-      radix_pass<uint16_t>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
+      radix_pass<uint16_t, 16>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
     } else {
       uint32_t* ki = (uint32_t*)(in_a ? keys_a : keys_b);
       uint32_t* ko = (uint32_t*)(in_a ? keys_b : keys_a);
-      radix_pass<uint32_t>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
+      radix_pass<uint32_t, 16>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
     }
     in_a = !in_a;
   }
@@ -255,25 +259,30 @@ __device__ __forceinline__ uint32_t lower_bound_tile(const KeyT* __restrict__ ke
   }
   return lo;
 }
+// a block of 256 threads resolves 255 tiles: thread i finds the first list position of tile t0 + i (ONE dependent
+// chain of ~log2 D loads per thread), the range of a tile is the pair of its own and its right neighbour's
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 identify_tile_ranges_kernel(const uint32_t* __restrict__ D_dev, const KeyT* __restrict__ keys, int ntiles,
                             uint2* __restrict__ ranges) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= ntiles) return;
+  __shared__ uint32_t s_lb[256];
+  const int t = blockIdx.x * 255 + threadIdx.x;
   const uint32_t n = *D_dev;
-  const uint32_t a = lower_bound_tile(keys, n, (uint32_t)t);
-  const uint32_t b = lower_bound_tile(keys, n, (uint32_t)t + 1u);
+  s_lb[threadIdx.x] = t <= ntiles ? lower_bound_tile(keys, n, (uint32_t)t) : n;
+  __syncthreads();
+  if (threadIdx.x == 255 || t >= ntiles) return;
+  const uint32_t a = s_lb[threadIdx.x], b = s_lb[threadIdx.x + 1];
   ranges[t] = a == b ? make_uint2(0u, 0u) : make_uint2(a, b);  // empty tiles read (0,0), as in the oracle
 }
 
 cudaError_t gs_launch_ranges(const uint32_t* D_dev, const void* keys, int key_bytes, uint2* ranges, int ntiles,
                              cudaStream_t stream) {
   if (ntiles == 0) return cudaSuccess;
+  const int blocks = (ntiles + 254) / 255;
   if (key_bytes == 2)
-    identify_tile_ranges_kernel<uint16_t><<<(ntiles + 255) / 256, 256, 0, stream>>>(D_dev, (const uint16_t*)keys, ntiles, ranges);
+    identify_tile_ranges_kernel<uint16_t><<<blocks, 256, 0, stream>>>(D_dev, (const uint16_t*)keys, ntiles, ranges);
   else
-    identify_tile_ranges_kernel<uint32_t><<<(ntiles + 255) / 256, 256, 0, stream>>>(D_dev, (const uint32_t*)keys, ntiles, ranges);
+    identify_tile_ranges_kernel<uint32_t><<<blocks, 256, 0, stream>>>(D_dev, (const uint32_t*)keys, ntiles, ranges);
   return cudaGetLastError();
 }
 

@@ -288,7 +288,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->sort_v0, Nn * 4);
   GS_ENSURE(c, c->sort_v1, Nn * 4);
   GS_ENSURE(c, c->dup_sums, (size_t)(gs_dup_num_blocks(N > 0 ? N : 1) + 1) * 4);
-  GS_ENSURE(c, c->radix_counts, (size_t)256 * (c->radix_grid + 1) * 4);
+  GS_ENSURE(c, c->radix_counts, (size_t)256 * (1024 + 1) * 4);  // RS_MAX_GRID
   GS_ENSURE(c, c->ranges, (size_t)d.ntiles * sizeof(uint2));
   GS_ENSURE(c, c->final_state, P * 16);
   GS_ENSURE(c, c->tile_order, (size_t)d.ntiles * 4);

@@ -17,21 +17,21 @@
 
 #define RS_THREADS 256
 #define RS_WARPS (RS_THREADS / 32)
-#define RS_ITEMS 16
-#define RS_TILE (RS_THREADS * RS_ITEMS)
 #define RS_BINS 256
-#define RS_MAX_GRID 608  // persistent grid size limit (the scan kernel has one thread per chunk)
+#define RS_MAX_GRID 1024  // persistent grid size limit (the scan kernel has one thread per chunk)
+// pairs per thread and tile: 16 (4096-pair tiles) for the multi-million pair lists; 8 (2048-pair tiles, twice the
+// blocks, half the serial ranking rounds per block) for the N-sized depth argsort, which is latency-bound
 
 struct RadixChunk {
   uint32_t begin, end;  // element range of this block
 };
 
-__device__ __forceinline__ RadixChunk radix_chunk(uint32_t n) {
-  const uint32_t tiles = (n + RS_TILE - 1) / RS_TILE;
+__device__ __forceinline__ RadixChunk radix_chunk(uint32_t n, uint32_t tile) {
+  const uint32_t tiles = (n + tile - 1) / tile;
   const uint32_t tpb = (tiles + gridDim.x - 1) / gridDim.x;
   RadixChunk c;
-  const uint64_t b = (uint64_t)blockIdx.x * tpb * RS_TILE;
-  const uint64_t e = b + (uint64_t)tpb * RS_TILE;
+  const uint64_t b = (uint64_t)blockIdx.x * tpb * tile;
+  const uint64_t e = b + (uint64_t)tpb * tile;
   c.begin = (uint32_t)(b < n ? b : n);
   c.end = (uint32_t)(e < n ? e : n);
   return c;
@@ -45,16 +45,16 @@ __device__ __forceinline__ RadixChunk radix_chunk(uint32_t n) {
 template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS)
 radix_hist_kernel(const KeyT* __restrict__ keys, uint32_t n_host, const uint32_t* __restrict__ n_dev, int shift,
-                  uint32_t* __restrict__ counts) {
+                  uint32_t tile, uint32_t* __restrict__ counts) {
   __shared__ uint32_t s_hist[RS_WARPS][RS_BINS];
   constexpr int VEC = 16 / sizeof(KeyT);
   const uint32_t n = n_dev ? *n_dev : n_host;
-  const RadixChunk c = radix_chunk(n);
+  const RadixChunk c = radix_chunk(n, tile);
   const int warp = threadIdx.x >> 5;
   for (int k = threadIdx.x; k < RS_WARPS * RS_BINS; k += RS_THREADS) (&s_hist[0][0])[k] = 0;
   __syncthreads();
   uint32_t* h = s_hist[warp];
-  const uint32_t nvec = (c.end - c.begin) / VEC;  // c.begin is a multiple of RS_TILE: 16-byte aligned
+  const uint32_t nvec = (c.end - c.begin) / VEC;  // c.begin is a multiple of the tile size: 16-byte aligned
   const uint4* vp = reinterpret_cast<const uint4*>(keys + c.begin);
   for (uint32_t v = threadIdx.x; v < nvec; v += RS_THREADS) {
     const uint4 q = __ldg(vp + v);
@@ -110,11 +110,12 @@ __global__ void __launch_bounds__(RS_SCAN_THREADS) radix_scan_kernel(uint32_t* _
 }
 
 // vals_in == nullptr: the value of element i is i (first pass of an argsort)
-template <typename KeyT>
+template <typename KeyT, int RS_ITEMS>
 __global__ void __launch_bounds__(RS_THREADS, 4)
 radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ vals_out, uint32_t n_host, const uint32_t* __restrict__ n_dev, int shift,
                      const uint32_t* __restrict__ counts) {
+  constexpr uint32_t RS_TILE = RS_THREADS * RS_ITEMS;
   __shared__ KeyT s_keys[RS_TILE];
   __shared__ uint32_t s_vals[RS_TILE];
   __shared__ uint32_t s_whist[RS_WARPS][RS_BINS + 1];
@@ -124,7 +125,7 @@ radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
   __shared__ uint32_t s_wsum[RS_WARPS];
 
   const uint32_t n = n_dev ? *n_dev : n_host;
-  const RadixChunk c = radix_chunk(n);
+  const RadixChunk c = radix_chunk(n, RS_TILE);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
   {  // first global slot of (digit tid, this block) = all smaller digits + this digit in earlier blocks
@@ -145,7 +146,7 @@ radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
   }
 
   for (uint32_t t0 = c.begin; t0 < c.end; t0 += RS_TILE) {
-    const uint32_t tile_n = min((uint32_t)RS_TILE, c.end - t0);
+    const uint32_t tile_n = min(RS_TILE, c.end - t0);
     for (int k = tid; k < RS_WARPS * (RS_BINS + 1); k += RS_THREADS) (&s_whist[0][0])[k] = 0;
     __syncthreads();
 
@@ -238,13 +239,13 @@ radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
 
 // One full pass.  `counts` must hold 256 * (grid + 1) uint32.  keys_out may be null on the last pass when the
 // sorted keys are not needed.
-template <typename KeyT>
+template <typename KeyT, int ITEMS>
 static cudaError_t radix_pass(const KeyT* keys_in, KeyT* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
                               uint32_t n_host, const uint32_t* n_dev, int shift, uint32_t* counts, int grid,
                               cudaStream_t stream) {
-  radix_hist_kernel<KeyT><<<grid, RS_THREADS, 0, stream>>>(keys_in, n_host, n_dev, shift, counts);
+  radix_hist_kernel<KeyT><<<grid, RS_THREADS, 0, stream>>>(keys_in, n_host, n_dev, shift, RS_THREADS * ITEMS, counts);
   radix_scan_kernel<<<RS_BINS, RS_SCAN_THREADS, 0, stream>>>(counts, (uint32_t)grid);
-  radix_scatter_kernel<KeyT><<<grid, RS_THREADS, 0, stream>>>(keys_in, keys_out, vals_in, vals_out, n_host, n_dev, shift,
-                                                              counts);
+  radix_scatter_kernel<KeyT, ITEMS><<<grid, RS_THREADS, 0, stream>>>(keys_in, keys_out, vals_in, vals_out, n_host, n_dev,
+                                                                     shift, counts);
   return cudaGetLastError();
 }
