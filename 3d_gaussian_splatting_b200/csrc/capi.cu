@@ -31,11 +31,17 @@ cudaError_t gs_launch_blend_forward(const GsDims&, const uint32_t*, const uint2*
 cudaError_t gs_launch_blend_backward(const GsDims&, const uint2*, const uint32_t*, const GsGeom*, const float[3],
                                      const float4*, const uint32_t*, const float*, const float4*, const uint2*,
                                      const uint32_t*, uint32_t*, const uint32_t*, float4*, int, cudaStream_t);
-cudaError_t gs_launch_preprocess_backward(const gs_settings&, const gs_gaussians&, const gs_gradients&, int,
+cudaError_t gs_launch_preprocess_backward(const gs_settings&, const gs_gaussians&, const gs_gradients&, int, int,
                                           const int*, const uint8_t*, const float4*, cudaStream_t);
+cudaError_t gs_launch_adam_peer(int, int, int, int, float* const[], const float* const[], float* const[6],
+                                float* const[6], const int[6], const double[6], const long long[6], double, double,
+                                double, const int*, const float*, int*, float*, float*, const float*, cudaStream_t);
 cudaError_t gs_launch_adam(int, float* const[6], float* const[6], float* const[6], float* const[6], const int[6],
                            const double[6], const long long[6], double, double, double, const int*, const float*, int*,
                            float*, float*, int, const float*, cudaStream_t);
+cudaError_t gs_launch_adam_counts(int, int, float* const[], float* const[], float* const[], float* const[],
+                                  const size_t[], const double[], const long long[], double, double, double,
+                                  const int*, const float*, int*, float*, float*, int, const float*, cudaStream_t);
 cudaError_t gs_launch_l1_loss(size_t, const float*, const float*, float, float*, double*, float*, cudaStream_t);
 size_t gs_ssim_workspace_bytes(int H, int W);
 cudaError_t gs_launch_photometric_loss(int, int, const float*, const float*, float, float*, double*, float*, float*,
@@ -70,6 +76,12 @@ struct gs_ctx {
   uint64_t dup_cap_fixed = 0;         // > 0: caller-fixed pair capacity, no host synchronisation in gs_forward
   float* overflow_mirror = nullptr;   // optional caller-owned device float raised to 1.0 on overflow
   bool D_pending = false;             // D of the last forward not yet read back
+  // multi-GPU gradient routing (gs_set_gradient_routing): rows [q*R, (q+1)*R) of the six parameter gradients go
+  // to route_table[q*6 + k] (the slot this rank owns inside rank q's buffer; q == route_rank: local memory)
+  int route_shards = 0, route_rows = 0, route_rank = 0;
+  float* route_table[8 * 6] = {};
+  cudaStream_t route_stream = nullptr;  // the remote shards' K4b launches (NVLink-bound) run beside the local one
+  cudaEvent_t route_fork = nullptr, route_join = nullptr;
   // state of the last forward
   int N = -1, H = 0, W = 0, ntiles = 0;
   uint64_t D = 0;
@@ -196,6 +208,9 @@ void gs_destroy(gs_ctx* c) {
   if (c->d_host_pinned) cudaFreeHost(c->d_host_pinned);
   for (int i = 0; i < 2 * GS_NUM_STAGES; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+  if (c->route_stream) cudaStreamDestroy(c->route_stream);
+  if (c->route_fork) cudaEventDestroy(c->route_fork);
+  if (c->route_join) cudaEventDestroy(c->route_join);
   delete c;
 }
 
@@ -436,9 +451,50 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
   }
   {
     StageTimer t(c, 7, stream);
-    GS_CUDA_CHECK(c, gs_launch_preprocess_backward(*st, *in, *grads, N, (const int*)c->radii.ptr,
-                                                   (const uint8_t*)c->clamped.ptr, (const float4*)c->grad_geom.ptr,
-                                                   stream));
+    if (c->route_shards == 0) {
+      GS_CUDA_CHECK(c, gs_launch_preprocess_backward(*st, *in, *grads, 0, N, (const int*)c->radii.ptr,
+                                                     (const uint8_t*)c->clamped.ptr,
+                                                     (const float4*)c->grad_geom.ptr, stream));
+    } else {
+      // one launch per owner rank, the parameter-gradient sinks re-based so that global row i lands at row
+      // i - q*R of the owner's slot.  Rotated start (own shard last): at any moment every rank stores to a
+      // different peer, so no GPU's NVLink ingress is shared by several senders.
+      if (grads->accumulate || in->colors_precomp || in->cov3D_precomp || !in->sh_rest) {
+        gs_set_error(c, "gradient routing needs the raw split-SH parameter layout and accumulate == 0");
+        return GS_EINVAL;
+      }
+      const int G = c->route_shards, R = c->route_rows;
+      const int wrest = 3 * ((st->max_sh_degree + 1) * (st->max_sh_degree + 1) - 1);
+      // the remote shards go to a side stream: their stores are NVLink-bound and overlap the HBM-bound local shard
+      if (!c->route_stream) {
+        GS_CUDA_CHECK(c, cudaStreamCreateWithFlags(&c->route_stream, cudaStreamNonBlocking));
+        GS_CUDA_CHECK(c, cudaEventCreateWithFlags(&c->route_fork, cudaEventDisableTiming));
+        GS_CUDA_CHECK(c, cudaEventCreateWithFlags(&c->route_join, cudaEventDisableTiming));
+      }
+      GS_CUDA_CHECK(c, cudaEventRecord(c->route_fork, stream));
+      GS_CUDA_CHECK(c, cudaStreamWaitEvent(c->route_stream, c->route_fork, 0));
+      for (int j = 1; j <= G; ++j) {
+        const int q = (c->route_rank + j) % G;
+        cudaStream_t ls = q == c->route_rank ? stream : c->route_stream;
+        const long long b = (long long)q * R, e = b + R < N ? b + R : N;
+        if (b >= e) continue;
+        float* const* t = c->route_table + q * 6;
+        gs_gradients g = *grads;
+        g.dL_dmeans3D = t[0] - 3 * b;
+        g.dL_dsh_dc = t[1] - 3 * b;
+        g.dL_dsh_rest = wrest > 0 ? t[2] - (long long)wrest * b : nullptr;
+        g.dL_dopacities = t[3] - b;
+        g.dL_dscales = t[4] - 3 * b;
+        g.dL_drotations = t[5] - 4 * b;
+        g.sh_dc_stride = 3;
+        g.sh_rest_stride = wrest;
+        GS_CUDA_CHECK(c, gs_launch_preprocess_backward(*st, *in, g, (int)b, (int)e, (const int*)c->radii.ptr,
+                                                       (const uint8_t*)c->clamped.ptr,
+                                                       (const float4*)c->grad_geom.ptr, ls));
+      }
+      GS_CUDA_CHECK(c, cudaEventRecord(c->route_join, c->route_stream));
+      GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->route_join, 0));
+    }
   }
   if (st->debug) {
     GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
@@ -471,6 +527,141 @@ int gs_adam_densify_step(gs_ctx* c, int N, float* const params[6], float* const 
   GS_CUDA_CHECK(c, gs_launch_adam(N, params, grads, exp_avg, exp_avg_sq, widths, lr, step, beta1, beta2, eps, radii,
                                   dL_dmeans2D, max_radii2D, xyz_grad_accum, denom, zero_grads, skip_guard,
                                   (cudaStream_t)stream_));
+  return GS_OK;
+}
+
+int gs_adam_step_flat(gs_ctx* c, int nseg, float* const params[], float* const grads[], float* const exp_avg[],
+                      float* const exp_avg_sq[], const unsigned long long counts[], const double lr[],
+                      const long long step[], double beta1, double beta2, double eps, int zero_grads,
+                      const float* skip_guard, void* stream_) {
+  if (!c || nseg < 0 || nseg > 6 || (nseg > 0 && (!params || !grads || !exp_avg || !exp_avg_sq || !counts || !lr || !step))) {
+    gs_set_error(c, "gs_adam_step_flat: bad argument (at most 6 segments)");
+    return GS_EINVAL;
+  }
+  size_t cnt[6] = {0, 0, 0, 0, 0, 0};
+  for (int s = 0; s < nseg; ++s) {
+    cnt[s] = (size_t)counts[s];
+    if (cnt[s] > 0 && (!params[s] || !grads[s] || !exp_avg[s] || !exp_avg_sq[s])) {
+      gs_set_error(c, "segment %d: null pointer", s);
+      return GS_EINVAL;
+    }
+    if (step[s] < 1) {
+      gs_set_error(c, "segment %d: step must be >= 1 (libtorch increments before use)", s);
+      return GS_EINVAL;
+    }
+  }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_CUDA_CHECK(c, gs_launch_adam_counts(0, nseg, params, grads, exp_avg, exp_avg_sq, cnt, lr, step, beta1, beta2, eps,
+                                         nullptr, nullptr, nullptr, nullptr, nullptr, zero_grads, skip_guard,
+                                         (cudaStream_t)stream_));
+  return GS_OK;
+}
+
+int gs_set_gradient_routing(gs_ctx* c, int nranks, int rank, int rows_per_shard, float* const table[]) {
+  if (!c) return GS_EINVAL;
+  if (nranks == 0) {
+    c->route_shards = 0;
+    return GS_OK;
+  }
+  if (nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks || rows_per_shard <= 0 || rows_per_shard % 128 || !table) {
+    gs_set_error(c, "gs_set_gradient_routing: 1..8 ranks, rows_per_shard a positive multiple of 128");
+    return GS_EINVAL;
+  }
+  for (int i = 0; i < nranks * 6; ++i) {
+    if (!table[i] || ((uintptr_t)table[i] & 15)) {
+      gs_set_error(c, "gs_set_gradient_routing: slot %d null or not 16-byte aligned", i);
+      return GS_EINVAL;
+    }
+    c->route_table[i] = table[i];
+  }
+  c->route_shards = nranks;
+  c->route_rank = rank;
+  c->route_rows = rows_per_shard;
+  return GS_OK;
+}
+
+int gs_adam_step_peer(gs_ctx* c, int nranks, int rank, int N, int rows_per_shard, float* const params[],
+                      const float* const slots[], float* const exp_avg[6], float* const exp_avg_sq[6],
+                      const int widths[6], const double lr[6], const long long step[6], double beta1, double beta2,
+                      double eps, const int* radii, const float* dL_dmeans2D, int* max_radii2D,
+                      float* xyz_grad_accum, float* denom, const float* skip_guard, void* stream_) {
+  if (!c || nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks || N < 0 || rows_per_shard <= 0 ||
+      rows_per_shard % 128 || !params || !slots || !exp_avg || !exp_avg_sq || !widths || !lr || !step) {
+    gs_set_error(c, "gs_adam_step_peer: bad argument (1..8 ranks, rows_per_shard a positive multiple of 128)");
+    return GS_EINVAL;
+  }
+  if ((long long)rows_per_shard * nranks < N) {
+    gs_set_error(c, "gs_adam_step_peer: %d shards of %d rows do not cover N = %d", nranks, rows_per_shard, N);
+    return GS_EINVAL;
+  }
+  for (int k = 0; k < 6; ++k) {
+    if (step[k] < 1) {
+      gs_set_error(c, "segment %d: step must be >= 1 (libtorch increments before use)", k);
+      return GS_EINVAL;
+    }
+    if (widths[k] <= 0) continue;
+    bool ok = exp_avg[k] && exp_avg_sq[k] && !((uintptr_t)exp_avg[k] & 15) && !((uintptr_t)exp_avg_sq[k] & 15);
+    for (int r = 0; r < nranks; ++r)
+      ok = ok && params[r * 6 + k] && slots[r * 6 + k] && !((uintptr_t)params[r * 6 + k] & 15) &&
+           !((uintptr_t)slots[r * 6 + k] & 15);
+    if (!ok) {
+      gs_set_error(c, "segment %d: null or unaligned pointer", k);
+      return GS_EINVAL;
+    }
+  }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_CUDA_CHECK(c, gs_launch_adam_peer(nranks, rank, N, rows_per_shard, params, slots, exp_avg, exp_avg_sq, widths, lr,
+                                       step, beta1, beta2, eps, radii, dL_dmeans2D, max_radii2D, xyz_grad_accum,
+                                       denom, skip_guard, (cudaStream_t)stream_));
+  return GS_OK;
+}
+
+// ---- peer memory (one process per GPU, NVLink): plain cudaMalloc + CUDA IPC handles ----
+int gs_peer_alloc(gs_ctx* c, unsigned long long bytes, void** ptr, unsigned char handle[64]) {
+  if (!c || !ptr || !handle) {
+    gs_set_error(c, "gs_peer_alloc: null argument");
+    return GS_EINVAL;
+  }
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  void* p = nullptr;
+  GS_CUDA_CHECK(c, cudaMalloc(&p, (size_t)bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    gs_set_error(c, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+    return GS_ECUDA;
+  }
+  GS_CUDA_CHECK(c, cudaMemset(p, 0, (size_t)bytes));
+  memcpy(handle, &h, 64);
+  *ptr = p;
+  return GS_OK;
+}
+
+int gs_peer_open(gs_ctx* c, const unsigned char handle[64], void** ptr) {
+  if (!c || !ptr || !handle) {
+    gs_set_error(c, "gs_peer_open: null argument");
+    return GS_EINVAL;
+  }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, 64);
+  GS_CUDA_CHECK(c, cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return GS_OK;
+}
+
+int gs_peer_close(gs_ctx* c, void* ptr) {
+  if (!c) return GS_EINVAL;
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_CUDA_CHECK(c, cudaIpcCloseMemHandle(ptr));
+  return GS_OK;
+}
+
+int gs_peer_free(gs_ctx* c, void* ptr) {
+  if (!c) return GS_EINVAL;
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_CUDA_CHECK(c, cudaFree(ptr));
   return GS_OK;
 }
 

@@ -113,26 +113,29 @@ __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_
   }
 }
 
-cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6], float* const exp_avg[6],
-                           float* const exp_avg_sq[6], const int widths[6], const double lr[6],
-                           const long long step[6], double beta1, double beta2, double eps, const int* radii,
-                           const float* dL_dmeans2D, int* max_radii2D, float* xyz_grad_accum, float* denom,
-                           int zero_grads, const float* skip_guard, cudaStream_t stream) {
+// counts[s]: floats in segment s (0 = absent)
+cudaError_t gs_launch_adam_counts(int N, int nseg, float* const params[], float* const grads[], float* const exp_avg[],
+                                  float* const exp_avg_sq[], const size_t counts[], const double lr[],
+                                  const long long step[], double beta1, double beta2, double eps, const int* radii,
+                                  const float* dL_dmeans2D, int* max_radii2D, float* xyz_grad_accum, float* denom,
+                                  int zero_grads, const float* skip_guard, cudaStream_t stream) {
   AdamArgs a;
   int blocks = 0;
   for (int s = 0; s < 6; ++s) {
     AdamSeg& g = a.seg[s];
-    g.p = params[s];
-    g.g = grads[s];
-    g.m = exp_avg[s];
-    g.v = exp_avg_sq[s];
-    g.n = (params[s] && widths[s] > 0) ? (size_t)N * widths[s] : 0;
+    const bool on = s < nseg && params[s] && counts[s] > 0;
+    g.p = on ? params[s] : nullptr;
+    g.g = on ? grads[s] : nullptr;
+    g.m = on ? exp_avg[s] : nullptr;
+    g.v = on ? exp_avg_sq[s] : nullptr;
+    g.n = on ? counts[s] : 0;
     g.block_start = blocks;
     g.vec_ok = ((((uintptr_t)g.p | (uintptr_t)g.g | (uintptr_t)g.m | (uintptr_t)g.v) & 15) == 0);
     // libtorch evaluates the bias corrections in double and applies them as fp32 scalars
-    const double bc1 = 1.0 - pow(beta1, (double)step[s]);
-    const double bc2 = 1.0 - pow(beta2, (double)step[s]);
-    g.neg_step = (float)(-(lr[s] / bc1));
+    const long long st = on ? step[s] : 1;
+    const double bc1 = 1.0 - pow(beta1, (double)st);
+    const double bc2 = 1.0 - pow(beta2, (double)st);
+    g.neg_step = (float)(-((on ? lr[s] : 0.0) / bc1));
     g.inv_bc2_sqrt = 1.0f / (float)sqrt(bc2);
     blocks += (int)((g.n + AD_FLOATS_PER_BLOCK - 1) / AD_FLOATS_PER_BLOCK);
   }
@@ -155,6 +158,174 @@ cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6],
   a.denom = denom;
   if (blocks == 0) return cudaSuccess;
   adam_stats_kernel<<<blocks, AD_THREADS, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
+cudaError_t gs_launch_adam(int N, float* const params[6], float* const grads[6], float* const exp_avg[6],
+                           float* const exp_avg_sq[6], const int widths[6], const double lr[6],
+                           const long long step[6], double beta1, double beta2, double eps, const int* radii,
+                           const float* dL_dmeans2D, int* max_radii2D, float* xyz_grad_accum, float* denom,
+                           int zero_grads, const float* skip_guard, cudaStream_t stream) {
+  size_t counts[6];
+  for (int s = 0; s < 6; ++s) counts[s] = (params[s] && widths[s] > 0) ? (size_t)N * widths[s] : 0;
+  return gs_launch_adam_counts(N, 6, params, grads, exp_avg, exp_avg_sq, counts, lr, step, beta1, beta2, eps, radii,
+                               dL_dmeans2D, max_radii2D, xyz_grad_accum, denom, zero_grads, skip_guard, stream);
+}
+
+// ---- sharded step over peer memory (multi-GPU, one process per GPU) ----
+// Rank r owns the Gaussians [r*R, (r+1)*R).  The backward of every rank has stored its gradient rows for this
+// shard straight into this rank's slot buffers (K4b writes through NVLink, preprocess_bwd.cu); this kernel sums
+// the G slots in RANK ORDER (deterministic; for G = 2 the same value as any all-reduce), applies Adam to the
+// owned rows (moments exist only here) and stores the new parameters into the replica of EVERY rank -- its own
+// through HBM, the others through NVLink -- so reduce-scatter, optimiser and all-gather are one pass over the
+// shard with no staging copy.
+#define ADP_MAX_RANKS 8
+struct AdamPeerSeg {
+  float* p;                         // own replica, at the shard's first row
+  float* m;
+  float* v;
+  const float* src[ADP_MAX_RANKS];  // gradient slots (local memory), one per source rank
+  float* dst[ADP_MAX_RANKS - 1];    // the other ranks' replicas (peer memory), at the shard's first row
+  size_t n;
+  int block_start;
+  float neg_step, inv_bc2_sqrt;
+};
+struct AdamPeerArgs {
+  AdamPeerSeg seg[6];
+  int stats_block_start, total_blocks;
+  float b1, b2, omb1, omb2, eps;
+  const float* skip_guard;
+  int N;
+  const int* radii;
+  const float* dL_dmeans2D;
+  int* max_radii2D;
+  float* xyz_grad_accum;
+  float* denom;
+};
+
+template <int G>
+__global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_constant__ AdamPeerArgs a) {
+  if (a.skip_guard && __ldg(a.skip_guard) != 0.0f) return;
+  const int b = blockIdx.x;
+  if (b >= a.stats_block_start) {
+    const int i = (b - a.stats_block_start) * AD_THREADS + threadIdx.x;
+    if (i < a.N) {
+      const int r = a.radii[i];
+      if (r > 0) {
+        if (r > a.max_radii2D[i]) a.max_radii2D[i] = r;
+        const float2 g = reinterpret_cast<const float2*>(a.dL_dmeans2D)[i];
+        a.xyz_grad_accum[i] += __fsqrt_rn(__fadd_rn(__fmul_rn(g.x, g.x), __fmul_rn(g.y, g.y)));
+        a.denom[i] += 1.0f;
+      }
+    }
+    return;
+  }
+  int si = 0;
+#pragma unroll
+  for (int k = 1; k < 6; ++k)
+    if (b >= a.seg[k].block_start) si = k;
+  const AdamPeerSeg& s = a.seg[si];
+  const float b1 = a.b1, b2 = a.b2, omb1 = a.omb1, omb2 = a.omb2, eps = a.eps;
+  const float neg_step = s.neg_step, inv_bc2_sqrt = s.inv_bc2_sqrt;
+  constexpr int FPB = AD_THREADS * 4;  // one float4 per thread: G + 3 vector loads in flight
+  const size_t base = (size_t)(b - s.block_start) * FPB;
+  if (base + FPB <= s.n) {
+    const size_t v0 = base / 4 + threadIdx.x;
+    float4 g = __ldcs(reinterpret_cast<const float4*>(s.src[0]) + v0);
+    float4 gs[G > 1 ? G - 1 : 1];
+#pragma unroll
+    for (int r = 1; r < G; ++r) gs[r - 1] = __ldcs(reinterpret_cast<const float4*>(s.src[r]) + v0);
+    float4 m = __ldcs(reinterpret_cast<const float4*>(s.m) + v0);
+    float4 v = __ldcs(reinterpret_cast<const float4*>(s.v) + v0);
+    float4 p = __ldcs(reinterpret_cast<const float4*>(s.p) + v0);
+#pragma unroll
+    for (int r = 1; r < G; ++r) {
+      g.x = __fadd_rn(g.x, gs[r - 1].x);
+      g.y = __fadd_rn(g.y, gs[r - 1].y);
+      g.z = __fadd_rn(g.z, gs[r - 1].z);
+      g.w = __fadd_rn(g.w, gs[r - 1].w);
+    }
+    adam_one(p.x, g.x, m.x, v.x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+    adam_one(p.y, g.y, m.y, v.y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+    adam_one(p.z, g.z, m.z, v.z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+    adam_one(p.w, g.w, m.w, v.w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+#pragma unroll
+    for (int r = 0; r < G - 1; ++r) reinterpret_cast<float4*>(s.dst[r])[v0] = p;  // NVLink stores first
+    __stcs(reinterpret_cast<float4*>(s.m) + v0, m);
+    __stcs(reinterpret_cast<float4*>(s.v) + v0, v);
+    reinterpret_cast<float4*>(s.p)[v0] = p;   // read again by the next forward: normal caching
+  } else {
+    for (size_t idx = base + threadIdx.x; idx < s.n && idx < base + FPB; idx += AD_THREADS) {
+      float g = s.src[0][idx];
+#pragma unroll
+      for (int r = 1; r < G; ++r) g = __fadd_rn(g, s.src[r][idx]);
+      float p = s.p[idx], m = s.m[idx], v = s.v[idx];
+      adam_one(p, g, m, v, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+#pragma unroll
+      for (int r = 0; r < G - 1; ++r) s.dst[r][idx] = p;
+      s.p[idx] = p;
+      s.m[idx] = m;
+      s.v[idx] = v;
+    }
+  }
+}
+
+// params[r*6+k]: rank r's (N, widths[k]) array (r == rank: local, else peer-mapped); slots[s*6+k]: the local slot
+// for source rank s (R x widths[k]); exp_avg / exp_avg_sq: shard-local (R x widths[k]).
+cudaError_t gs_launch_adam_peer(int nranks, int rank, int N, int R, float* const params[],
+                                const float* const slots[], float* const exp_avg[6], float* const exp_avg_sq[6],
+                                const int widths[6], const double lr[6], const long long step[6], double beta1,
+                                double beta2, double eps, const int* radii, const float* dL_dmeans2D,
+                                int* max_radii2D, float* xyz_grad_accum, float* denom, const float* skip_guard,
+                                cudaStream_t stream) {
+  AdamPeerArgs a;
+  const long long row0 = (long long)rank * R;
+  const long long rows = row0 >= N ? 0 : ((long long)N - row0 < R ? (long long)N - row0 : (long long)R);
+  int blocks = 0;
+  for (int k = 0; k < 6; ++k) {
+    AdamPeerSeg& g = a.seg[k];
+    const bool on = widths[k] > 0 && rows > 0 && params[rank * 6 + k];
+    const size_t off = (size_t)row0 * widths[k];
+    g.p = on ? params[rank * 6 + k] + off : nullptr;
+    g.m = on ? exp_avg[k] : nullptr;
+    g.v = on ? exp_avg_sq[k] : nullptr;
+    for (int s = 0; s < ADP_MAX_RANKS; ++s) g.src[s] = (on && s < nranks) ? slots[s * 6 + k] : nullptr;
+    int d = 0;
+    for (int r = 0; r < nranks; ++r)
+      if (r != rank) g.dst[d++] = on ? params[r * 6 + k] + off : nullptr;
+    for (; d < ADP_MAX_RANKS - 1; ++d) g.dst[d] = nullptr;
+    g.n = on ? (size_t)rows * widths[k] : 0;
+    g.block_start = blocks;
+    const long long st = on ? step[k] : 1;
+    const double bc1 = 1.0 - pow(beta1, (double)st);
+    const double bc2 = 1.0 - pow(beta2, (double)st);
+    g.neg_step = (float)(-((on ? lr[k] : 0.0) / bc1));
+    g.inv_bc2_sqrt = 1.0f / (float)sqrt(bc2);
+    blocks += (int)((g.n + AD_THREADS * 4 - 1) / (AD_THREADS * 4));
+  }
+  a.stats_block_start = blocks;
+  const bool stats = radii && dL_dmeans2D && max_radii2D && xyz_grad_accum && denom;
+  if (stats) blocks += (N + AD_THREADS - 1) / AD_THREADS;
+  a.total_blocks = blocks;
+  a.b1 = (float)beta1;
+  a.b2 = (float)beta2;
+  a.omb1 = (float)(1.0 - beta1);
+  a.omb2 = (float)(1.0 - beta2);
+  a.eps = (float)eps;
+  a.skip_guard = skip_guard;
+  a.N = N;
+  a.radii = radii;
+  a.dL_dmeans2D = dL_dmeans2D;
+  a.max_radii2D = max_radii2D;
+  a.xyz_grad_accum = xyz_grad_accum;
+  a.denom = denom;
+  if (blocks == 0) return cudaSuccess;
+  switch (nranks) {
+#define ADP_CASE(G) case G: adam_peer_kernel<G><<<blocks, AD_THREADS, 0, stream>>>(a); break;
+    ADP_CASE(1) ADP_CASE(2) ADP_CASE(3) ADP_CASE(4) ADP_CASE(5) ADP_CASE(6) ADP_CASE(7) ADP_CASE(8)
+#undef ADP_CASE
+    default: return cudaErrorInvalidValue;
+  }
   return cudaGetLastError();
 }
 

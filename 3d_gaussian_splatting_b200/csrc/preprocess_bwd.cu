@@ -438,11 +438,12 @@ preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_
 #define PBB_SMEM_BYTES (PBB_FLOATS * 4 + 16)
 
 __global__ void __launch_bounds__(PBB_ROWS)
-preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a) {
+preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a,
+                                const int first) {
   extern __shared__ __align__(128) float s_buf[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_buf + PBB_FLOATS);
   const int tid = threadIdx.x;
-  const size_t row0 = (size_t)blockIdx.x * PBB_ROWS;
+  const size_t row0 = (size_t)first + (size_t)blockIdx.x * PBB_ROWS;
   const size_t i = row0 + tid;
   const int W = a.rest_width_max;  // == sh_rest_stride (dense rows), 0..45
   const bool load_sh = a.rest_width_act > 0;
@@ -523,14 +524,16 @@ preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __
 
 static bool aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 
-cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussians& in, const gs_gradients& out, int N,
-                                          const int* radii, const uint8_t* clamped, const float4* grad_geom,
-                                          cudaStream_t stream) {
-  if (N == 0) return cudaSuccess;
+// Rows [row_begin, row_end) only (the whole model: 0, N).  The multi-GPU step launches one range per owner rank
+// with the parameter-gradient sinks pointing into that rank's slot buffer (capi.cu, gradient routing).
+cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussians& in, const gs_gradients& out,
+                                          int row_begin, int row_end, const int* radii, const uint8_t* clamped,
+                                          const float4* grad_geom, cudaStream_t stream) {
+  if (row_end <= row_begin) return cudaSuccess;
   PreBwdArgs a;
   a.in = in;
   a.out = out;
-  a.N = N;
+  a.N = row_end;
   a.radii = radii;
   a.clamped = clamped;
   a.grad_geom = grad_geom;
@@ -552,8 +555,9 @@ cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussi
                      aligned16(out.dL_dscales) && aligned16(out.dL_drotations) && aligned16(out.dL_dopacities) &&
                      aligned16(out.dL_dmeans2D) && aligned16(out.dL_dsh_dc) && aligned16(out.dL_dsh_rest) &&
                      aligned16(grad_geom);
-  int first = 0;
-  if (dense && N >= PBB_ROWS) {
+  int first = row_begin;
+  const int N = row_end - row_begin;
+  if (dense && N >= PBB_ROWS && row_begin % 4 == 0) {
     static bool attr_set = false;
     if (!attr_set) {
       cudaError_t e = cudaFuncSetAttribute(preprocess_backward_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -562,12 +566,12 @@ cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussi
       attr_set = true;
     }
     const int blocks = N / PBB_ROWS;
-    preprocess_backward_bulk_kernel<<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a);
-    first = blocks * PBB_ROWS;
+    preprocess_backward_bulk_kernel<<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, first);
+    first += blocks * PBB_ROWS;
   }
-  if (first < N) {
+  if (first < row_end) {
     const size_t smem = a.rest_width_max > 0 ? (size_t)PB_THREADS * a.pitch * sizeof(float) : 0;
-    const int blocks = (N - first + PB_THREADS - 1) / PB_THREADS;
+    const int blocks = (row_end - first + PB_THREADS - 1) / PB_THREADS;
     preprocess_backward_kernel<<<blocks, PB_THREADS, smem, stream>>>(st, a, first);
   }
   return cudaGetLastError();

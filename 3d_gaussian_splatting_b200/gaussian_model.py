@@ -175,6 +175,21 @@ class Trainer:
         self._guard_tensor = None
         self.skip_guard = None          # device float the Adam step honours (all-reduced slab tail when multi-GPU)
         self.retries = 0
+        self.peer = None                # multi-GPU: parallel.PeerShardedAdam (exchange fused into K4b / K5)
+        self.sharded = None             # multi-GPU: parallel.ShardedAdam (reduce-scatter / sharded Adam / all-gather)
+
+    def shard_optimizer(self, rank: int, world: int, group=None):
+        """Shard the Adam state over the ranks (parallel.ShardedAdam).  Call before reserve_pairs()."""
+        from . import parallel
+        adam = lambda segs, guard: self.rast.adam_step_flat(segs, skip_guard=guard)
+        self.sharded = parallel.ShardedAdam(self.g, rank, world, adam, group=group)
+        return self.sharded
+
+    def shard_optimizer_peer(self, rank: int, world: int, group=None):
+        """Fused multi-GPU step over peer memory (parallel.PeerShardedAdam).  Call before reserve_pairs()."""
+        from . import parallel
+        self.peer = parallel.PeerShardedAdam(self.g, self.rast, rank, world, group=group)
+        return self.peer
 
     def reserve_pairs(self, pairs: int, guard: torch.Tensor | None = None):
         """Fix the (tile, Gaussian) pair capacity so that forwards run without synchronising the host.  An
@@ -219,6 +234,18 @@ class Trainer:
     def optimizer_step(self, radii):
         g = self.g
         g.step_count = [s + 1 for s in g.step_count]
+        if self.peer is not None:
+            self.peer.step(g.lr, g.step_count, radii=radii, dL_dmeans2D=g.grad_means2D, max_radii2D=g.max_radii2D_,
+                           xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_, use_guard=bool(self.pair_capacity))
+            return
+        if self.sharded is not None:
+            self.sharded.step(g.lr, g.step_count, use_guard=bool(self.pair_capacity))
+            none6 = [None] * 6    # statistics only (per-rank partial sums, merged when consumed)
+            self.rast.adam_densify_step(g.N, none6, none6, none6, none6, g.widths, g.lr, g.step_count, radii=radii,
+                                        dL_dmeans2D=g.grad_means2D, max_radii2D=g.max_radii2D_,
+                                        xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_,
+                                        skip_guard=self.skip_guard if self.pair_capacity else None)
+            return
         self.rast.adam_densify_step(g.N, g.params(), g.grads, g.exp_avg, g.exp_avg_sq, g.widths, g.lr, g.step_count,
                                     radii=radii, dL_dmeans2D=g.grad_means2D, max_radii2D=g.max_radii2D_,
                                     xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_,

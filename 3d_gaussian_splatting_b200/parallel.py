@@ -61,3 +61,175 @@ def merge_densify_stats(max_radii2D: torch.Tensor, xyz_gradient_accum: torch.Ten
         dist.all_reduce(denom, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(max_radii2D, op=dist.ReduceOp.MAX, group=group)
     return max_radii2D, xyz_gradient_accum, denom
+
+
+class ShardedAdam:
+    """Optimiser state sharded across the ranks (ZeRO-1 shape, but over ONE flat slab of 59 floats per Gaussian):
+
+        gradients   : reduce-scatter   -> every rank holds the SUM over ranks of its 1/world slice
+        Adam        : each rank updates the slice of the parameter slab it owns (moments exist only there)
+        parameters  : all-gather (in place) -> every rank holds the updated replica again
+
+    Same bytes on the wire as the all-reduce it replaces, but the Adam step -- the HBM-bound 16 B/float kernel that
+    is the largest single stage of a step -- shrinks by 1/world, and so does the moment memory.
+    The model's six parameter tensors (and gradient sinks) are re-bound as views of two flat slabs, each group
+    16-byte aligned, the total padded to world * align floats so that every slice boundary is kernel-friendly.
+
+    adam_fn(segments, skip_guard): segments = [(p, g, m, v, lr, step), ...] 1-D views of equal length -- the
+    rasterizer's adam_step_flat on the GPU; a plain callable in the gloo tests.
+    """
+
+    def __init__(self, model, rank: int, world: int, adam_fn, group=None, align: int = 1024):
+        params = model.params()
+        self.model, self.rank, self.world, self.group, self.adam_fn = model, rank, world, group, adam_fn
+        self.sizes = [int(p.numel()) for p in params]
+        self.offsets, off = [], 0
+        for s in self.sizes:
+            self.offsets.append(off)
+            off += (s + 3) // 4 * 4
+        q = world * align
+        self.total = (off + q - 1) // q * q
+        self.shard_len = self.total // world
+        self.lo, self.hi = rank * self.shard_len, (rank + 1) * self.shard_len
+        dev = params[0].device
+        self.param_slab = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        self.grad_slab = torch.zeros(self.total, dtype=torch.float32, device=dev)
+        self.grad_shard = torch.zeros(self.shard_len, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(self.shard_len, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(self.shard_len, dtype=torch.float32, device=dev)
+        self.guard = torch.zeros(1, dtype=torch.float32, device=dev)
+        views = []
+        for o, s, p in zip(self.offsets, self.sizes, params):
+            v = self.param_slab[o:o + s].view_as(p)
+            v.copy_(p)
+            views.append(v)
+        (model.xyz_, model.features_dc_, model.features_rest_, model.opacity_, model.scaling_, model.rotation_) = views
+        model.grads = [self.grad_slab[o:o + s].view_as(p) for o, s, p in zip(self.offsets, self.sizes, params)]
+        model.exp_avg = model.exp_avg_sq = None     # the dense moments are not used (and not kept) in this mode
+        # the pieces of the owned slice, cut at the parameter-group boundaries: (group, start, stop) in slab floats
+        self.pieces = [(k, max(o, self.lo), min(o + s, self.hi)) for k, (o, s) in enumerate(zip(self.offsets, self.sizes))
+                       if max(o, self.lo) < min(o + s, self.hi)]
+        b = dist.get_backend(group) if dist.is_initialized() else "none"
+        self._native = (b == "nccl")   # gloo has neither reduce_scatter_tensor nor in-place all_gather_into_tensor
+
+    def segments(self, lr, step):
+        lo = self.lo
+        return [(self.param_slab[a:b], self.grad_shard[a - lo:b - lo], self.exp_avg[a - lo:b - lo],
+                 self.exp_avg_sq[a - lo:b - lo], lr[k], step[k]) for k, a, b in self.pieces]
+
+    def step(self, lr, step, use_guard: bool = False):
+        """lr / step: per-group learning rates and (already incremented) step counts.  The gradient slab is
+        consumed (left zeroed for the next backward when the backward accumulates; the plain backward overwrites)."""
+        multi = dist.is_initialized() and self.world > 1
+        if multi and use_guard:    # a rank whose forward overflowed its pair capacity makes EVERY rank skip the step
+            dist.all_reduce(self.guard, op=dist.ReduceOp.MAX, group=self.group)
+        if not multi:
+            self.grad_shard.copy_(self.grad_slab)
+        elif self._native:
+            dist.reduce_scatter_tensor(self.grad_shard, self.grad_slab, op=dist.ReduceOp.SUM, group=self.group)
+        else:
+            dist.all_reduce(self.grad_slab, op=dist.ReduceOp.SUM, group=self.group)
+            self.grad_shard.copy_(self.grad_slab[self.lo:self.hi])
+        self.adam_fn(self.segments(lr, step), self.guard if use_guard else None)
+        if not multi:
+            return
+        if self._native:
+            dist.all_gather_into_tensor(self.param_slab, self.param_slab[self.lo:self.hi], group=self.group)
+        else:
+            parts = [torch.empty(self.shard_len, dtype=torch.float32, device=self.param_slab.device)
+                     for _ in range(self.world)]
+            dist.all_gather(parts, self.param_slab[self.lo:self.hi].clone(), group=self.group)
+            self.param_slab.copy_(torch.cat(parts))
+
+
+class PeerShardedAdam:
+    """The multi-GPU step with reduce-scatter, optimiser and all-gather FUSED into the kernels on either side
+    (include/gsplat_b200.h, "the multi-GPU step over peer memory"):
+
+        backward (K4b) : stores the gradient rows of shard q straight into rank q's slot buffer over NVLink
+        barrier 1      : one-float NCCL all-reduce (MAX of the overflow guards)
+        Adam (K5)      : sums the world slots of the owned rows, updates them, stores the new parameters into
+                         every rank's replica over NVLink
+        barrier 2      : one-float NCCL all-reduce
+
+    Per rank and step the wire carries (world-1)/world of the gradient and parameter bytes once each -- the same
+    as reduce-scatter + all-gather -- but no byte is staged, re-read or re-written in HBM for the exchange, and
+    Adam touches 1/world of the model.  Every rank allocates ONE peer-mapped buffer holding its parameter replica
+    and its slot buffer; the 64-byte IPC handles travel through torch.distributed (all_gather_object).
+
+    rast: the rank's Rasterizer.  exchange(handle) -> list of all ranks' handles (default: all_gather_object).
+    """
+
+    def __init__(self, model, rast, rank: int, world: int, group=None):
+        self.model, self.rast, self.rank, self.world, self.group = model, rast, rank, world, group
+        params = model.params()
+        N = self.N = int(params[0].shape[0])
+        self.widths = [int(p.numel() // max(N, 1)) for p in params]
+        R = self.R = ((N + world - 1) // world + 127) // 128 * 128
+        # layout of a rank's buffer (floats): six (N, C) parameter arrays, then world slots of six (R, C) arrays
+        self.p_off, off = [], 0
+        for c in self.widths:
+            self.p_off.append(off)
+            off += (N * c + 3) // 4 * 4
+        self.s_off = []
+        for s in range(world):
+            row = []
+            for c in self.widths:
+                row.append(off)
+                off += R * c
+            self.s_off.append(row)
+        self.total = off
+        self.base, handle = rast.peer_alloc(self.total * 4)
+        handles = [None] * world
+        if world > 1:
+            dist.all_gather_object(handles, handle, group=group)
+        else:
+            handles[0] = handle
+        self.bases = [self.base if r == rank else rast.peer_open(handles[r]) for r in range(world)]
+        self.flat = rast.wrap(self.base, self.total)
+        views = []
+        for o, c, p in zip(self.p_off, self.widths, params):
+            v = self.flat[o:o + N * c].view_as(p)
+            v.copy_(p)
+            views.append(v)
+        (model.xyz_, model.features_dc_, model.features_rest_, model.opacity_, model.scaling_, model.rotation_) = views
+        model.grads = [None] * 6
+        model.exp_avg = [torch.zeros(R * c, dtype=torch.float32, device=self.flat.device) for c in self.widths]
+        model.exp_avg_sq = [torch.zeros(R * c, dtype=torch.float32, device=self.flat.device) for c in self.widths]
+        self.guard = torch.zeros(1, dtype=torch.float32, device=self.flat.device)
+        self.sync = torch.zeros(1, dtype=torch.float32, device=self.flat.device)
+        # params[r][k]: rank r's replica; slots[s][k]: MY slot for source s; routing[q][k]: my slot INSIDE rank q
+        self.param_ptrs = [[self.bases[r] + 4 * self.p_off[k] for k in range(6)] for r in range(world)]
+        self.slot_ptrs = [[self.base + 4 * self.s_off[s][k] for k in range(6)] for s in range(world)]
+        routing = [[self.bases[q] + 4 * self.s_off[rank][k] for k in range(6)] for q in range(world)]
+        rast.set_gradient_routing(world, rank, R, routing)
+        self.barrier()   # every replica initialised and every mapping in place before anyone stores remotely
+
+    def barrier(self):
+        """Stream-ordered barrier across the ranks (one-float NCCL all-reduce)."""
+        if dist.is_initialized() and self.world > 1:
+            dist.all_reduce(self.sync, op=dist.ReduceOp.MAX, group=self.group)
+
+    def slot(self, src: int, k: int) -> torch.Tensor:
+        """The gradient rows source rank `src` stored for my shard, group k: (R, widths[k])."""
+        o = self.s_off[src][k]
+        return self.flat[o:o + self.R * self.widths[k]].view(self.R, self.widths[k])
+
+    def step(self, lr, step, radii=None, dL_dmeans2D=None, max_radii2D=None, xyz_grad_accum=None, denom=None,
+             use_guard: bool = False):
+        m = self.model
+        # barrier 1: every rank's backward has landed in the slots; carries the overflow guard along
+        if dist.is_initialized() and self.world > 1:
+            dist.all_reduce(self.guard, op=dist.ReduceOp.MAX, group=self.group)
+        self.rast.adam_step_peer(self.world, self.rank, self.N, self.R, self.param_ptrs, self.slot_ptrs, m.exp_avg,
+                                 m.exp_avg_sq, self.widths, lr, step, radii=radii, dL_dmeans2D=dL_dmeans2D,
+                                 max_radii2D=max_radii2D, xyz_grad_accum=xyz_grad_accum, denom=denom,
+                                 skip_guard=self.guard if use_guard else None)
+        self.barrier()   # barrier 2: every replica complete before the next forward reads it
+
+    def close(self):
+        self.rast.set_gradient_routing(0)
+        for r, b in enumerate(self.bases):
+            if r != self.rank:
+                self.rast.peer_close(b)
+        self.rast.peer_free(self.base)

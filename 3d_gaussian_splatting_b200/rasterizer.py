@@ -179,6 +179,14 @@ class Rasterizer:
                 grads[name] = (torch.zeros if accumulate else torch.empty)(shape, dtype=torch.float32, device=dev)
             return grads[name]
         gg = GsGradients()
+        if getattr(self, "_routing", False):
+            # gs_set_gradient_routing: the six parameter gradients go to the owner ranks' slot buffers
+            gg.dL_dmeans2D = sink("means2D", (N, 2)).data_ptr()
+            dL = _f32c(dL_dout_color, "dL_dout_color")
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            check(self._ctx, lib.gs_backward(self._ctx, C.byref(st), N, C.byref(pk.g), _ptr(dL), C.byref(gg),
+                                             C.c_void_p(stream)))
+            return grads
         gg.dL_dmeans3D = sink("means3D", (N, 3)).data_ptr()
         gg.dL_dopacities = sink("opacities", (N, 1)).data_ptr()
         gg.dL_dmeans2D = sink("means2D", (N, 2)).data_ptr()
@@ -245,6 +253,77 @@ class Rasterizer:
             (C.c_double * 6)(*[float(x) for x in lr]), (C.c_longlong * 6)(*[int(s) for s in step]), float(beta1),
             float(beta2), float(eps), _ptr(radii), _ptr(dL_dmeans2D), _ptr(max_radii2D), _ptr(xyz_grad_accum),
             _ptr(denom), int(zero_grads), C.c_void_p(skip_guard) if skip_guard else None, C.c_void_p(stream)))
+
+    def adam_step_flat(self, segments, beta1=0.9, beta2=0.999, eps=1e-8, zero_grads=False, skip_guard=None):
+        """Adam over up to six contiguous float ranges: segments = [(p, g, m, v, lr, step), ...] with 1-D views of
+        equal length (the slice of a flat parameter slab a rank owns, cut at the parameter-group boundaries)."""
+        assert len(segments) <= 6
+        VP6 = C.c_void_p * 6
+        pad = lambda xs, fill: list(xs) + [fill] * (6 - len(xs))
+        ptrs = lambda k: VP6(*pad([s[k].data_ptr() for s in segments], None))
+        if isinstance(skip_guard, torch.Tensor):
+            skip_guard = skip_guard.data_ptr()
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._ctx, lib.gs_adam_step_flat(
+            self._ctx, len(segments), ptrs(0), ptrs(1), ptrs(2), ptrs(3),
+            (C.c_ulonglong * 6)(*pad([int(s[0].numel()) for s in segments], 0)),
+            (C.c_double * 6)(*pad([float(s[4]) for s in segments], 0.0)),
+            (C.c_longlong * 6)(*pad([int(s[5]) for s in segments], 1)), float(beta1), float(beta2), float(eps),
+            int(zero_grads), C.c_void_p(skip_guard) if skip_guard else None, C.c_void_p(stream)))
+
+    # ---- multi-GPU step over peer memory --------------------------------------------------------
+    def peer_alloc(self, nbytes: int):
+        """Zero-filled device buffer other processes may map: (device pointer, 64-byte IPC handle)."""
+        ptr, h = C.c_void_p(), C.create_string_buffer(64)
+        check(self._ctx, lib.gs_peer_alloc(self._ctx, int(nbytes), C.byref(ptr), h))
+        return int(ptr.value), bytes(h.raw)
+
+    def peer_open(self, handle: bytes) -> int:
+        ptr = C.c_void_p()
+        check(self._ctx, lib.gs_peer_open(self._ctx, handle, C.byref(ptr)))
+        return int(ptr.value)
+
+    def peer_close(self, ptr: int):
+        check(self._ctx, lib.gs_peer_close(self._ctx, C.c_void_p(ptr)))
+
+    def peer_free(self, ptr: int):
+        check(self._ctx, lib.gs_peer_free(self._ctx, C.c_void_p(ptr)))
+
+    def wrap(self, ptr: int, nfloats: int) -> torch.Tensor:
+        """A float32 torch view of raw device memory (no copy, no ownership)."""
+        class _Raw:
+            pass
+        r = _Raw()
+        r.__cuda_array_interface__ = dict(shape=(int(nfloats),), typestr="<f4", data=(int(ptr), False), version=2)
+        t = torch.as_tensor(r, device=self.device)
+        assert t.data_ptr() == ptr
+        return t
+
+    def set_gradient_routing(self, nranks: int, rank: int = 0, rows_per_shard: int = 0, table=None):
+        """table[q][k]: device pointer of this rank's slot for group k inside rank q's slot buffer; nranks=0: off."""
+        if not nranks:
+            check(self._ctx, lib.gs_set_gradient_routing(self._ctx, 0, 0, 0, None))
+            self._routing = False
+            return
+        flat = (C.c_void_p * (nranks * 6))(*[int(table[q][k]) for q in range(nranks) for k in range(6)])
+        check(self._ctx, lib.gs_set_gradient_routing(self._ctx, nranks, rank, rows_per_shard, flat))
+        self._routing = True
+
+    def adam_step_peer(self, nranks, rank, N, rows_per_shard, params, slots, exp_avg, exp_avg_sq, widths, lr, step,
+                       beta1=0.9, beta2=0.999, eps=1e-8, radii=None, dL_dmeans2D=None, max_radii2D=None,
+                       xyz_grad_accum=None, denom=None, skip_guard=None):
+        """params[r][k] / slots[s][k]: device pointers (ints); exp_avg / exp_avg_sq: six shard-local tensors."""
+        if isinstance(skip_guard, torch.Tensor):
+            skip_guard = skip_guard.data_ptr()
+        tab = lambda t: (C.c_void_p * (nranks * 6))(*[int(t[r][k]) for r in range(nranks) for k in range(6)])
+        VP6 = C.c_void_p * 6
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._ctx, lib.gs_adam_step_peer(
+            self._ctx, nranks, rank, int(N), int(rows_per_shard), tab(params), tab(slots),
+            VP6(*[t.data_ptr() for t in exp_avg]), VP6(*[t.data_ptr() for t in exp_avg_sq]), (C.c_int * 6)(*widths),
+            (C.c_double * 6)(*[float(x) for x in lr]), (C.c_longlong * 6)(*[int(x) for x in step]), float(beta1),
+            float(beta2), float(eps), _ptr(radii), _ptr(dL_dmeans2D), _ptr(max_radii2D), _ptr(xyz_grad_accum),
+            _ptr(denom), C.c_void_p(skip_guard) if skip_guard else None, C.c_void_p(stream)))
 
     def loss(self, image, gt, lambda_dssim=0.0, want_grad=True):
         """(1-lambda)*L1 + lambda*(1-SSIM); returns (loss 1-element device tensor, dL/dimage)."""

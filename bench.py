@@ -42,6 +42,9 @@ def parse_args():
     ap.add_argument("--config", default=DEFAULT_CONFIG)
     ap.add_argument("--views", type=int, default=8, help="distinct camera views cycled per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dp-mode", default="peer", choices=["peer", "sharded", "allreduce"],
+                    help="N>1: peer = exchange fused into K4b/K5 over NVLink peer memory (sharded Adam); sharded = NCCL "
+                         "reduce-scatter + sharded Adam + all-gather; allreduce = NCCL all-reduce + replicated Adam")
     ap.add_argument("--N", type=int, default=None, help="override the Gaussian count (debugging only)")
     return ap.parse_args()
 
@@ -248,10 +251,22 @@ def run_ours(args, rank, world, local_rank):
     opt = gm.OptimizationParams()
     trainer = gm.Trainer(model, opt, bg=(0.0, 0.0, 0.0), lambda_dssim=LAMBDA_DSSIM)
     g = model
-    # one contiguous gradient slab (a single all-reduce per step when world > 1)
-    gslab = par.GradientSlab(g.params())
-    slab = gslab.flat
-    g.grads = gslab.views
+    sharded = None
+    grad_mb = 4e-6 * sum(p.numel() for p in g.params())
+    if world > 1 and args.dp_mode == "peer":
+        # K4b stores gradient rows into the owner's slots over NVLink; K5 sums them, updates the owned shard and
+        # stores the parameters into every replica; two one-float NCCL all-reduces order the ranks
+        sharded = trainer.shard_optimizer_peer(rank, world)
+        slab, guard = None, sharded.guard
+    elif world > 1 and args.dp_mode == "sharded":
+        # gradients reduce-scattered, Adam on the 1/world slice this rank owns, parameters all-gathered
+        sharded = trainer.shard_optimizer(rank, world)
+        slab, guard = sharded.grad_slab, sharded.guard
+    else:
+        # one contiguous gradient slab (a single all-reduce per step when world > 1)
+        gslab = par.GradientSlab(g.params())
+        slab, guard = gslab.flat, gslab.guard
+        g.grads = gslab.views
 
     # ground truth = render of the scene with SH perturbed by N(0, 0.05^2)  
     rng = np.random.Generator(np.random.Philox(99))
@@ -268,9 +283,9 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.synchronize()
     # fixed (tile, Gaussian) pair capacity: the forward then never waits for the host (include/gsplat_b200.h);
     # an overflowing iteration would be skipped on the device and is reported below
-    trainer.reserve_pairs(int(1.3 * max_pairs) + 1024, guard=gslab.guard if world > 1 else None)
+    trainer.reserve_pairs(int(1.3 * max_pairs) + 1024, guard=guard if world > 1 else None)
 
-    if world > 1:
+    if world > 1 and sharded is None:
         trainer.grad_sync = gslab.all_reduce     # ONE NCCL all-reduce of the gradient slab per iteration
 
     def step_device(i):
@@ -374,7 +389,13 @@ def run_ours(args, rank, world, local_rank):
                        "views_per_rank_per_step": 1, "loss": LOSS_NAME, "N_vis": N_vis, "D": D, "D_eff": D_eff,
                        "pixel_gaussian_interactions": interactions,
                        "l2_policy": "inputs larger than L2 (params+Adam state 1.13 GB per step vs 126 MB L2)",
-                       "parallelism": f"camera-sharded dp{world}, one NCCL all-reduce of {slab.numel() * 4 / 1e6:.0f} MB grads per step"
+                       "parallelism": (f"camera-sharded dp{world}, {grad_mb:.0f} MB of gradients per rank: "
+                                       + {"peer": "K4b stores them into the owner ranks' slots over NVLink, K5 sums the "
+                                                  "slots, updates the owned 1/%d of the rows and stores the parameters "
+                                                  "into every replica (2 one-float NCCL all-reduces as barriers)" % world,
+                                          "sharded": "NCCL reduce-scatter -> Adam on the owned 1/%d slice -> NCCL "
+                                                     "all-gather" % world,
+                                          "allreduce": "one NCCL all-reduce, replicated Adam"}[args.dp_mode])
                        if world > 1 else "single GPU"},
             "raster_fwd_bwd_ms": fwd_bwd_ms, "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,
@@ -385,7 +406,9 @@ def run_ours(args, rank, world, local_rank):
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                     "h2d_bytes_per_step": int(gts_host[0].numel() * 4 + 172), "d2h_bytes_per_step": 4},
             "pair_capacity": trainer.pair_capacity, "capacity_retries": trainer.retries,
-            "gpu_launches": OWN_KERNELS_PER_STEP * args.steps,
+            # own kernels only (NCCL's are not counted); the routed K4b of the peer mode is one launch per owner rank
+            "gpu_launches": (OWN_KERNELS_PER_STEP + (world - 1 if world > 1 and args.dp_mode == "peer" else 0)
+                             + (1 if world > 1 and args.dp_mode == "sharded" else 0)) * args.steps,
             "library_launches": LIB_KERNELS_PER_STEP * args.steps,
             "clocks": clocks,
         }), flush=True)

@@ -155,6 +155,52 @@ GS_API int gs_adam_densify_step(gs_ctx *ctx, int N, float *const params[6], floa
                                 float *xyz_grad_accum, float *denom, int zero_grads, const float *skip_guard,
                                 void *stream);
 
+/* The same Adam update over up to six arbitrary contiguous float ranges (counts[s] floats each): the form a
+ * rank uses when the optimiser state is SHARDED across GPUs -- gradients reduce-scattered, each rank updating
+ * the slice of the flat parameter slab it owns (a slice intersects at most the six parameter groups), the
+ * updated parameters all-gathered (3d_gaussian_splatting_b200/parallel.py ShardedAdam).  No statistics. */
+GS_API int gs_adam_step_flat(gs_ctx *ctx, int nseg, float *const params[], float *const grads[],
+                             float *const exp_avg[], float *const exp_avg_sq[], const unsigned long long counts[],
+                             const double lr[], const long long step[], double beta1, double beta2, double eps,
+                             int zero_grads, const float *skip_guard, void *stream);
+
+/* ---- peer memory for the multi-GPU step (one process per GPU on one NVLink / NVSwitch node) ----
+ * gs_peer_alloc: device buffer (zero-filled) that other processes may map; handle = the 64-byte CUDA IPC handle
+ * to hand to the peers (any transport -- the Python host uses torch.distributed).  gs_peer_open maps a peer's
+ * buffer into this process (peer access enabled on demand); kernels then load / store through the returned
+ * pointer over NVLink.  The reference has no multi-device path: B200-native extension. */
+GS_API int gs_peer_alloc(gs_ctx *ctx, unsigned long long bytes, void **ptr, unsigned char handle[64]);
+GS_API int gs_peer_open(gs_ctx *ctx, const unsigned char handle[64], void **ptr);
+GS_API int gs_peer_close(gs_ctx *ctx, void *ptr);
+GS_API int gs_peer_free(gs_ctx *ctx, void *ptr);
+
+/* ---- the multi-GPU step over peer memory: reduce-scatter, optimiser and all-gather fused into K4b and K5 ----
+ * Rank r of nranks (<= 8) OWNS the Gaussians [r*R, (r+1)*R), R = rows_per_shard (a multiple of 128), and holds
+ * the Adam moments of those rows only.  Every rank keeps a full parameter replica and a slot buffer with one
+ * slot per source rank; both are peer-mapped (gs_peer_alloc / gs_peer_open).
+ *
+ * gs_set_gradient_routing: from now on gs_backward stores the six parameter gradients of rows [q*R, (q+1)*R)
+ * through table[q*6 + k] -- this rank's slot inside rank q's buffer (group k in the order xyz, f_dc, f_rest,
+ * opacity, scaling, rotation; (R, widths[k]) floats, 16-byte aligned) -- instead of the gs_gradients sinks
+ * (dL_dmeans2D stays local).  The stores cross NVLink from inside the backward kernel; nothing is staged.
+ * nranks == 0 switches routing off.
+ *
+ * gs_adam_step_peer: sums the nranks slots of the owned rows in rank order, applies the Adam step of
+ * gs_adam_densify_step to them and stores the new parameters into the replica of every rank: params[r*6 + k] is
+ * rank r's (N, widths[k]) array (r == rank: local).  slots[s*6 + k]: the local slot of source rank s.
+ * exp_avg / exp_avg_sq: (R, widths[k]) shard-local moments.  Statistics as in gs_adam_densify_step (per rank).
+ *
+ * Ordering is the caller's: every rank's gs_backward must have completed before any rank's gs_adam_step_peer
+ * runs, and every gs_adam_step_peer before the next gs_forward -- two stream-ordered barriers per step (the
+ * Python host uses a one-float NCCL all-reduce for each: the overflow guard and the loss). */
+GS_API int gs_set_gradient_routing(gs_ctx *ctx, int nranks, int rank, int rows_per_shard, float *const table[]);
+GS_API int gs_adam_step_peer(gs_ctx *ctx, int nranks, int rank, int N, int rows_per_shard, float *const params[],
+                             const float *const slots[], float *const exp_avg[6], float *const exp_avg_sq[6],
+                             const int widths[6], const double lr[6], const long long step[6], double beta1,
+                             double beta2, double eps, const int *radii, const float *dL_dmeans2D,
+                             int *max_radii2D, float *xyz_grad_accum, float *denom, const float *skip_guard,
+                             void *stream);
+
 /* ---- running without the host round-trip ----------------------------------------------------
  * By default gs_forward synchronises the stream once, to size the (tile, Gaussian) pair lists from
  * the data-dependent pair count D.  gs_set_duplicate_capacity(ctx, pairs > 0) fixes the capacity
