@@ -33,6 +33,10 @@ cudaError_t gs_launch_blend_backward(const GsDims&, const uint2*, const uint32_t
                                      const uint32_t*, uint32_t*, const uint32_t*, float4*, int, cudaStream_t);
 cudaError_t gs_launch_preprocess_backward(const gs_settings&, const gs_gaussians&, const gs_gradients&, int, int,
                                           const int*, const uint8_t*, const float4*, cudaStream_t);
+cudaError_t gs_launch_preprocess_backward_adam(const gs_settings&, const gs_gaussians&, float*, int, const int*,
+                                               const uint8_t*, const float4*, float* const[6], float* const[6],
+                                               const double[6], const long long[6], double, double, double, int*,
+                                               float*, float*, const float*, int*, cudaStream_t);
 cudaError_t gs_launch_adam_peer(int, int, int, int, float* const[], const float* const[], float* const[6],
                                 float* const[6], const int[6], const double[6], const long long[6], double, double,
                                 double, const int*, const float*, int*, float*, float*, const float*, cudaStream_t);
@@ -71,11 +75,12 @@ struct gs_ctx {
   // segmented backward: per-segment pixel checkpoints, (tile, segment) work list, {work_count, work_cursor}
   DevBuf ckpt, work_items, counters;
   int num_sms = 148;
-  DevBuf loss_acc, ssim_work;
+  DevBuf loss_acc, ssim_work, tail_grads;
   uint32_t* d_host_pinned = nullptr;  // readback: bytes 0..7 D (u64), 8..11 overflow flag
   uint64_t dup_cap_fixed = 0;         // > 0: caller-fixed pair capacity, no host synchronisation in gs_forward
   float* overflow_mirror = nullptr;   // optional caller-owned device float raised to 1.0 on overflow
   bool D_pending = false;             // D of the last forward not yet read back
+  bool reuse_blend_gradients = false; // test hook: gs_backward_adam_step consumes the records of the last gs_backward
   // multi-GPU gradient routing (gs_set_gradient_routing): rows [q*R, (q+1)*R) of the six parameter gradients go
   // to route_table[q*6 + k] (the slot this rank owns inside rank q's buffer; q == route_rank: local memory)
   int route_shards = 0, route_rows = 0, route_rank = 0;
@@ -202,7 +207,8 @@ void gs_destroy(gs_ctx* c) {
   DevBuf* bufs[] = {&c->geom,   &c->depths, &c->radii,  &c->tiles,   &c->rects, &c->clamped,   &c->grad_geom, &c->sort_k0,
                     &c->sort_k1, &c->sort_v0, &c->sort_v1, &c->dup_sums, &c->radix_counts,
                     &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_state,  &c->n_contrib,
-                    &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters, &c->loss_acc, &c->ssim_work};
+                    &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters, &c->loss_acc, &c->ssim_work,
+                    &c->tail_grads};
   for (DevBuf* b : bufs)
     if (b->ptr) cudaFree(b->ptr);
   if (c->d_host_pinned) cudaFreeHost(c->d_host_pinned);
@@ -501,6 +507,127 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
     GS_CUDA_CHECK(c, cudaGetLastError());
   }
   c->have_backward = true;
+  return GS_OK;
+}
+
+int gs_backward_adam_step(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, const float* dL_dout_color,
+                          float* dL_dmeans2D, float* const exp_avg[6], float* const exp_avg_sq[6], const double lr[6],
+                          const long long step[6], double beta1, double beta2, double eps, int* max_radii2D,
+                          float* xyz_grad_accum, float* denom, const float* skip_guard, void* stream_) {
+  int rc = validate(c, st, N, in);
+  if (rc != GS_OK) return rc;
+  if (!dL_dout_color || !exp_avg || !exp_avg_sq || !lr || !step) {
+    gs_set_error(c, "gs_backward_adam_step: null argument");
+    return GS_EINVAL;
+  }
+  if (in->colors_precomp || in->cov3D_precomp || !in->sh_dc || in->sh_dc_stride != 3 || !in->scales || !in->rotations) {
+    gs_set_error(c, "gs_backward_adam_step needs the trainable layout: means3D, scales, rotations, opacities, "
+                    "sh_dc (N,1,3) and sh_rest (N,K-1,3) as separate dense tensors");
+    return GS_EINVAL;
+  }
+  const int wrest = 3 * ((st->max_sh_degree + 1) * (st->max_sh_degree + 1) - 1);
+  if (wrest > 0 && (!in->sh_rest || in->sh_rest_stride != wrest)) {
+    gs_set_error(c, "gs_backward_adam_step: sh_rest must be dense (stride %d)", wrest);
+    return GS_EINVAL;
+  }
+  for (int k = 0; k < 6; ++k) {
+    if (step[k] < 1) {
+      gs_set_error(c, "segment %d: step must be >= 1 (libtorch increments before use)", k);
+      return GS_EINVAL;
+    }
+    if (!(k == 2 && wrest == 0) && (!exp_avg[k] || !exp_avg_sq[k])) {
+      gs_set_error(c, "segment %d: exp_avg / exp_avg_sq missing", k);
+      return GS_EINVAL;
+    }
+  }
+  if (!c->have_forward || c->N != N || c->H != st->H || c->W != st->W) {
+    gs_set_error(c, "gs_backward_adam_step needs the matching gs_forward (same N, H, W) to have run on this context");
+    return GS_ESTATE;
+  }
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  if (N == 0) return GS_OK;
+  const GsDims d = gs_dims(*st);
+  GS_ENSURE(c, c->grad_geom, (size_t)N * 48);
+  if (!(c->reuse_blend_gradients && c->have_backward)) {
+    StageTimer t(c, 6, stream);
+    GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
+    GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, c->point_list,
+                                              (const GsGeom*)c->geom.ptr, st->bg, (const float4*)c->final_state.ptr,
+                                              (const uint32_t*)c->n_contrib.ptr, dL_dout_color,
+                                              (const float4*)c->ckpt.ptr, (const uint2*)c->work_items.ptr,
+                                              (const uint32_t*)c->counters.ptr, (uint32_t*)c->counters.ptr + 1,
+                                              (const uint32_t*)c->tile_last.ptr, (float4*)c->grad_geom.ptr,
+                                              c->num_sms, stream));
+  }
+  {
+    StageTimer t(c, 7, stream);
+    int covered = 0;
+    GS_CUDA_CHECK(c, gs_launch_preprocess_backward_adam(*st, *in, dL_dmeans2D, N, (const int*)c->radii.ptr,
+                                                        (const uint8_t*)c->clamped.ptr,
+                                                        (const float4*)c->grad_geom.ptr, exp_avg, exp_avg_sq, lr, step,
+                                                        beta1, beta2, eps, max_radii2D, xyz_grad_accum, denom,
+                                                        skip_guard, &covered, stream));
+    if (covered < N) {
+      // ragged tail (< 128 rows) or a layout the fused kernel does not take: separate K4b into scratch gradients,
+      // then K5 on those rows.  Scratch rows are addressed with the global row index (re-based pointers).
+      const long long b = covered, rows = (long long)N - covered;
+      GS_ENSURE(c, c->tail_grads, (size_t)rows * (17 + wrest) * 4 + 7 * 16);
+      float* base = (float*)c->tail_grads.ptr;
+      auto take = [&](long long floats) {
+        float* p = base;
+        base += (floats + 3) / 4 * 4;
+        return p;
+      };
+      float* gk[6] = {take(rows * 3), take(rows * 3), take(rows * (wrest > 0 ? wrest : 1)), take(rows),
+                      take(rows * 3), take(rows * 4)};
+      float* g2 = take(rows * 2);
+      gs_gradients g;
+      memset(&g, 0, sizeof(g));
+      g.dL_dmeans3D = gk[0] - 3 * b;
+      g.dL_dsh_dc = gk[1] - 3 * b;
+      g.dL_dsh_rest = wrest > 0 ? gk[2] - (long long)wrest * b : nullptr;
+      g.dL_dopacities = gk[3] - b;
+      g.dL_dscales = gk[4] - 3 * b;
+      g.dL_drotations = gk[5] - 4 * b;
+      g.dL_dmeans2D = (dL_dmeans2D ? dL_dmeans2D : g2 - 2 * b);
+      g.sh_dc_stride = 3;
+      g.sh_rest_stride = wrest;
+      GS_CUDA_CHECK(c, gs_launch_preprocess_backward(*st, *in, g, (int)b, N, (const int*)c->radii.ptr,
+                                                     (const uint8_t*)c->clamped.ptr, (const float4*)c->grad_geom.ptr,
+                                                     stream));
+      const int widths[6] = {3, 3, wrest, 1, 3, 4};
+      float* pk[6] = {const_cast<float*>(in->means3D) + 3 * b, const_cast<float*>(in->sh_dc) + 3 * b,
+                      wrest > 0 ? const_cast<float*>(in->sh_rest) + (long long)wrest * b : nullptr,
+                      const_cast<float*>(in->opacities) + b, const_cast<float*>(in->scales) + 3 * b,
+                      const_cast<float*>(in->rotations) + 4 * b};
+      float* mk[6];
+      float* vk[6];
+      size_t cnt[6];
+      for (int k = 0; k < 6; ++k) {
+        mk[k] = exp_avg[k] ? exp_avg[k] + (long long)widths[k] * b : nullptr;
+        vk[k] = exp_avg_sq[k] ? exp_avg_sq[k] + (long long)widths[k] * b : nullptr;
+        cnt[k] = pk[k] ? (size_t)rows * widths[k] : 0;
+      }
+      const bool stats = max_radii2D && xyz_grad_accum && denom;
+      GS_CUDA_CHECK(c, gs_launch_adam_counts((int)rows, 6, pk, gk, mk, vk, cnt, lr, step, beta1, beta2, eps,
+                                             stats ? (const int*)c->radii.ptr + b : nullptr,
+                                             stats ? g.dL_dmeans2D + 2 * b : nullptr,
+                                             stats ? max_radii2D + b : nullptr, stats ? xyz_grad_accum + b : nullptr,
+                                             stats ? denom + b : nullptr, 0, skip_guard, stream));
+    }
+  }
+  if (st->debug) {
+    GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
+    GS_CUDA_CHECK(c, cudaGetLastError());
+  }
+  c->have_backward = true;
+  return GS_OK;
+}
+
+int gs_debug_reuse_blend_gradients(gs_ctx* c, int on) {
+  if (!c) return GS_EINVAL;
+  c->reuse_blend_gradients = on != 0;
   return GS_OK;
 }
 

@@ -40,16 +40,6 @@ struct AdamArgs {
   float* denom;
 };
 
-__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float b1, float b2, float omb1,
-                                         float omb2, float eps, float neg_step, float inv_bc2_sqrt) {
-  const float mi = __fmaf_rn(omb1, g, __fmul_rn(m, b1));
-  const float vi = __fmaf_rn(__fmul_rn(omb2, g), g, __fmul_rn(v, b2));
-  const float denom = __fadd_rn(__fmul_rn(__fsqrt_rn(vi), inv_bc2_sqrt), eps);
-  m = mi;
-  v = vi;
-  p = __fmaf_rn(neg_step, __fdiv_rn(mi, denom), p);
-}
-
 __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_constant__ AdamArgs a) {
   if (a.skip_guard && __ldg(a.skip_guard) != 0.0f) return;
   const int b = blockIdx.x;
@@ -91,10 +81,10 @@ __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_
     }
 #pragma unroll
     for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
-      adam_one(p[k].x, g[k].x, m[k].x, v[k].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-      adam_one(p[k].y, g[k].y, m[k].y, v[k].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-      adam_one(p[k].z, g[k].z, m[k].z, v[k].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-      adam_one(p[k].w, g[k].w, m[k].w, v[k].w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      gs_adam_one(p[k].x, g[k].x, m[k].x, v[k].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      gs_adam_one(p[k].y, g[k].y, m[k].y, v[k].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      gs_adam_one(p[k].z, g[k].z, m[k].z, v[k].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      gs_adam_one(p[k].w, g[k].w, m[k].w, v[k].w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
       __stcs(mp + k * AD_THREADS, m[k]);
       __stcs(vp + k * AD_THREADS, v[k]);
       __stcs(pp + k * AD_THREADS, p[k]);
@@ -104,7 +94,7 @@ __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_
     // ragged tail / unaligned segment: scalar, still coalesced
     for (size_t idx = base + threadIdx.x; idx < s.n && idx < base + AD_FLOATS_PER_BLOCK; idx += AD_THREADS) {
       float p = s.p[idx], m = s.m[idx], v = s.v[idx];
-      adam_one(p, s.g[idx], m, v, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      gs_adam_one(p, s.g[idx], m, v, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
       s.p[idx] = p;
       s.m[idx] = m;
       s.v[idx] = v;
@@ -245,10 +235,10 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
       g.z = __fadd_rn(g.z, gs[r - 1].z);
       g.w = __fadd_rn(g.w, gs[r - 1].w);
     }
-    adam_one(p.x, g.x, m.x, v.x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-    adam_one(p.y, g.y, m.y, v.y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-    adam_one(p.z, g.z, m.z, v.z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-    adam_one(p.w, g.w, m.w, v.w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+    gs_adam_one(p.x, g.x, m.x, v.x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+    gs_adam_one(p.y, g.y, m.y, v.y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+    gs_adam_one(p.z, g.z, m.z, v.z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+    gs_adam_one(p.w, g.w, m.w, v.w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
 #pragma unroll
     for (int r = 0; r < G - 1; ++r) reinterpret_cast<float4*>(s.dst[r])[v0] = p;  // NVLink stores first
     __stcs(reinterpret_cast<float4*>(s.m) + v0, m);
@@ -260,7 +250,7 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
 #pragma unroll
       for (int r = 1; r < G; ++r) g = __fadd_rn(g, s.src[r][idx]);
       float p = s.p[idx], m = s.m[idx], v = s.v[idx];
-      adam_one(p, g, m, v, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      gs_adam_one(p, g, m, v, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
 #pragma unroll
       for (int r = 0; r < G - 1; ++r) s.dst[r][idx] = p;
       s.p[idx] = p;

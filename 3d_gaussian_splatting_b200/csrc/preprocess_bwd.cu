@@ -522,6 +522,142 @@ preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __
   }
 }
 
+// ---- K4b + K5 fused (single-GPU training step) -------------------------------------------------
+// The gradient rows a block has just produced sit in shared memory; instead of storing them (236 B/row) for
+// the optimiser to read back (another 236 B/row), the block applies the Adam update of optim.cu to its own
+// 128 rows right away: moments from HBM, parameters from L2 (the block's own TMA loads fetched them a moment
+// ago), gradients from shared memory.  Per row: 48 B record + 236 B parameters in; 472 B moments in and out;
+// 236 B parameters out = 1464 B instead of 2172 B for the two separate kernels, and one launch less.  The
+// densification statistics of K5 are folded in as well (radius, |dL/dmean2D|), so dL_dmeans2D need not be
+// stored either (optional sink).  Bit-identical to K4b followed by K5: same pb_compute, same gs_adam_one.
+struct FusedAdamArgs {
+  float* p[6];  // group order of GaussianModel::setup: xyz, f_dc, f_rest, opacity, scaling, rotation
+  float* m[6];
+  float* v[6];
+  float neg_step[6], inv_bc2_sqrt[6];
+  float b1, b2, omb1, omb2, eps;
+  const float* skip_guard;
+  int* max_radii2D;  // the three statistics: all or none
+  float* xyz_grad_accum;
+  float* denom;
+};
+
+#define PBF_UNROLL 4
+
+__device__ __forceinline__ void pbf_adam_slice(const float* s_g, float* gp, float* gm, float* gv, const int nvec,
+                                               const FusedAdamArgs& f, const int k, const int tid) {
+  const float b1 = f.b1, b2 = f.b2, omb1 = f.omb1, omb2 = f.omb2, eps = f.eps;
+  const float neg_step = f.neg_step[k], inv_bc2_sqrt = f.inv_bc2_sqrt[k];
+  float4* __restrict__ pp = reinterpret_cast<float4*>(gp);
+  float4* __restrict__ mp = reinterpret_cast<float4*>(gm);
+  float4* __restrict__ vp = reinterpret_cast<float4*>(gv);
+  const float4* sg = reinterpret_cast<const float4*>(s_g);
+  for (int j0 = tid; j0 < nvec; j0 += PBB_ROWS * PBF_UNROLL) {
+    float4 p[PBF_UNROLL], m[PBF_UNROLL], v[PBF_UNROLL];
+#pragma unroll
+    for (int u = 0; u < PBF_UNROLL; ++u) {
+      const int j = j0 + u * PBB_ROWS;
+      if (j < nvec) {
+        m[u] = __ldcs(mp + j);
+        v[u] = __ldcs(vp + j);
+        p[u] = pp[j];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < PBF_UNROLL; ++u) {
+      const int j = j0 + u * PBB_ROWS;
+      if (j < nvec) {
+        const float4 g = sg[j];
+        gs_adam_one(p[u].x, g.x, m[u].x, v[u].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+        gs_adam_one(p[u].y, g.y, m[u].y, v[u].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+        gs_adam_one(p[u].z, g.z, m[u].z, v[u].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+        gs_adam_one(p[u].w, g.w, m[u].w, v[u].w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+        __stcs(mp + j, m[u]);
+        __stcs(vp + j, v[u]);
+        pp[j] = p[u];  // read again by the next forward
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(PBB_ROWS)
+preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a,
+                                const __grid_constant__ FusedAdamArgs f) {
+  if (f.skip_guard && __ldg(f.skip_guard) != 0.0f) return;  // overflowed forward: the whole step is void
+  extern __shared__ __align__(128) float s_buf[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_buf + PBB_FLOATS);
+  const int tid = threadIdx.x;
+  const size_t row0 = (size_t)blockIdx.x * PBB_ROWS;
+  const size_t i = row0 + tid;
+  const int W = a.rest_width_max;
+  const bool load_sh = a.rest_width_act > 0;
+
+  if (tid == 0) {
+    tma::mbar_init(bar, 1);
+    tma::fence_mbar_init();
+    const uint32_t sh_bytes = load_sh ? (uint32_t)(PBB_ROWS * W * 4) : 0u;
+    const uint32_t op_bytes = a.in.raw_params ? PBB_ROWS * 4u : 0u;
+    tma::mbar_arrive_expect_tx(bar, sh_bytes + op_bytes + PBB_ROWS * (12u + 12u + 16u + 48u));
+    tma::load(s_buf + PBB_OFF_GG, a.grad_geom + 3 * row0, PBB_ROWS * 48u, bar);
+    tma::load(s_buf + PBB_OFF_XYZ, a.in.means3D + 3 * row0, PBB_ROWS * 12u, bar);
+    tma::load(s_buf + PBB_OFF_SCL, a.in.scales + 3 * row0, PBB_ROWS * 12u, bar);
+    tma::load(s_buf + PBB_OFF_ROT, a.in.rotations + 4 * row0, PBB_ROWS * 16u, bar);
+    if (op_bytes) tma::load(s_buf + PBB_OFF_OP, a.in.opacities + row0, op_bytes, bar);
+    if (sh_bytes) tma::load(s_buf + PBB_OFF_SH, a.in.sh_rest + row0 * W, sh_bytes, bar);
+  }
+  const int radius = a.radii[i];
+  const bool visible = radius > 0;
+  const uint32_t cm = a.clamped[i];
+  __syncthreads();
+  tma::mbar_wait(bar, 0);
+
+  PbOut o;
+  pb_zero(o);
+  float* srow = s_buf + PBB_OFF_SH + tid * W;
+  if (visible) {
+    const float4* gg = reinterpret_cast<const float4*>(s_buf + PBB_OFF_GG) + 3 * tid;
+    const float4 G0 = gg[0], G1 = gg[1];
+    const float G2x = s_buf[PBB_OFF_GG + 12 * tid + 8];
+    const float p[3] = {s_buf[PBB_OFF_XYZ + 3 * tid], s_buf[PBB_OFF_XYZ + 3 * tid + 1], s_buf[PBB_OFF_XYZ + 3 * tid + 2]};
+    const float scl[3] = {s_buf[PBB_OFF_SCL + 3 * tid], s_buf[PBB_OFF_SCL + 3 * tid + 1], s_buf[PBB_OFF_SCL + 3 * tid + 2]};
+    const float4 q4 = reinterpret_cast<const float4*>(s_buf + PBB_OFF_ROT)[tid];
+    const float opac_in = a.in.raw_params ? s_buf[PBB_OFF_OP + tid] : 0.f;
+    pb_compute(st, a, p, q4, scl, opac_in, nullptr, G0, G1, G2x, cm, srow, true, o);
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    s_buf[PBB_OFF_XYZ + 3 * tid + c] = o.gm[c];
+    s_buf[PBB_OFF_SCL + 3 * tid + c] = o.gs[c];
+    s_buf[PBB_OFF_DC + 3 * tid + c] = o.gdc[c];
+  }
+  reinterpret_cast<float4*>(s_buf + PBB_OFF_ROT)[tid] = make_float4(o.gq[0], o.gq[1], o.gq[2], o.gq[3]);
+  s_buf[PBB_OFF_OP + tid] = o.gop;
+  {
+    const int kmax = W / 3;
+#pragma unroll
+    for (int k = 0; k < 15; ++k)
+      if (k < kmax) {
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) srow[3 * k + ch] = o.basis[k] * o.gr[ch];
+      }
+  }
+  // densification statistics of this row (K5's second half) and the optional dL_dmeans2D sink
+  if (f.max_radii2D && visible) {
+    if (radius > f.max_radii2D[i]) f.max_radii2D[i] = radius;
+    f.xyz_grad_accum[i] += __fsqrt_rn(__fadd_rn(__fmul_rn(o.g2x, o.g2x), __fmul_rn(o.g2y, o.g2y)));
+    f.denom[i] += 1.0f;
+  }
+  if (a.out.dL_dmeans2D) reinterpret_cast<float2*>(a.out.dL_dmeans2D)[i] = make_float2(o.g2x, o.g2y);
+  __syncthreads();
+  // ---- Adam over the block's rows, group by group (each slice is contiguous in HBM and in shared memory) ----
+  pbf_adam_slice(s_buf + PBB_OFF_SH, f.p[2] + row0 * W, f.m[2] + row0 * W, f.v[2] + row0 * W, PBB_ROWS * W / 4, f, 2, tid);
+  pbf_adam_slice(s_buf + PBB_OFF_XYZ, f.p[0] + 3 * row0, f.m[0] + 3 * row0, f.v[0] + 3 * row0, PBB_ROWS * 3 / 4, f, 0, tid);
+  pbf_adam_slice(s_buf + PBB_OFF_DC, f.p[1] + 3 * row0, f.m[1] + 3 * row0, f.v[1] + 3 * row0, PBB_ROWS * 3 / 4, f, 1, tid);
+  pbf_adam_slice(s_buf + PBB_OFF_OP, f.p[3] + row0, f.m[3] + row0, f.v[3] + row0, PBB_ROWS / 4, f, 3, tid);
+  pbf_adam_slice(s_buf + PBB_OFF_SCL, f.p[4] + 3 * row0, f.m[4] + 3 * row0, f.v[4] + 3 * row0, PBB_ROWS * 3 / 4, f, 4, tid);
+  pbf_adam_slice(s_buf + PBB_OFF_ROT, f.p[5] + 4 * row0, f.m[5] + 4 * row0, f.v[5] + 4 * row0, PBB_ROWS, f, 5, tid);
+}
+
 static bool aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 
 // Rows [row_begin, row_end) only (the whole model: 0, N).  The multi-GPU step launches one range per owner rank
@@ -574,5 +710,74 @@ cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussi
     const int blocks = (row_end - first + PB_THREADS - 1) / PB_THREADS;
     preprocess_backward_kernel<<<blocks, PB_THREADS, smem, stream>>>(st, a, first);
   }
+  return cudaGetLastError();
+}
+
+
+// Fused K4b + K5 over rows [0, floor(N/128)*128); returns the number of rows it covered in *covered (0 when the
+// layout does not qualify -- the caller then runs the separate kernels).  Parameters are in.{means3D, sh_dc,
+// sh_rest, opacities, scales, rotations}, updated in place.
+cudaError_t gs_launch_preprocess_backward_adam(const gs_settings& st, const gs_gaussians& in, float* dL_dmeans2D, int N,
+                                               const int* radii, const uint8_t* clamped, const float4* grad_geom,
+                                               float* const exp_avg[6], float* const exp_avg_sq[6], const double lr[6],
+                                               const long long step[6], double beta1, double beta2, double eps,
+                                               int* max_radii2D, float* xyz_grad_accum, float* denom,
+                                               const float* skip_guard, int* covered, cudaStream_t stream) {
+  *covered = 0;
+  if (N < PBB_ROWS) return cudaSuccess;
+  PreBwdArgs a;
+  a.in = in;
+  memset(&a.out, 0, sizeof(a.out));
+  a.out.dL_dmeans2D = dL_dmeans2D;
+  a.N = N;
+  a.radii = radii;
+  a.clamped = clamped;
+  a.grad_geom = grad_geom;
+  a.focal_x = (float)st.W / (2.0f * st.tanfovx);
+  a.focal_y = (float)st.H / (2.0f * st.tanfovy);
+  const int kact = (st.sh_degree + 1) * (st.sh_degree + 1);
+  const int kmax = (st.max_sh_degree + 1) * (st.max_sh_degree + 1);
+  a.rest_width_act = 3 * (kact - 1);
+  a.rest_width_max = 3 * (kmax - 1);
+  a.pitch = a.rest_width_max | 1;
+  const int W = a.rest_width_max;
+  float* params[6] = {const_cast<float*>(in.means3D), const_cast<float*>(in.sh_dc), const_cast<float*>(in.sh_rest),
+                      const_cast<float*>(in.opacities), const_cast<float*>(in.scales), const_cast<float*>(in.rotations)};
+  bool ok = !in.colors_precomp && !in.cov3D_precomp && in.sh_dc && in.sh_dc_stride == 3 &&
+            (W == 0 || (in.sh_rest && in.sh_rest_stride == W)) && (W * 4 * PBB_ROWS) % 16 == 0 &&
+            aligned16(grad_geom) && aligned16(dL_dmeans2D);
+  FusedAdamArgs f;
+  for (int k = 0; k < 6; ++k) {
+    const bool on = !(k == 2 && W == 0);
+    f.p[k] = on ? params[k] : nullptr;
+    f.m[k] = on ? exp_avg[k] : nullptr;
+    f.v[k] = on ? exp_avg_sq[k] : nullptr;
+    if (on) ok = ok && f.p[k] && f.m[k] && f.v[k] && aligned16(f.p[k]) && aligned16(f.m[k]) && aligned16(f.v[k]);
+    const double bc1 = 1.0 - pow(beta1, (double)step[k]);
+    const double bc2 = 1.0 - pow(beta2, (double)step[k]);
+    f.neg_step[k] = (float)(-(lr[k] / bc1));
+    f.inv_bc2_sqrt[k] = 1.0f / (float)sqrt(bc2);
+  }
+  if (!ok) return cudaSuccess;
+  f.b1 = (float)beta1;
+  f.b2 = (float)beta2;
+  f.omb1 = (float)(1.0 - beta1);
+  f.omb2 = (float)(1.0 - beta2);
+  f.eps = (float)eps;
+  f.skip_guard = skip_guard;
+  const bool stats = max_radii2D && xyz_grad_accum && denom;
+  f.max_radii2D = stats ? max_radii2D : nullptr;
+  f.xyz_grad_accum = stats ? xyz_grad_accum : nullptr;
+  f.denom = stats ? denom : nullptr;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(preprocess_backward_adam_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         PBB_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const int blocks = N / PBB_ROWS;
+  preprocess_backward_adam_kernel<<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, f);
+  *covered = blocks * PBB_ROWS;
   return cudaGetLastError();
 }

@@ -175,6 +175,7 @@ class Trainer:
         self._guard_tensor = None
         self.skip_guard = None          # device float the Adam step honours (all-reduced slab tail when multi-GPU)
         self.retries = 0
+        self.fused_step = True          # single GPU: backward and Adam in one call (gs_backward_adam_step)
         self.peer = None                # multi-GPU: parallel.PeerShardedAdam (exchange fused into K4b / K5)
         self.sharded = None             # multi-GPU: parallel.ShardedAdam (reduce-scatter / sharded Adam / all-gather)
 
@@ -205,7 +206,8 @@ class Trainer:
         else:
             self.skip_guard = self.rast.overflow_guard_ptr()
 
-    def forward_backward(self, cam, gt_dev: torch.Tensor, accumulate: bool = False, gt_host=None):
+    def forward_backward(self, cam, gt_dev: torch.Tensor, accumulate: bool = False, gt_host=None,
+                         fused_optimizer: bool = False):
         """render + loss + backward for one view with the gradients left in the model's sinks.
         gt_host: pinned host image to copy into gt_dev first.  The image is not needed before the loss, so the
         copy is issued on a side stream AFTER the render has been enqueued and runs underneath it; the compute
@@ -228,7 +230,14 @@ class Trainer:
         loss, dL = self.rast.loss(out["render"], gt_dev, self.lambda_dssim)
         if gt_host is not None:
             self._gt_free.record(torch.cuda.current_stream(self.g.device))
-        self.rast.backward(dL, grads=self.g.grad_sinks(), accumulate=accumulate)
+        if fused_optimizer:
+            g = self.g
+            g.step_count = [s + 1 for s in g.step_count]
+            self.rast.backward_adam_step(dL, g.exp_avg, g.exp_avg_sq, g.lr, g.step_count, max_radii2D=g.max_radii2D_,
+                                         xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_,
+                                         skip_guard=self.skip_guard if self.pair_capacity else None)
+        else:
+            self.rast.backward(dL, grads=self.g.grad_sinks(), accumulate=accumulate)
         return loss, out
 
     def optimizer_step(self, radii):
@@ -271,6 +280,10 @@ class Trainer:
         self.g.update_learning_rate(self.iteration)
         if self.iteration % 1000 == 0:
             self.g.oneup_SH_degree()
+        if self.fused_step and self.grad_sync is None and self.peer is None and self.sharded is None:
+            # single GPU: K4b and K5 fused (gs_backward_adam_step) -- the gradient tensors never reach HBM
+            loss, out = self.forward_backward(cam, gt_dev, gt_host=gt_host, fused_optimizer=True)
+            return loss
         loss, out = self.forward_backward(cam, gt_dev, gt_host=gt_host)
         if self.grad_sync is not None:
             self.grad_sync()

@@ -217,6 +217,25 @@ class Rasterizer:
                                          C.c_void_p(stream)))
         return grads
 
+    def backward_adam_step(self, dL_dout_color, exp_avg, exp_avg_sq, lr, step, beta1=0.9, beta2=0.999, eps=1e-8,
+                           dL_dmeans2D=None, max_radii2D=None, xyz_grad_accum=None, denom=None, skip_guard=None):
+        """Backward of the last forward with the Adam update fused into its per-Gaussian kernel
+        (gs_backward_adam_step): the tensors given to forward() -- means3D, sh_dc, sh_rest, opacities, scales,
+        rotations -- are the parameters and are updated in place; exp_avg / exp_avg_sq in the order of
+        GaussianModel::setup (xyz, f_dc, f_rest, opacity, scaling, rotation)."""
+        st, N, pk = self._last
+        if isinstance(skip_guard, torch.Tensor):
+            skip_guard = skip_guard.data_ptr()
+        VP6 = C.c_void_p * 6
+        arr = lambda ts: VP6(*[None if t is None or t.numel() == 0 else t.data_ptr() for t in ts])
+        dL = _f32c(dL_dout_color, "dL_dout_color")
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._ctx, lib.gs_backward_adam_step(
+            self._ctx, C.byref(st), N, C.byref(pk.g), _ptr(dL), _ptr(dL_dmeans2D), arr(exp_avg), arr(exp_avg_sq),
+            (C.c_double * 6)(*[float(x) for x in lr]), (C.c_longlong * 6)(*[int(x) for x in step]), float(beta1),
+            float(beta2), float(eps), _ptr(max_radii2D), _ptr(xyz_grad_accum), _ptr(denom),
+            C.c_void_p(skip_guard) if skip_guard else None, C.c_void_p(stream)))
+
     # ---- running without the host round-trip ---------------------------------------------------
     def set_duplicate_capacity(self, pairs: int):
         """pairs > 0: fixed (tile, Gaussian) pair capacity, gs_forward never waits for the host; 0: synchronous."""

@@ -123,6 +123,9 @@ def stage_bytes(N, N_vis, D, D_eff, P, T, K):
         "blend_bwd": 40 * D_eff + 20 * P + 36 * N_vis,
         "preprocess_bwd": (44 + 12 * K) * N_vis + 36 * N_vis + 4 * N + (44 + 12 * K) * N,
         "adam_stats": 28 * (11 + 3 * K) * N + 36 * N_vis,
+        # K4b + K5 fused (single GPU): record 48 + parameters 4w in; moments 8w in, 8w out; parameters 4w out;
+        # radii / clamp mask / statistics ~ 24 B  (w = 11 + 3K floats per Gaussian)
+        "preprocess_bwd_adam": (48 + 24 * (11 + 3 * K) + 24) * N,
         # (1-lambda) L1 + lambda D-SSIM: fwd reads image + target, writes 3 partial maps; bwd reads them + both images,
         # writes dL/dimage (12 B per pixel each)
         "loss": 12 * P * (2 + 3 + 5 + 1),
@@ -223,7 +226,7 @@ def run_reference(args, rank, world):
 # ---- GPU arm -----------------------------------------------------------------------------------
 # preprocess, depth sort 4 x (hist, scan, scatter), dup block sums + scan + duplicate, tile sort 2 x 3, tile
 # ranges, tile order, blend_forward, ssim forward + backward + finalize, blend_backward, preprocess_backward, adam_stats
-OWN_KERNELS_PER_STEP = 1 + 12 + 3 + 6 + 2 + 1 + 3 + 1 + 1 + 1
+OWN_KERNELS_PER_STEP = 1 + 12 + 3 + 6 + 2 + 1 + 3 + 1 + 1 + 1   # separate K4b and K5; the fused single-GPU step: one less
 LAMBDA_DSSIM = 0.2   # lambda_dssim_ default (src/arguments/params.h:62)
 LOSS_NAME = "0.8*L1 + 0.2*(1-SSIM)"
 LIB_KERNELS_PER_STEP = 0   # no library kernels on the path (the radix sort and scans are this repo's own)
@@ -333,20 +336,34 @@ def run_ours(args, rank, world, local_rank):
     acc = {}
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     extra = {"loss": [], "adam_stats": []}
+    fused = world == 1 and trainer.fused_step
     for i in range(8):
         cam, gt = my_cams[i % args.views], gts_dev[i % args.views]
         out = gm.render(cam, g, trainer.pipe, trainer.bg, trainer.rast)
         ev[0].record(); loss, dL = trainer.rast.loss(out["render"], gt, LAMBDA_DSSIM); ev[1].record()
-        trainer.rast.backward(dL, grads=g.grad_sinks())
-        ev[2].record(); trainer.optimizer_step(out["radii"]); ev[3].record()
+        if fused:     # K4b and K5 are one kernel: its time is the library's stage 7
+            g.step_count = [s + 1 for s in g.step_count]
+            trainer.rast.backward_adam_step(dL, g.exp_avg, g.exp_avg_sq, g.lr, g.step_count,
+                                            max_radii2D=g.max_radii2D_, xyz_grad_accum=g.xyz_gradient_accum_,
+                                            denom=g.denom_, skip_guard=trainer.skip_guard)
+        else:
+            trainer.rast.backward(dL, grads=g.grad_sinks())
+        ev[2].record()
+        if not fused:
+            trainer.optimizer_step(out["radii"])
+        ev[3].record()
         torch.cuda.synchronize()
         if i >= 2:
             for k, v in trainer.rast.stage_ms().items():
                 acc.setdefault(k, []).append(v)
-            extra["loss"].append(ev[0].elapsed_time(ev[1])); extra["adam_stats"].append(ev[2].elapsed_time(ev[3]))
+            extra["loss"].append(ev[0].elapsed_time(ev[1]))
+            if not fused:
+                extra["adam_stats"].append(ev[2].elapsed_time(ev[3]))
     trainer.rast.set_profiling(False)
     stage_ms = {k: float(np.median(v)) for k, v in acc.items()}
-    stage_ms.update({k: float(np.median(v)) for k, v in extra.items()})
+    stage_ms.update({k: float(np.median(v)) for k, v in extra.items() if v})
+    if fused:
+        stage_ms["preprocess_bwd_adam"] = stage_ms.pop("preprocess_bwd")
     radii = out["radii"]
     N_vis = int((radii > 0).sum().item())
     D = int(trainer.rast.debug_get("NUM_RENDERED")[0])
@@ -359,13 +376,15 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_kind = peaks()
     dom = max(stage_ms, key=lambda k: stage_ms[k])
     ach = by[dom] / (stage_ms[dom] * 1e-3) / 1e9
+    by = {k: v for k, v in by.items() if k in stage_ms}
     step_bytes = sum(by.values())
     stages = {k: {"ms": round(stage_ms[k], 4), "alg_GB": round(by[k] / 1e9, 4),
                   "GBps": round(by[k] / (stage_ms[k] * 1e-3) / 1e9, 1) if stage_ms[k] > 0 else None,
                   "frac_hbm": round(by[k] / (stage_ms[k] * 1e-3) / 1e9 / peak, 4) if stage_ms[k] > 0 else None}
               for k in stage_ms}
-    fwd_bwd_ms = sum(stage_ms[k] for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd",
-                                           "blend_bwd", "preprocess_bwd"))
+    # (the fused single-GPU step has no separate K4b: its K4b+K5 kernel is counted whole)
+    fwd_bwd_ms = sum(stage_ms.get(k, 0.0) for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges",
+                                                    "blend_fwd", "blend_bwd", "preprocess_bwd", "preprocess_bwd_adam"))
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -397,7 +416,7 @@ def run_ours(args, rank, world, local_rank):
                                                      "all-gather" % world,
                                           "allreduce": "one NCCL all-reduce, replicated Adam"}[args.dp_mode])
                        if world > 1 else "single GPU"},
-            "raster_fwd_bwd_ms": fwd_bwd_ms, "train_it_per_s_per_gpu": 1e3 / ms_per_step,
+            "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": None, "peak_kind": peak_kind,
@@ -407,7 +426,7 @@ def run_ours(args, rank, world, local_rank):
                     "h2d_bytes_per_step": int(gts_host[0].numel() * 4 + 172), "d2h_bytes_per_step": 4},
             "pair_capacity": trainer.pair_capacity, "capacity_retries": trainer.retries,
             # own kernels only (NCCL's are not counted); the routed K4b of the peer mode is one launch per owner rank
-            "gpu_launches": (OWN_KERNELS_PER_STEP + (world - 1 if world > 1 and args.dp_mode == "peer" else 0)
+            "gpu_launches": (OWN_KERNELS_PER_STEP - (1 if world == 1 and trainer.fused_step else 0) + (world - 1 if world > 1 and args.dp_mode == "peer" else 0)
                              + (1 if world > 1 and args.dp_mode == "sharded" else 0)) * args.steps,
             "library_launches": LIB_KERNELS_PER_STEP * args.steps,
             "clocks": clocks,

@@ -155,6 +155,26 @@ GS_API int gs_adam_densify_step(gs_ctx *ctx, int N, float *const params[6], floa
                                 float *xyz_grad_accum, float *denom, int zero_grads, const float *skip_guard,
                                 void *stream);
 
+/* ---- backward + optimiser in one call (the single-GPU training step) -------------------------
+ * gs_backward followed by gs_adam_densify_step on the same model, with the per-Gaussian half of the backward
+ * and the Adam update FUSED into one kernel: a block turns its 128 gradient rows into parameter updates while
+ * they are still in shared memory, so the six gradient tensors are never written to or read from HBM
+ * (1464 B instead of 2172 B per Gaussian at SH degree 3, one launch less).  Bit-identical to the two calls.
+ * `in` must be the trainable layout (raw or activated; sh_dc (N,1,3) + sh_rest (N,K-1,3) dense, no precomputed
+ * colours / covariances); its six arrays ARE the parameters and are updated in place, in the group order of
+ * GaussianModel::setup (src/scene/gaussian_model.cpp:323-345).  dL_dmeans2D: optional (N,2) sink.  Statistics
+ * and skip_guard as in gs_adam_densify_step. */
+GS_API int gs_backward_adam_step(gs_ctx *ctx, const gs_settings *settings, int N, const gs_gaussians *in,
+                                 const float *dL_dout_color, float *dL_dmeans2D, float *const exp_avg[6],
+                                 float *const exp_avg_sq[6], const double lr[6], const long long step[6],
+                                 double beta1, double beta2, double eps, int *max_radii2D, float *xyz_grad_accum,
+                                 float *denom, const float *skip_guard, void *stream);
+
+/* Test hook: with on != 0, gs_backward_adam_step skips the blend backward and consumes the per-Gaussian gradient
+ * records the last gs_backward left in the context -- the blend backward sums with fp32 atomics, so this is what
+ * makes "fused == separate" checkable bit for bit. */
+GS_API int gs_debug_reuse_blend_gradients(gs_ctx *ctx, int on);
+
 /* The same Adam update over up to six arbitrary contiguous float ranges (counts[s] floats each): the form a
  * rank uses when the optimiser state is SHARDED across GPUs -- gradients reduce-scattered, each rank updating
  * the slice of the flat parameter slab it owns (a slice intersects at most the six parameter groups), the
