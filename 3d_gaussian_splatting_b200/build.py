@@ -4,7 +4,8 @@
 csrc/ with nvcc for sm_100a (-lineinfo so ncu source pages map to our code) and links one
 shared library next to this file.  The built .so is git-ignored but travels to the GPU box.
 preprocess.cu is compiled with --fmad=false: its integer outputs (radii, tile counts, sort
-keys) must be bit-identical to the CPU oracle, so no fused multiply-add contraction there.
+keys) must be bit-identical to the CPU oracle, so no fused multiply-add contraction there;
+preprocess_bwd.cu likewise, so that its three kernel variants agree bit for bit.
 """
 from __future__ import annotations
 
@@ -22,6 +23,9 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden", "--use_fast_math=false"]
 PER_FILE = {
     "preprocess.cu": ["--fmad=false"],
+    # K4b exists in three kernels (generic, TMA-staged, fused with Adam) that must produce the same gradient bits:
+    # without contraction every operation is a single IEEE operation, whatever the surrounding code
+    "preprocess_bwd.cu": ["--fmad=false"],
 }
 # host compiler: the image exports CC/CXX pointing at a gcc without libgomp etc.; use the system one
 CCBIN = "/usr/bin/g++"

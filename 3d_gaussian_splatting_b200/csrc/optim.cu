@@ -81,6 +81,7 @@ __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_
     }
 #pragma unroll
     for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
+      if (gs_adam_idle(g[k], m[k], v[k])) continue;  // exact fixed point (gs_common.cuh): nothing to write
       gs_adam_one(p[k].x, g[k].x, m[k].x, v[k].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
       gs_adam_one(p[k].y, g[k].y, m[k].y, v[k].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
       gs_adam_one(p[k].z, g[k].z, m[k].z, v[k].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
@@ -235,6 +236,7 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
       g.z = __fadd_rn(g.z, gs[r - 1].z);
       g.w = __fadd_rn(g.w, gs[r - 1].w);
     }
+    if (gs_adam_idle(g, m, v)) return;  // exact fixed point: every replica already holds this p, nothing crosses NVLink
     gs_adam_one(p.x, g.x, m.x, v.x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
     gs_adam_one(p.y, g.y, m.y, v.y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
     gs_adam_one(p.z, g.z, m.z, v.z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);

@@ -544,43 +544,39 @@ struct FusedAdamArgs {
 
 #define PBF_UNROLL 4
 
-__device__ __forceinline__ void pbf_adam_slice(const float* s_g, float* gp, float* gm, float* gv, const int nvec,
-                                               const FusedAdamArgs& f, const int k, const int tid) {
-  const float b1 = f.b1, b2 = f.b2, omb1 = f.omb1, omb2 = f.omb2, eps = f.eps;
-  const float neg_step = f.neg_step[k], inv_bc2_sqrt = f.inv_bc2_sqrt[k];
-  float4* __restrict__ pp = reinterpret_cast<float4*>(gp);
-  float4* __restrict__ mp = reinterpret_cast<float4*>(gm);
-  float4* __restrict__ vp = reinterpret_cast<float4*>(gv);
-  const float4* sg = reinterpret_cast<const float4*>(s_g);
-  for (int j0 = tid; j0 < nvec; j0 += PBB_ROWS * PBF_UNROLL) {
-    float4 p[PBF_UNROLL], m[PBF_UNROLL], v[PBF_UNROLL];
-#pragma unroll
-    for (int u = 0; u < PBF_UNROLL; ++u) {
-      const int j = j0 + u * PBB_ROWS;
-      if (j < nvec) {
-        m[u] = __ldcs(mp + j);
-        v[u] = __ldcs(vp + j);
-        p[u] = pp[j];
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < PBF_UNROLL; ++u) {
-      const int j = j0 + u * PBB_ROWS;
-      if (j < nvec) {
-        const float4 g = sg[j];
-        gs_adam_one(p[u].x, g.x, m[u].x, v[u].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-        gs_adam_one(p[u].y, g.y, m[u].y, v[u].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-        gs_adam_one(p[u].z, g.z, m[u].z, v[u].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-        gs_adam_one(p[u].w, g.w, m[u].w, v[u].w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-        __stcs(mp + j, m[u]);
-        __stcs(vp + j, v[u]);
-        pp[j] = p[u];  // read again by the next forward
-      }
-    }
-  }
+// The block's 128 x (11 + 3K) gradient floats as chunks of 32 float4 (512 B), every chunk inside ONE group because
+// each group's slice is 128 rows x C floats = C chunks: chunk index -> (group, offset).  A warp walks chunks
+// warp, warp + 4, ... four at a time, so every round has 12 independent 16-byte loads per thread in flight
+// whatever the group sizes (a per-group loop would spend a latency round on each of the five small groups).
+struct PbfChunk {
+  const float4* g;  // shared memory
+  float4* p;
+  float4* m;
+  float4* v;
+  int k;
+};
+
+__device__ __forceinline__ PbfChunk pbf_chunk(const float* s_buf, const FusedAdamArgs& f, const size_t row0, const int W,
+                                              int c) {
+  // chunk order: f_rest (W of them), xyz 3, f_dc 3, opacity 1, scaling 3, rotation 4
+  int k, soff, cw;  // group, smem slice offset, floats per row
+  if (c < W) { k = 2; soff = PBB_OFF_SH; cw = W; }
+  else if ((c -= W) < 3) { k = 0; soff = PBB_OFF_XYZ; cw = 3; }
+  else if ((c -= 3) < 3) { k = 1; soff = PBB_OFF_DC; cw = 3; }
+  else if ((c -= 3) < 1) { k = 3; soff = PBB_OFF_OP; cw = 1; }
+  else if ((c -= 1) < 3) { k = 4; soff = PBB_OFF_SCL; cw = 3; }
+  else { c -= 3; k = 5; soff = PBB_OFF_ROT; cw = 4; }
+  const size_t goff = row0 * cw + (size_t)c * 128;  // floats
+  PbfChunk r;
+  r.g = reinterpret_cast<const float4*>(s_buf + soff + c * 128);
+  r.p = reinterpret_cast<float4*>(f.p[k] + goff);
+  r.m = reinterpret_cast<float4*>(f.m[k] + goff);
+  r.v = reinterpret_cast<float4*>(f.v[k] + goff);
+  r.k = k;
+  return r;
 }
 
-__global__ void __launch_bounds__(PBB_ROWS)
+__global__ void __launch_bounds__(PBB_ROWS, 5)
 preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a,
                                 const __grid_constant__ FusedAdamArgs f) {
   if (f.skip_guard && __ldg(f.skip_guard) != 0.0f) return;  // overflowed forward: the whole step is void
@@ -604,6 +600,18 @@ preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __
     tma::load(s_buf + PBB_OFF_ROT, a.in.rotations + 4 * row0, PBB_ROWS * 16u, bar);
     if (op_bytes) tma::load(s_buf + PBB_OFF_OP, a.in.opacities + row0, op_bytes, bar);
     if (sh_bytes) tma::load(s_buf + PBB_OFF_SH, a.in.sh_rest + row0 * W, sh_bytes, bar);
+    // the Adam phase below reads the moments (and the one parameter slice not staged above) with plain loads:
+    // pull them into L2 now, underneath the gradient math
+    const int cw[6] = {3, 3, W, 1, 3, 4};
+#pragma unroll
+    for (int k = 0; k < 6; ++k)
+      if (cw[k] > 0) {
+        tma::prefetch_l2(f.m[k] + row0 * cw[k], PBB_ROWS * 4u * cw[k]);
+        tma::prefetch_l2(f.v[k] + row0 * cw[k], PBB_ROWS * 4u * cw[k]);
+      }
+    tma::prefetch_l2(f.p[1] + 3 * row0, PBB_ROWS * 12u);
+    if (!load_sh && W > 0) tma::prefetch_l2(f.p[2] + row0 * W, (uint32_t)(PBB_ROWS * W * 4));
+    if (!a.in.raw_params) tma::prefetch_l2(f.p[3] + row0, PBB_ROWS * 4u);
   }
   const int radius = a.radii[i];
   const bool visible = radius > 0;
@@ -649,13 +657,40 @@ preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __
   }
   if (a.out.dL_dmeans2D) reinterpret_cast<float2*>(a.out.dL_dmeans2D)[i] = make_float2(o.g2x, o.g2y);
   __syncthreads();
-  // ---- Adam over the block's rows, group by group (each slice is contiguous in HBM and in shared memory) ----
-  pbf_adam_slice(s_buf + PBB_OFF_SH, f.p[2] + row0 * W, f.m[2] + row0 * W, f.v[2] + row0 * W, PBB_ROWS * W / 4, f, 2, tid);
-  pbf_adam_slice(s_buf + PBB_OFF_XYZ, f.p[0] + 3 * row0, f.m[0] + 3 * row0, f.v[0] + 3 * row0, PBB_ROWS * 3 / 4, f, 0, tid);
-  pbf_adam_slice(s_buf + PBB_OFF_DC, f.p[1] + 3 * row0, f.m[1] + 3 * row0, f.v[1] + 3 * row0, PBB_ROWS * 3 / 4, f, 1, tid);
-  pbf_adam_slice(s_buf + PBB_OFF_OP, f.p[3] + row0, f.m[3] + row0, f.v[3] + row0, PBB_ROWS / 4, f, 3, tid);
-  pbf_adam_slice(s_buf + PBB_OFF_SCL, f.p[4] + 3 * row0, f.m[4] + 3 * row0, f.v[4] + 3 * row0, PBB_ROWS * 3 / 4, f, 4, tid);
-  pbf_adam_slice(s_buf + PBB_OFF_ROT, f.p[5] + 4 * row0, f.m[5] + 4 * row0, f.v[5] + 4 * row0, PBB_ROWS, f, 5, tid);
+  // ---- Adam over the block's rows (chunked, see pbf_chunk) ----
+  const int nchunks = W + 14;
+  const int warp = tid >> 5, lane = tid & 31;
+  const float b1 = f.b1, b2 = f.b2, omb1 = f.omb1, omb2 = f.omb2, eps = f.eps;
+  for (int c0 = warp; c0 < nchunks; c0 += 4 * PBF_UNROLL) {
+    PbfChunk ch[PBF_UNROLL];
+    float4 p[PBF_UNROLL], m[PBF_UNROLL], v[PBF_UNROLL];
+#pragma unroll
+    for (int u = 0; u < PBF_UNROLL; ++u) {
+      const int c = c0 + 4 * u;
+      if (c < nchunks) {
+        ch[u] = pbf_chunk(s_buf, f, row0, W, c);
+        m[u] = __ldcs(ch[u].m + lane);
+        v[u] = __ldcs(ch[u].v + lane);
+        p[u] = ch[u].p[lane];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < PBF_UNROLL; ++u) {
+      const int c = c0 + 4 * u;
+      if (c < nchunks) {
+        const float4 g = ch[u].g[lane];
+        if (gs_adam_idle(g, m[u], v[u])) continue;  // exact fixed point (gs_common.cuh): nothing to write
+        const float neg_step = f.neg_step[ch[u].k], inv_bc2_sqrt = f.inv_bc2_sqrt[ch[u].k];
+        gs_adam_one(p[u].x, g.x, m[u].x, v[u].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+        gs_adam_one(p[u].y, g.y, m[u].y, v[u].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+        gs_adam_one(p[u].z, g.z, m[u].z, v[u].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+        gs_adam_one(p[u].w, g.w, m[u].w, v[u].w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+        __stcs(ch[u].m + lane, m[u]);
+        __stcs(ch[u].v + lane, v[u]);
+        ch[u].p[lane] = p[u];  // read again by the next forward
+      }
+    }
+  }
 }
 
 static bool aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }

@@ -56,6 +56,10 @@ __device__ __forceinline__ void reduce_add_f32(void* gmem_dst, const void* smem_
                "r"(smem_u32(smem_src)), "r"(bytes)
                : "memory");
 }
+// global -> L2 only (no destination, no completion): warms a range the block will read with plain loads later
+__device__ __forceinline__ void prefetch_l2(const void* gmem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem_src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // wait until the bulk groups have finished READING shared memory (enough to reuse / release it)
 __device__ __forceinline__ void wait_group_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }

@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--dp-mode", default="peer", choices=["peer", "sharded", "allreduce"],
                     help="N>1: peer = exchange fused into K4b/K5 over NVLink peer memory (sharded Adam); sharded = NCCL "
                          "reduce-scatter + sharded Adam + all-gather; allreduce = NCCL all-reduce + replicated Adam")
+    ap.add_argument("--no-fused", action="store_true", help="N=1: separate K4b and K5 launches instead of the fused kernel")
     ap.add_argument("--N", type=int, default=None, help="override the Gaussian count (debugging only)")
     return ap.parse_args()
 
@@ -253,6 +254,7 @@ def run_ours(args, rank, world, local_rank):
     model = gm.GaussianModel(deg, local_rank).load_scene(scene)
     opt = gm.OptimizationParams()
     trainer = gm.Trainer(model, opt, bg=(0.0, 0.0, 0.0), lambda_dssim=LAMBDA_DSSIM)
+    trainer.fused_step = not args.no_fused
     g = model
     sharded = None
     grad_mb = 4e-6 * sum(p.numel() for p in g.params())
@@ -386,6 +388,10 @@ def run_ours(args, rank, world, local_rank):
     fwd_bwd_ms = sum(stage_ms.get(k, 0.0) for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges",
                                                     "blend_fwd", "blend_bwd", "preprocess_bwd", "preprocess_bwd_adam"))
 
+    adam_idle_frac = None
+    if g.exp_avg_sq is not None:
+        nz = sum(int((t != 0).sum().item()) for t in g.exp_avg_sq if t is not None)
+        adam_idle_frac = round(1.0 - nz / max(1, sum(t.numel() for t in g.exp_avg_sq if t is not None)), 4)
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = CpuStep(scene, cams, deg, args.views)
@@ -416,6 +422,9 @@ def run_ours(args, rank, world, local_rank):
                                                      "all-gather" % world,
                                           "allreduce": "one NCCL all-reduce, replicated Adam"}[args.dp_mode])
                        if world > 1 else "single GPU"},
+            # share of parameter floats whose Adam moments are still exactly 0 (never received a gradient): the Adam
+            # kernels skip those vectors (an exact fixed point of the update), so K5's time depends on it
+            "adam_idle_frac": adam_idle_frac,
             "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
