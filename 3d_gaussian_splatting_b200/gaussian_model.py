@@ -302,3 +302,66 @@ class Trainer:
             torch.cuda.current_stream(self.g.device).synchronize()
             if not self.check_overflow():   # capacity mode only: an overflowed iteration was skipped on the device
                 return float(self._loss_host[0])
+
+    def train(self, cams, gts_host, n_steps: int, first: int = 0, depth: int = 2, on_loss=None):
+        """The training loop of the reference (src/utils/train_utils.cpp:120-150: for each iteration pick a view,
+        render, loss, backward, optimiser step, log) with HOST ground-truth images, as a software pipeline: the
+        host enqueues iteration i while the device is still working on iteration i - depth + 1, so the device
+        never waits for the host.  Every iteration still copies its pinned ground truth host->device and its loss
+        device->host; the host just reads loss i after it has enqueued iteration i + depth - 1.
+        cams / gts_host: sequences cycled by iteration index (first + i).  Returns the list of per-iteration
+        losses (floats, in order); on_loss(i, loss) is called as each arrives.
+
+        Fixed pair capacity (reserve_pairs) is required -- the synchronous forward would stall the pipeline.  An
+        iteration whose forward overflows the capacity is skipped on the device (Adam guard); the host learns of
+        it `depth - 1` iterations late, drains the pipeline, doubles the capacity and runs that view again at the
+        end (the Adam bias-correction counters of the iterations that were already in flight stay one ahead)."""
+        assert self.pair_capacity, "Trainer.train needs reserve_pairs() (capacity mode)"
+        dev = self.g.device
+        shape = gts_host[0].shape
+        if self._gt_dev is None or self._gt_dev.shape != shape:
+            self._gt_dev = torch.empty(shape, dtype=torch.float32, device=dev)
+        ring = max(2, int(depth)) + 1
+        if getattr(self, "_ring", None) is None or self._ring[0].shape[0] != ring:
+            self._ring = (torch.zeros(ring, 2, dtype=torch.float32).pin_memory(),
+                          [torch.cuda.Event() for _ in range(ring)])
+            gp = self.skip_guard if isinstance(self.skip_guard, int) else None
+            self._guard_view = self._guard_tensor if self._guard_tensor is not None else self.rast.wrap(gp, 1)
+        slots, events = self._ring
+        stream = torch.cuda.current_stream(dev)
+        losses, pending, redo = [None] * n_steps, [], []
+
+        def retire():
+            j, slot = pending.pop(0)
+            events[slot].synchronize()
+            if slots[slot, 1] != 0.0:      # iteration j overflowed: skipped on the device
+                redo.append(j)
+                return
+            losses[j] = float(slots[slot, 0])
+            if on_loss is not None:
+                on_loss(j, losses[j])
+
+        def enqueue(j, slot):
+            v = (first + j) % len(cams)
+            loss = self.train_step_device(cams[v], self._gt_dev, gt_host=gts_host[v])
+            slots[slot, 0:1].copy_(loss.reshape(1), non_blocking=True)
+            slots[slot, 1:2].copy_(self._guard_view, non_blocking=True)
+            events[slot].record(stream)
+            pending.append((j, slot))
+
+        for i in range(n_steps):
+            if len(pending) >= depth:
+                retire()
+            enqueue(i, i % ring)
+        while pending:
+            retire()
+        while redo:      # rare: overflowed views, one at a time with a grown capacity
+            batch, redo = redo, []
+            D, _ = self.rast.forward_status()
+            self.pair_capacity = max(2 * self.pair_capacity, int(1.25 * D))
+            self.rast.set_duplicate_capacity(self.pair_capacity)
+            self.retries += len(batch)
+            for j in batch:
+                enqueue(j, 0)
+                retire()
+        return losses

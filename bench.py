@@ -46,6 +46,8 @@ def parse_args():
                     help="N>1: peer = exchange fused into K4b/K5 over NVLink peer memory (sharded Adam); sharded = NCCL "
                          "reduce-scatter + sharded Adam + all-gather; allreduce = NCCL all-reduce + replicated Adam")
     ap.add_argument("--no-fused", action="store_true", help="N=1: separate K4b and K5 launches instead of the fused kernel")
+    ap.add_argument("--e2e-api", default="loop", choices=["loop", "step"],
+                    help="e2e leg: Trainer.train (pipelined loop, default) or one synchronous Trainer.train_step per step")
     ap.add_argument("--N", type=int, default=None, help="override the Gaussian count (debugging only)")
     return ap.parse_args()
 
@@ -330,7 +332,20 @@ def run_ours(args, rank, world, local_rank):
     assert not trainer.rast.forward_status()[1], "pair capacity overflow inside the timed region"
     ms_per_step = total_ms / args.steps
     value = world * 1.0 / (ms_per_step * 1e-3)
-    e2e_ms, _ = timed(step_e2e, args.steps, warm)
+    # end to end through the public training loop (Trainer.train, the reference's train() loop shape): pinned HOST
+    # ground truth copied in and the loss copied out EVERY iteration; the loop is a depth-2 software pipeline, so
+    # the host reads loss i while the device already works on iteration i + 1.  One call = args.steps iterations.
+    e2e_losses = []
+
+    def loop_e2e(first, n):
+        e2e_losses[:] = trainer.train(my_cams[:args.views], gts_host[:args.views], n, first=first)
+
+    if args.e2e_api == "loop":
+        # timed() runs fn(0) as its one warm-up call (`warm` iterations), then fn(1) timed (args.steps iterations)
+        e2e_ms, _ = timed(lambda i: loop_e2e(0, warm) if i == 0 else loop_e2e(warm, args.steps), 1, 1)
+        assert len(e2e_losses) == args.steps and all(np.isfinite(l) for l in e2e_losses), "e2e loop lost a loss"
+    else:
+        e2e_ms, _ = timed(step_e2e, args.steps, warm)
     e2e_value = world * 1.0 / (e2e_ms / args.steps * 1e-3)
 
     # ---- per-stage device times (CUDA events recorded by the library around each stage) ----
@@ -432,7 +447,10 @@ def run_ours(args, rank, world, local_rank):
                          "step_frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
             "cpu_baseline": cpu_baseline,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
-                    "h2d_bytes_per_step": int(gts_host[0].numel() * 4 + 172), "d2h_bytes_per_step": 4},
+                    "h2d_bytes_per_step": int(gts_host[0].numel() * 4 + 172),
+                    "d2h_bytes_per_step": 8 if args.e2e_api == "loop" else 4,
+                    "api": ("Trainer.train: depth-2 pipelined loop, ground truth H2D + loss/overflow flag D2H every "
+                            "iteration" if args.e2e_api == "loop" else "Trainer.train_step: one synchronous call per step")},
             "pair_capacity": trainer.pair_capacity, "capacity_retries": trainer.retries,
             # own kernels only (NCCL's are not counted); the routed K4b of the peer mode is one launch per owner rank
             "gpu_launches": (OWN_KERNELS_PER_STEP - (1 if world == 1 and trainer.fused_step else 0) + (world - 1 if world > 1 and args.dp_mode == "peer" else 0)
