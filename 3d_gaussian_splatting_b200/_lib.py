@@ -57,7 +57,7 @@ EXPORTS = (
     "gs_version", "gs_create", "gs_destroy", "gs_last_error", "gs_forward", "gs_backward",
     "gs_adam_densify_step", "gs_loss", "gs_debug_size", "gs_debug_get", "gs_set_profiling", "gs_get_stage_ms",
     "gs_focal2fov", "gs_get_world2view2", "gs_get_projection_matrix", "gs_camera_settings", "gs_expon_lr",
-    "gs_adam_step_flat", "gs_backward_adam_step", "gs_debug_reuse_blend_gradients", "gs_set_gradient_routing", "gs_adam_step_peer", "gs_peer_alloc", "gs_peer_open", "gs_peer_close", "gs_peer_free", "gs_set_duplicate_capacity", "gs_set_overflow_mirror", "gs_overflow_guard", "gs_get_forward_status",
+    "gs_adam_step_flat", "gs_backward_adam_step", "gs_densify_plan", "gs_densify_apply", "gs_reset_opacity", "gs_debug_reuse_blend_gradients", "gs_set_gradient_routing", "gs_adam_step_peer", "gs_peer_alloc", "gs_peer_open", "gs_peer_close", "gs_peer_free", "gs_set_duplicate_capacity", "gs_set_overflow_mirror", "gs_overflow_guard", "gs_get_forward_status",
 )
 
 
@@ -89,6 +89,10 @@ def _load() -> C.CDLL:
     lib.gs_backward_adam_step.argtypes = [vp, C.POINTER(GsSettings), i, C.POINTER(GsGaussians), vp, vp, vp * 6, vp * 6,
                                           d * 6, C.c_longlong * 6, d, d, d, vp, vp, vp, vp, vp]
     lib.gs_debug_reuse_blend_gradients.argtypes = [vp, i]
+    f = C.c_float
+    lib.gs_densify_plan.argtypes = [vp, i, vp, vp, vp, vp, f, f, f, f, f, i * 4, vp]
+    lib.gs_densify_apply.argtypes = [vp, i, i * 6, vp * 6, vp * 6, vp * 6, vp * 6, vp * 6, vp * 6, C.c_ulonglong, vp]
+    lib.gs_reset_opacity.argtypes = [vp, i, vp, vp, vp, vp]
     lib.gs_set_gradient_routing.argtypes = [vp, i, i, i, C.POINTER(vp)]
     lib.gs_adam_step_peer.argtypes = [vp, i, i, i, i, C.POINTER(vp), C.POINTER(vp), vp * 6, vp * 6, i * 6, d * 6,
                                       C.c_longlong * 6, d, d, d, vp, vp, vp, vp, vp, vp, vp]

@@ -37,6 +37,12 @@ cudaError_t gs_launch_preprocess_backward_adam(const gs_settings&, const gs_gaus
                                                const uint8_t*, const float4*, float* const[6], float* const[6],
                                                const double[6], const long long[6], double, double, double, int*,
                                                float*, float*, const float*, int*, cudaStream_t);
+cudaError_t gs_launch_densify_plan(int, const float*, const float*, const float*, const float*, float, float, float,
+                                   float, float, uint8_t*, uint32_t*, uint32_t*, uint32_t*, cudaStream_t);
+cudaError_t gs_launch_densify_apply(int, const uint8_t*, const uint32_t*, const uint32_t*, const int[6], float* const[6],
+                                    float* const[6], float* const[6], float* const[6], float* const[6],
+                                    float* const[6], unsigned long long, cudaStream_t);
+cudaError_t gs_launch_reset_opacity(int, float*, float*, float*, cudaStream_t);
 cudaError_t gs_launch_adam_peer(int, int, int, int, float* const[], const float* const[], float* const[6],
                                 float* const[6], const int[6], const double[6], const long long[6], double, double,
                                 double, const int*, const float*, int*, float*, float*, const float*, cudaStream_t);
@@ -76,6 +82,8 @@ struct gs_ctx {
   DevBuf ckpt, work_items, counters;
   int num_sms = 148;
   DevBuf loss_acc, ssim_work, tail_grads;
+  DevBuf dz_codes, dz_counts;  // densification plan: per-Gaussian outcome codes, per-block counts -> offsets + totals
+  int dz_N = -1;               // N of the pending plan (gs_densify_plan -> gs_densify_apply)
   uint32_t* d_host_pinned = nullptr;  // readback: bytes 0..7 D (u64), 8..11 overflow flag
   uint64_t dup_cap_fixed = 0;         // > 0: caller-fixed pair capacity, no host synchronisation in gs_forward
   float* overflow_mirror = nullptr;   // optional caller-owned device float raised to 1.0 on overflow
@@ -208,7 +216,8 @@ void gs_destroy(gs_ctx* c) {
                     &c->sort_k1, &c->sort_v0, &c->sort_v1, &c->dup_sums, &c->radix_counts,
                     &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_state,  &c->n_contrib,
                     &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters, &c->loss_acc, &c->ssim_work,
-                    &c->tail_grads};
+                    &c->tail_grads, &c->dz_codes,
+                    &c->dz_counts};
   for (DevBuf* b : bufs)
     if (b->ptr) cudaFree(b->ptr);
   if (c->d_host_pinned) cudaFreeHost(c->d_host_pinned);
@@ -622,6 +631,81 @@ int gs_backward_adam_step(gs_ctx* c, const gs_settings* st, int N, const gs_gaus
     GS_CUDA_CHECK(c, cudaGetLastError());
   }
   c->have_backward = true;
+  return GS_OK;
+}
+
+// ---- densify / prune / opacity reset (densify.cu) ----
+int gs_densify_plan(gs_ctx* c, int N, const float* xyz_grad_accum, const float* denom, const float* opacities,
+                    const float* scales, float grad_threshold, float min_opacity, float extent, float percent_dense,
+                    float max_screen_size, int counts[4], void* stream_) {
+  if (!c || N < 0 || !counts || (N > 0 && (!xyz_grad_accum || !denom || !opacities || !scales))) {
+    gs_set_error(c, "gs_densify_plan: null argument");
+    return GS_EINVAL;
+  }
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  const int nb = (N + 255) / 256;
+  GS_ENSURE(c, c->dz_codes, (size_t)N + 16);
+  GS_ENSURE(c, c->dz_counts, ((size_t)nb * 4 + 8) * 4);
+  uint32_t* totals = (uint32_t*)c->dz_counts.ptr + (size_t)nb * 4;
+  GS_CUDA_CHECK(c, gs_launch_densify_plan(N, xyz_grad_accum, denom, opacities, scales, grad_threshold, min_opacity,
+                                          extent, percent_dense, max_screen_size, (uint8_t*)c->dz_codes.ptr,
+                                          (uint32_t*)c->dz_counts.ptr, totals, nullptr, stream));
+  uint32_t h[4];
+  GS_CUDA_CHECK(c, cudaMemcpyAsync(h, totals, 16, cudaMemcpyDeviceToHost, stream));
+  GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
+  const long long n_new = (long long)h[0] + h[1] + 2ll * h[2];
+  if (n_new > 0x7fffffffll) {
+    gs_set_error(c, "gs_densify_plan: %lld Gaussians after the step exceed the int32 index range", n_new);
+    return GS_EINVAL;
+  }
+  counts[0] = (int)h[0];
+  counts[1] = (int)h[1];
+  counts[2] = (int)h[2];
+  counts[3] = (int)((long long)h[3] - n_new);
+  c->dz_N = N;
+  return GS_OK;
+}
+
+int gs_densify_apply(gs_ctx* c, int N, const int widths[6], float* const src_params[6], float* const src_exp_avg[6],
+                     float* const src_exp_avg_sq[6], float* const dst_params[6], float* const dst_exp_avg[6],
+                     float* const dst_exp_avg_sq[6], unsigned long long seed, void* stream_) {
+  if (!c || !widths || !src_params || !src_exp_avg || !src_exp_avg_sq || !dst_params || !dst_exp_avg || !dst_exp_avg_sq) {
+    gs_set_error(c, "gs_densify_apply: null argument");
+    return GS_EINVAL;
+  }
+  if (c->dz_N != N) {
+    gs_set_error(c, "gs_densify_apply needs the gs_densify_plan of the same N to have run on this context");
+    return GS_ESTATE;
+  }
+  if (widths[0] != 3 || widths[3] != 1 || widths[4] != 3 || widths[5] != 4) {
+    gs_set_error(c, "gs_densify_apply: group widths must be xyz 3, f_dc, f_rest, opacity 1, scaling 3, rotation 4");
+    return GS_EINVAL;
+  }
+  for (int k = 0; k < 6; ++k)
+    if (widths[k] > 0 && N > 0 && (!src_params[k] || !src_exp_avg[k] || !src_exp_avg_sq[k] || !dst_params[k] ||
+                                   !dst_exp_avg[k] || !dst_exp_avg_sq[k])) {
+      gs_set_error(c, "gs_densify_apply: group %d has a null slab", k);
+      return GS_EINVAL;
+    }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  const int nb = (N + 255) / 256;
+  const uint32_t* totals = (const uint32_t*)c->dz_counts.ptr + (size_t)nb * 4;
+  GS_CUDA_CHECK(c, gs_launch_densify_apply(N, (const uint8_t*)c->dz_codes.ptr, (const uint32_t*)c->dz_counts.ptr, totals,
+                                           widths, src_params, src_exp_avg, src_exp_avg_sq, dst_params, dst_exp_avg,
+                                           dst_exp_avg_sq, seed, (cudaStream_t)stream_));
+  c->dz_N = -1;
+  c->have_forward = false;  // N changed: the forward state no longer matches the model
+  return GS_OK;
+}
+
+int gs_reset_opacity(gs_ctx* c, int N, float* opacities, float* exp_avg, float* exp_avg_sq, void* stream_) {
+  if (!c || N < 0 || (N > 0 && (!opacities || !exp_avg || !exp_avg_sq))) {
+    gs_set_error(c, "gs_reset_opacity: null argument");
+    return GS_EINVAL;
+  }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_CUDA_CHECK(c, gs_launch_reset_opacity(N, opacities, exp_avg, exp_avg_sq, (cudaStream_t)stream_));
   return GS_OK;
 }
 

@@ -121,6 +121,34 @@ class GaussianModel:
         self.lr[0] = self.xyz_scheduler_args(iteration)
         return self.lr[0]
 
+    # ---- densification (published 3DGS algorithm; oracle/orc_densify.c is the specification) ----
+    def densify_and_prune(self, rast: Rasterizer, max_grad: float, min_opacity: float, extent: float,
+                          max_screen_size: float = 0.0, seed: int = 0):
+        """Clone / split / prune in one classification + one scatter pass (csrc/densify.cu), carrying the Adam
+        moments along; the statistics restart from zero, as after the published step.  Returns the counts
+        [kept originals, kept clones, kept split parents, pruned]."""
+        N = self.N
+        counts = rast.densify_plan(self.xyz_gradient_accum_, self.denom_, self.opacity_, self.scaling_, max_grad,
+                                   min_opacity, extent, self.percent_dense, max_screen_size)
+        n_new = counts[0] + counts[1] + 2 * counts[2]
+        src = self.params()
+        shapes = [(n_new,) + tuple(p.shape[1:]) for p in src]
+        new = lambda: [torch.empty(s, dtype=torch.float32, device=self.device) for s in shapes]
+        dst_p, dst_m, dst_v = new(), new(), new()
+        rast.densify_apply(N, self.widths, (src, self.exp_avg, self.exp_avg_sq), (dst_p, dst_m, dst_v), seed)
+        (self.xyz_, self.features_dc_, self.features_rest_, self.opacity_, self.scaling_, self.rotation_) = dst_p
+        self.exp_avg, self.exp_avg_sq = dst_m, dst_v
+        self.grads = [torch.zeros_like(p) for p in dst_p]
+        self.grad_means2D = torch.zeros((n_new, 2), device=self.device)
+        self.xyz_gradient_accum_ = torch.zeros((n_new, 1), device=self.device)
+        self.denom_ = torch.zeros((n_new, 1), device=self.device)
+        self.max_radii2D_ = torch.zeros(n_new, dtype=torch.int32, device=self.device)
+        return counts
+
+    def reset_opacity(self, rast: Rasterizer):
+        """opacity <- logit(min(sigmoid(opacity), 0.01)), fresh Adam state for the group (opacity_reset_interval_)."""
+        rast.reset_opacity(self.opacity_, self.exp_avg[3], self.exp_avg_sq[3])
+
     def grad_sinks(self):
         g = self.grads
         return dict(means3D=g[0], sh_dc=g[1], sh_rest=g[2], opacities=g[3], scales=g[4], rotations=g[5],
@@ -260,6 +288,29 @@ class Trainer:
                                     xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_,
                                     skip_guard=self.skip_guard if self.pair_capacity else None)
 
+    def densification_due(self, iteration: int) -> bool:
+        o = self.opt
+        return (iteration < o.densify_until_iter and iteration > o.densify_from_iter
+                and iteration % o.densification_interval == 0) or \
+               (iteration < o.densify_until_iter and iteration % o.opacity_reset_interval == 0)
+
+    def densification_step(self, iteration: int, extent: float, white_background: bool = False):
+        """The block of the published loop that follows the optimiser bookkeeping of iteration `iteration`
+        (schedule parameters: src/arguments/params.h:61-67).  Changes N: the caller must have drained any
+        pipelined iterations.  Single GPU / all-reduce data parallelism (every rank holds the merged statistics and
+        the same seed, hence the same outcome)."""
+        o, g = self.opt, self.g
+        assert self.peer is None and self.sharded is None, "densification with a sharded optimiser: not wired yet"
+        done = None
+        if iteration < o.densify_until_iter:
+            if iteration > o.densify_from_iter and iteration % o.densification_interval == 0:
+                size_threshold = 20.0 if iteration > o.opacity_reset_interval else 0.0
+                done = g.densify_and_prune(self.rast, o.densify_grad_threshold, 0.005, extent, size_threshold,
+                                           seed=iteration)
+            if iteration % o.opacity_reset_interval == 0 or (white_background and iteration == o.densify_from_iter):
+                g.reset_opacity(self.rast)
+        return done
+
     def check_overflow(self) -> bool:
         """After the step's stream synchronisation: did the last forward overflow the fixed capacity?  If so the
         device skipped the optimiser step; roll the host-side counters back and double the capacity."""
@@ -303,7 +354,8 @@ class Trainer:
             if not self.check_overflow():   # capacity mode only: an overflowed iteration was skipped on the device
                 return float(self._loss_host[0])
 
-    def train(self, cams, gts_host, n_steps: int, first: int = 0, depth: int = 2, on_loss=None):
+    def train(self, cams, gts_host, n_steps: int, first: int = 0, depth: int = 2, on_loss=None,
+              densify_extent: float | None = None):
         """The training loop of the reference (src/utils/train_utils.cpp:120-150: for each iteration pick a view,
         render, loss, backward, optimiser step, log) with HOST ground-truth images, as a software pipeline: the
         host enqueues iteration i while the device is still working on iteration i - depth + 1, so the device
@@ -315,7 +367,12 @@ class Trainer:
         Fixed pair capacity (reserve_pairs) is required -- the synchronous forward would stall the pipeline.  An
         iteration whose forward overflows the capacity is skipped on the device (Adam guard); the host learns of
         it `depth - 1` iterations late, drains the pipeline, doubles the capacity and runs that view again at the
-        end (the Adam bias-correction counters of the iterations that were already in flight stay one ahead)."""
+        end (the Adam bias-correction counters of the iterations that were already in flight stay one ahead).
+
+        densify_extent (the scene extent): run the densification schedule of the published loop
+        (densification_step) -- the pipeline is drained first, since N changes.  Unlike the published loop, whose
+        freshly concatenated parameters carry no gradient in that iteration, the iteration's optimiser step has
+        already been applied when the model is densified."""
         assert self.pair_capacity, "Trainer.train needs reserve_pairs() (capacity mode)"
         dev = self.g.device
         shape = gts_host[0].shape
@@ -353,6 +410,10 @@ class Trainer:
             if len(pending) >= depth:
                 retire()
             enqueue(i, i % ring)
+            if densify_extent is not None and self.densification_due(self.iteration):
+                while pending:
+                    retire()
+                self.densification_step(self.iteration, densify_extent)
         while pending:
             retire()
         while redo:      # rare: overflowed views, one at a time with a grown capacity

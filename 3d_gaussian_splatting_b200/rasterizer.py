@@ -290,6 +290,33 @@ class Rasterizer:
             (C.c_longlong * 6)(*pad([int(s[5]) for s in segments], 1)), float(beta1), float(beta2), float(eps),
             int(zero_grads), C.c_void_p(skip_guard) if skip_guard else None, C.c_void_p(stream)))
 
+    # ---- densify / prune / opacity reset ------------------------------------------------------
+    def densify_plan(self, xyz_grad_accum, denom, opacities, scales, grad_threshold, min_opacity, extent,
+                     percent_dense=0.01, max_screen_size=0.0):
+        """Classify every Gaussian (gs_densify_plan).  Returns [kept originals, kept clones, kept split parents,
+        pruned]; the new N is the first two plus twice the third.  Synchronises the current stream."""
+        N = int(opacities.shape[0])
+        counts = (C.c_int * 4)()
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._ctx, lib.gs_densify_plan(self._ctx, N, _ptr(xyz_grad_accum), _ptr(denom), _ptr(opacities),
+                                             _ptr(scales), float(grad_threshold), float(min_opacity), float(extent),
+                                             float(percent_dense), float(max_screen_size), counts, C.c_void_p(stream)))
+        return list(counts)
+
+    def densify_apply(self, N, widths, src, dst, seed=0):
+        """src / dst: (params, exp_avg, exp_avg_sq), each six tensors; moves rows and moments (gs_densify_apply)."""
+        VP6 = C.c_void_p * 6
+        arr = lambda ts: VP6(*[None if t is None or t.numel() == 0 else t.data_ptr() for t in ts])
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._ctx, lib.gs_densify_apply(self._ctx, int(N), (C.c_int * 6)(*widths), arr(src[0]), arr(src[1]),
+                                              arr(src[2]), arr(dst[0]), arr(dst[1]), arr(dst[2]), int(seed),
+                                              C.c_void_p(stream)))
+
+    def reset_opacity(self, opacities, exp_avg, exp_avg_sq):
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._ctx, lib.gs_reset_opacity(self._ctx, int(opacities.shape[0]), _ptr(opacities), _ptr(exp_avg),
+                                              _ptr(exp_avg_sq), C.c_void_p(stream)))
+
     # ---- multi-GPU step over peer memory --------------------------------------------------------
     def peer_alloc(self, nbytes: int):
         """Zero-filled device buffer other processes may map: (device pointer, 64-byte IPC handle)."""

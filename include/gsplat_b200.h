@@ -170,6 +170,33 @@ GS_API int gs_backward_adam_step(gs_ctx *ctx, const gs_settings *settings, int N
                                  double beta1, double beta2, double eps, int *max_radii2D, float *xyz_grad_accum,
                                  float *denom, const float *skip_guard, void *stream);
 
+/* ---- densify / prune / opacity reset with optimiser-state surgery ------------------------------
+ * The consumers of the statistics gs_adam_densify_step accumulates (max_radii2D_, xyz_gradient_accum_, denom_,
+ * src/scene/gaussian_model.h:18-20; percent_dense_ :44) under the schedule the reference parses
+ * (src/arguments/params.h:61-67: densification_interval_, opacity_reset_interval_, densify_from_iter_,
+ * densify_until_iter_, densify_grad_threshold_).  The reference declares the state, not the step; the algorithm
+ * is the published 3DGS densify_and_prune (clone small high-gradient Gaussians, split large ones into two
+ * samples shrunk by 1.6, prune split parents / faint / over-large ones), specified in oracle/orc_densify.c.
+ *
+ * Two calls, because the caller owns the slabs and N changes:
+ *   gs_densify_plan   classifies every Gaussian (raw opacity logits and log-scales in) and returns
+ *                     counts = {kept originals, kept clones, kept split parents, pruned};
+ *                     the new N is counts[0] + counts[1] + 2*counts[2].  Synchronises the stream (12 bytes back).
+ *   gs_densify_apply  moves parameters AND Adam moments from the old slabs to caller-allocated new ones of the
+ *                     new N, in the published order [originals | clones | first children | second children];
+ *                     new Gaussians get zero moments.  Group order and widths as gs_adam_densify_step.
+ *                     seed: the counter-based generator of the split samples (oracle/orc_densify.c).
+ * The three statistics buffers are all-zero after the published step: the caller re-allocates them zeroed.
+ * gs_reset_opacity: opacity <- logit(min(sigmoid(opacity), 0.01)), fresh Adam state for the opacity group. */
+GS_API int gs_densify_plan(gs_ctx *ctx, int N, const float *xyz_grad_accum, const float *denom,
+                           const float *opacities, const float *scales, float grad_threshold, float min_opacity,
+                           float extent, float percent_dense, float max_screen_size, int counts[4], void *stream);
+GS_API int gs_densify_apply(gs_ctx *ctx, int N, const int widths[6], float *const src_params[6],
+                            float *const src_exp_avg[6], float *const src_exp_avg_sq[6], float *const dst_params[6],
+                            float *const dst_exp_avg[6], float *const dst_exp_avg_sq[6], unsigned long long seed,
+                            void *stream);
+GS_API int gs_reset_opacity(gs_ctx *ctx, int N, float *opacities, float *exp_avg, float *exp_avg_sq, void *stream);
+
 /* Test hook: with on != 0, gs_backward_adam_step skips the blend backward and consumes the per-Gaussian gradient
  * records the last gs_backward left in the context -- the blend backward sums with fp32 atomics, so this is what
  * makes "fused == separate" checkable bit for bit. */

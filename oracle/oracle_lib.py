@@ -218,6 +218,46 @@ class Oracle:
         self.lib.orc_densify_stats(C.c_int(radii.shape[0]), self.p(radii), self.p(dL_dmean2D),
                                    self.p(max_radii2D), self.p(accum), self.p(denom))
 
+    # ---- densify / prune / opacity reset (orc_densify.c) -------------------------------------
+    class DensifyParams(C.Structure):
+        _fields_ = [("grad_threshold", C.c_float), ("min_opacity", C.c_float), ("extent", C.c_float),
+                    ("percent_dense", C.c_float), ("max_screen_size", C.c_float), ("seed", C.c_ulonglong)]
+
+    def split_normals(self, seed, parent, copy):
+        z = (C.c_float * 3)()
+        self.lib.orc_split_normals(C.c_ulonglong(seed), C.c_ulonglong(parent), C.c_int(copy), z)
+        return np.array(z[:], np.float32)
+
+    def densify_and_prune(self, params, exp_avg, exp_avg_sq, xyz_grad_accum, denom, max_radii2D, grad_threshold,
+                          min_opacity, extent, percent_dense=0.01, max_screen_size=0.0, seed=0):
+        """params / exp_avg / exp_avg_sq: six float32 arrays (xyz, f_dc, f_rest, opacity, scaling, rotation), N rows.
+        Returns (new_params, new_exp_avg, new_exp_avg_sq, counts[4])."""
+        N = params[0].shape[0]
+        widths = [int(p.size // max(N, 1)) for p in params]
+        f32 = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+        P, M, V = [f32(a) for a in params], [f32(a) for a in exp_avg], [f32(a) for a in exp_avg_sq]
+        cap = 2 * N + 1
+        out = [[np.zeros((cap, max(w, 1)), np.float32) for w in widths] for _ in range(3)]
+        FP6 = C.POINTER(C.c_float) * 6
+        ptr = lambda arrs: FP6(*[a.ctypes.data_as(C.POINTER(C.c_float)) for a in arrs])
+        prm = self.DensifyParams(grad_threshold, min_opacity, extent, percent_dense, max_screen_size, seed)
+        counts = (C.c_int * 4)()
+        self.lib.orc_densify_and_prune.restype = C.c_int
+        n = self.lib.orc_densify_and_prune(
+            C.c_int(N), (C.c_int * 6)(*widths), ptr(P), ptr(M), ptr(V),
+            f32(xyz_grad_accum).ctypes.data_as(C.POINTER(C.c_float)), f32(denom).ctypes.data_as(C.POINTER(C.c_float)),
+            np.ascontiguousarray(max_radii2D, dtype=np.int32).ctypes.data_as(C.POINTER(C.c_int)), C.byref(prm),
+            ptr(out[0]), ptr(out[1]), ptr(out[2]), counts)
+        shp = lambda a, src: a.reshape(-1)[:n * (src.size // max(N, 1))].reshape((n,) + src.shape[1:])
+        res = [[shp(o, src).copy() for o, src in zip(out[j], params)] for j in range(3)]
+        return res[0], res[1], res[2], list(counts)
+
+    def reset_opacity(self, opacity, exp_avg, exp_avg_sq):
+        for a in (opacity, exp_avg, exp_avg_sq):
+            assert a.dtype == np.float32 and a.flags.c_contiguous
+        fp = lambda a: a.ctypes.data_as(C.POINTER(C.c_float))
+        self.lib.orc_reset_opacity(C.c_int(opacity.size), fp(opacity), fp(exp_avg), fp(exp_avg_sq))
+
     def photometric_loss(self, img, gt, lambda_dssim=0.2, want_grad=True):
         """(1-lambda) L1 + lambda (1 - SSIM) (orc_ssim.c); returns (loss, dL/dimg or None, l1, ssim)."""
         img = self.arr(img); gt = self.arr(gt)
