@@ -185,7 +185,24 @@ class PeerShardedAdam:
             dist.all_gather_object(handles, handle, group=group)
         else:
             handles[0] = handle
-        self.bases = [self.base if r == rank else rast.peer_open(handles[r]) for r in range(world)]
+        # map the peers' buffers; every rank must succeed or every rank gives up (same exception everywhere, so
+        # the caller can fall back to an NCCL mode without ranks diverging)
+        self.bases, failure = [], None
+        for r in range(world):
+            try:
+                self.bases.append(self.base if r == rank else rast.peer_open(handles[r]))
+            except Exception as e:      # e.g. CUDA IPC not permitted between these processes
+                failure = failure or f"rank {rank} cannot map rank {r}: {e}"
+                self.bases.append(0)
+        if world > 1:
+            ok = torch.tensor([0.0 if failure else 1.0], device=params[0].device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if ok.item() == 0.0:
+                for r, b in enumerate(self.bases):
+                    if r != rank and b:
+                        rast.peer_close(b)
+                rast.peer_free(self.base)
+                raise RuntimeError("peer memory unavailable: " + (failure or "another rank failed to map a peer"))
         self.flat = rast.wrap(self.base, self.total)
         views = []
         for o, c, p in zip(self.p_off, self.widths, params):

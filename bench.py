@@ -263,8 +263,15 @@ def run_ours(args, rank, world, local_rank):
     if world > 1 and args.dp_mode == "peer":
         # K4b stores gradient rows into the owner's slots over NVLink; K5 sums them, updates the owned shard and
         # stores the parameters into every replica; two one-float NCCL all-reduces order the ranks
-        sharded = trainer.shard_optimizer_peer(rank, world)
-        slab, guard = None, sharded.guard
+        try:
+            sharded = trainer.shard_optimizer_peer(rank, world)
+            slab, guard = None, sharded.guard
+        except RuntimeError as e:       # raised on every rank alike (PeerShardedAdam): fall back to the NCCL mode
+            if rank == 0:
+                print(f"[bench] {e}; falling back to --dp-mode sharded", file=sys.stderr)
+            args.dp_mode = "sharded"
+    if world > 1 and args.dp_mode == "peer":
+        pass
     elif world > 1 and args.dp_mode == "sharded":
         # gradients reduce-scattered, Adam on the 1/world slice this rank owns, parameters all-gathered
         sharded = trainer.shard_optimizer(rank, world)
