@@ -155,6 +155,21 @@ class GaussianModel:
                     means2D=self.grad_means2D)
 
 
+class ViewSampler:
+    """Camera sampling WITHOUT replacement, as the training loop the reference transliterates does it: a stack of
+    all training views, one popped at a random position per iteration, refilled when empty
+    (loop skeleton: src/utils/train_utils.cpp:128-145).  Seeded, so that every rank of a data-parallel job can
+    draw the same permutation and take its own slice of it."""
+
+    def __init__(self, n_views: int, seed: int = 0):
+        self.n, self.rng, self.stack = int(n_views), np.random.Generator(np.random.Philox(seed)), []
+
+    def __call__(self) -> int:
+        if not self.stack:
+            self.stack = list(range(self.n))
+        return self.stack.pop(int(self.rng.integers(0, len(self.stack))))
+
+
 def render(viewpoint_camera, pc: GaussianModel, pipe: PipelineParams, bg_color, rast: Rasterizer,
            scaling_modifier: float = 1.0, fused_activations: bool = True, with_visibility: bool = True):
     """The missing render(viewpoint_cam, gaussians, pipe, background) call.  Returns
@@ -355,13 +370,14 @@ class Trainer:
                 return float(self._loss_host[0])
 
     def train(self, cams, gts_host, n_steps: int, first: int = 0, depth: int = 2, on_loss=None,
-              densify_extent: float | None = None):
+              densify_extent: float | None = None, sampler=None):
         """The training loop of the reference (src/utils/train_utils.cpp:120-150: for each iteration pick a view,
         render, loss, backward, optimiser step, log) with HOST ground-truth images, as a software pipeline: the
         host enqueues iteration i while the device is still working on iteration i - depth + 1, so the device
         never waits for the host.  Every iteration still copies its pinned ground truth host->device and its loss
         device->host; the host just reads loss i after it has enqueued iteration i + depth - 1.
-        cams / gts_host: sequences cycled by iteration index (first + i).  Returns the list of per-iteration
+        cams / gts_host: sequences cycled by iteration index (first + i), or drawn by `sampler` (a ViewSampler:
+        without replacement, as the published loop does).  Returns the list of per-iteration
         losses (floats, in order); on_loss(i, loss) is called as each arrives.
 
         Fixed pair capacity (reserve_pairs) is required -- the synchronous forward would stall the pipeline.  An
@@ -398,8 +414,12 @@ class Trainer:
             if on_loss is not None:
                 on_loss(j, losses[j])
 
+        drawn = {}
+
         def enqueue(j, slot):
-            v = (first + j) % len(cams)
+            if j not in drawn:      # (a repeated iteration after an overflow keeps its view)
+                drawn[j] = sampler() if sampler is not None else (first + j) % len(cams)
+            v = drawn[j]
             loss = self.train_step_device(cams[v], self._gt_dev, gt_host=gts_host[v])
             slots[slot, 0:1].copy_(loss.reshape(1), non_blocking=True)
             slots[slot, 1:2].copy_(self._guard_view, non_blocking=True)

@@ -23,6 +23,7 @@ import threading
 import time
 
 import numpy as np
+from ctypes import c_int as C_int
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -155,7 +156,10 @@ class CpuStep:
         self.step = 0
         self.gts = {}
         self.views = views
-        self.cores = os.cpu_count() or 1
+        # all host cores, whatever OMP_NUM_THREADS the launcher exported (torchrun sets it to 1)
+        want = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        self.o.lib.orc_set_threads.restype = C_int
+        self.cores = int(self.o.lib.orc_set_threads(C_int(want)))
 
     def settings(self, cam):
         return self.RS(cam.image_height, cam.image_width, cam.tanfovx, cam.tanfovy, (0.0, 0.0, 0.0), 1.0,

@@ -66,3 +66,15 @@ double orc_l1_loss(size_t n, const real *img, const real *gt, real *dL_dimg) {
   }
   return acc / (double)n;
 }
+
+/* Thread control for the timed CPU leg (bench.py): launchers such as torchrun export OMP_NUM_THREADS=1, which
+ * would silently turn the "all host cores" baseline into a single-threaded one. */
+#ifdef _OPENMP
+#include <omp.h>
+int orc_set_threads(int n) {
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+}
+#else
+int orc_set_threads(int n) { (void)n; return 1; }
+#endif

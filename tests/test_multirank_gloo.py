@@ -135,3 +135,13 @@ def test_sharded_adam_world2_matches_dense_adam():
     for p in procs:
         p.join(60)
     assert res == [(0, True), (1, True)]
+
+
+def test_view_sampler_without_replacement():
+    gm = importlib.import_module("3d_gaussian_splatting_b200.gaussian_model")
+    s = gm.ViewSampler(7, seed=3)
+    for _ in range(3):                      # every epoch is a permutation of all views
+        assert sorted(s() for _ in range(7)) == list(range(7))
+    a, b = gm.ViewSampler(50, seed=1), gm.ViewSampler(50, seed=1)
+    seq = [a() for _ in range(120)]
+    assert seq == [b() for _ in range(120)] and seq[:50] != list(range(50))
