@@ -136,6 +136,16 @@ def stage_bytes(N, N_vis, D, D_eff, P, T, K):
     }
 
 
+def measured_traffic(stage):
+    """DRAM bytes per launch of the stage's kernel from the committed ncu capture (profiles/traffic.json), or None."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            v = json.load(f).get(stage)
+        return float(v) if v else None
+    except (OSError, ValueError):
+        return None
+
+
 # ---- CPU leg: the oracle port timed on the host cores ------------------------------------------
 class CpuStep:
     """One full train step (render, L1, backward, Adam + stats) of the CPU oracle on the same scene.
@@ -454,7 +464,7 @@ def run_ours(args, rank, world, local_rank):
             "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "traffic": None, "peak_kind": peak_kind,
+                         "frac": ach / peak, "traffic": measured_traffic(dom), "peak_kind": peak_kind,
                          "step_frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
             "cpu_baseline": cpu_baseline,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,

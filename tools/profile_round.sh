@@ -11,6 +11,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 120 --csv \
     --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launch.log 2>&1
 [ "${2:-}" = "launches" ] && exit 0
 ncu --set full --clock-control none --import-source on \
-    -k regex:'preprocess|duplicate|identify|blend|adam|l1_loss|order_tiles|radix|scan|ssim' -s 120 -c 72 \
+    -k regex:'preprocess|duplicate|identify|blend|adam|l1_loss|order_tiles|radix|scan|ssim' -s 136 -c 36 \
     -f -o gpurun_out/${TAG}_full $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
 ls -la gpurun_out/
