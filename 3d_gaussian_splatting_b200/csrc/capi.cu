@@ -43,6 +43,9 @@ cudaError_t gs_launch_densify_apply(int, const uint8_t*, const uint32_t*, const 
                                     float* const[6], float* const[6], float* const[6], float* const[6],
                                     float* const[6], unsigned long long, cudaStream_t);
 cudaError_t gs_launch_reset_opacity(int, float*, float*, float*, cudaStream_t);
+cudaError_t gs_launch_preprocess_backward_routed(const gs_settings&, const gs_gaussians&, const gs_gradients&, int, int,
+                                                 int, int, float* const[], const int*, const uint8_t*, const float4*,
+                                                 cudaStream_t);
 cudaError_t gs_launch_adam_peer(int, int, int, int, float* const[], const float* const[], float* const[6],
                                 float* const[6], const int[6], const double[6], const long long[6], double, double,
                                 double, const int*, const float*, int*, float*, float*, const float*, cudaStream_t);
@@ -93,8 +96,6 @@ struct gs_ctx {
   // to route_table[q*6 + k] (the slot this rank owns inside rank q's buffer; q == route_rank: local memory)
   int route_shards = 0, route_rows = 0, route_rank = 0;
   float* route_table[8 * 6] = {};
-  cudaStream_t route_stream = nullptr;  // the remote shards' K4b launches (NVLink-bound) run beside the local one
-  cudaEvent_t route_fork = nullptr, route_join = nullptr;
   // state of the last forward
   int N = -1, H = 0, W = 0, ntiles = 0;
   uint64_t D = 0;
@@ -223,9 +224,6 @@ void gs_destroy(gs_ctx* c) {
   if (c->d_host_pinned) cudaFreeHost(c->d_host_pinned);
   for (int i = 0; i < 2 * GS_NUM_STAGES; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
-  if (c->route_stream) cudaStreamDestroy(c->route_stream);
-  if (c->route_fork) cudaEventDestroy(c->route_fork);
-  if (c->route_join) cudaEventDestroy(c->route_join);
   delete c;
 }
 
@@ -453,7 +451,7 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
   if (N == 0) return GS_OK;
   const GsDims d = gs_dims(*st);
   GS_ENSURE(c, c->grad_geom, (size_t)N * 48);
-  {
+  if (!(c->reuse_blend_gradients && c->have_backward)) {
     StageTimer t(c, 6, stream);
     GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
     GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, c->point_list,
@@ -471,44 +469,15 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
                                                      (const uint8_t*)c->clamped.ptr,
                                                      (const float4*)c->grad_geom.ptr, stream));
     } else {
-      // one launch per owner rank, the parameter-gradient sinks re-based so that global row i lands at row
-      // i - q*R of the owner's slot.  Rotated start (own shard last): at any moment every rank stores to a
-      // different peer, so no GPU's NVLink ingress is shared by several senders.
+      // one launch for all owner ranks: consecutive blocks store to different owners' slots (PbRoute)
       if (grads->accumulate || in->colors_precomp || in->cov3D_precomp || !in->sh_rest) {
         gs_set_error(c, "gradient routing needs the raw split-SH parameter layout and accumulate == 0");
         return GS_EINVAL;
       }
-      const int G = c->route_shards, R = c->route_rows;
-      const int wrest = 3 * ((st->max_sh_degree + 1) * (st->max_sh_degree + 1) - 1);
-      // the remote shards go to a side stream: their stores are NVLink-bound and overlap the HBM-bound local shard
-      if (!c->route_stream) {
-        GS_CUDA_CHECK(c, cudaStreamCreateWithFlags(&c->route_stream, cudaStreamNonBlocking));
-        GS_CUDA_CHECK(c, cudaEventCreateWithFlags(&c->route_fork, cudaEventDisableTiming));
-        GS_CUDA_CHECK(c, cudaEventCreateWithFlags(&c->route_join, cudaEventDisableTiming));
-      }
-      GS_CUDA_CHECK(c, cudaEventRecord(c->route_fork, stream));
-      GS_CUDA_CHECK(c, cudaStreamWaitEvent(c->route_stream, c->route_fork, 0));
-      for (int j = 1; j <= G; ++j) {
-        const int q = (c->route_rank + j) % G;
-        cudaStream_t ls = q == c->route_rank ? stream : c->route_stream;
-        const long long b = (long long)q * R, e = b + R < N ? b + R : N;
-        if (b >= e) continue;
-        float* const* t = c->route_table + q * 6;
-        gs_gradients g = *grads;
-        g.dL_dmeans3D = t[0] - 3 * b;
-        g.dL_dsh_dc = t[1] - 3 * b;
-        g.dL_dsh_rest = wrest > 0 ? t[2] - (long long)wrest * b : nullptr;
-        g.dL_dopacities = t[3] - b;
-        g.dL_dscales = t[4] - 3 * b;
-        g.dL_drotations = t[5] - 4 * b;
-        g.sh_dc_stride = 3;
-        g.sh_rest_stride = wrest;
-        GS_CUDA_CHECK(c, gs_launch_preprocess_backward(*st, *in, g, (int)b, (int)e, (const int*)c->radii.ptr,
-                                                       (const uint8_t*)c->clamped.ptr,
-                                                       (const float4*)c->grad_geom.ptr, ls));
-      }
-      GS_CUDA_CHECK(c, cudaEventRecord(c->route_join, c->route_stream));
-      GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->route_join, 0));
+      GS_CUDA_CHECK(c, gs_launch_preprocess_backward_routed(*st, *in, *grads, N, c->route_shards, c->route_rank,
+                                                            c->route_rows, c->route_table, (const int*)c->radii.ptr,
+                                                            (const uint8_t*)c->clamped.ptr,
+                                                            (const float4*)c->grad_geom.ptr, stream));
     }
   }
   if (st->debug) {

@@ -186,6 +186,8 @@ struct AdamPeerArgs {
   int stats_block_start, total_blocks;
   float b1, b2, omb1, omb2, eps;
   const float* skip_guard;
+  int rank;        // the slot this rank's own backward wrote (local, dense)
+  int sparse_seg;  // segment whose REMOTE slots are written sparsely and must be re-zeroed after use (-1: none)
   int N;
   const int* radii;
   const float* dL_dmeans2D;
@@ -196,9 +198,11 @@ struct AdamPeerArgs {
 
 template <int G>
 __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_constant__ AdamPeerArgs a) {
-  if (a.skip_guard && __ldg(a.skip_guard) != 0.0f) return;
+  // an overflowed forward voids the step -- but the SPARSE slots (see below) must still be cleared
+  const bool skip = a.skip_guard && __ldg(a.skip_guard) != 0.0f;
   const int b = blockIdx.x;
   if (b >= a.stats_block_start) {
+    if (skip) return;
     const int i = (b - a.stats_block_start) * AD_THREADS + threadIdx.x;
     if (i < a.N) {
       const int r = a.radii[i];
@@ -216,25 +220,41 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
   for (int k = 1; k < 6; ++k)
     if (b >= a.seg[k].block_start) si = k;
   const AdamPeerSeg& s = a.seg[si];
+  // The f_rest slots are written SPARSELY by the peers' backward (only rows with a non-zero gradient cross
+  // NVLink, preprocess_bwd.cu): a row that is not written must read as zero, so whatever this kernel consumes
+  // from a remote f_rest slot it puts back to zero (local stores, non-zero vectors only).
+  const bool sparse = si == a.sparse_seg;
+  if (skip && !sparse) return;
   const float b1 = a.b1, b2 = a.b2, omb1 = a.omb1, omb2 = a.omb2, eps = a.eps;
   const float neg_step = s.neg_step, inv_bc2_sqrt = s.inv_bc2_sqrt;
   constexpr int FPB = AD_THREADS * 4;  // one float4 per thread: G + 3 vector loads in flight
   const size_t base = (size_t)(b - s.block_start) * FPB;
   if (base + FPB <= s.n) {
     const size_t v0 = base / 4 + threadIdx.x;
-    float4 g = __ldcs(reinterpret_cast<const float4*>(s.src[0]) + v0);
-    float4 gs[G > 1 ? G - 1 : 1];
+    float4 gs[G];
 #pragma unroll
-    for (int r = 1; r < G; ++r) gs[r - 1] = __ldcs(reinterpret_cast<const float4*>(s.src[r]) + v0);
-    float4 m = __ldcs(reinterpret_cast<const float4*>(s.m) + v0);
-    float4 v = __ldcs(reinterpret_cast<const float4*>(s.v) + v0);
-    float4 p = __ldcs(reinterpret_cast<const float4*>(s.p) + v0);
+    for (int r = 0; r < G; ++r) gs[r] = __ldcs(reinterpret_cast<const float4*>(s.src[r]) + v0);
+    float4 m, v, p;
+    if (!skip) {
+      m = __ldcs(reinterpret_cast<const float4*>(s.m) + v0);
+      v = __ldcs(reinterpret_cast<const float4*>(s.v) + v0);
+      p = __ldcs(reinterpret_cast<const float4*>(s.p) + v0);
+    }
+    if (sparse) {
+#pragma unroll
+      for (int r = 0; r < G; ++r)
+        if (r != a.rank && ((__float_as_uint(gs[r].x) | __float_as_uint(gs[r].y) | __float_as_uint(gs[r].z) |
+                             __float_as_uint(gs[r].w)) & 0x7fffffffu))
+          reinterpret_cast<float4*>(const_cast<float*>(s.src[r]))[v0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (skip) return;
+    float4 g = gs[0];
 #pragma unroll
     for (int r = 1; r < G; ++r) {
-      g.x = __fadd_rn(g.x, gs[r - 1].x);
-      g.y = __fadd_rn(g.y, gs[r - 1].y);
-      g.z = __fadd_rn(g.z, gs[r - 1].z);
-      g.w = __fadd_rn(g.w, gs[r - 1].w);
+      g.x = __fadd_rn(g.x, gs[r].x);
+      g.y = __fadd_rn(g.y, gs[r].y);
+      g.z = __fadd_rn(g.z, gs[r].z);
+      g.w = __fadd_rn(g.w, gs[r].w);
     }
     if (gs_adam_idle(g, m, v)) return;  // exact fixed point: every replica already holds this p, nothing crosses NVLink
     gs_adam_one(p.x, g.x, m.x, v.x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
@@ -248,9 +268,14 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
     reinterpret_cast<float4*>(s.p)[v0] = p;   // read again by the next forward: normal caching
   } else {
     for (size_t idx = base + threadIdx.x; idx < s.n && idx < base + FPB; idx += AD_THREADS) {
-      float g = s.src[0][idx];
+      float g = 0.f;
 #pragma unroll
-      for (int r = 1; r < G; ++r) g = __fadd_rn(g, s.src[r][idx]);
+      for (int r = 0; r < G; ++r) {
+        const float gr = s.src[r][idx];
+        g = r == 0 ? gr : __fadd_rn(g, gr);
+        if (sparse && r != a.rank && gr != 0.0f) const_cast<float*>(s.src[r])[idx] = 0.0f;
+      }
+      if (skip) continue;
       float p = s.p[idx], m = s.m[idx], v = s.v[idx];
       gs_adam_one(p, g, m, v, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
 #pragma unroll
@@ -305,6 +330,8 @@ cudaError_t gs_launch_adam_peer(int nranks, int rank, int N, int R, float* const
   a.omb2 = (float)(1.0 - beta2);
   a.eps = (float)eps;
   a.skip_guard = skip_guard;
+  a.rank = rank;
+  a.sparse_seg = 2;  // f_rest: 76% of the gradient bytes at SH degree 3
   a.N = N;
   a.radii = radii;
   a.dL_dmeans2D = dL_dmeans2D;

@@ -437,13 +437,46 @@ preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_
 #define PBB_FLOATS (PBB_OFF_DC + PBB_ROWS * 3)
 #define PBB_SMEM_BYTES (PBB_FLOATS * 4 + 16)
 
+// Multi-GPU gradient routing (capi.cu, gs_set_gradient_routing): rows [q*R, (q+1)*R) of the six parameter
+// gradients belong to rank q and are stored through vb[q][k] -- the "virtual base" of this rank's slot inside
+// rank q's buffer, re-based so that the global row index addresses it (slot + (i - q*R)*C == vb + i*C).
+// Consecutive blocks serve DIFFERENT owners (block b -> owner (b % G + rank + 1) % G, chunk b / G), so all G-1
+// NVLink destinations and the local HBM are written concurrently for the whole kernel, and no GPU's ingress is
+// hit by every sender at once.
+struct PbRoute {
+  int G;  // 0: no routing (sinks of PreBwdArgs)
+  int rank, R;
+  int nblk[8];    // full 128-row blocks among rank q's valid rows
+  float* vb[8][6];  // order: xyz, f_dc, f_rest, opacity, scaling, rotation
+};
+
 __global__ void __launch_bounds__(PBB_ROWS)
 preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a,
-                                const int first) {
+                                const int first, const __grid_constant__ PbRoute rt) {
   extern __shared__ __align__(128) float s_buf[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(s_buf + PBB_FLOATS);
   const int tid = threadIdx.x;
-  const size_t row0 = (size_t)first + (size_t)blockIdx.x * PBB_ROWS;
+  size_t row0 = (size_t)first + (size_t)blockIdx.x * PBB_ROWS;
+  float* o_xyz = a.out.dL_dmeans3D;
+  float* o_dc = a.out.dL_dsh_dc;
+  float* o_sh = a.out.dL_dsh_rest;
+  float* o_op = a.out.dL_dopacities;
+  float* o_scl = a.out.dL_dscales;
+  float* o_rot = a.out.dL_drotations;
+  bool sparse_sh = false;  // remote f_rest slot: only rows with a non-zero gradient are sent (see below)
+  if (rt.G > 0) {
+    const int q = ((int)(blockIdx.x % rt.G) + rt.rank + 1) % rt.G;
+    sparse_sh = q != rt.rank;
+    const int c = (int)(blockIdx.x / rt.G);
+    if (c >= rt.nblk[q]) return;  // (whole block: nothing has touched the barrier yet)
+    row0 = (size_t)q * rt.R + (size_t)c * PBB_ROWS;
+    o_xyz = rt.vb[q][0];
+    o_dc = rt.vb[q][1];
+    o_sh = rt.vb[q][2];
+    o_op = rt.vb[q][3];
+    o_scl = rt.vb[q][4];
+    o_rot = rt.vb[q][5];
+  }
   const size_t i = row0 + tid;
   const int W = a.rest_width_max;  // == sh_rest_stride (dense rows), 0..45
   const bool load_sh = a.rest_width_act > 0;
@@ -479,6 +512,14 @@ preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __
     const float opac_in = a.in.raw_params ? s_buf[PBB_OFF_OP + tid] : 0.f;
     pb_compute(st, a, p, q4, scl, opac_in, nullptr, G0, G1, G2x, cm, srow, true, o);
   }
+  __shared__ uint32_t s_live[PBB_ROWS / 32];
+  {
+    // dL/dSH = basis x dL/dcolour: a Gaussian whose colour gradient is exactly zero (culled, or behind the
+    // early-termination front of every pixel it covers) has an all-zero f_rest gradient row
+    const bool live = visible && (o.gr[0] != 0.0f || o.gr[1] != 0.0f || o.gr[2] != 0.0f);
+    const uint32_t lw = __ballot_sync(0xffffffffu, live);
+    if ((tid & 31) == 0) s_live[tid >> 5] = lw;
+  }
   // gradients overwrite the input slices in place (each thread touches only its own rows)
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
@@ -509,17 +550,29 @@ preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __
       else tma::store((gptr), s_buf + (soff), (bytes));                     \
     }                                                                       \
   } while (0)
-    PBB_OUT(a.out.dL_dmeans3D ? a.out.dL_dmeans3D + 3 * row0 : nullptr, PBB_OFF_XYZ, PBB_ROWS * 12u);
-    PBB_OUT(a.out.dL_dscales ? a.out.dL_dscales + 3 * row0 : nullptr, PBB_OFF_SCL, PBB_ROWS * 12u);
-    PBB_OUT(a.out.dL_drotations ? a.out.dL_drotations + 4 * row0 : nullptr, PBB_OFF_ROT, PBB_ROWS * 16u);
-    PBB_OUT(a.out.dL_dopacities ? a.out.dL_dopacities + row0 : nullptr, PBB_OFF_OP, PBB_ROWS * 4u);
+    if (W > 0 && !sparse_sh) PBB_OUT(o_sh ? o_sh + row0 * W : nullptr, PBB_OFF_SH, (uint32_t)(PBB_ROWS * W * 4));
+    PBB_OUT(o_xyz ? o_xyz + 3 * row0 : nullptr, PBB_OFF_XYZ, PBB_ROWS * 12u);
+    PBB_OUT(o_scl ? o_scl + 3 * row0 : nullptr, PBB_OFF_SCL, PBB_ROWS * 12u);
+    PBB_OUT(o_rot ? o_rot + 4 * row0 : nullptr, PBB_OFF_ROT, PBB_ROWS * 16u);
+    PBB_OUT(o_op ? o_op + row0 : nullptr, PBB_OFF_OP, PBB_ROWS * 4u);
     PBB_OUT(a.out.dL_dmeans2D ? a.out.dL_dmeans2D + 2 * row0 : nullptr, PBB_OFF_M2D, PBB_ROWS * 8u);
-    PBB_OUT(a.out.dL_dsh_dc ? a.out.dL_dsh_dc + 3 * row0 : nullptr, PBB_OFF_DC, PBB_ROWS * 12u);
-    if (W > 0) PBB_OUT(a.out.dL_dsh_rest ? a.out.dL_dsh_rest + row0 * W : nullptr, PBB_OFF_SH, (uint32_t)(PBB_ROWS * W * 4));
+    PBB_OUT(o_dc ? o_dc + 3 * row0 : nullptr, PBB_OFF_DC, PBB_ROWS * 12u);
 #undef PBB_OUT
     tma::commit_group();
-    tma::wait_group_read0();  // shared memory must stay alive until the copies have read it
   }
+  if (sparse_sh && W > 0 && o_sh) {
+    // SPARSE push of the f_rest rows (76% of the gradient bytes): a row crosses NVLink only if it is non-zero;
+    // the owner re-zeroes what it consumes (adam_peer_kernel), so an unwritten row reads as zero.  One warp per
+    // row, 4-byte lanes: a 180-B row is two store instructions.
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int r = warp; r < PBB_ROWS; r += PBB_ROWS / 32) {
+      if (!((s_live[r >> 5] >> (r & 31)) & 1u)) continue;
+      float* dst = o_sh + (row0 + r) * W;
+      const float* src = s_buf + PBB_OFF_SH + r * W;
+      for (int c = lane; c < W; c += 32) dst[c] = src[c];
+    }
+  }
+  if (tid == 0) tma::wait_group_read0();  // shared memory must stay alive until the copies have read it
 }
 
 // ---- K4b + K5 fused (single-GPU training step) -------------------------------------------------
@@ -737,7 +790,9 @@ cudaError_t gs_launch_preprocess_backward(const gs_settings& st, const gs_gaussi
       attr_set = true;
     }
     const int blocks = N / PBB_ROWS;
-    preprocess_backward_bulk_kernel<<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, first);
+    PbRoute none;
+    memset(&none, 0, sizeof(none));
+    preprocess_backward_bulk_kernel<<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, first, none);
     first += blocks * PBB_ROWS;
   }
   if (first < row_end) {
@@ -814,5 +869,83 @@ cudaError_t gs_launch_preprocess_backward_adam(const gs_settings& st, const gs_g
   const int blocks = N / PBB_ROWS;
   preprocess_backward_adam_kernel<<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, f);
   *covered = blocks * PBB_ROWS;
+  return cudaGetLastError();
+}
+
+
+// The routed K4b of the multi-GPU step: ONE launch covers all owners (interleaved, see PbRoute); table[q*6 + k] is
+// this rank's slot for group k inside rank q's buffer.  The ragged tail (N % 128 rows, all in one shard) goes
+// through the generic kernel.  `out` supplies only the local dL_dmeans2D sink.
+cudaError_t gs_launch_preprocess_backward_routed(const gs_settings& st, const gs_gaussians& in, const gs_gradients& out,
+                                                 int N, int G, int rank, int R, float* const table[], const int* radii,
+                                                 const uint8_t* clamped, const float4* grad_geom, cudaStream_t stream) {
+  if (N == 0) return cudaSuccess;
+  const int kmax = (st.max_sh_degree + 1) * (st.max_sh_degree + 1);
+  const int W = 3 * (kmax - 1);
+  const int cw[6] = {3, 3, W, 1, 3, 4};
+  PbRoute rt;
+  memset(&rt, 0, sizeof(rt));
+  rt.G = G;
+  rt.rank = rank;
+  rt.R = R;
+  int max_blk = 0;
+  for (int q = 0; q < G; ++q) {
+    const long long b = (long long)q * R;
+    const long long rows = b >= N ? 0 : ((long long)N - b < R ? (long long)N - b : (long long)R);
+    rt.nblk[q] = (int)(rows / PBB_ROWS);
+    if (rt.nblk[q] > max_blk) max_blk = rt.nblk[q];
+    for (int k = 0; k < 6; ++k) rt.vb[q][k] = (k == 2 && W == 0) ? nullptr : table[q * 6 + k] - b * cw[k];
+  }
+  PreBwdArgs a;
+  a.in = in;
+  a.out = out;
+  a.out.dL_dmeans3D = a.out.dL_dsh_dc = a.out.dL_dsh_rest = a.out.dL_dopacities = a.out.dL_dscales = a.out.dL_drotations = nullptr;
+  a.out.dL_dcov3D = a.out.dL_dcolors = nullptr;
+  a.out.accumulate = 0;
+  a.N = N;
+  a.radii = radii;
+  a.clamped = clamped;
+  a.grad_geom = grad_geom;
+  a.focal_x = (float)st.W / (2.0f * st.tanfovx);
+  a.focal_y = (float)st.H / (2.0f * st.tanfovy);
+  const int kact = (st.sh_degree + 1) * (st.sh_degree + 1);
+  a.rest_width_act = 3 * (kact - 1);
+  a.rest_width_max = W;
+  a.pitch = W | 1;
+  const bool dense = !in.colors_precomp && !in.cov3D_precomp && (W == 0 || in.sh_rest_stride == W) && in.sh_dc_stride == 3 &&
+                     (W * 4 * PBB_ROWS) % 16 == 0 && aligned16(in.means3D) && aligned16(in.scales) &&
+                     aligned16(in.rotations) && aligned16(in.opacities) && (W == 0 || aligned16(in.sh_rest)) &&
+                     aligned16(out.dL_dmeans2D) && aligned16(grad_geom);
+  if (!dense) return cudaErrorInvalidValue;
+  if (max_blk > 0) {
+    cudaError_t e = cudaFuncSetAttribute(preprocess_backward_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         PBB_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
+    preprocess_backward_bulk_kernel<<<G * max_blk, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, 0, rt);
+  }
+  // tails: rows of shard q beyond its full blocks
+  for (int q = 0; q < G; ++q) {
+    const long long b = (long long)q * R;
+    const long long rows = b >= N ? 0 : ((long long)N - b < R ? (long long)N - b : (long long)R);
+    const long long t0 = b + (long long)rt.nblk[q] * PBB_ROWS, t1 = b + rows;
+    if (t1 <= t0) continue;
+    gs_gradients g = out;
+    g.dL_dmeans3D = rt.vb[q][0];
+    g.dL_dsh_dc = rt.vb[q][1];
+    g.dL_dsh_rest = rt.vb[q][2];
+    g.dL_dopacities = rt.vb[q][3];
+    g.dL_dscales = rt.vb[q][4];
+    g.dL_drotations = rt.vb[q][5];
+    g.dL_dcov3D = g.dL_dcolors = nullptr;
+    g.sh_dc_stride = 3;
+    g.sh_rest_stride = W;
+    g.accumulate = 0;
+    PreBwdArgs at = a;
+    at.out = g;
+    at.N = (int)t1;
+    const size_t smem = W > 0 ? (size_t)PB_THREADS * at.pitch * sizeof(float) : 0;
+    const int blocks = (int)((t1 - t0 + PB_THREADS - 1) / PB_THREADS);
+    preprocess_backward_kernel<<<blocks, PB_THREADS, smem, stream>>>(st, at, (int)t0);
+  }
   return cudaGetLastError();
 }

@@ -197,8 +197,8 @@ GS_API int gs_densify_apply(gs_ctx *ctx, int N, const int widths[6], float *cons
                             void *stream);
 GS_API int gs_reset_opacity(gs_ctx *ctx, int N, float *opacities, float *exp_avg, float *exp_avg_sq, void *stream);
 
-/* Test hook: with on != 0, gs_backward_adam_step skips the blend backward and consumes the per-Gaussian gradient
- * records the last gs_backward left in the context -- the blend backward sums with fp32 atomics, so this is what
+/* Test hook: with on != 0, gs_backward and gs_backward_adam_step skip the blend backward and consume the
+ * per-Gaussian gradient records the previous backward left in the context -- the blend backward sums with fp32 atomics, so this is what
  * makes "fused == separate" checkable bit for bit. */
 GS_API int gs_debug_reuse_blend_gradients(gs_ctx *ctx, int on);
 
