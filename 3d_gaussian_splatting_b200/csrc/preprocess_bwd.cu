@@ -11,6 +11,8 @@
 //  * preprocess_backward_kernel — generic fallback (precomputed cov3D / colours, strided or
 //    unaligned tensors, ragged tail): SH rows staged through shared memory with coalesced loops.
 // With raw_params the activation Jacobians (exp, sigmoid, normalise) are applied here too.
+#include <stdlib.h>
+
 #include "gs_common.cuh"
 #include "tma_bulk.cuh"
 

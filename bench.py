@@ -136,6 +136,14 @@ def stage_bytes(N, N_vis, D, D_eff, P, T, K):
     }
 
 
+def measured_issue_pct():
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            return json.load(f).get("issue_pct", {})
+    except (OSError, ValueError):
+        return {}
+
+
 def measured_traffic(stage):
     """DRAM bytes per launch of the stage's kernel from the committed ncu capture (profiles/traffic.json), or None."""
     try:
@@ -420,6 +428,9 @@ def run_ours(args, rank, world, local_rank):
                   "GBps": round(by[k] / (stage_ms[k] * 1e-3) / 1e9, 1) if stage_ms[k] > 0 else None,
                   "frac_hbm": round(by[k] / (stage_ms[k] * 1e-3) / 1e9 / peak, 4) if stage_ms[k] > 0 else None}
               for k in stage_ms}
+    for k, v in measured_issue_pct().items():      # issue-slot utilisation from the committed ncu capture
+        if k in stages:
+            stages[k]["issue_pct_ncu"] = v
     # (the fused single-GPU step has no separate K4b: its K4b+K5 kernel is counted whole)
     fwd_bwd_ms = sum(stage_ms.get(k, 0.0) for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges",
                                                     "blend_fwd", "blend_bwd", "preprocess_bwd", "preprocess_bwd_adam"))
