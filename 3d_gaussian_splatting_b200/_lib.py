@@ -52,12 +52,28 @@ class GsGradients(C.Structure):
     ]
 
 
+class GsTrainConfig(C.Structure):
+    """gs_train_config (OptimizationParams of src/arguments/params.h:52-68 + spatial_lr_scale, bg, seed)"""
+    _fields_ = [
+        ("position_lr_init", C.c_double), ("position_lr_final", C.c_double), ("position_lr_delay_mult", C.c_double),
+        ("position_lr_max_steps", C.c_int),
+        ("feature_lr", C.c_double), ("opacity_lr", C.c_double), ("scaling_lr", C.c_double), ("rotation_lr", C.c_double),
+        ("percent_dense", C.c_double), ("lambda_dssim", C.c_double),
+        ("densification_interval", C.c_int), ("opacity_reset_interval", C.c_int), ("densify_from_iter", C.c_int),
+        ("densify_until_iter", C.c_int),
+        ("densify_grad_threshold", C.c_double), ("spatial_lr_scale", C.c_double),
+        ("bg", C.c_float * 3), ("seed", C.c_uint), ("active_sh_degree", C.c_int),
+    ]
+
+
 # every symbol include/gsplat_b200.h declares (tests check the library exports all of them)
 EXPORTS = (
     "gs_version", "gs_create", "gs_destroy", "gs_last_error", "gs_forward", "gs_backward",
     "gs_adam_densify_step", "gs_loss", "gs_debug_size", "gs_debug_get", "gs_set_profiling", "gs_get_stage_ms",
     "gs_focal2fov", "gs_get_world2view2", "gs_get_projection_matrix", "gs_camera_settings", "gs_expon_lr",
-    "gs_adam_step_flat", "gs_backward_adam_step", "gs_densify_plan", "gs_densify_apply", "gs_reset_opacity", "gs_debug_reuse_blend_gradients", "gs_set_gradient_routing", "gs_adam_step_peer", "gs_peer_alloc", "gs_peer_open", "gs_peer_close", "gs_peer_free", "gs_set_duplicate_capacity", "gs_set_overflow_mirror", "gs_overflow_guard", "gs_get_forward_status",
+    "gs_adam_step_flat", "gs_trainer_create", "gs_trainer_destroy", "gs_trainer_last_error", "gs_trainer_add_view", "gs_trainer_run",
+    "gs_trainer_num_gaussians", "gs_trainer_iteration", "gs_trainer_retries", "gs_trainer_get_params",
+    "gs_backward_adam_step", "gs_densify_plan", "gs_densify_apply", "gs_reset_opacity", "gs_debug_reuse_blend_gradients", "gs_set_gradient_routing", "gs_adam_step_peer", "gs_peer_alloc", "gs_peer_open", "gs_peer_close", "gs_peer_free", "gs_set_duplicate_capacity", "gs_set_overflow_mirror", "gs_overflow_guard", "gs_get_forward_status",
 )
 
 
@@ -89,6 +105,17 @@ def _load() -> C.CDLL:
     lib.gs_backward_adam_step.argtypes = [vp, C.POINTER(GsSettings), i, C.POINTER(GsGaussians), vp, vp, vp * 6, vp * 6,
                                           d * 6, C.c_longlong * 6, d, d, d, vp, vp, vp, vp, vp]
     lib.gs_debug_reuse_blend_gradients.argtypes = [vp, i]
+    lib.gs_trainer_create.argtypes = [C.POINTER(vp), i, C.POINTER(GsTrainConfig), i, i, vp, vp, vp, vp, vp, vp]
+    lib.gs_trainer_destroy.argtypes = [vp]
+    lib.gs_trainer_destroy.restype = None
+    lib.gs_trainer_last_error.argtypes = [vp]
+    lib.gs_trainer_last_error.restype = C.c_char_p
+    lib.gs_trainer_add_view.argtypes = [vp, C.POINTER(GsSettings), vp]
+    lib.gs_trainer_run.argtypes = [vp, i, vp, i, C.c_float]
+    lib.gs_trainer_num_gaussians.argtypes = [vp]
+    lib.gs_trainer_iteration.argtypes = [vp]
+    lib.gs_trainer_retries.argtypes = [vp]
+    lib.gs_trainer_get_params.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     f = C.c_float
     lib.gs_densify_plan.argtypes = [vp, i, vp, vp, vp, vp, f, f, f, f, f, i * 4, vp]
     lib.gs_densify_apply.argtypes = [vp, i, i * 6, vp * 6, vp * 6, vp * 6, vp * 6, vp * 6, vp * 6, C.c_ulonglong, vp]

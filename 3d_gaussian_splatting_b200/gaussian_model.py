@@ -14,6 +14,8 @@ from __future__ import annotations
 
 from dataclasses import dataclass
 
+import ctypes as C
+
 import numpy as np
 import torch
 
@@ -153,6 +155,84 @@ class GaussianModel:
         g = self.grads
         return dict(means3D=g[0], sh_dc=g[1], sh_rest=g[2], opacities=g[3], scales=g[4], rotations=g[5],
                     means2D=self.grad_means2D)
+
+
+class NativeTrainer:
+    """ctypes handle on the NATIVE training loop (csrc/trainer.cu, gs_trainer_*): the model, the optimiser state and
+    the pipelined loop live in C++; Python only hands over the initial parameters, the cameras and the pinned
+    ground-truth images, and receives the losses.  Same schedules as Trainer / the reference's OptimizationParams."""
+
+    def __init__(self, scene, opt: OptimizationParams | None = None, device: int = 0, bg=(0.0, 0.0, 0.0),
+                 spatial_lr_scale: float = 1.0, lambda_dssim: float | None = None, seed: int = 0,
+                 active_sh_degree: int | None = None):
+        from . import _lib
+        self._L = _lib
+        o = opt or OptimizationParams()
+        cfg = _lib.GsTrainConfig(
+            o.position_lr_init, o.position_lr_final, o.position_lr_delay_mult, o.position_lr_max_steps, o.feature_lr,
+            o.opacity_lr, o.scaling_lr, o.rotation_lr, o.percent_dense,
+            o.lambda_dssim if lambda_dssim is None else lambda_dssim, o.densification_interval,
+            o.opacity_reset_interval, o.densify_from_iter, o.densify_until_iter, o.densify_grad_threshold,
+            spatial_lr_scale, (C.c_float * 3)(*bg), seed,
+            scene.max_sh_degree if active_sh_degree is None else active_sh_degree)   # (as GaussianModel.load_scene)
+        f32 = lambda a: np.ascontiguousarray(a, dtype=np.float32)
+        self._init = [f32(scene.xyz), f32(scene.features_dc), f32(scene.features_rest), f32(scene.opacity_logits),
+                      f32(scene.log_scales), f32(scene.raw_rotations)]
+        self.K = 1 + self._init[2].shape[1]
+        self._t = C.c_void_p()
+        ptr = lambda a: a.ctypes.data_as(C.c_void_p) if a.size else None
+        rc = _lib.lib.gs_trainer_create(C.byref(self._t), device, C.byref(cfg), int(self._init[0].shape[0]), self.K,
+                                        *[ptr(a) for a in self._init])
+        if rc != 0:
+            raise RuntimeError("gs_trainer_create: " + (_lib.lib.gs_last_error(None) or b"").decode())
+        self._keep = []
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"{what}: " + (self._L.lib.gs_trainer_last_error(self._t) or b"").decode())
+
+    def add_view(self, cam, gt_host: torch.Tensor):
+        """cam: camera.Camera; gt_host: (3,H,W) float32 host tensor (pinned: asynchronous copies); kept alive here."""
+        assert gt_host.dtype == torch.float32 and not gt_host.is_cuda and gt_host.is_contiguous()
+        self._keep.append(gt_host)
+        self._check(self._L.lib.gs_trainer_add_view(self._t, C.byref(cam._st), C.c_void_p(gt_host.data_ptr())), "add_view")
+
+    def run(self, n: int, cyclic: bool = False, densify_extent: float = 0.0):
+        losses = np.zeros(n, np.float32)
+        self._check(self._L.lib.gs_trainer_run(self._t, int(n), losses.ctypes.data_as(C.c_void_p), int(cyclic),
+                                               float(densify_extent)), "gs_trainer_run")
+        return losses.tolist()
+
+    @property
+    def N(self):
+        return int(self._L.lib.gs_trainer_num_gaussians(self._t))
+
+    @property
+    def iteration(self):
+        return int(self._L.lib.gs_trainer_iteration(self._t))
+
+    @property
+    def retries(self):
+        return int(self._L.lib.gs_trainer_retries(self._t))
+
+    def params(self):
+        N = self.N
+        shapes = [(N, 3), (N, 1, 3), (N, self.K - 1, 3), (N, 1), (N, 3), (N, 4)]
+        out = [np.zeros(s, np.float32) for s in shapes]
+        self._check(self._L.lib.gs_trainer_get_params(self._t, *[a.ctypes.data_as(C.c_void_p) if a.size else None
+                                                                   for a in out]), "get_params")
+        return out
+
+    def close(self):
+        if getattr(self, "_t", None):
+            self._L.lib.gs_trainer_destroy(self._t)
+            self._t = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class ViewSampler:

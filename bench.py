@@ -47,8 +47,9 @@ def parse_args():
                     help="N>1: peer = exchange fused into K4b/K5 over NVLink peer memory (sharded Adam); sharded = NCCL "
                          "reduce-scatter + sharded Adam + all-gather; allreduce = NCCL all-reduce + replicated Adam")
     ap.add_argument("--no-fused", action="store_true", help="N=1: separate K4b and K5 launches instead of the fused kernel")
-    ap.add_argument("--e2e-api", default="loop", choices=["loop", "step"],
-                    help="e2e leg: Trainer.train (pipelined loop, default) or one synchronous Trainer.train_step per step")
+    ap.add_argument("--e2e-api", default="loop", choices=["loop", "step", "native"],
+                    help="e2e leg: Trainer.train (pipelined Python loop, default), one synchronous Trainer.train_step per "
+                         "step, or the native C++ loop gs_trainer_run (N=1 only; wall-clock timed)")
     ap.add_argument("--N", type=int, default=None, help="override the Gaussian count (debugging only)")
     return ap.parse_args()
 
@@ -369,7 +370,20 @@ def run_ours(args, rank, world, local_rank):
     def loop_e2e(first, n):
         e2e_losses[:] = trainer.train(my_cams[:args.views], gts_host[:args.views], n, first=first)
 
-    if args.e2e_api == "loop":
+    if args.e2e_api == "native" and world == 1:
+        # the loop in C++ (csrc/trainer.cu): its own model copy, its own streams; timed by the host clock around the
+        # call, which returns only after the last iteration's loss has arrived
+        nt = gm.NativeTrainer(scene, opt, device=local_rank, lambda_dssim=LAMBDA_DSSIM)
+        for cam, gt in zip(my_cams[:args.views], gts_host[:args.views]):
+            nt.add_view(cam, gt)
+        nt.run(warm, cyclic=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e2e_losses[:] = nt.run(args.steps, cyclic=True)
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+        assert all(np.isfinite(l) for l in e2e_losses) and nt.retries == 0
+        nt.close()
+    elif args.e2e_api in ("loop", "native"):
         # timed() runs fn(0) as its one warm-up call (`warm` iterations), then fn(1) timed (args.steps iterations)
         e2e_ms, _ = timed(lambda i: loop_e2e(0, warm) if i == 0 else loop_e2e(warm, args.steps), 1, 1)
         assert len(e2e_losses) == args.steps and all(np.isfinite(l) for l in e2e_losses), "e2e loop lost a loss"
@@ -480,9 +494,13 @@ def run_ours(args, rank, world, local_rank):
             "cpu_baseline": cpu_baseline,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
                     "h2d_bytes_per_step": int(gts_host[0].numel() * 4 + 172),
-                    "d2h_bytes_per_step": 8 if args.e2e_api == "loop" else 4,
-                    "api": ("Trainer.train: depth-2 pipelined loop, ground truth H2D + loss/overflow flag D2H every "
-                            "iteration" if args.e2e_api == "loop" else "Trainer.train_step: one synchronous call per step")},
+                    "d2h_bytes_per_step": 4 if args.e2e_api == "step" else 8,
+                    "api": {"loop": "Trainer.train: depth-2 pipelined loop, ground truth H2D + loss/overflow flag D2H every "
+                                    "iteration",
+                            "native": "gs_trainer_run (C++ loop over the C ABI): depth-2 pipeline, ground truth H2D + "
+                                      "loss/overflow flag D2H every iteration; host-clock timed",
+                            "step": "Trainer.train_step: one synchronous call per step"}[
+                                args.e2e_api if world == 1 or args.e2e_api != "native" else "loop"]},
             "pair_capacity": trainer.pair_capacity, "capacity_retries": trainer.retries,
             # own kernels only (NCCL's are not counted); the routed K4b of the peer mode is one launch per owner rank
             "gpu_launches": (OWN_KERNELS_PER_STEP - (1 if world == 1 and trainer.fused_step else 0) + (world - 1 if world > 1 and args.dp_mode == "peer" else 0)

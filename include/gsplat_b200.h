@@ -303,6 +303,47 @@ GS_API int gs_debug_get(gs_ctx *ctx, int what, void *host_dst, size_t bytes);
 GS_API int gs_set_profiling(gs_ctx *ctx, int enabled);
 GS_API int gs_get_stage_ms(gs_ctx *ctx, float ms[GS_NUM_STAGES]);
 
+/* ---- the training loop, native ------------------------------------------------------------------
+ * The loop the reference leaves as a stub (src/utils/train_utils.cpp:97-147, body commented out at :138-144),
+ * over the entry points above: no Python, no libtorch.  The trainer OWNS the model (parameters, Adam moments,
+ * statistics) on `device`; gs_trainer_run is a depth-2 software pipeline (host one iteration behind the device,
+ * ground truth host->device and loss device->host every iteration), with the reference's schedules
+ * (src/arguments/params.h:52-68) and, when densify_extent > 0, densification / opacity reset.
+ * gs_train_config mirrors OptimizationParams (same names without the trailing underscore). */
+typedef struct gs_train_config {
+  double position_lr_init, position_lr_final, position_lr_delay_mult;
+  int position_lr_max_steps;
+  double feature_lr, opacity_lr, scaling_lr, rotation_lr;
+  double percent_dense, lambda_dssim;
+  int densification_interval, opacity_reset_interval, densify_from_iter, densify_until_iter;
+  double densify_grad_threshold;
+  double spatial_lr_scale; /* GaussianModel::spatial_lr_scale_ (the NeRF++ radius) */
+  float bg[3];             /* background colour (white_background_ ? 1 : 0) */
+  unsigned int seed;       /* view sampling */
+  int active_sh_degree;    /* SH degree at the first iteration (the reference starts at 0 and adds one every 1000) */
+} gs_train_config;
+typedef struct gs_trainer gs_trainer;
+#define GS_SAMPLE_SHUFFLE 0 /* without replacement: a stack of all views, one popped at random, refilled when empty */
+#define GS_SAMPLE_CYCLIC 1  /* views in the order they were added */
+
+/* Parameters in the layout of GaussianModel (xyz (N,3), features_dc (N,1,3), features_rest (N,K-1,3), opacity
+ * (N,1), scaling (N,3), rotation (N,4); raw, i.e. before the activations); host or device pointers; copied. */
+GS_API int gs_trainer_create(gs_trainer **out, int device, const gs_train_config *cfg, int N, int sh_coeffs,
+                             const float *xyz, const float *features_dc, const float *features_rest,
+                             const float *opacity, const float *scaling, const float *rotation);
+GS_API void gs_trainer_destroy(gs_trainer *t);
+GS_API const char *gs_trainer_last_error(const gs_trainer *t);
+/* camera: H, W, tanfov, matrices, campos (gs_camera_settings fills them); gt_host: (3,H,W) floats, caller-owned
+ * and alive as long as the trainer (pinned memory makes the per-iteration copy asynchronous). */
+GS_API int gs_trainer_add_view(gs_trainer *t, const gs_settings *camera, const float *gt_host);
+/* n_iterations more iterations; losses[n_iterations] (host) receives every iteration's loss in order. */
+GS_API int gs_trainer_run(gs_trainer *t, int n_iterations, float *losses, int sampling, float densify_extent);
+GS_API int gs_trainer_num_gaussians(const gs_trainer *t);
+GS_API int gs_trainer_iteration(const gs_trainer *t);
+GS_API int gs_trainer_retries(const gs_trainer *t); /* iterations repeated after a pair-capacity overflow */
+GS_API int gs_trainer_get_params(gs_trainer *t, float *xyz, float *features_dc, float *features_rest,
+                                 float *opacity, float *scaling, float *rotation); /* any may be NULL */
+
 /* ---- host-side conventions (CPU, no device needed) -----------------------------------------
  * C restatements of the reference's math helpers so that a C/C++ caller can build gs_settings
  * exactly as Camera's constructor would. */
