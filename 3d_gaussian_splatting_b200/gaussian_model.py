@@ -299,6 +299,7 @@ class Trainer:
         self.skip_guard = None          # device float the Adam step honours (all-reduced slab tail when multi-GPU)
         self.retries = 0
         self.fused_step = True          # single GPU: backward and Adam in one call (gs_backward_adam_step)
+        self.on_resize = None           # callable run after a densification step changed N (e.g. rebuild a gradient slab)
         self.peer = None                # multi-GPU: parallel.PeerShardedAdam (exchange fused into K4b / K5)
         self.sharded = None             # multi-GPU: parallel.ShardedAdam (reduce-scatter / sharded Adam / all-gather)
 
@@ -392,18 +393,50 @@ class Trainer:
     def densification_step(self, iteration: int, extent: float, white_background: bool = False):
         """The block of the published loop that follows the optimiser bookkeeping of iteration `iteration`
         (schedule parameters: src/arguments/params.h:61-67).  Changes N: the caller must have drained any
-        pipelined iterations.  Single GPU / all-reduce data parallelism (every rank holds the merged statistics and
-        the same seed, hence the same outcome)."""
+        pipelined iterations.  Data parallel (all-reduce or peer mode): the per-rank statistics are merged first, so
+        every rank takes the same decisions with the same seed; the peer mode re-shards the optimiser state over
+        new peer buffers."""
         o, g = self.opt, self.g
-        assert self.peer is None and self.sharded is None, "densification with a sharded optimiser: not wired yet"
+        assert self.sharded is None, "densification with the NCCL-sharded optimiser is not wired (use the peer mode)"
         done = None
         if iteration < o.densify_until_iter:
             if iteration > o.densify_from_iter and iteration % o.densification_interval == 0:
                 size_threshold = 20.0 if iteration > o.opacity_reset_interval else 0.0
+                if self.peer is not None or self.grad_sync is not None:
+                    # data parallel: every rank accumulated the statistics of its own views -> merge, then every
+                    # rank takes the same decisions (same statistics, same seed) on its replica
+                    from . import parallel
+                    parallel.merge_densify_stats(g.max_radii2D_, g.xyz_gradient_accum_, g.denom_)
+                if self.peer is not None:
+                    # the step needs (and produces) the FULL optimiser state: gather the moment shards, release the
+                    # peer buffers (N changes), densify, shard again over new buffers
+                    old = self.peer
+                    m_full, v_full = old.gather_moments()
+                    old.detach_model()
+                    old.close()
+                    g.exp_avg, g.exp_avg_sq = m_full, v_full
                 done = g.densify_and_prune(self.rast, o.densify_grad_threshold, 0.005, extent, size_threshold,
                                            seed=iteration)
+                if self.peer is not None:
+                    from . import parallel
+                    self.peer = parallel.PeerShardedAdam(g, self.rast, old.rank, old.world, group=old.group,
+                                                         moments=(g.exp_avg, g.exp_avg_sq))
+                    if self.pair_capacity:
+                        self.reserve_pairs(self.pair_capacity, guard=self.peer.guard)
+                elif self.on_resize is not None:
+                    self.on_resize()
             if iteration % o.opacity_reset_interval == 0 or (white_background and iteration == o.densify_from_iter):
-                g.reset_opacity(self.rast)
+                if self.peer is not None:
+                    # every rank resets its whole replica (same values everywhere); the moments are sharded: the
+                    # kernel gets throw-away full-size moments and the owned shard is cleared here
+                    scratch = torch.empty_like(g.opacity_)
+                    self.rast.reset_opacity(g.opacity_, scratch, scratch)
+                    g.exp_avg[3].zero_()
+                    g.exp_avg_sq[3].zero_()
+                    torch.cuda.synchronize(g.opacity_.device)
+                    self.peer.barrier()
+                else:
+                    g.reset_opacity(self.rast)
         return done
 
     def check_overflow(self) -> bool:
@@ -502,7 +535,8 @@ class Trainer:
             v = drawn[j]
             loss = self.train_step_device(cams[v], self._gt_dev, gt_host=gts_host[v])
             slots[slot, 0:1].copy_(loss.reshape(1), non_blocking=True)
-            slots[slot, 1:2].copy_(self._guard_view, non_blocking=True)
+            guard = self._guard_tensor if self._guard_tensor is not None else self._guard_view
+            slots[slot, 1:2].copy_(guard, non_blocking=True)
             events[slot].record(stream)
             pending.append((j, slot))
 

@@ -160,7 +160,9 @@ class PeerShardedAdam:
     rast: the rank's Rasterizer.  exchange(handle) -> list of all ranks' handles (default: all_gather_object).
     """
 
-    def __init__(self, model, rast, rank: int, world: int, group=None):
+    def __init__(self, model, rast, rank: int, world: int, group=None, moments=None):
+        """moments: optional (exp_avg[6], exp_avg_sq[6]) FULL (N, C) arrays to start the owned shards from (after a
+        densification step, which needs and produces the full optimiser state); default: zeros."""
         self.model, self.rast, self.rank, self.world, self.group = model, rast, rank, world, group
         params = model.params()
         N = self.N = int(params[0].shape[0])
@@ -211,8 +213,16 @@ class PeerShardedAdam:
             views.append(v)
         (model.xyz_, model.features_dc_, model.features_rest_, model.opacity_, model.scaling_, model.rotation_) = views
         model.grads = [None] * 6
-        model.exp_avg = [torch.zeros(R * c, dtype=torch.float32, device=self.flat.device) for c in self.widths]
-        model.exp_avg_sq = [torch.zeros(R * c, dtype=torch.float32, device=self.flat.device) for c in self.widths]
+        lo, hi = min(rank * R, N), min((rank + 1) * R, N)
+        shard = []
+        for full in (moments if moments is not None else (None, None)):
+            ts = [torch.zeros(R * c, dtype=torch.float32, device=self.flat.device) for c in self.widths]
+            if full is not None:
+                for t, f, c in zip(ts, full, self.widths):
+                    if c > 0 and hi > lo:
+                        t[:(hi - lo) * c].copy_(f.reshape(N, c)[lo:hi].reshape(-1))
+            shard.append(ts)
+        model.exp_avg, model.exp_avg_sq = shard
         self.guard = torch.zeros(1, dtype=torch.float32, device=self.flat.device)
         self.sync = torch.zeros(1, dtype=torch.float32, device=self.flat.device)
         # params[r][k]: rank r's replica; slots[s][k]: MY slot for source s; routing[q][k]: my slot INSIDE rank q
@@ -244,9 +254,40 @@ class PeerShardedAdam:
                                  skip_guard=self.guard if use_guard else None)
         self.barrier()   # barrier 2: every replica complete before the next forward reads it
 
+    def gather_moments(self):
+        """The FULL (N, C) Adam moments on every rank (all-gather of the shards): what a densification step or a
+        checkpoint needs.  Rare (once per densification interval), so plain NCCL."""
+        out = []
+        for shard in (self.model.exp_avg, self.model.exp_avg_sq):
+            full = []
+            for t, c, p in zip(shard, self.widths, self.model.params()):
+                if c == 0:
+                    full.append(torch.zeros_like(p))
+                    continue
+                buf = torch.empty(self.world * self.R * c, dtype=torch.float32, device=t.device)
+                if dist.is_initialized() and self.world > 1:
+                    dist.all_gather_into_tensor(buf, t, group=self.group)
+                else:
+                    buf.copy_(t)
+                full.append(buf[:self.N * c].view_as(p).clone())
+            out.append(full)
+        return out[0], out[1]
+
+    def detach_model(self):
+        """Give the model private copies of its parameters (they are views of the peer buffer) so that the buffer
+        can be released."""
+        m = self.model
+        (m.xyz_, m.features_dc_, m.features_rest_, m.opacity_, m.scaling_, m.rotation_) = [p.clone() for p in m.params()]
+
     def close(self):
+        torch.cuda.synchronize(self.flat.device)
+        self.barrier()                        # nobody is still storing into a peer's buffer
         self.rast.set_gradient_routing(0)
         for r, b in enumerate(self.bases):
             if r != self.rank:
                 self.rast.peer_close(b)
+        torch.cuda.synchronize(self.flat.device)
+        self.barrier()                        # every mapping is gone before any owner frees
+        torch.cuda.synchronize(self.flat.device)
+        self.flat = None
         self.rast.peer_free(self.base)
