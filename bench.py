@@ -51,6 +51,9 @@ def parse_args():
                     help="e2e leg: Trainer.train (pipelined Python loop, default), one synchronous Trainer.train_step per "
                          "step, or the native C++ loop gs_trainer_run (N=1 only; wall-clock timed)")
     ap.add_argument("--N", type=int, default=None, help="override the Gaussian count (debugging only)")
+    ap.add_argument("--mode", default="train", choices=["train", "render"],
+                    help="train: the headline train step (default).  render: forward-only render throughput sweep over "
+                         "the config's cameras (BASELINE.json configs[3]: Mpix/s with the sort / blend breakdown)")
     return ap.parse_args()
 
 
@@ -449,6 +452,32 @@ def run_ours(args, rank, world, local_rank):
     fwd_bwd_ms = sum(stage_ms.get(k, 0.0) for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges",
                                                     "blend_fwd", "blend_bwd", "preprocess_bwd", "preprocess_bwd_adam"))
 
+    # ---- the rasterizer alone (BASELINE.json "fwd+bwd raster ms"): gs_forward + gs_backward, no loss, no optimiser;
+    # dL/dimage = seeded U(-1,1)/P, loss-independent.  Single GPU only (the multi-GPU modes route
+    # the backward's stores to the owner ranks).
+    raster = None
+    if world == 1:
+        rs = np.random.Generator(np.random.Philox(4321))
+        dL_seed = torch.from_numpy(((2.0 * rs.random((3, H, W)) - 1.0) / P).astype(np.float32)).to(dev)
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(12)]
+        for i, e in enumerate(evs):
+            cam = my_cams[i % args.views]
+            e[0].record()
+            gm.render(cam, g, trainer.pipe, trainer.bg, trainer.rast, with_visibility=False)
+            e[1].record()
+            trainer.rast.backward(dL_seed, grads=g.grad_sinks())
+            e[2].record()
+        torch.cuda.synchronize()
+        f_ms = float(np.median([e[0].elapsed_time(e[1]) for e in evs[3:]]))
+        b_ms = float(np.median([e[1].elapsed_time(e[2]) for e in evs[3:]]))
+        fb_ms = float(np.median([e[0].elapsed_time(e[2]) for e in evs[3:]]))
+        rb = sum(by.get(k, 0) for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd",
+                                        "blend_bwd")) + stage_bytes(N, N_vis, D, D_eff, P, T, K)["preprocess_bwd"]
+        raster = {"fwd_ms": round(f_ms, 4), "bwd_ms": round(b_ms, 4), "fwd_bwd_ms": round(fb_ms, 4),
+                  "alg_GB": round(rb / 1e9, 4), "frac_hbm": round(rb / (fb_ms * 1e-3) / 1e9 / peak, 4),
+                  "what": "gs_forward + gs_backward (K1-K3, K4a, K4b with the six gradient tensors written to HBM), "
+                          "dL/dimage = seeded U(-1,1)/P, median of 9 after 3 warm-ups, CUDA events"}
+
     adam_idle_frac = None
     if g.exp_avg_sq is not None:
         nz = sum(int((t != 0).sum().item()) for t in g.exp_avg_sq if t is not None)
@@ -486,6 +515,7 @@ def run_ours(args, rank, world, local_rank):
             # share of parameter floats whose Adam moments are still exactly 0 (never received a gradient): the Adam
             # kernels skip those vectors (an exact fixed point of the update), so K5's time depends on it
             "adam_idle_frac": adam_idle_frac,
+            "raster": raster,
             "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
@@ -512,6 +542,84 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_render_sweep(args, local_rank):
+    """--mode render: forward-only render throughput over the config's cameras (BASELINE.json configs[3]: 4 M
+    Gaussians at 1920x1080), Mpix/s with the per-stage breakdown.  One JSON line; not the headline metric."""
+    import torch
+    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
+    gm = importlib.import_module("3d_gaussian_splatting_b200.gaussian_model")
+    torch.cuda.set_device(local_rank)
+    scene, cams, deg = syn.make_config(args.config, N=args.N)
+    cams = cams[:max(1, args.views)]
+    H, W = cams[0].image_height, cams[0].image_width
+    P, T, K, N = H * W, ((H + 15) // 16) * ((W + 15) // 16), (deg + 1) ** 2, scene.N
+    model = gm.GaussianModel(deg, local_rank).load_scene(scene)
+    rast = importlib.import_module("3d_gaussian_splatting_b200.rasterizer").Rasterizer(local_rank)
+    pipe, bg = gm.PipelineParams(), (0.0, 0.0, 0.0)
+    max_pairs, per_view = 0, []
+    for cam in cams:      # synchronous mode: exact pair counts per view
+        out = gm.render(cam, model, pipe, bg, rast, with_visibility=False)
+        torch.cuda.synchronize()
+        Dv = rast.forward_status()[0]
+        max_pairs = max(max_pairs, Dv)
+        per_view.append(Dv)
+    rast.set_duplicate_capacity(int(1.2 * max_pairs) + 1024)      # from here on no host round-trip
+    warm = max(args.warmup, 3)
+    for i in range(warm):
+        gm.render(cams[i % len(cams)], model, pipe, bg, rast, with_visibility=False)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    n = max(args.steps, len(cams))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n):
+        gm.render(cams[i % len(cams)], model, pipe, bg, rast, with_visibility=False)
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    assert not rast.forward_status()[1], "pair capacity overflow inside the timed region"
+    ms = e0.elapsed_time(e1) / n
+    rast.set_profiling(True)
+    acc = {}
+    for i in range(len(cams)):
+        out = gm.render(cams[i], model, pipe, bg, rast, with_visibility=False)
+        torch.cuda.synchronize()
+        for k, v in rast.stage_ms().items():
+            if v > 0:
+                acc.setdefault(k, []).append(v)
+    rast.set_profiling(False)
+    stage_ms = {k: float(np.median(v)) for k, v in acc.items()}
+    N_vis = int((out["radii"] > 0).sum().item())
+    D = int(rast.debug_get("NUM_RENDERED")[0])
+    ncon = torch.from_numpy(rast.debug_get("N_CONTRIB").astype(np.int64)).reshape(H, W)
+    pad = torch.zeros(((H + 15) // 16 * 16, (W + 15) // 16 * 16), dtype=torch.int64)
+    pad[:H, :W] = ncon
+    D_eff = int(pad.reshape(pad.shape[0] // 16, 16, pad.shape[1] // 16, 16).amax(dim=(1, 3)).sum().item())
+    by = stage_bytes(N, N_vis, D, D_eff, P, T, K)
+    peak, peak_kind = peaks()
+    fwd_bytes = sum(by[k] for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd"))
+    binning = sum(stage_ms.get(k, 0.0) for k in ("depth_sort", "scan_duplicate", "sort", "ranges"))
+    print(json.dumps({
+        "metric": "render_mpix_per_s", "value": P / (ms * 1e-3) / 1e6, "unit": "Mpix/s", "n_gpus": 1, "steps": n,
+        "warmup": warm, "ms_per_step": ms, "frames_per_s": 1e3 / ms, "higher_is_better": True, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": args.config, "mode": "forward-only render", "N": N, "W": W, "H": H, "sh_degree": deg,
+                   "tiles": T, "views": len(cams), "N_vis": N_vis, "D_last_view": D, "D_max": max_pairs,
+                   "D_mean": float(np.mean(per_view)), "D_eff_last_view": D_eff,
+                   "pixel_gaussian_interactions": int(ncon.sum().item())},
+        "breakdown_ms": {"preprocess": round(stage_ms.get("preprocess", 0.0), 4), "binning_total": round(binning, 4),
+                         "depth_sort": round(stage_ms.get("depth_sort", 0.0), 4),
+                         "scan_duplicate": round(stage_ms.get("scan_duplicate", 0.0), 4),
+                         "tile_sort": round(stage_ms.get("sort", 0.0), 4), "ranges": round(stage_ms.get("ranges", 0.0), 4),
+                         "blend_fwd": round(stage_ms.get("blend_fwd", 0.0), 4)},
+        "roofline": {"bound": "hbm", "kernel": "forward (K1 + K2 + K3)", "achieved": fwd_bytes / (ms * 1e-3) / 1e9,
+                     "peak": peak, "unit": "GB/s", "frac": fwd_bytes / (ms * 1e-3) / 1e9 / peak, "traffic": None,
+                     "peak_kind": peak_kind},
+        "clocks": clocks,
+    }), flush=True)
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -519,6 +627,9 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+    elif args.mode == "render":
+        if rank == 0:
+            run_render_sweep(args, local_rank)
     else:
         run_ours(args, rank, world, local_rank)
 
