@@ -69,13 +69,6 @@ __device__ __forceinline__ uint32_t rect_alive(uint4 r) {
   const uint32_t area = rect_area(r);
   return area > GS_CULL_MAX_TILES ? area : (uint32_t)(__popc(r.z) + __popc(r.w));
 }
-// index (inside the rectangle) of the k-th alive tile
-__device__ __forceinline__ uint32_t rect_kth_alive(uint4 r, uint32_t k) {
-  if (rect_area(r) > GS_CULL_MAX_TILES) return k;
-  const uint32_t c = (uint32_t)__popc(r.z);
-  return k < c ? __fns(r.z, 0, (int)k + 1) : 32u + __fns(r.w, 0, (int)(k - c) + 1);
-}
-
 __global__ void __launch_bounds__(DUP_THREADS)
 dup_block_sums_kernel(int N, const uint32_t* __restrict__ order, const uint4* __restrict__ rects,
                       uint32_t* __restrict__ block_sums) {
@@ -136,23 +129,48 @@ dup_scan_sums_kernel(int nb, uint32_t* __restrict__ block_sums, unsigned long lo
   }
 }
 
+// index (inside the rectangle) of the k-th alive tile: binary descent over popcounts (the generic __fns costs more)
+__device__ __forceinline__ uint32_t kth_set_bit64(uint32_t lo, uint32_t hi, uint32_t k) {
+  const uint32_t c = (uint32_t)__popc(lo);
+  uint32_t word = lo, pos = 0;
+  if (k >= c) { k -= c; word = hi; pos = 32; }
+  uint32_t t = (uint32_t)__popc(word & 0xFFFFu);
+  if (k >= t) { k -= t; word >>= 16; pos += 16; }
+  t = (uint32_t)__popc(word & 0xFFu);
+  if (k >= t) { k -= t; word >>= 8; pos += 8; }
+  t = (uint32_t)__popc(word & 0xFu);
+  if (k >= t) { k -= t; word >>= 4; pos += 4; }
+  t = (uint32_t)__popc(word & 0x3u);
+  if (k >= t) { k -= t; word >>= 2; pos += 2; }
+  if (k >= (word & 1u)) pos += 1;
+  return pos;
+}
+
 // A block expands 1024 consecutive ranks of the depth order.  Thread t first scans the tile counts of
-// ranks 4t .. 4t+3; then the block's output slots [0, total) are dealt round-robin to the threads: slot j
-// finds its owner by binary search in the shared prefix array and derives its tile from the owner's
-// rectangle and alive-tile mask (exact tile culling, gs_common.cuh), so both output arrays are written fully coalesced whatever the rectangle sizes are (no
-// per-thread loops over big splats).  cap: capacity of the pair buffers (pairs past it are dropped and
+// ranks 4t .. 4t+3.  The block's output slots [0, total) are then produced in rounds of DUP_ROUND: every rank
+// with tiles marks its first slot with (rank + 1), an inclusive max-scan over the marks (8 slots per thread, one
+// 16-byte shared load / store each) turns them into the owner of every slot, and the slots are dealt round-robin
+// to the threads: slot j reads its owner, derives its tile from the owner's rectangle and alive-tile mask (exact
+// tile culling, gs_common.cuh), so both output arrays are written fully coalesced whatever the rectangle sizes are
+// (no per-thread loops over big splats, and no per-slot search: the first version's 10-step binary search per slot
+// was 2/3 of this kernel's instructions).  cap: capacity of the pair buffers (pairs past it are dropped and
 // *overflow is raised -- only possible when the caller fixed the capacity in advance).
+#define DUP_SLOTS 8
+#define DUP_ROUND (DUP_THREADS * DUP_SLOTS)
 template <typename KeyT>
 __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint4* __restrict__ rects,
                            const uint32_t* __restrict__ block_base, KeyT* __restrict__ tile_ids,
                            uint32_t* __restrict__ values, int gx, uint32_t cap, uint32_t* __restrict__ overflow) {
   __shared__ uint32_t s_warp[DUP_THREADS / 32];
+  __shared__ uint32_t s_wmax[DUP_THREADS / 32];
   __shared__ uint32_t s_off[DUP_BLOCK];
   __shared__ uint32_t s_id[DUP_BLOCK];
   __shared__ uint4 s_rect[DUP_BLOCK];
-  const int r0 = blockIdx.x * DUP_BLOCK + threadIdx.x * DUP_ITEMS;
-  uint32_t cnt[DUP_ITEMS];
+  __shared__ __align__(16) uint16_t s_owner[DUP_ROUND];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int r0 = blockIdx.x * DUP_BLOCK + tid * DUP_ITEMS;
+  uint32_t cnt[DUP_ITEMS], myoff[DUP_ITEMS];
   uint32_t sum = 0;
 #pragma unroll
   for (int k = 0; k < DUP_ITEMS; ++k) {
@@ -162,8 +180,8 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
       id = order[r0 + k];
       rc = __ldg(rects + id);
     }
-    s_id[threadIdx.x * DUP_ITEMS + k] = id;
-    s_rect[threadIdx.x * DUP_ITEMS + k] = rc;
+    s_id[tid * DUP_ITEMS + k] = id;
+    s_rect[tid * DUP_ITEMS + k] = rc;
     cnt[k] = rect_alive(rc);
     sum += cnt[k];
   }
@@ -171,30 +189,78 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
   uint32_t off = block_exclusive_scan_256(sum, s_warp, total);
 #pragma unroll
   for (int k = 0; k < DUP_ITEMS; ++k) {
-    s_off[threadIdx.x * DUP_ITEMS + k] = off;
+    s_off[tid * DUP_ITEMS + k] = off;
+    myoff[k] = off;
     off += cnt[k];
   }
-  __syncthreads();
   const uint32_t base = block_base[blockIdx.x];
   uint32_t limit = total;
   if ((unsigned long long)base + total > cap) {
     limit = base < cap ? cap - base : 0u;  // (the scan kernel has raised the overflow flag)
   }
-  for (uint32_t j = threadIdx.x; j < limit; j += DUP_THREADS) {
-    // owner = last entry with s_off <= j (entries with zero tiles share an offset with their successor and are
-    // skipped because the search returns the LAST such entry)
-    int lo = 0, hi = DUP_BLOCK - 1;
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (s_off[mid] <= j) lo = mid;
-      else hi = mid - 1;
+  uint32_t carry = 0;  // owner mark of the last slot of the previous round
+  for (uint32_t lo = 0; lo < limit; lo += DUP_ROUND) {
+    reinterpret_cast<uint4*>(s_owner)[tid] = make_uint4(0u, 0u, 0u, 0u);
+    __syncthreads();  // (also orders s_off / s_id / s_rect before the first round's reads)
+#pragma unroll
+    for (int k = 0; k < DUP_ITEMS; ++k) {
+      const uint32_t rel = myoff[k] - lo;  // wraps for offsets below lo
+      if (cnt[k] > 0 && rel < DUP_ROUND) s_owner[rel] = (uint16_t)(tid * DUP_ITEMS + k + 1);
     }
-    const uint4 rc = s_rect[lo];
-    const uint32_t k = rect_kth_alive(rc, j - s_off[lo]);
-    const uint32_t x0 = rc.x & 0xFFFFu, y0 = rc.x >> 16, w = (rc.y & 0xFFFFu) - x0;
-    const uint32_t row = k / w, col = k - row * w;
-    tile_ids[base + j] = (KeyT)((y0 + row) * (uint32_t)gx + x0 + col);
-    values[base + j] = s_id[lo];
+    __syncthreads();
+    // inclusive max-scan of the marks (they increase with the slot): owner of a slot = last mark at or before it
+    const uint4 m = reinterpret_cast<const uint4*>(s_owner)[tid];
+    uint32_t e[DUP_SLOTS] = {m.x & 0xFFFFu, m.x >> 16, m.y & 0xFFFFu, m.y >> 16,
+                             m.z & 0xFFFFu, m.z >> 16, m.w & 0xFFFFu, m.w >> 16};
+#pragma unroll
+    for (int i = 1; i < DUP_SLOTS; ++i) e[i] = max(e[i], e[i - 1]);
+    uint32_t incl = e[DUP_SLOTS - 1];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl = max(incl, t);
+    }
+    uint32_t pre = __shfl_up_sync(0xffffffffu, incl, 1);
+    if (lane == 0) pre = 0;
+    if (lane == 31) s_wmax[warp] = incl;
+    __syncthreads();
+    uint32_t tot = carry;
+    pre = max(pre, carry);
+#pragma unroll
+    for (int w = 0; w < DUP_THREADS / 32; ++w) {
+      const uint32_t t = s_wmax[w];
+      if (w < warp) pre = max(pre, t);
+      tot = max(tot, t);
+    }
+    carry = tot;
+#pragma unroll
+    for (int i = 0; i < DUP_SLOTS; ++i) e[i] = max(e[i], pre);
+    reinterpret_cast<uint4*>(s_owner)[tid] =
+        make_uint4(e[0] | (e[1] << 16), e[2] | (e[3] << 16), e[4] | (e[5] << 16), e[6] | (e[7] << 16));
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < DUP_SLOTS; ++i) {
+      const uint32_t jr = (uint32_t)tid + (uint32_t)i * DUP_THREADS;
+      const uint32_t j = lo + jr;
+      if (j < limit) {
+        const uint32_t owner = (uint32_t)s_owner[jr] - 1u;
+        const uint4 rc = s_rect[owner];
+        uint32_t k = j - s_off[owner];
+        const uint32_t x0 = rc.x & 0xFFFFu, y0 = rc.x >> 16, w = (rc.y & 0xFFFFu) - x0;
+        uint32_t row;
+        if (rect_area(rc) > GS_CULL_MAX_TILES) {
+          row = k / w;
+        } else {
+          k = kth_set_bit64(rc.z, rc.w, k);
+          // k < 64, w <= 64: (k + 0.5) / w is at least 1/128 away from an integer, far beyond the division's error
+          row = __float2uint_rz(__fdividef((float)k + 0.5f, (float)w));
+        }
+        const uint32_t col = k - row * w;
+        tile_ids[base + j] = (KeyT)((y0 + row) * (uint32_t)gx + x0 + col);
+        values[base + j] = s_id[owner];
+      }
+    }
+    __syncthreads();  // the next round clears s_owner
   }
 }
 

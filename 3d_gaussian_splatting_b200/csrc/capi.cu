@@ -2,6 +2,7 @@
 // management and stage orchestration.  No torch types, no exceptions across the boundary, no
 // CPU fallback: compute entry points fail with GS_ECUDA when no sm_100 device is usable.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -24,6 +25,7 @@ cudaError_t gs_launch_duplicate(int, const uint32_t*, const uint4*, const uint32
 cudaError_t gs_launch_tile_sort(const uint32_t*, int, int, void*, void*, uint32_t*, uint32_t*, uint32_t*, int, int*,
                                 cudaStream_t);
 cudaError_t gs_launch_ranges(const uint32_t*, const void*, int, uint2*, int, cudaStream_t);
+cudaError_t gs_launch_depth_keys(const gs_settings&, const float*, int, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_order_tiles(int, const uint2*, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_blend_forward(const GsDims&, const uint32_t*, const uint2*, const uint32_t*, const GsGeom*,
                                     const float[3], float*, float4*, uint32_t*, float4*, uint2*, uint32_t*, uint32_t*,
@@ -72,6 +74,11 @@ struct gs_ctx {
   // per-Gaussian
   DevBuf geom, depths, radii, tiles, rects, clamped, grad_geom;
   DevBuf sort_k0, sort_k1, sort_v0, sort_v1, dup_sums;  // depth argsort ping-pong (order = sort_v1), scan partials
+  DevBuf depth_keys;                                    // sort keys written ahead of K1 (depth_key_kernel)
+  // the depth argsort runs beside K1 on this stream (fork after the counters are cleared, join before the scan)
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool overlap_depth_sort = true;
   // per-duplicate: tile ids (u16, u32 beyond 65536 tiles) and Gaussian ids, ping-pong
   DevBuf keys_a, keys_b, vals_a, vals_b;
   DevBuf radix_counts;
@@ -206,6 +213,20 @@ int gs_create(gs_ctx** out, int device) {
     return GS_ECUDA;
   }
   for (int i = 0; i < 2 * GS_NUM_STAGES; ++i) cudaEventCreate(&c->ev[i]);
+  // highest priority: the sort's twelve small launches must not queue behind K1's 12 500 blocks
+  int prio_lo = 0, prio_hi = 0;
+  cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+  if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+    gs_set_error(nullptr, "cudaStreamCreate/cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
+    gs_destroy(c);
+    return GS_ECUDA;
+  }
+  {
+    const char* env = getenv("GS_NO_SORT_OVERLAP");  // measurement switch: run the depth argsort after K1 on the caller's stream
+    if (env && env[0] == '1') c->overlap_depth_sort = false;
+  }
   *out = c;
   return GS_OK;
 }
@@ -214,7 +235,7 @@ void gs_destroy(gs_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   DevBuf* bufs[] = {&c->geom,   &c->depths, &c->radii,  &c->tiles,   &c->rects, &c->clamped,   &c->grad_geom, &c->sort_k0,
-                    &c->sort_k1, &c->sort_v0, &c->sort_v1, &c->dup_sums, &c->radix_counts,
+                    &c->sort_k1, &c->sort_v0, &c->sort_v1, &c->dup_sums, &c->radix_counts, &c->depth_keys,
                     &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_state,  &c->n_contrib,
                     &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters, &c->loss_acc, &c->ssim_work,
                     &c->tail_grads, &c->dz_codes,
@@ -222,6 +243,9 @@ void gs_destroy(gs_ctx* c) {
   for (DevBuf* b : bufs)
     if (b->ptr) cudaFree(b->ptr);
   if (c->d_host_pinned) cudaFreeHost(c->d_host_pinned);
+  if (c->side) cudaStreamDestroy(c->side);
+  if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+  if (c->ev_join) cudaEventDestroy(c->ev_join);
   for (int i = 0; i < 2 * GS_NUM_STAGES; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   delete c;
@@ -311,6 +335,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->tiles, Nn * 4);
   GS_ENSURE(c, c->rects, Nn * 16);
   GS_ENSURE(c, c->clamped, Nn);
+  GS_ENSURE(c, c->depth_keys, Nn * 4);
   GS_ENSURE(c, c->sort_k0, Nn * 4);
   GS_ENSURE(c, c->sort_k1, Nn * 4);
   GS_ENSURE(c, c->sort_v0, Nn * 4);
@@ -338,18 +363,36 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   uint64_t D = 0;
   GS_CUDA_CHECK(c, cudaMemsetAsync(c->counters.ptr, 0, 64, stream));
   if (N > 0) {
-    {
+    // The depth argsort reads only the view depth, so it is forked onto the context's second stream and runs
+    // beside K1 (the latency-bound N-sized sort fills the issue slots K1 leaves); the scan joins the two.
+    const bool overlap = c->overlap_depth_sort;
+    cudaStream_t sort_stream = overlap ? c->side : stream;
+    if (overlap) {
+      GS_CUDA_CHECK(c, cudaEventRecord(c->ev_fork, stream));
+      GS_CUDA_CHECK(c, cudaStreamWaitEvent(c->side, c->ev_fork, 0));
+    } else {
       StageTimer t(c, 0, stream);
       GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
                                             (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint4*)c->rects.ptr,
                                             (uint8_t*)c->clamped.ptr, stream));
     }
     {
-      StageTimer t(c, 1, stream);
-      GS_CUDA_CHECK(c, gs_launch_depth_sort(N, (const uint32_t*)c->depths.ptr, (uint32_t*)c->sort_k0.ptr,
+      StageTimer t(c, 1, sort_stream);
+      GS_CUDA_CHECK(c, gs_launch_depth_keys(*st, in->means3D, N, (uint32_t*)c->depth_keys.ptr, sort_stream));
+      GS_CUDA_CHECK(c, gs_launch_depth_sort(N, (const uint32_t*)c->depth_keys.ptr, (uint32_t*)c->sort_k0.ptr,
                                             (uint32_t*)c->sort_k1.ptr, (uint32_t*)c->sort_v0.ptr,
                                             (uint32_t*)c->sort_v1.ptr, (uint32_t*)c->radix_counts.ptr, c->radix_grid,
-                                            stream));
+                                            sort_stream));
+    }
+    if (overlap) {
+      GS_CUDA_CHECK(c, cudaEventRecord(c->ev_join, c->side));
+      {
+        StageTimer t(c, 0, stream);
+        GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
+                                              (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint4*)c->rects.ptr,
+                                              (uint8_t*)c->clamped.ptr, stream));
+      }
+      GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->ev_join, 0));
     }
     {
       StageTimer t(c, 2, stream);

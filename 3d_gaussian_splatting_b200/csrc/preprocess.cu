@@ -439,6 +439,30 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
   }
 }
 
+
+// ---- depth keys ahead of K1 ---------------------------------------------------------------------
+// The depth argsort needs nothing but the view depth, 12 of the 236 B a Gaussian occupies, so it does not have to
+// wait for K1: this kernel evaluates pv[2] with the expression pp_compute uses (same translation unit, no
+// contraction: the same bits) and the sort runs beside K1 on the context's second stream (capi.cu).  A Gaussian
+// behind the near plane gets key 0 like in K1; one that K1 culls later (degenerate covariance, empty rectangle)
+// keeps its depth here -- it emits no (tile, Gaussian) pair, so its place in the order is immaterial.
+__global__ void __launch_bounds__(256)
+depth_key_kernel(const __grid_constant__ gs_settings st, const float* __restrict__ means3D, int N,
+                 uint32_t* __restrict__ keys) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= N) return;
+  const float* V = st.viewmatrix;
+  const float p[3] = {__ldg(means3D + 3 * (size_t)i), __ldg(means3D + 3 * (size_t)i + 1), __ldg(means3D + 3 * (size_t)i + 2)};
+  const float z = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
+  keys[i] = z > GS_NEAR_Z ? __float_as_uint(z) : 0u;
+}
+
+cudaError_t gs_launch_depth_keys(const gs_settings& st, const float* means3D, int N, uint32_t* keys, cudaStream_t stream) {
+  if (N == 0) return cudaSuccess;
+  depth_key_kernel<<<(N + 255) / 256, 256, 0, stream>>>(st, means3D, N, keys);
+  return cudaGetLastError();
+}
+
 static bool pp_aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 
 cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, int N, GsGeom* geom, float* depths,

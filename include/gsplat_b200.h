@@ -280,7 +280,8 @@ enum {
   GS_DBG_RGB = 3,           /* (N,3) f32 */
   GS_DBG_CLAMPED = 4,       /* (N) u8, bit c set when channel c was clamped at 0 */
   GS_DBG_TILES_TOUCHED = 5, /* (N) u32 */
-  GS_DBG_DEPTH_ORDER = 6,   /* (N) u32 Gaussian ids in (depth bits, id) order: the first level of the sort */
+  GS_DBG_DEPTH_ORDER = 6,   /* (N) u32 Gaussian ids in (depth bits, id) order: the first level of the sort.  Keys are written
+                               ahead of K1, so only the relative order of VISIBLE Gaussians (radii > 0) is specified */
   GS_DBG_KEYS_SORTED = 7,   /* (D) u64 tile << 32 | depth bits, rebuilt from the sorted (tile, id) pairs */
   GS_DBG_POINT_LIST = 8,    /* (D) u32 */
   GS_DBG_RANGES = 9,        /* (T,2) u32 */

@@ -1,0 +1,14 @@
+"""Print the headline numbers and the per-stage table of bench.py JSON lines (one file per argument)."""
+import json
+import sys
+
+for path in sys.argv[1:]:
+    for line in open(path):
+        if not line.startswith("{"):
+            continue
+        d = json.loads(line)
+        e2e = d.get("e2e") or {}
+        print(f"{path}: {d.get('value', 0):.1f} {d.get('unit')}  {d.get('ms_per_step', 0):.4f} ms/step  e2e {e2e.get('ms_per_step', 0):.4f} ms"
+              f"  raster {d.get('raster_fwd_bwd_ms')}")
+        st = d.get("stages") or {}
+        print("   " + "  ".join(f"{k}={v['ms']:.3f}" for k, v in st.items()))
