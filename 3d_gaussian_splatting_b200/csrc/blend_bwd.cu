@@ -8,8 +8,8 @@
 // arithmetic (so T and the prefix colour C are the forward's bits), and gets the colour behind the
 // current Gaussian from the final pixel colour:  Cb = out - C_prefix_after  (includes bg * T_final).
 //     dL/dalpha_i = sum_ch dL/dC_ch * (c_ch * T_i - Cb_ch / (1 - alpha_i))
-// Persistent 64-thread blocks pull work items from an atomic cursor; every thread owns a 2x2 pixel
-// quad, so a segment needs only two cross-lane reductions per Gaussian: per-thread partial sums of
+// Persistent warps pull work items (a 16x8 half of a tile x one segment) from an atomic cursor; every thread owns
+// a 2x2 pixel quad, so a segment needs only two cross-lane reductions per Gaussian: per-thread partial sums of
 // the 9 gradient components are reduced with a halving butterfly (8 values in 4+2+1+1+1 shuffles,
 // the 9th in 5) and leave the SM as ONE predicated red.global.add.f32 (9 lanes, 9 consecutive floats).
 //
@@ -20,76 +20,50 @@
 #include "gs_common.cuh"
 
 #define BB_THREADS 64
-#define BB_PER_THREAD (GS_SEG / BB_THREADS)
+#define BB_WARPS (BB_THREADS / 32)
+#define BB_PER_LANE (GS_SEG / 32)
 
-__global__ void __launch_bounds__(BB_THREADS)
+// Every WARP is autonomous: it pulls its own work item -- (tile, segment, upper or lower 16x8 half of the tile) --
+// stages the segment's records into its own shared-memory slice and never meets a block barrier.  (The first
+// version paired the two halves of a tile in one 64-thread block: 17% of its issue slots were spent at the barrier
+// waiting for the slower half, profiles/r01k.)
+__global__ void __launch_bounds__(BB_THREADS, 10)
 blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                       const GsGeom* __restrict__ geom, float bg0, float bg1, float bg2,
                       const float4* __restrict__ final_state, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
                       const float4* __restrict__ ckpt, const uint2* __restrict__ work_items,
                       const uint32_t* __restrict__ work_count, uint32_t* __restrict__ work_cursor,
                       const uint32_t* __restrict__ tile_last, float* __restrict__ grad_geom) {
-  __shared__ float4 s_q0[GS_SEG];
-  __shared__ float4 s_q1[GS_SEG];
-  __shared__ float s_b[GS_SEG];
-  __shared__ uint32_t s_id[GS_SEG];
-  __shared__ uint32_t s_bits[BB_THREADS / 32][GS_SEG / 32];  // [pixel warp][32-entry word]: entries alive for it
-  __shared__ uint32_t s_work;
+  __shared__ float4 s_q0_all[BB_WARPS][GS_SEG];
+  __shared__ float4 s_q1_all[BB_WARPS][GS_SEG];
+  __shared__ float s_b_all[BB_WARPS][GS_SEG];
+  __shared__ uint32_t s_id_all[BB_WARPS][GS_SEG];
 
-  const int tid = threadIdx.x, lane = tid & 31;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float4* const s_q0 = s_q0_all[wib];
+  float4* const s_q1 = s_q1_all[wib];
+  float* const s_b = s_b_all[wib];
+  uint32_t* const s_id = s_id_all[wib];
   const size_t plane = (size_t)d.H * d.W;
   const float ddelx_dx = 0.5f * (float)d.W, ddely_dy = 0.5f * (float)d.H;
-  const uint32_t nwork = *work_count;
+  const uint32_t nwork = 2u * *work_count;  // two halves per (tile, segment)
 
   for (;;) {
-    __syncthreads();
-    if (tid == 0) s_work = atomicAdd(work_cursor, 1u);
-    __syncthreads();
-    const uint32_t w = s_work;
+    uint32_t w = 0;
+    if (lane == 0) w = atomicAdd(work_cursor, 1u);
+    w = __shfl_sync(0xffffffffu, w, 0);
     if (w >= nwork) break;
-    const uint2 item = work_items[w];
+    const uint2 item = work_items[w >> 1];
+    const int half = (int)(w & 1u);
     const int tile = (int)item.x;
     const int seg = (int)item.y;
     const int k0 = seg << GS_SEG_SHIFT;                                  // first list entry of the segment
     const int n = min(GS_SEG, (int)tile_last[tile] - k0);                // entries in it
     const uint2 range = ranges[tile];
     const int tx = tile % d.gx, ty = tile / d.gx;
-    const int qx = 2 * (tid & 7), qy = 2 * (tid >> 3);
+    const int qx = 2 * (lane & 7), qy = 2 * (lane >> 3) + 8 * half;
     const int x0 = tx * GS_TILE + qx, y0 = ty * GS_TILE + qy;
 
-    // gather the segment's records (coalesced ids, L2-resident 48-B records)
-    // the loading thread also decides which of the two pixel warps (16x8 pixel boxes) its entry can reach with
-    // alpha >= 1/255 (gs_box_alive, the conservative test of the exact tile cull): a warp then walks only those
-#pragma unroll
-    for (int u = 0; u < BB_PER_THREAD; ++u) {
-      const int j = tid + u * BB_THREADS;
-      uint32_t alive = 0;
-      if (j < n) {
-        const uint32_t id = __ldg(point_list + range.x + (uint32_t)(k0 + j));
-        const float4* gp = reinterpret_cast<const float4*>(geom + id);
-        const float4 q0 = __ldg(gp), q1 = __ldg(gp + 1), q2 = __ldg(gp + 2);
-        s_id[j] = id;
-        s_q0[j] = q0;
-        s_q1[j] = q1;
-        s_b[j] = q2.x;
-        GsCull c;
-        c.hA = q0.z;
-        c.B = q0.w;
-        c.hC = q1.x;
-        c.rA = __frcp_rn(2.0f * q0.z);
-        c.rC = __frcp_rn(2.0f * q1.x);
-        c.thr = q2.z;
-        const float bx = (float)(tx * GS_TILE), by = (float)(ty * GS_TILE);
-#pragma unroll
-        for (int w = 0; w < BB_THREADS / 32; ++w)
-          if (gs_box_alive(c, q0.x, q0.y, bx, bx + 15.0f, by + (float)(8 * w), by + (float)(8 * w + 7))) alive |= 1u << w;
-      }
-#pragma unroll
-      for (int w = 0; w < BB_THREADS / 32; ++w) {
-        const uint32_t word = __ballot_sync(0xffffffffu, (alive >> w) & 1u);
-        if (lane == 0) s_bits[w][u * (BB_THREADS / 32) + (tid >> 5)] = word;
-      }
-    }
     // per-pixel state
     float pixx[4], pixy[4], T[4], C0[4], C1[4], C2[4], O0[4], O1[4], O2[4], dL0[4], dL1[4], dL2[4];
     int last[4];
@@ -123,12 +97,43 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
     int warp_last = my_last;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
-    __syncthreads();
     const int jend = min(n, warp_last - k0);  // this warp only needs entries k < warp_last
+    if (jend <= 0) continue;
 
-    for (int wd = 0; wd < GS_SEG / 32; ++wd) {
-     uint32_t word = s_bits[tid >> 5][wd];
-     if ((wd << 5) + 32 > jend) word &= (wd << 5) < jend ? (0xFFFFFFFFu >> (32 - (jend - (wd << 5)))) : 0u;
+    // gather the records this warp needs (coalesced ids, L2-resident 48-B records); the loading lane also decides
+    // whether its entry can reach alpha >= 1/255 anywhere in the warp's 16x8 pixel box (gs_box_alive, the
+    // conservative test of the exact tile cull): the warp then walks only those
+    uint32_t words[BB_PER_LANE];
+    __syncwarp();  // every lane has finished reading the previous item's records
+#pragma unroll
+    for (int u = 0; u < BB_PER_LANE; ++u) {
+      const int j = lane + 32 * u;
+      bool alive = false;
+      if (j < jend) {
+        const uint32_t id = __ldg(point_list + range.x + (uint32_t)(k0 + j));
+        const float4* gp = reinterpret_cast<const float4*>(geom + id);
+        const float4 q0 = __ldg(gp), q1 = __ldg(gp + 1), q2 = __ldg(gp + 2);
+        s_id[j] = id;
+        s_q0[j] = q0;
+        s_q1[j] = q1;
+        s_b[j] = q2.x;
+        GsCull c;
+        c.hA = q0.z;
+        c.B = q0.w;
+        c.hC = q1.x;
+        c.rA = __frcp_rn(2.0f * q0.z);
+        c.rC = __frcp_rn(2.0f * q1.x);
+        c.thr = q2.z;
+        const float bx = (float)(tx * GS_TILE), by = (float)(ty * GS_TILE + 8 * half);
+        alive = gs_box_alive(c, q0.x, q0.y, bx, bx + 15.0f, by, by + 7.0f);
+      }
+      words[u] = __ballot_sync(0xffffffffu, alive);
+    }
+    __syncwarp();
+
+#pragma unroll
+    for (int wd = 0; wd < BB_PER_LANE; ++wd) {
+     uint32_t word = words[wd];
      while (word) {
       const int j = (wd << 5) + __ffs(word) - 1;
       word &= word - 1;
