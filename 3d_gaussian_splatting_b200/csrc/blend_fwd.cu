@@ -20,16 +20,25 @@
 
 #define BF_THREADS 256
 
-__global__ void __launch_bounds__(BF_THREADS)
+// 48-byte record, global -> shared, asynchronously and without staging registers (LDGSTS); .ca keeps the line in L1
+// for the other seven warps of the tile
+__device__ __forceinline__ void bf_copy_record(GsGeom* dst, const GsGeom* src) {
+  const uint32_t s = (uint32_t)__cvta_generic_to_shared(dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(s), "l"(src) : "memory");
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(s + 16u), "l"(reinterpret_cast<const char*>(src) + 16) : "memory");
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(s + 32u), "l"(reinterpret_cast<const char*>(src) + 32) : "memory");
+}
+__device__ __forceinline__ void bf_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bf_wait_1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+__global__ void __launch_bounds__(BF_THREADS, 4)
 blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
                      const uint32_t* __restrict__ point_list, const GsGeom* __restrict__ geom, float bg0, float bg1,
                      float bg2, float* __restrict__ out_color, float4* __restrict__ final_state,
                      uint32_t* __restrict__ n_contrib, float4* __restrict__ ckpt, uint2* __restrict__ work_items,
                      uint32_t* __restrict__ work_count, uint32_t* __restrict__ tile_last) {
-  __shared__ float4 s_q0[BF_THREADS];
-  __shared__ float4 s_q1[BF_THREADS];
-  __shared__ float s_b[BF_THREADS];
-  __shared__ uint32_t s_bits[BF_THREADS / 32][BF_THREADS / 32];  // [pixel warp][32-entry word]: entries alive for it
+  // per-warp slices, double-buffered: the 32 records of the chunk the warp is walking and of the next one
+  __shared__ GsGeom s_g_all[BF_THREADS / 32][2][32];
   __shared__ uint32_t s_wlast[BF_THREADS / 32];
 
   const int tile = (int)tile_order[blockIdx.x];
@@ -43,93 +52,97 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
   const uint2 range = ranges[tile];
   const int total = (int)(range.y - range.x);
   float4* my_ckpt = ckpt + ((size_t)(range.x >> GS_SEG_SHIFT) + (size_t)tile) * GS_TILE_PIX + (ly * GS_TILE + lx);
+  // the warp's 8x4 box of pixel centres
+  const float bx = (float)(tx * GS_TILE + (warp & 1) * 8), by = (float)(ty * GS_TILE + (warp >> 1) * 4);
+  const uint32_t* plist = point_list + range.x + lane;
 
   bool done = !inside;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
   uint32_t last_contributor = 0;
 
-  for (int lo = 0; lo < total; lo += BF_THREADS) {
-    if (__syncthreads_and(done)) break;
-    const int n = min(BF_THREADS, total - lo);
-    // ---- stage 256 entries; the loading thread also decides, for each of the 8 pixel warps (8x4 pixel
-    //      boxes), whether its entry can reach alpha >= 1/255 anywhere in that box (gs_box_alive: the same
-    //      conservative test as the tile cull, so skipping a dead (warp, entry) pair never changes a pixel) ----
-    uint32_t alive8 = 0;
-    if (tid < n) {
-      const uint32_t id = __ldg(point_list + range.x + lo + tid);
-      const float4* gp = reinterpret_cast<const float4*>(geom + id);
-      const float4 q0 = __ldg(gp), q1 = __ldg(gp + 1), q2 = __ldg(gp + 2);
-      s_q0[tid] = q0;
-      s_q1[tid] = q1;
-      s_b[tid] = q2.x;
+  // Every warp walks the tile list on its own, 32 entries at a time, and stops when its 32 pixels have terminated:
+  // no block barrier inside the loop (the first version staged 256 entries per block between two barriers, and 30%
+  // of its issue slots were warps waiting there for the slowest of the eight, profiles/r01k).  The records of the
+  // next chunk are in flight (cp.async, global -> shared without registers) while the current one is walked, the
+  // ids one chunk further ahead; the eight warps of a tile gather the same records, so most gathers hit L1.
+  uint32_t id_next = 0;
+  if (lane < total) {
+    const uint32_t id0 = __ldg(plist);
+    bf_copy_record(&s_g_all[warp][0][lane], geom + id0);
+  }
+  bf_commit();
+  if (32 + lane < total) id_next = __ldg(plist + 32);
+  for (int pos = 0, buf = 0; pos < total; pos += 32, buf ^= 1) {
+    if (__all_sync(0xffffffffu, done)) break;
+    // segment boundary: checkpoint the state in front of entry pos
+    if ((pos & (GS_SEG - 1)) == 0 && pos > 0 && !done)
+      my_ckpt[(size_t)(pos >> GS_SEG_SHIFT) * GS_TILE_PIX] = make_float4(T, C0, C1, C2);
+    __syncwarp();  // every lane has finished reading the buffer the next copies overwrite
+    if (pos + 32 + lane < total) bf_copy_record(&s_g_all[warp][buf ^ 1][lane], geom + id_next);
+    bf_commit();
+    if (pos + 64 + lane < total) id_next = __ldg(plist + pos + 64);
+    bf_wait_1();  // this chunk's records have landed (the next chunk's may still be in flight)
+    __syncwarp();
+    const GsGeom* s_g = s_g_all[warp][buf];
+    // ---- the loading lane decides whether its entry can reach alpha >= 1/255 anywhere in the warp's box
+    //      (gs_box_alive: the same conservative test as the tile cull, so skipping a dead (warp, entry) pair
+    //      never changes a pixel) ----
+    bool alive = false;
+    if (pos + lane < total) {
+      const float4 q0 = s_g[lane].q0;
+      const float hC = s_g[lane].q1.x;
       GsCull c;
       c.hA = q0.z;
       c.B = q0.w;
-      c.hC = q1.x;
+      c.hC = hC;
       c.rA = __frcp_rn(2.0f * q0.z);
-      c.rC = __frcp_rn(2.0f * q1.x);
-      c.thr = q2.z;
-      const float x0 = (float)(tx * GS_TILE), y0 = (float)(ty * GS_TILE);
+      c.rC = __frcp_rn(2.0f * hC);
+      c.thr = s_g[lane].q2.z;
+      alive = gs_box_alive(c, q0.x, q0.y, bx, bx + 7.0f, by, by + 3.0f);
+    }
+    uint32_t word = __ballot_sync(0xffffffffu, alive);
+    // ---- walk the alive entries in list order ----
+    while (word) {
+      // up to four alive entries at a time: their power / alpha are independent, only T is sequential
+      int jj[4];
+      float alpha[4];
 #pragma unroll
-      for (int w = 0; w < BF_THREADS / 32; ++w) {
-        const float bx = x0 + (float)((w & 1) * 8), by = y0 + (float)((w >> 1) * 4);
-        if (gs_box_alive(c, q0.x, q0.y, bx, bx + 7.0f, by, by + 3.0f)) alive8 |= 1u << w;
+      for (int u = 0; u < 4; ++u) {
+        jj[u] = word ? __ffs(word) - 1 : -1;
+        word &= word - 1;
       }
-    }
 #pragma unroll
-    for (int w = 0; w < BF_THREADS / 32; ++w) {
-      const uint32_t word = __ballot_sync(0xffffffffu, (alive8 >> w) & 1u);
-      if (lane == 0) s_bits[w][warp] = word;
-    }
-    __syncthreads();
-    // ---- this warp walks only its alive entries, in list order, 32-entry word by word ----
-    const int nwords = (n + 31) >> 5;
-    for (int wd = 0; wd < nwords && !__all_sync(0xffffffffu, done); ++wd) {
-      // segment boundary: checkpoint the state in front of entry lo + 32*wd
-      const int pos = lo + (wd << 5);
-      if ((pos & (GS_SEG - 1)) == 0 && pos > 0 && !done)
-        my_ckpt[(size_t)(pos >> GS_SEG_SHIFT) * GS_TILE_PIX] = make_float4(T, C0, C1, C2);
-      uint32_t word = s_bits[warp][wd];
-      while (word) {
-        // up to four alive entries at a time: their power / alpha are independent, only T is sequential
-        int jj[4];
-        float alpha[4];
+      for (int u = 0; u < 4; ++u) {
+        const int j = max(jj[u], 0);
+        const float4 q0 = s_g[j].q0;
+        const float hC = s_g[j].q1.x, op = s_g[j].q1.y;
+        const float dx = q0.x - pixx, dy = q0.y - pixy;
+        const float power = gs_power(q0.z, q0.w, hC, dx, dy);
+        float G;
+        const float a = gs_alpha(op, power, G);
+        alpha[u] = (jj[u] >= 0 && !(power > 0.0f) && !(a < GS_ALPHA_MIN)) ? a : 0.0f;
+      }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          jj[u] = word ? (wd << 5) + __ffs(word) - 1 : -1;
-          word &= word - 1;
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int j = max(jj[u], 0);
-          const float4 q0 = s_q0[j];
-          const float hC = s_q1[j].x, op = s_q1[j].y;
-          const float dx = q0.x - pixx, dy = q0.y - pixy;
-          const float power = gs_power(q0.z, q0.w, hC, dx, dy);
-          float G;
-          const float a = gs_alpha(op, power, G);
-          alpha[u] = (jj[u] >= 0 && !(power > 0.0f) && !(a < GS_ALPHA_MIN)) ? a : 0.0f;
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (alpha[u] != 0.0f && !done) {
-            const float test_T = T * (1.0f - alpha[u]);
-            if (test_T < GS_T_MIN) {
-              done = true;
-            } else {
-              const int j = jj[u];
-              const float w = alpha[u] * T;
-              C0 = fmaf(s_q1[j].z, w, C0);
-              C1 = fmaf(s_q1[j].w, w, C1);
-              C2 = fmaf(s_b[j], w, C2);
-              T = test_T;
-              last_contributor = (uint32_t)(lo + j + 1);
-            }
+      for (int u = 0; u < 4; ++u) {
+        if (alpha[u] != 0.0f && !done) {
+          const float test_T = T * (1.0f - alpha[u]);
+          if (test_T < GS_T_MIN) {
+            done = true;
+          } else {
+            const int j = jj[u];
+            const float w = alpha[u] * T;
+            C0 = fmaf(s_g[j].q1.z, w, C0);
+            C1 = fmaf(s_g[j].q1.w, w, C1);
+            C2 = fmaf(s_g[j].q2.x, w, C2);
+            T = test_T;
+            last_contributor = (uint32_t)(pos + j + 1);
           }
         }
       }
+      if (__all_sync(0xffffffffu, done)) break;
     }
   }
+  asm volatile("cp.async.wait_all;" ::: "memory");  // no copy may outlive the warp
   if (inside) {
     const size_t pix = (size_t)py * d.W + px;
     const size_t plane = (size_t)d.H * d.W;
