@@ -91,7 +91,7 @@ dup_block_sums_kernel(int N, const uint32_t* __restrict__ order, const uint4* __
 __global__ void __launch_bounds__(1024)
 dup_scan_sums_kernel(int nb, uint32_t* __restrict__ block_sums, unsigned long long* __restrict__ total,
                      uint32_t* __restrict__ total32, unsigned long long cap, uint32_t* __restrict__ overflow,
-                     float* __restrict__ guard, float* __restrict__ mirror) {
+                     float* __restrict__ guard, float* __restrict__ mirror, uint32_t* __restrict__ host_status) {
   __shared__ unsigned long long s_warp[32];
   const int per = (nb + 1023) / 1024;
   const int lo = min(nb, (int)threadIdx.x * per), hi = min(nb, lo + per);
@@ -125,6 +125,12 @@ dup_scan_sums_kernel(int nb, uint32_t* __restrict__ block_sums, unsigned long lo
       *overflow = 1u;
       *guard = 1.0f;
       if (mirror) *mirror = 1.0f;
+    }
+    // status words straight into the caller's pinned (device-mapped) host buffer: D (u64), overflow flag --
+    // no copy operation on the stream
+    if (host_status) {
+      *reinterpret_cast<unsigned long long*>(host_status) = tot;
+      host_status[2] = tot > cap ? 1u : 0u;
     }
   }
 }
@@ -268,11 +274,12 @@ int gs_dup_num_blocks(int N) { return (N + DUP_BLOCK - 1) / DUP_BLOCK; }
 
 cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint4* rects, uint32_t* block_sums,
                                unsigned long long* total, uint32_t* total32, unsigned long long cap,
-                               uint32_t* overflow, float* guard, float* mirror, cudaStream_t stream) {
+                               uint32_t* overflow, float* guard, float* mirror, uint32_t* host_status,
+                               cudaStream_t stream) {
   if (N == 0) return cudaMemsetAsync(total, 0, 8, stream);
   const int nb = gs_dup_num_blocks(N);
   dup_block_sums_kernel<<<nb, DUP_THREADS, 0, stream>>>(N, order, rects, block_sums);
-  dup_scan_sums_kernel<<<1, 1024, 0, stream>>>(nb, block_sums, total, total32, cap, overflow, guard, mirror);
+  dup_scan_sums_kernel<<<1, 1024, 0, stream>>>(nb, block_sums, total, total32, cap, overflow, guard, mirror, host_status);
   return cudaGetLastError();
 }
 

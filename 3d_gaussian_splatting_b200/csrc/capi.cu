@@ -19,7 +19,7 @@ cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uin
                                  cudaStream_t);
 int gs_dup_num_blocks(int N);
 cudaError_t gs_launch_dup_scan(int, const uint32_t*, const uint4*, uint32_t*, unsigned long long*, uint32_t*,
-                               unsigned long long, uint32_t*, float*, float*, cudaStream_t);
+                               unsigned long long, uint32_t*, float*, float*, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_duplicate(int, const uint32_t*, const uint4*, const uint32_t*, void*, int, uint32_t*, int,
                                 uint32_t, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_tile_sort(const uint32_t*, int, int, void*, void*, uint32_t*, uint32_t*, uint32_t*, int, int*,
@@ -94,7 +94,10 @@ struct gs_ctx {
   DevBuf loss_acc, ssim_work, tail_grads;
   DevBuf dz_codes, dz_counts;  // densification plan: per-Gaussian outcome codes, per-block counts -> offsets + totals
   int dz_N = -1;               // N of the pending plan (gs_densify_plan -> gs_densify_apply)
-  uint32_t* d_host_pinned = nullptr;  // readback: bytes 0..7 D (u64), 8..11 overflow flag
+  uint32_t* d_host_pinned = nullptr;  // readback: bytes 0..7 D (u64), 8..11 overflow flag (written by the scan kernel)
+  uint32_t* d_host_mapped = nullptr;  // device address of the same buffer
+  cudaEvent_t ev_zero = nullptr;      // grad_geom cleared on the side stream during the forward
+  bool grad_geom_zeroed = false;
   uint64_t dup_cap_fixed = 0;         // > 0: caller-fixed pair capacity, no host synchronisation in gs_forward
   float* overflow_mirror = nullptr;   // optional caller-owned device float raised to 1.0 on overflow
   bool D_pending = false;             // D of the last forward not yet read back
@@ -207,7 +210,9 @@ int gs_create(gs_ctx** out, int device) {
   c->device = device;
   c->num_sms = prop.multiProcessorCount;
   c->radix_grid = 4 * c->num_sms < 608 ? 4 * c->num_sms : 608;  // RS_MAX_GRID
-  if (cudaSetDevice(device) != cudaSuccess || cudaMallocHost((void**)&c->d_host_pinned, 64) != cudaSuccess) {
+  if (cudaSetDevice(device) != cudaSuccess ||
+      cudaHostAlloc((void**)&c->d_host_pinned, 64, cudaHostAllocMapped) != cudaSuccess ||
+      cudaHostGetDevicePointer((void**)&c->d_host_mapped, c->d_host_pinned, 0) != cudaSuccess) {
     gs_set_error(nullptr, "cudaSetDevice/cudaMallocHost failed: %s", cudaGetErrorString(cudaGetLastError()));
     delete c;
     return GS_ECUDA;
@@ -218,7 +223,8 @@ int gs_create(gs_ctx** out, int device) {
   cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
   if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+      cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_zero, cudaEventDisableTiming) != cudaSuccess) {
     gs_set_error(nullptr, "cudaStreamCreate/cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
     gs_destroy(c);
     return GS_ECUDA;
@@ -246,6 +252,7 @@ void gs_destroy(gs_ctx* c) {
   if (c->side) cudaStreamDestroy(c->side);
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
+  if (c->ev_zero) cudaEventDestroy(c->ev_zero);
   for (int i = 0; i < 2 * GS_NUM_STAGES; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   delete c;
@@ -336,6 +343,8 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->rects, Nn * 16);
   GS_ENSURE(c, c->clamped, Nn);
   GS_ENSURE(c, c->depth_keys, Nn * 4);
+  GS_ENSURE(c, c->grad_geom, Nn * 48);
+  c->grad_geom_zeroed = false;
   GS_ENSURE(c, c->sort_k0, Nn * 4);
   GS_ENSURE(c, c->sort_k1, Nn * 4);
   GS_ENSURE(c, c->sort_v0, Nn * 4);
@@ -386,6 +395,10 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
     }
     if (overlap) {
       GS_CUDA_CHECK(c, cudaEventRecord(c->ev_join, c->side));
+      // the backward's accumulation records are cleared here, off the critical path (consumed by gs_backward*)
+      GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, c->side));
+      GS_CUDA_CHECK(c, cudaEventRecord(c->ev_zero, c->side));
+      c->grad_geom_zeroed = true;
       {
         StageTimer t(c, 0, stream);
         GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
@@ -400,9 +413,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
       const unsigned long long cap = async_mode ? c->dup_cap_fixed : 0xFFFFFFF0ull;
       GS_CUDA_CHECK(c, gs_launch_dup_scan(N, (const uint32_t*)c->sort_v1.ptr, (const uint4*)c->rects.ptr,
                                           (uint32_t*)c->dup_sums.ptr, D64_dev, D_dev, cap, overflow_dev, guard_dev,
-                                          c->overflow_mirror, stream));
-      GS_CUDA_CHECK(c, cudaMemcpyAsync(c->d_host_pinned, D64_dev, 8, cudaMemcpyDeviceToHost, stream));
-      GS_CUDA_CHECK(c, cudaMemcpyAsync(c->d_host_pinned + 2, overflow_dev, 4, cudaMemcpyDeviceToHost, stream));
+                                          c->overflow_mirror, c->d_host_mapped, stream));
       if (async_mode) {
         // caller-fixed capacity: nothing to wait for; an overflow poisons the step (guard) and is reported by
         // gs_get_forward_status once the caller has synchronised
@@ -496,7 +507,12 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
   GS_ENSURE(c, c->grad_geom, (size_t)N * 48);
   if (!(c->reuse_blend_gradients && c->have_backward)) {
     StageTimer t(c, 6, stream);
-    GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
+    if (c->grad_geom_zeroed) {
+      GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->ev_zero, 0));
+      c->grad_geom_zeroed = false;
+    } else {
+      GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
+    }
     GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, c->point_list,
                                               (const GsGeom*)c->geom.ptr, st->bg, (const float4*)c->final_state.ptr,
                                               (const uint32_t*)c->n_contrib.ptr, dL_dout_color,
@@ -572,7 +588,12 @@ int gs_backward_adam_step(gs_ctx* c, const gs_settings* st, int N, const gs_gaus
   GS_ENSURE(c, c->grad_geom, (size_t)N * 48);
   if (!(c->reuse_blend_gradients && c->have_backward)) {
     StageTimer t(c, 6, stream);
-    GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
+    if (c->grad_geom_zeroed) {
+      GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->ev_zero, 0));
+      c->grad_geom_zeroed = false;
+    } else {
+      GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
+    }
     GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, c->point_list,
                                               (const GsGeom*)c->geom.ptr, st->bg, (const float4*)c->final_state.ptr,
                                               (const uint32_t*)c->n_contrib.ptr, dL_dout_color,

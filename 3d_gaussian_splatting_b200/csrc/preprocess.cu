@@ -254,10 +254,14 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
 }
 
 // Exact tile cull of one warp's Gaussians, load-balanced: the candidate (Gaussian, tile) pairs of the 32 lanes are
-// flattened (exclusive scan of the rectangle areas), lane l tests candidates l, l+32, ...: it finds the owner by
-// binary search in the shared offsets, evaluates gs_tile_alive with the owner's parameters and ORs the result into
-// the owner's 64-bit mask.  Same decisions as the per-thread loop (same function, same inputs), without the
-// divergence of 32 different rectangle sizes.  sw: this warp's scratch (32 lanes x PP_CULL_WORDS words).
+// flattened (exclusive scan of the rectangle areas), lane l tests candidates l, l+32, ...: it evaluates gs_tile_alive
+// with the owner's parameters and ORs the result into the owner's 64-bit mask.  Same decisions as the per-thread loop
+// (same function, same inputs), without the divergence of 32 different rectangle sizes.
+// Owner of a candidate, without a search: the lanes that have candidates store their records compacted (slot = rank
+// among those lanes); per batch of 32 candidates one REDUX.OR collects the bit mask of the offsets that start inside
+// the batch, and the owner's slot is (owners started before the batch) + popc(starts at or below my position) - 1.
+// (The first version's 5-step binary search in shared memory was 20% of K1's stall samples.)
+// sw: this warp's scratch (32 slots x PP_CULL_WORDS words).
 #define PP_CULL_WORDS 15  // 14 used; odd pitch: conflict-free owner look-ups
 __device__ __forceinline__ void pp_warp_cull(PpOut& o, uint32_t* sw) {
   const int lane = threadIdx.x & 31;
@@ -273,44 +277,48 @@ __device__ __forceinline__ void pp_warp_cull(PpOut& o, uint32_t* sw) {
     if (lane >= d) incl += t;
   }
   const int total = __shfl_sync(0xffffffffu, incl, 31);
-  uint32_t* me = sw + lane * PP_CULL_WORDS;
-  me[0] = (uint32_t)(incl - cnt);
-  me[1] = __float_as_uint(o.g.q0.x);
-  me[2] = __float_as_uint(o.g.q0.y);
-  me[3] = __float_as_uint(o.cs.hA);
-  me[4] = __float_as_uint(o.cs.B);
-  me[5] = __float_as_uint(o.cs.hC);
-  me[6] = __float_as_uint(o.cs.rA);
-  me[7] = __float_as_uint(o.cs.rC);
-  me[8] = __float_as_uint(o.cs.thr);
-  me[9] = (uint32_t)x0 | ((uint32_t)y0 << 16);
-  me[10] = (uint32_t)w;
-  me[11] = __float_as_uint(1.0f / (float)(w > 0 ? w : 1));
-  me[12] = 0u;
-  me[13] = 0u;
+  const int off = incl - cnt;
+  const uint32_t owners = __ballot_sync(0xffffffffu, cand);
+  uint32_t* me = sw + __popc(owners & ((1u << lane) - 1u)) * PP_CULL_WORDS;
+  if (cand) {
+    me[0] = (uint32_t)off;
+    me[1] = __float_as_uint(o.g.q0.x);
+    me[2] = __float_as_uint(o.g.q0.y);
+    me[3] = __float_as_uint(o.cs.hA);
+    me[4] = __float_as_uint(o.cs.B);
+    me[5] = __float_as_uint(o.cs.hC);
+    me[6] = __float_as_uint(o.cs.rA);
+    me[7] = __float_as_uint(o.cs.rC);
+    me[8] = __float_as_uint(o.cs.thr);
+    me[9] = (uint32_t)x0 | ((uint32_t)y0 << 16);
+    me[10] = (uint32_t)w;
+    me[11] = __float_as_uint(1.0f / (float)w);
+    me[12] = 0u;
+    me[13] = 0u;
+  }
   __syncwarp();
-  for (int c = lane; c < total; c += 32) {
-    int lo = 0, hi = 31;  // owner = last lane whose offset is <= c (lanes without candidates share their successor's)
-#pragma unroll
-    for (int it = 0; it < 5; ++it) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (sw[mid * PP_CULL_WORDS] <= (uint32_t)c) lo = mid;
-      else hi = mid - 1;
+  int started = 0;  // owners whose first candidate lies before the current batch
+  for (int cb = 0; cb < total; cb += 32) {
+    const uint32_t rel = (uint32_t)(off - cb);  // wraps for offsets below cb
+    const uint32_t starts = __reduce_or_sync(0xffffffffu, (cand && rel < 32u) ? 1u << rel : 0u);
+    const int c = cb + lane;
+    if (c < total) {
+      uint32_t* ow = sw + (started + __popc(starts & (0xFFFFFFFFu >> (31 - lane))) - 1) * PP_CULL_WORDS;
+      const int k = c - (int)ow[0];
+      const int ww = (int)ow[10];
+      const int row = __float2int_rd(((float)k + 0.5f) * __uint_as_float(ow[11]));  // exact for k, ww <= 64
+      const int col = k - row * ww;
+      GsCull cs;
+      cs.hA = __uint_as_float(ow[3]);
+      cs.B = __uint_as_float(ow[4]);
+      cs.hC = __uint_as_float(ow[5]);
+      cs.rA = __uint_as_float(ow[6]);
+      cs.rC = __uint_as_float(ow[7]);
+      cs.thr = __uint_as_float(ow[8]);
+      const int tx = (int)(ow[9] & 0xFFFFu) + col, ty = (int)(ow[9] >> 16) + row;
+      if (gs_tile_alive(cs, __uint_as_float(ow[1]), __uint_as_float(ow[2]), tx, ty)) atomicOr(&ow[12 + (k >> 5)], 1u << (k & 31));
     }
-    uint32_t* ow = sw + lo * PP_CULL_WORDS;
-    const int k = c - (int)ow[0];
-    const int ww = (int)ow[10];
-    const int row = __float2int_rd(((float)k + 0.5f) * __uint_as_float(ow[11]));  // exact for k, ww <= 64
-    const int col = k - row * ww;
-    GsCull cs;
-    cs.hA = __uint_as_float(ow[3]);
-    cs.B = __uint_as_float(ow[4]);
-    cs.hC = __uint_as_float(ow[5]);
-    cs.rA = __uint_as_float(ow[6]);
-    cs.rC = __uint_as_float(ow[7]);
-    cs.thr = __uint_as_float(ow[8]);
-    const int tx = (int)(ow[9] & 0xFFFFu) + col, ty = (int)(ow[9] >> 16) + row;
-    if (gs_tile_alive(cs, __uint_as_float(ow[1]), __uint_as_float(ow[2]), tx, ty)) atomicOr(&ow[12 + (k >> 5)], 1u << (k & 31));
+    started += __popc(starts);
   }
   __syncwarp();
   if (cand) {
