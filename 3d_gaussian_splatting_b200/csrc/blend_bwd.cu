@@ -143,39 +143,41 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
       const float cb = s_b[j];
       float a_mx = 0.f, a_my = 0.f, a_A = 0.f, a_B = 0.f, a_C = 0.f, a_o = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f;
       bool any = false;
+      // Branch-free over the four pixels (a skipped pixel runs the same arithmetic with alpha = 0, G = 0, which leaves
+      // its state and every sum unchanged bit for bit): four independent dependency chains the scheduler can
+      // interleave, instead of eight divergent branches per entry.
 #pragma unroll
       for (int p = 0; p < 4; ++p) {
         const float dx = q0.x - pixx[p], dy = q0.y - pixy[p];
         const float power = gs_power(q0.z, q0.w, q1.x, dx, dy);
-        if (k < last[p] && !(power > 0.0f)) {
-          float G;
-          const float alpha = gs_alpha(q1.y, power, G);
-          if (!(alpha < GS_ALPHA_MIN)) {
-            any = true;
-            const float one_m = 1.0f - alpha;
-            const float Ti = T[p];
-            const float wgt = alpha * Ti;
-            C0[p] = fmaf(q1.z, wgt, C0[p]);   // same FMAs as the forward: prefix colour incl. this Gaussian
-            C1[p] = fmaf(q1.w, wgt, C1[p]);
-            C2[p] = fmaf(cb, wgt, C2[p]);
-            T[p] = Ti * one_m;
-            const float inv = __fdividef(1.0f, one_m);
-            a_r = fmaf(wgt, dL0[p], a_r);
-            a_g = fmaf(wgt, dL1[p], a_g);
-            a_b = fmaf(wgt, dL2[p], a_b);
-            float dL_dalpha = (q1.z * Ti - (O0[p] - C0[p]) * inv) * dL0[p];
-            dL_dalpha = fmaf(q1.w * Ti - (O1[p] - C1[p]) * inv, dL1[p], dL_dalpha);
-            dL_dalpha = fmaf(cb * Ti - (O2[p] - C2[p]) * inv, dL2[p], dL_dalpha);
-            a_o = fmaf(G, dL_dalpha, a_o);
-            const float wg = q1.y * dL_dalpha * G;  // dL/dG * G
-            const float wdx = wg * dx, wdy = wg * dy;
-            a_mx += wdx;               // sum w dx
-            a_my += wdy;               // sum w dy
-            a_A = fmaf(wdx, dx, a_A);  // sum w dx^2
-            a_B = fmaf(wdx, dy, a_B);  // sum w dx dy
-            a_C = fmaf(wdy, dy, a_C);  // sum w dy^2
-          }
-        }
+        float Gf;
+        const float af = gs_alpha(q1.y, power, Gf);
+        const bool valid = k < last[p] && !(power > 0.0f) && !(af < GS_ALPHA_MIN);
+        any |= valid;
+        const float alpha = valid ? af : 0.0f;
+        const float G = valid ? Gf : 0.0f;
+        const float one_m = 1.0f - alpha;
+        const float Ti = T[p];
+        const float wgt = alpha * Ti;
+        C0[p] = fmaf(q1.z, wgt, C0[p]);   // same FMAs as the forward: prefix colour incl. this Gaussian
+        C1[p] = fmaf(q1.w, wgt, C1[p]);
+        C2[p] = fmaf(cb, wgt, C2[p]);
+        T[p] = Ti * one_m;
+        const float inv = __fdividef(1.0f, one_m);
+        a_r = fmaf(wgt, dL0[p], a_r);
+        a_g = fmaf(wgt, dL1[p], a_g);
+        a_b = fmaf(wgt, dL2[p], a_b);
+        float dL_dalpha = (q1.z * Ti - (O0[p] - C0[p]) * inv) * dL0[p];
+        dL_dalpha = fmaf(q1.w * Ti - (O1[p] - C1[p]) * inv, dL1[p], dL_dalpha);
+        dL_dalpha = fmaf(cb * Ti - (O2[p] - C2[p]) * inv, dL2[p], dL_dalpha);
+        a_o = fmaf(G, dL_dalpha, a_o);
+        const float wg = q1.y * dL_dalpha * G;  // dL/dG * G
+        const float wdx = wg * dx, wdy = wg * dy;
+        a_mx += wdx;               // sum w dx
+        a_my += wdy;               // sum w dy
+        a_A = fmaf(wdx, dx, a_A);  // sum w dx^2
+        a_B = fmaf(wdx, dy, a_B);  // sum w dx dy
+        a_C = fmaf(wdy, dy, a_C);  // sum w dy^2
       }
       if (__ballot_sync(0xffffffffu, any) == 0u) continue;
       // moments -> gradient components (A = 2*hA, C = 2*hC)

@@ -16,9 +16,14 @@
 //   * the work items (tile, segment) for segment < ceil(max_pixel(n_contrib) / GS_SEG).
 // Skip decisions (power > 0, alpha < 1/255) use the specified numerics in gs_common.cuh and are
 // bit-identical to the oracle's; colour accumulation uses FMAs (smooth differences only).
+#include <stdlib.h>
+
 #include "gs_common.cuh"
 
-#define BF_THREADS 256
+// A tile is 8 boxes of 8x4 pixels, one warp each.  The warps are autonomous, so a block is only a scheduling unit:
+// BF_WARPS boxes of one tile per block (small blocks free their registers and shared memory as soon as their boxes
+// have terminated instead of waiting for the slowest box of the tile).
+#define BF_WARPS_DEFAULT 1
 
 // 48-byte record, global -> shared, asynchronously and without staging registers (LDGSTS); .ca keeps the line in L1
 // for the other seven warps of the tile
@@ -31,20 +36,22 @@ __device__ __forceinline__ void bf_copy_record(GsGeom* dst, const GsGeom* src) {
 __device__ __forceinline__ void bf_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bf_wait_1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
-__global__ void __launch_bounds__(BF_THREADS, 4)
+template <int BF_WARPS>
+__global__ void __launch_bounds__(32 * BF_WARPS, 32 / BF_WARPS)
 blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
                      const uint32_t* __restrict__ point_list, const GsGeom* __restrict__ geom, float bg0, float bg1,
                      float bg2, float* __restrict__ out_color, float4* __restrict__ final_state,
                      uint32_t* __restrict__ n_contrib, float4* __restrict__ ckpt, uint2* __restrict__ work_items,
-                     uint32_t* __restrict__ work_count, uint32_t* __restrict__ tile_last) {
+                     uint32_t* __restrict__ work_count, uint32_t* __restrict__ tile_last /* [ntiles] max, then [ntiles] arrivals; zeroed */) {
   // per-warp slices, double-buffered: the 32 records of the chunk the warp is walking and of the next one
-  __shared__ GsGeom s_g_all[BF_THREADS / 32][2][32];
-  __shared__ uint32_t s_wlast[BF_THREADS / 32];
+  constexpr int BF_BLOCKS_PER_TILE = 8 / BF_WARPS;
+  __shared__ GsGeom s_g_all[BF_WARPS][2][32];
 
-  const int tile = (int)tile_order[blockIdx.x];
+  const int tile = (int)tile_order[blockIdx.x / BF_BLOCKS_PER_TILE];
   const int tx = tile % d.gx, ty = tile / d.gx;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int lx = (warp & 1) * 8 + (lane & 7), ly = (warp >> 1) * 4 + (lane >> 3);
+  const int box = (int)(blockIdx.x % BF_BLOCKS_PER_TILE) * BF_WARPS + warp;  // 0..7: column box & 1, row box >> 1
+  const int lx = (box & 1) * 8 + (lane & 7), ly = (box >> 1) * 4 + (lane >> 3);
   const int px = tx * GS_TILE + lx, py = ty * GS_TILE + ly;
   const bool inside = px < d.W && py < d.H;
   const float pixx = (float)px, pixy = (float)py;
@@ -53,7 +60,7 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
   const int total = (int)(range.y - range.x);
   float4* my_ckpt = ckpt + ((size_t)(range.x >> GS_SEG_SHIFT) + (size_t)tile) * GS_TILE_PIX + (ly * GS_TILE + lx);
   // the warp's 8x4 box of pixel centres
-  const float bx = (float)(tx * GS_TILE + (warp & 1) * 8), by = (float)(ty * GS_TILE + (warp >> 1) * 4);
+  const float bx = (float)(tx * GS_TILE + (box & 1) * 8), by = (float)(ty * GS_TILE + (box >> 1) * 4);
   const uint32_t* plist = point_list + range.x + lane;
 
   bool done = !inside;
@@ -152,23 +159,31 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
     out_color[plane + pix] = fmaf(T, bg1, C1);
     out_color[2 * plane + pix] = fmaf(T, bg2, C2);
   }
-  // ---- work items of the segmented backward: (tile, s) for s < ceil(tile_last / GS_SEG) ----
+  // ---- work items of the segmented backward: (tile, s) for s < ceil(tile_last / GS_SEG), written by the last of
+  //      the tile's eight boxes to arrive (tile_last is a running maximum, the second half of the array counts
+  //      arrivals; both are zeroed before the launch) ----
   uint32_t wl = last_contributor;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) wl = max(wl, __shfl_xor_sync(0xffffffffu, wl, o));
-  if (lane == 0) s_wlast[warp] = wl;
-  __syncthreads();
-  if (warp == 0) {
-    uint32_t tl = lane < BF_THREADS / 32 ? s_wlast[lane] : 0u;
-#pragma unroll
-    for (int o = 4; o > 0; o >>= 1) tl = max(tl, __shfl_xor_sync(0xffffffffu, tl, o));
+  uint32_t arrived = 0;
+  if (lane == 0) {
+    if (wl > 0) atomicMax(tile_last + tile, wl);
+    __threadfence();
+    arrived = atomicAdd(tile_last + d.ntiles + tile, 1u);
+  }
+  arrived = __shfl_sync(0xffffffffu, arrived, 0);
+  if (arrived == 7u) {
+    uint32_t tl = 0;
+    if (lane == 0) {
+      __threadfence();
+      tl = atomicMax(tile_last + tile, 0u);
+    }
     tl = __shfl_sync(0xffffffffu, tl, 0);
     const uint32_t nseg = (tl + GS_SEG - 1) >> GS_SEG_SHIFT;
     uint32_t pos = 0;
     if (lane == 0 && nseg > 0) pos = atomicAdd(work_count, nseg);
     pos = __shfl_sync(0xffffffffu, pos, 0);
     for (uint32_t s = lane; s < nseg; s += 32) work_items[pos + s] = make_uint2((uint32_t)tile, s);
-    if (lane == 0) tile_last[tile] = tl;
   }
 }
 
@@ -178,8 +193,24 @@ cudaError_t gs_launch_blend_forward(const GsDims& d, const uint32_t* tile_order,
                                     uint2* work_items, uint32_t* work_count, uint32_t* tile_last,
                                     cudaStream_t stream) {
   if (d.ntiles == 0) return cudaSuccess;
-  blend_forward_kernel<<<d.ntiles, BF_THREADS, 0, stream>>>(d, tile_order, ranges, point_list, geom, bg[0], bg[1],
-                                                           bg[2], out_color, final_state, n_contrib, ckpt, work_items,
-                                                           work_count, tile_last);
+  cudaError_t e = cudaMemsetAsync(tile_last, 0, (size_t)d.ntiles * 8, stream);
+  if (e != cudaSuccess) return e;
+  static int warps = 0;
+  if (warps == 0) {
+    const char* env = getenv("GS_BF_WARPS");  // tuning switch: boxes of a tile per block (1, 2, 4 or 8)
+    warps = env ? atoi(env) : BF_WARPS_DEFAULT;
+    if (warps != 1 && warps != 2 && warps != 4 && warps != 8) warps = BF_WARPS_DEFAULT;
+  }
+#define BF_LAUNCH(WARPS)                                                                                              \
+  blend_forward_kernel<WARPS><<<d.ntiles * (8 / WARPS), 32 * WARPS, 0, stream>>>(                                     \
+      d, tile_order, ranges, point_list, geom, bg[0], bg[1], bg[2], out_color, final_state, n_contrib, ckpt, work_items, \
+      work_count, tile_last)
+  switch (warps) {
+    case 1: BF_LAUNCH(1); break;
+    case 2: BF_LAUNCH(2); break;
+    case 4: BF_LAUNCH(4); break;
+    default: BF_LAUNCH(8); break;
+  }
+#undef BF_LAUNCH
   return cudaGetLastError();
 }

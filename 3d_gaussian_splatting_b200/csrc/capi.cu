@@ -354,7 +354,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->ranges, (size_t)d.ntiles * sizeof(uint2));
   GS_ENSURE(c, c->final_state, P * 16);
   GS_ENSURE(c, c->tile_order, (size_t)d.ntiles * 4);
-  GS_ENSURE(c, c->tile_last, (size_t)d.ntiles * 4);
+  GS_ENSURE(c, c->tile_last, (size_t)d.ntiles * 8);  // running maximum + arrival counter per tile
   GS_ENSURE(c, c->counters, 64);
   GS_ENSURE(c, c->n_contrib, P * 4);
   // device counters: [0] backward work items, [1] backward cursor, bytes 8..15 D (u64), [4] D (u32, clamped to the
