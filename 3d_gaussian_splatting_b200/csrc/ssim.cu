@@ -59,12 +59,28 @@ ssim_forward_kernel(int H, int W, const float* __restrict__ img, const float* __
   const float* xp = img + blockIdx.z * plane;
   const float* yp = gt + blockIdx.z * plane;
 
-  for (int k = tid; k < SS_HY * SS_HX; k += SS_THREADS) {
-    const int r = k / SS_HX, c = k - r * SS_HX;
-    const int gy = y0 + r - SS_R, gx = x0 + c - SS_R;
-    const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
-    s_x[r][c] = in ? __ldg(xp + (size_t)gy * W + gx) : 0.f;
-    s_y[r][c] = in ? __ldg(yp + (size_t)gy * W + gx) : 0.f;
+  // halo staging: all loads of a thread are issued before the first store (one memory latency per block, not nine)
+  constexpr int SS_STAGE = (SS_HY * SS_HX + SS_THREADS - 1) / SS_THREADS;
+  {
+    float vx[SS_STAGE], vy[SS_STAGE];
+#pragma unroll
+    for (int i = 0; i < SS_STAGE; ++i) {
+      const int k = tid + i * SS_THREADS;
+      const int r = k / SS_HX, c = k - r * SS_HX;
+      const int gy = y0 + r - SS_R, gx = x0 + c - SS_R;
+      const bool in = k < SS_HY * SS_HX && gy >= 0 && gy < H && gx >= 0 && gx < W;
+      vx[i] = in ? __ldg(xp + (size_t)gy * W + gx) : 0.f;
+      vy[i] = in ? __ldg(yp + (size_t)gy * W + gx) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < SS_STAGE; ++i) {
+      const int k = tid + i * SS_THREADS;
+      const int r = k / SS_HX, c = k - r * SS_HX;
+      if (k < SS_HY * SS_HX) {
+        s_x[r][c] = vx[i];
+        s_y[r][c] = vy[i];
+      }
+    }
   }
   __syncthreads();
   // rows: 26 rows x 8 groups of 4 adjacent outputs; the 14 staged values (and their products) are reused by the 4
@@ -157,14 +173,30 @@ ssim_backward_kernel(int H, int W, const float* __restrict__ img, const float* _
   const int tid = threadIdx.x;
   const int x0 = blockIdx.x * SS_TX, y0 = blockIdx.y * SS_TY;
   const size_t plane = (size_t)H * W, base = blockIdx.z * plane;
-  for (int k = tid; k < SS_HY * SS_HX; k += SS_THREADS) {
-    const int r = k / SS_HX, c = k - r * SS_HX;
-    const int gy = y0 + r - SS_R, gx = x0 + c - SS_R;
-    const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
-    const size_t o = base + (size_t)gy * W + gx;
-    s_in[0][r][c] = in ? __ldg(dmu + o) : 0.f;
-    s_in[1][r][c] = in ? __ldg(de11 + o) : 0.f;
-    s_in[2][r][c] = in ? __ldg(de12 + o) : 0.f;
+  constexpr int SS_STAGE = (SS_HY * SS_HX + SS_THREADS - 1) / SS_THREADS;
+  {
+    float v0[SS_STAGE], v1[SS_STAGE], v2[SS_STAGE];
+#pragma unroll
+    for (int i = 0; i < SS_STAGE; ++i) {
+      const int k = tid + i * SS_THREADS;
+      const int r = k / SS_HX, c = k - r * SS_HX;
+      const int gy = y0 + r - SS_R, gx = x0 + c - SS_R;
+      const bool in = k < SS_HY * SS_HX && gy >= 0 && gy < H && gx >= 0 && gx < W;
+      const size_t o = base + (size_t)gy * W + gx;
+      v0[i] = in ? __ldg(dmu + o) : 0.f;
+      v1[i] = in ? __ldg(de11 + o) : 0.f;
+      v2[i] = in ? __ldg(de12 + o) : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < SS_STAGE; ++i) {
+      const int k = tid + i * SS_THREADS;
+      const int r = k / SS_HX, c = k - r * SS_HX;
+      if (k < SS_HY * SS_HX) {
+        s_in[0][r][c] = v0[i];
+        s_in[1][r][c] = v1[i];
+        s_in[2][r][c] = v2[i];
+      }
+    }
   }
   __syncthreads();
   for (int k = tid; k < SS_HY * (SS_TX / SS_V); k += SS_THREADS) {
