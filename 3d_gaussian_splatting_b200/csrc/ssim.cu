@@ -14,11 +14,11 @@
 #include "gs_common.cuh"
 
 #define SS_TX 32
-#define SS_TY 16
+#define SS_TY 32
 #define SS_R 5
 #define SS_HX (SS_TX + 2 * SS_R)  // 42
 #define SS_HY (SS_TY + 2 * SS_R)  // 26
-#define SS_THREADS 128            // every thread produces 4 outputs of each pass (register-blocked window)
+#define SS_THREADS 256            // every thread produces 4 outputs of each pass (register-blocked window)
 #define SS_V 4
 #define SS_PITCH (SS_HX + 1)      // 43: with 4-wide column groups the 32 lanes of a warp hit 32 different banks
 
