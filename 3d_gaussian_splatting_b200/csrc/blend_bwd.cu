@@ -99,6 +99,25 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
     for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(0xffffffffu, warp_last, o));
     const int jend = min(n, warp_last - k0);  // this warp only needs entries k < warp_last
     if (jend <= 0) continue;
+    // the state of the two x-adjacent pixels of each quad row as packed pairs (FFMA2 / FMUL2 / FADD2 inner loop)
+    gs_f2 npx2[2], npy2[2], T2[2], C0_2[2], C1_2[2], C2_2[2], O0_2[2], O1_2[2], O2_2[2], dL0_2[2], dL1_2[2], dL2_2[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      npx2[h] = gs_f2_pack(-pixx[2 * h], -pixx[2 * h + 1]);
+      npy2[h] = gs_f2_pack(-pixy[2 * h], -pixy[2 * h + 1]);
+      T2[h] = gs_f2_pack(T[2 * h], T[2 * h + 1]);
+      C0_2[h] = gs_f2_pack(C0[2 * h], C0[2 * h + 1]);
+      C1_2[h] = gs_f2_pack(C1[2 * h], C1[2 * h + 1]);
+      C2_2[h] = gs_f2_pack(C2[2 * h], C2[2 * h + 1]);
+      O0_2[h] = gs_f2_pack(O0[2 * h], O0[2 * h + 1]);
+      O1_2[h] = gs_f2_pack(O1[2 * h], O1[2 * h + 1]);
+      O2_2[h] = gs_f2_pack(O2[2 * h], O2[2 * h + 1]);
+      dL0_2[h] = gs_f2_pack(dL0[2 * h], dL0[2 * h + 1]);
+      dL1_2[h] = gs_f2_pack(dL1[2 * h], dL1[2 * h + 1]);
+      dL2_2[h] = gs_f2_pack(dL2[2 * h], dL2[2 * h + 1]);
+    }
+    const gs_f2 kNeg1 = gs_f2_pack(-1.0f, -1.0f), kOne = gs_f2_pack(1.0f, 1.0f);
+    const gs_f2 kNegLog2e = gs_f2_pack(-1.44269504088896340736f, -1.44269504088896340736f);
 
     // gather the records this warp needs (coalesced ids, L2-resident 48-B records); the loading lane also decides
     // whether its entry can reach alpha >= 1/255 anywhere in the warp's 16x8 pixel box (gs_box_alive, the
@@ -141,45 +160,84 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
       const float4 q0 = s_q0[j];
       const float4 q1 = s_q1[j];
       const float cb = s_b[j];
-      float a_mx = 0.f, a_my = 0.f, a_A = 0.f, a_B = 0.f, a_C = 0.f, a_o = 0.f, a_r = 0.f, a_g = 0.f, a_b = 0.f;
       bool any = false;
-      // Branch-free over the four pixels (a skipped pixel runs the same arithmetic with alpha = 0, G = 0, which leaves
-      // its state and every sum unchanged bit for bit): four independent dependency chains the scheduler can
-      // interleave, instead of eight divergent branches per entry.
+      // Branch-free and packed: the two x-adjacent pixels of a quad row share every FFMA2 / FMUL2 / FADD2 (each half
+      // is the scalar IEEE operation, so T and the prefix colour stay the forward's bits); a skipped pixel runs the
+      // same arithmetic with alpha = 0, G = 0, which leaves its state and every sum unchanged.
+      const gs_f2 mx2 = gs_f2_pack(q0.x, q0.x), my2 = gs_f2_pack(q0.y, q0.y);
+      const gs_f2 hA2 = gs_f2_pack(q0.z, q0.z), B2 = gs_f2_pack(q0.w, q0.w), hC2 = gs_f2_pack(q1.x, q1.x);
+      const gs_f2 op2 = gs_f2_pack(q1.y, q1.y);
+      const gs_f2 cr2 = gs_f2_pack(q1.z, q1.z), cg2 = gs_f2_pack(q1.w, q1.w), cb2 = gs_f2_pack(cb, cb);
+      gs_f2 s_mx, s_my, s_A, s_B, s_C, s_o, s_r, s_g, s_b2;  // initialised by the first pair (h == 0)
 #pragma unroll
-      for (int p = 0; p < 4; ++p) {
-        const float dx = q0.x - pixx[p], dy = q0.y - pixy[p];
-        const float power = gs_power(q0.z, q0.w, q1.x, dx, dy);
-        float Gf;
-        const float af = gs_alpha(q1.y, power, Gf);
-        const bool valid = k < last[p] && !(power > 0.0f) && !(af < GS_ALPHA_MIN);
-        any |= valid;
-        const float alpha = valid ? af : 0.0f;
-        const float G = valid ? Gf : 0.0f;
-        const float one_m = 1.0f - alpha;
-        const float Ti = T[p];
-        const float wgt = alpha * Ti;
-        C0[p] = fmaf(q1.z, wgt, C0[p]);   // same FMAs as the forward: prefix colour incl. this Gaussian
-        C1[p] = fmaf(q1.w, wgt, C1[p]);
-        C2[p] = fmaf(cb, wgt, C2[p]);
-        T[p] = Ti * one_m;
-        const float inv = __fdividef(1.0f, one_m);
-        a_r = fmaf(wgt, dL0[p], a_r);
-        a_g = fmaf(wgt, dL1[p], a_g);
-        a_b = fmaf(wgt, dL2[p], a_b);
-        float dL_dalpha = (q1.z * Ti - (O0[p] - C0[p]) * inv) * dL0[p];
-        dL_dalpha = fmaf(q1.w * Ti - (O1[p] - C1[p]) * inv, dL1[p], dL_dalpha);
-        dL_dalpha = fmaf(cb * Ti - (O2[p] - C2[p]) * inv, dL2[p], dL_dalpha);
-        a_o = fmaf(G, dL_dalpha, a_o);
-        const float wg = q1.y * dL_dalpha * G;  // dL/dG * G
-        const float wdx = wg * dx, wdy = wg * dy;
-        a_mx += wdx;               // sum w dx
-        a_my += wdy;               // sum w dy
-        a_A = fmaf(wdx, dx, a_A);  // sum w dx^2
-        a_B = fmaf(wdx, dy, a_B);  // sum w dx dy
-        a_C = fmaf(wdy, dy, a_C);  // sum w dy^2
+      for (int h = 0; h < 2; ++h) {
+        const gs_f2 dx2 = gs_f2_add(mx2, npx2[h]), dy2 = gs_f2_add(my2, npy2[h]);
+        // gs_power: q = fma(dx, fma(hA, dx, B * dy), (hC * dy) * dy), power = -q
+        const gs_f2 u2 = gs_f2_fma(hA2, dx2, gs_f2_mul(B2, dy2));
+        const gs_f2 qq2 = gs_f2_fma(dx2, u2, gs_f2_mul(gs_f2_mul(hC2, dy2), dy2));
+        const gs_f2 t2 = gs_f2_mul(qq2, kNegLog2e);  // power * log2(e): (-q) * c and q * (-c) are the same bits
+        float qq[2], tt[2], al[2], Gm[2];
+        gs_f2_unpack(qq2, qq[0], qq[1]);
+        gs_f2_unpack(t2, tt[0], tt[1]);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          float G;
+          asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(tt[e]));
+          float a = q1.y * G;
+          if (fabsf(a - GS_ALPHA_MIN) < 8e-8f) {  // guard band of gs_alpha: the skip decision is the oracle's
+            G = gs_exp_ref(-qq[e]);
+            a = __fmul_rn(q1.y, G);
+          }
+          a = fminf(GS_ALPHA_MAX, a);
+          const bool valid = k < last[2 * h + e] && !(qq[e] < 0.0f) && !(a < GS_ALPHA_MIN);  // power > 0 <=> q < 0
+          any |= valid;
+          al[e] = valid ? a : 0.0f;
+          Gm[e] = valid ? G : 0.0f;
+        }
+        const gs_f2 alpha2 = gs_f2_pack(al[0], al[1]), G2 = gs_f2_pack(Gm[0], Gm[1]);
+        const gs_f2 one_m2 = gs_f2_fma(alpha2, kNeg1, kOne);  // 1 - alpha, one rounding
+        const gs_f2 Ti2 = T2[h];
+        const gs_f2 wgt2 = gs_f2_mul(alpha2, Ti2);
+        C0_2[h] = gs_f2_fma(cr2, wgt2, C0_2[h]);  // same FMAs as the forward: prefix colour incl. this Gaussian
+        C1_2[h] = gs_f2_fma(cg2, wgt2, C1_2[h]);
+        C2_2[h] = gs_f2_fma(cb2, wgt2, C2_2[h]);
+        T2[h] = gs_f2_mul(Ti2, one_m2);
+        float om[2];
+        gs_f2_unpack(one_m2, om[0], om[1]);
+        const gs_f2 inv2 = gs_f2_pack(__fdividef(1.0f, om[0]), __fdividef(1.0f, om[1]));
+        s_r = h == 0 ? gs_f2_mul(wgt2, dL0_2[h]) : gs_f2_fma(wgt2, dL0_2[h], s_r);
+        s_g = h == 0 ? gs_f2_mul(wgt2, dL1_2[h]) : gs_f2_fma(wgt2, dL1_2[h], s_g);
+        s_b2 = h == 0 ? gs_f2_mul(wgt2, dL2_2[h]) : gs_f2_fma(wgt2, dL2_2[h], s_b2);
+        // dL/dalpha = sum_ch (c_ch * Ti - (O_ch - C_ch) / (1 - alpha)) * dL_ch
+        gs_f2 f0 = gs_f2_fma(gs_f2_mul(gs_f2_fma(C0_2[h], kNeg1, O0_2[h]), inv2), kNeg1, gs_f2_mul(cr2, Ti2));
+        gs_f2 f1 = gs_f2_fma(gs_f2_mul(gs_f2_fma(C1_2[h], kNeg1, O1_2[h]), inv2), kNeg1, gs_f2_mul(cg2, Ti2));
+        gs_f2 f2 = gs_f2_fma(gs_f2_mul(gs_f2_fma(C2_2[h], kNeg1, O2_2[h]), inv2), kNeg1, gs_f2_mul(cb2, Ti2));
+        gs_f2 dLa2 = gs_f2_mul(f0, dL0_2[h]);
+        dLa2 = gs_f2_fma(f1, dL1_2[h], dLa2);
+        dLa2 = gs_f2_fma(f2, dL2_2[h], dLa2);
+        s_o = h == 0 ? gs_f2_mul(G2, dLa2) : gs_f2_fma(G2, dLa2, s_o);
+        const gs_f2 wg2 = gs_f2_mul(gs_f2_mul(op2, dLa2), G2);  // dL/dG * G
+        const gs_f2 wdx2 = gs_f2_mul(wg2, dx2), wdy2 = gs_f2_mul(wg2, dy2);
+        s_mx = h == 0 ? wdx2 : gs_f2_add(s_mx, wdx2);                              // sum w dx
+        s_my = h == 0 ? wdy2 : gs_f2_add(s_my, wdy2);                              // sum w dy
+        s_A = h == 0 ? gs_f2_mul(wdx2, dx2) : gs_f2_fma(wdx2, dx2, s_A);           // sum w dx^2
+        s_B = h == 0 ? gs_f2_mul(wdx2, dy2) : gs_f2_fma(wdx2, dy2, s_B);           // sum w dx dy
+        s_C = h == 0 ? gs_f2_mul(wdy2, dy2) : gs_f2_fma(wdy2, dy2, s_C);           // sum w dy^2
       }
       if (__ballot_sync(0xffffffffu, any) == 0u) continue;
+      float a_mx, a_my, a_A, a_B, a_C, a_o, a_r, a_g, a_b;
+      {
+        float lo, hi;
+        gs_f2_unpack(s_mx, lo, hi); a_mx = lo + hi;
+        gs_f2_unpack(s_my, lo, hi); a_my = lo + hi;
+        gs_f2_unpack(s_A, lo, hi); a_A = lo + hi;
+        gs_f2_unpack(s_B, lo, hi); a_B = lo + hi;
+        gs_f2_unpack(s_C, lo, hi); a_C = lo + hi;
+        gs_f2_unpack(s_o, lo, hi); a_o = lo + hi;
+        gs_f2_unpack(s_r, lo, hi); a_r = lo + hi;
+        gs_f2_unpack(s_g, lo, hi); a_g = lo + hi;
+        gs_f2_unpack(s_b2, lo, hi); a_b = lo + hi;
+      }
       // moments -> gradient components (A = 2*hA, C = 2*hC)
       const float A = 2.0f * q0.z, B = q0.w, C = 2.0f * q1.x;
       float v[8];
@@ -237,7 +295,7 @@ cudaError_t gs_launch_blend_backward(const GsDims& d, const uint2* ranges, const
   if (d.ntiles == 0) return cudaSuccess;
   cudaError_t e = cudaMemsetAsync(work_cursor, 0, sizeof(uint32_t), stream);
   if (e != cudaSuccess) return e;
-  const int blocks = num_sms * 10;  // persistent: 95 regs x 64 threads -> 10 blocks per SM
+  const int blocks = num_sms * 10;  // persistent: 96 regs x 64 threads -> 10 blocks per SM
   blend_backward_kernel<<<blocks, BB_THREADS, 0, stream>>>(d, ranges, point_list, geom, bg[0], bg[1], bg[2],
                                                           final_state, n_contrib,
                                                           dL_dpixels, ckpt, work_items, work_count, work_cursor,
