@@ -8,8 +8,9 @@
 // arithmetic (so T and the prefix colour C are the forward's bits), and gets the colour behind the
 // current Gaussian from the final pixel colour:  Cb = out - C_prefix_after  (includes bg * T_final).
 //     dL/dalpha_i = sum_ch dL/dC_ch * (c_ch * T_i - Cb_ch / (1 - alpha_i))
-// Persistent warps pull work items (a 16x8 half of a tile x one segment) from an atomic cursor; every thread owns
-// a 2x2 pixel quad, so a segment needs only two cross-lane reductions per Gaussian: per-thread partial sums of
+// Persistent warps pull work items (a 16x4 pixel box of a tile x one segment) from an atomic cursor; every thread owns
+// two x-adjacent pixels (BB_QR = 1; 2x2 quads and 16x8 boxes with BB_QR = 2: 96 registers and 20 warps/SM against 61
+// and 32, measured 0.328 against 0.302 ms), so a segment needs four cross-lane reductions per Gaussian: per-thread partial sums of
 // the 9 gradient components are reduced with a halving butterfly (8 values in 4+2+1+1+1 shuffles,
 // the 9th in 5) and leave the SM as ONE predicated red.global.add.f32 (9 lanes, 9 consecutive floats).
 //
@@ -22,12 +23,20 @@
 #define BB_THREADS 64
 #define BB_WARPS (BB_THREADS / 32)
 #define BB_PER_LANE (GS_SEG / 32)
+// pixel rows per lane: a lane owns BB_QR rows of two x-adjacent pixels, a warp a 16 x (4 BB_QR) box, a tile has
+// BB_PARTS such boxes
+#ifndef BB_QR
+#define BB_QR 1
+#endif
+#define BB_NP (2 * BB_QR)
+#define BB_PARTS (4 / BB_QR)
+#define BB_BLOCKS_PER_SM (BB_QR == 1 ? 16 : 10)
 
-// Every WARP is autonomous: it pulls its own work item -- (tile, segment, upper or lower 16x8 half of the tile) --
+// Every WARP is autonomous: it pulls its own work item -- (tile, segment, one of the tile's BB_PARTS pixel boxes) --
 // stages the segment's records into its own shared-memory slice and never meets a block barrier.  (The first
 // version paired the two halves of a tile in one 64-thread block: 17% of its issue slots were spent at the barrier
 // waiting for the slower half, profiles/r01k.)
-__global__ void __launch_bounds__(BB_THREADS, 10)
+__global__ void __launch_bounds__(BB_THREADS, BB_BLOCKS_PER_SM)
 blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                       const GsGeom* __restrict__ geom, float bg0, float bg1, float bg2,
                       const float4* __restrict__ final_state, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpixels,
@@ -46,31 +55,32 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
   uint32_t* const s_id = s_id_all[wib];
   const size_t plane = (size_t)d.H * d.W;
   const float ddelx_dx = 0.5f * (float)d.W, ddely_dy = 0.5f * (float)d.H;
-  const uint32_t nwork = 2u * *work_count;  // two halves per (tile, segment)
+  const uint32_t nwork = (uint32_t)BB_PARTS * *work_count;  // BB_PARTS boxes per (tile, segment)
 
   for (;;) {
     uint32_t w = 0;
     if (lane == 0) w = atomicAdd(work_cursor, 1u);
     w = __shfl_sync(0xffffffffu, w, 0);
     if (w >= nwork) break;
-    const uint2 item = work_items[w >> 1];
-    const int half = (int)(w & 1u);
+    const uint2 item = work_items[w / BB_PARTS];
+    const int part = (int)(w % BB_PARTS);
     const int tile = (int)item.x;
     const int seg = (int)item.y;
     const int k0 = seg << GS_SEG_SHIFT;                                  // first list entry of the segment
     const int n = min(GS_SEG, (int)tile_last[tile] - k0);                // entries in it
     const uint2 range = ranges[tile];
     const int tx = tile % d.gx, ty = tile / d.gx;
-    const int qx = 2 * (lane & 7), qy = 2 * (lane >> 3) + 8 * half;
+    const int qx = 2 * (lane & 7), qy = BB_QR * (lane >> 3) + 4 * BB_QR * part;
     const int x0 = tx * GS_TILE + qx, y0 = ty * GS_TILE + qy;
 
     // per-pixel state
-    float pixx[4], pixy[4], T[4], C0[4], C1[4], C2[4], O0[4], O1[4], O2[4], dL0[4], dL1[4], dL2[4];
-    int last[4];
+    float pixx[BB_NP], pixy[BB_NP], T[BB_NP], C0[BB_NP], C1[BB_NP], C2[BB_NP], O0[BB_NP], O1[BB_NP], O2[BB_NP], dL0[BB_NP], dL1[BB_NP],
+        dL2[BB_NP];
+    int last[BB_NP];
     const float4* ck = ckpt + ((size_t)(range.x >> GS_SEG_SHIFT) + (size_t)tile + (size_t)seg) * GS_TILE_PIX;
     int my_last = 0;
 #pragma unroll
-    for (int p = 0; p < 4; ++p) {
+    for (int p = 0; p < BB_NP; ++p) {
       const int px = x0 + (p & 1), py = y0 + (p >> 1);
       const bool inside = px < d.W && py < d.H;
       pixx[p] = (float)px;
@@ -100,9 +110,10 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
     const int jend = min(n, warp_last - k0);  // this warp only needs entries k < warp_last
     if (jend <= 0) continue;
     // the state of the two x-adjacent pixels of each quad row as packed pairs (FFMA2 / FMUL2 / FADD2 inner loop)
-    gs_f2 npx2[2], npy2[2], T2[2], C0_2[2], C1_2[2], C2_2[2], O0_2[2], O1_2[2], O2_2[2], dL0_2[2], dL1_2[2], dL2_2[2];
+    gs_f2 npx2[BB_QR], npy2[BB_QR], T2[BB_QR], C0_2[BB_QR], C1_2[BB_QR], C2_2[BB_QR], O0_2[BB_QR], O1_2[BB_QR], O2_2[BB_QR], dL0_2[BB_QR],
+        dL1_2[BB_QR], dL2_2[BB_QR];
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
+    for (int h = 0; h < BB_QR; ++h) {
       npx2[h] = gs_f2_pack(-pixx[2 * h], -pixx[2 * h + 1]);
       npy2[h] = gs_f2_pack(-pixy[2 * h], -pixy[2 * h + 1]);
       T2[h] = gs_f2_pack(T[2 * h], T[2 * h + 1]);
@@ -143,8 +154,8 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
         c.rA = __frcp_rn(2.0f * q0.z);
         c.rC = __frcp_rn(2.0f * q1.x);
         c.thr = q2.z;
-        const float bx = (float)(tx * GS_TILE), by = (float)(ty * GS_TILE + 8 * half);
-        alive = gs_box_alive(c, q0.x, q0.y, bx, bx + 15.0f, by, by + 7.0f);
+        const float bx = (float)(tx * GS_TILE), by = (float)(ty * GS_TILE + 4 * BB_QR * part);
+        alive = gs_box_alive(c, q0.x, q0.y, bx, bx + 15.0f, by, by + (float)(4 * BB_QR - 1));
       }
       words[u] = __ballot_sync(0xffffffffu, alive);
     }
@@ -170,7 +181,7 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
       const gs_f2 cr2 = gs_f2_pack(q1.z, q1.z), cg2 = gs_f2_pack(q1.w, q1.w), cb2 = gs_f2_pack(cb, cb);
       gs_f2 s_mx, s_my, s_A, s_B, s_C, s_o, s_r, s_g, s_b2;  // initialised by the first pair (h == 0)
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
+      for (int h = 0; h < BB_QR; ++h) {
         const gs_f2 dx2 = gs_f2_add(mx2, npx2[h]), dy2 = gs_f2_add(my2, npy2[h]);
         // gs_power: q = fma(dx, fma(hA, dx, B * dy), (hC * dy) * dy), power = -q
         const gs_f2 u2 = gs_f2_fma(hA2, dx2, gs_f2_mul(B2, dy2));
@@ -295,7 +306,7 @@ cudaError_t gs_launch_blend_backward(const GsDims& d, const uint2* ranges, const
   if (d.ntiles == 0) return cudaSuccess;
   cudaError_t e = cudaMemsetAsync(work_cursor, 0, sizeof(uint32_t), stream);
   if (e != cudaSuccess) return e;
-  const int blocks = num_sms * 10;  // persistent: 96 regs x 64 threads -> 10 blocks per SM
+  const int blocks = num_sms * BB_BLOCKS_PER_SM;  // persistent: 96 regs x 64 threads -> 10 blocks per SM
   blend_backward_kernel<<<blocks, BB_THREADS, 0, stream>>>(d, ranges, point_list, geom, bg[0], bg[1], bg[2],
                                                           final_state, n_contrib,
                                                           dL_dpixels, ckpt, work_items, work_count, work_cursor,
