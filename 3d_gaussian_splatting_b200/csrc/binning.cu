@@ -297,6 +297,9 @@ cudaError_t gs_launch_duplicate(int N, const uint32_t* order, const uint4* rects
   return cudaGetLastError();
 }
 
+#ifndef RS_TILE_SORT_ITEMS
+#define RS_TILE_SORT_ITEMS 8
+#endif
 // ---- 3. tile sort -------------------------------------------------------------------------------
 // Sorts the D pairs by tile id.  Buffers a = input; the result is in `a` after an even number of
 // passes and in `b` after an odd number (returned through *result_in_b).
@@ -309,11 +312,11 @@ cudaError_t gs_launch_tile_sort(const uint32_t* D_dev, int tile_bits, int key_by
     if (key_bytes == 2) {
       uint16_t* ki = (uint16_t*)(in_a ? keys_a : keys_b);
       uint16_t* ko = (uint16_t*)(in_a ? keys_b : keys_a);
-      radix_pass<uint16_t, 16>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
+      radix_pass<uint16_t, RS_TILE_SORT_ITEMS>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
     } else {
       uint32_t* ki = (uint32_t*)(in_a ? keys_a : keys_b);
       uint32_t* ko = (uint32_t*)(in_a ? keys_b : keys_a);
-      radix_pass<uint32_t, 16>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
+      radix_pass<uint32_t, RS_TILE_SORT_ITEMS>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
     }
     in_a = !in_a;
   }

@@ -210,6 +210,10 @@ int gs_create(gs_ctx** out, int device) {
   c->device = device;
   c->num_sms = prop.multiProcessorCount;
   c->radix_grid = 4 * c->num_sms < 608 ? 4 * c->num_sms : 608;  // RS_MAX_GRID
+  {
+    const char* env = getenv("GS_RADIX_GRID");  // tuning switch: persistent grid of the tile sort
+    if (env && atoi(env) >= 1 && atoi(env) <= 1024) c->radix_grid = atoi(env);
+  }
   if (cudaSetDevice(device) != cudaSuccess ||
       cudaHostAlloc((void**)&c->d_host_pinned, 64, cudaHostAllocMapped) != cudaSuccess ||
       cudaHostGetDevicePointer((void**)&c->d_host_mapped, c->d_host_pinned, 0) != cudaSuccess) {
