@@ -70,14 +70,14 @@ __device__ __forceinline__ uint32_t rect_alive(uint4 r) {
   return area > GS_CULL_MAX_TILES ? area : (uint32_t)(__popc(r.z) + __popc(r.w));
 }
 __global__ void __launch_bounds__(DUP_THREADS)
-dup_block_sums_kernel(int N, const uint32_t* __restrict__ order, const uint4* __restrict__ rects,
+dup_block_sums_kernel(int N, const uint32_t* __restrict__ order, const uint32_t* __restrict__ tiles_touched,
                       uint32_t* __restrict__ block_sums) {
   __shared__ uint32_t s_warp[DUP_THREADS / 32];
   uint32_t sum = 0;
 #pragma unroll
   for (int k = 0; k < DUP_ITEMS; ++k) {
     const int r = blockIdx.x * DUP_BLOCK + k * DUP_THREADS + threadIdx.x;
-    if (r < N) sum += rect_alive(__ldg(rects + order[r]));
+    if (r < N) sum += __ldg(tiles_touched + order[r]);  // = rect_alive(rects[.]): K1 wrote both; 4-B gathers, 6.4 MB array
   }
   uint32_t tot;
   block_exclusive_scan_256(sum, s_warp, tot);
@@ -272,13 +272,13 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
 
 int gs_dup_num_blocks(int N) { return (N + DUP_BLOCK - 1) / DUP_BLOCK; }
 
-cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint4* rects, uint32_t* block_sums,
+cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* block_sums,
                                unsigned long long* total, uint32_t* total32, unsigned long long cap,
                                uint32_t* overflow, float* guard, float* mirror, uint32_t* host_status,
                                cudaStream_t stream) {
   if (N == 0) return cudaMemsetAsync(total, 0, 8, stream);
   const int nb = gs_dup_num_blocks(N);
-  dup_block_sums_kernel<<<nb, DUP_THREADS, 0, stream>>>(N, order, rects, block_sums);
+  dup_block_sums_kernel<<<nb, DUP_THREADS, 0, stream>>>(N, order, tiles_touched, block_sums);
   dup_scan_sums_kernel<<<1, 1024, 0, stream>>>(nb, block_sums, total, total32, cap, overflow, guard, mirror, host_status);
   return cudaGetLastError();
 }

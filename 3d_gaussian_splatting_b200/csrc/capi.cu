@@ -18,7 +18,7 @@ cudaError_t gs_launch_preprocess(const gs_settings&, const gs_gaussians&, int, G
 cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, int,
                                  cudaStream_t);
 int gs_dup_num_blocks(int N);
-cudaError_t gs_launch_dup_scan(int, const uint32_t*, const uint4*, uint32_t*, unsigned long long*, uint32_t*,
+cudaError_t gs_launch_dup_scan(int, const uint32_t*, const uint32_t*, uint32_t*, unsigned long long*, uint32_t*,
                                unsigned long long, uint32_t*, float*, float*, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_duplicate(int, const uint32_t*, const uint4*, const uint32_t*, void*, int, uint32_t*, int,
                                 uint32_t, uint32_t*, cudaStream_t);
@@ -415,7 +415,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
       StageTimer t(c, 2, stream);
       const bool async_mode = c->dup_cap_fixed > 0;
       const unsigned long long cap = async_mode ? c->dup_cap_fixed : 0xFFFFFFF0ull;
-      GS_CUDA_CHECK(c, gs_launch_dup_scan(N, (const uint32_t*)c->sort_v1.ptr, (const uint4*)c->rects.ptr,
+      GS_CUDA_CHECK(c, gs_launch_dup_scan(N, (const uint32_t*)c->sort_v1.ptr, (const uint32_t*)c->tiles.ptr,
                                           (uint32_t*)c->dup_sums.ptr, D64_dev, D_dev, cap, overflow_dev, guard_dev,
                                           c->overflow_mirror, c->d_host_mapped, stream));
       if (async_mode) {
