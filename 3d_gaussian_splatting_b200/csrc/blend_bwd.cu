@@ -215,7 +215,10 @@ blend_backward_kernel(GsDims d, const uint2* __restrict__ ranges, const uint32_t
         T2[h] = gs_f2_mul(Ti2, one_m2);
         float om[2];
         gs_f2_unpack(one_m2, om[0], om[1]);
-        const gs_f2 inv2 = gs_f2_pack(__fdividef(1.0f, om[0]), __fdividef(1.0f, om[1]));
+        float iv[2];  // 1 / (1 - alpha), 1 - alpha in [0.01, 1]: one MUFU.RCP each (gradient value only, no decision)
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iv[0]) : "f"(om[0]));
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iv[1]) : "f"(om[1]));
+        const gs_f2 inv2 = gs_f2_pack(iv[0], iv[1]);
         s_r = h == 0 ? gs_f2_mul(wgt2, dL0_2[h]) : gs_f2_fma(wgt2, dL0_2[h], s_r);
         s_g = h == 0 ? gs_f2_mul(wgt2, dL1_2[h]) : gs_f2_fma(wgt2, dL1_2[h], s_g);
         s_b2 = h == 0 ? gs_f2_mul(wgt2, dL2_2[h]) : gs_f2_fma(wgt2, dL2_2[h], s_b2);
