@@ -45,7 +45,7 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
                      uint32_t* __restrict__ work_count, uint32_t* __restrict__ tile_last /* [ntiles] max, then [ntiles] arrivals; zeroed */) {
   // per-warp slices, double-buffered: the 32 records of the chunk the warp is walking and of the next one
   constexpr int BF_BLOCKS_PER_TILE = 8 / BF_WARPS;
-  __shared__ GsGeom s_g_all[BF_WARPS][2][32];
+  __shared__ GsGeom s_g_all[BF_WARPS][2][33];  // slot 32 of each buffer: the null record (opacity 0: never contributes)
 
   const int tile = (int)tile_order[blockIdx.x / BF_BLOCKS_PER_TILE];
   const int tx = tile % d.gx, ty = tile / d.gx;
@@ -63,6 +63,11 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
   const float bx = (float)(tx * GS_TILE + (box & 1) * 8), by = (float)(ty * GS_TILE + (box >> 1) * 4);
   const uint32_t* plist = point_list + range.x + lane;
 
+  if (lane < 2) {
+    GsGeom z;
+    z.q0 = z.q1 = z.q2 = make_float4(0.f, 0.f, 0.f, 0.f);
+    s_g_all[warp][lane][32] = z;
+  }
   bool done = !inside;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
   uint32_t last_contributor = 0;
@@ -109,25 +114,26 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
     }
     uint32_t word = __ballot_sync(0xffffffffu, alive);
     // ---- walk the alive entries in list order ----
+    int last_j = -1;  // last entry of this chunk that contributed to my pixel
     while (word) {
       // up to four alive entries at a time: their power / alpha are independent, only T is sequential
       int jj[4];
       float alpha[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        jj[u] = word ? __ffs(word) - 1 : -1;
+        jj[u] = word ? __ffs(word) - 1 : 32;  // 32: the null record (alpha = 0)
         word &= word - 1;
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const int j = max(jj[u], 0);
+        const int j = jj[u];
         const float4 q0 = s_g[j].q0;
         const float hC = s_g[j].q1.x, op = s_g[j].q1.y;
         const float dx = q0.x - pixx, dy = q0.y - pixy;
         const float power = gs_power(q0.z, q0.w, hC, dx, dy);
         float G;
         const float a = gs_alpha(op, power, G);
-        alpha[u] = (jj[u] >= 0 && !(power > 0.0f) && !(a < GS_ALPHA_MIN)) ? a : 0.0f;
+        alpha[u] = (!(power > 0.0f) && !(a < GS_ALPHA_MIN)) ? a : 0.0f;
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
@@ -142,12 +148,13 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
             C1 = fmaf(s_g[j].q1.w, w, C1);
             C2 = fmaf(s_g[j].q2.x, w, C2);
             T = test_T;
-            last_contributor = (uint32_t)(pos + j + 1);
+            last_j = j;
           }
         }
       }
       if (__all_sync(0xffffffffu, done)) break;
     }
+    if (last_j >= 0) last_contributor = (uint32_t)(pos + last_j + 1);
   }
   asm volatile("cp.async.wait_all;" ::: "memory");  // no copy may outlive the warp
   if (inside) {
