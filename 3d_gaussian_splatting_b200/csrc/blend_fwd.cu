@@ -137,20 +137,19 @@ blend_forward_kernel(GsDims d, const uint32_t* __restrict__ tile_order, const ui
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        if (alpha[u] != 0.0f && !done) {
-          const float test_T = T * (1.0f - alpha[u]);
-          if (test_T < GS_T_MIN) {
-            done = true;
-          } else {
-            const int j = jj[u];
-            const float w = alpha[u] * T;
-            C0 = fmaf(s_g[j].q1.z, w, C0);
-            C1 = fmaf(s_g[j].q1.w, w, C1);
-            C2 = fmaf(s_g[j].q2.x, w, C2);
-            T = test_T;
-            last_j = j;
-          }
-        }
+        // branch-free: an entry that does not contribute runs the same FMAs with weight 0 (state unchanged bit for bit)
+        const int j = jj[u];
+        const bool cand = alpha[u] != 0.0f && !done;
+        const float test_T = T * (1.0f - alpha[u]);
+        const bool term = cand && test_T < GS_T_MIN;
+        done |= term;
+        const bool app = cand && !term;
+        const float w = app ? alpha[u] * T : 0.0f;
+        C0 = fmaf(s_g[j].q1.z, w, C0);
+        C1 = fmaf(s_g[j].q1.w, w, C1);
+        C2 = fmaf(s_g[j].q2.x, w, C2);
+        T = app ? test_T : T;
+        last_j = app ? j : last_j;
       }
       if (__all_sync(0xffffffffu, done)) break;
     }
