@@ -253,9 +253,9 @@ def run_reference(args, rank, world):
 
 
 # ---- GPU arm -----------------------------------------------------------------------------------
-# preprocess, depth sort 4 x (hist, scan, scatter), dup block sums + scan + duplicate, tile sort 2 x 3, tile
+# depth keys, preprocess, depth sort 4 x (hist, scan, scatter), dup block sums + scan + duplicate, tile sort 2 x 3, tile
 # ranges, tile order, blend_forward, ssim forward + backward + finalize, blend_backward, preprocess_backward, adam_stats
-OWN_KERNELS_PER_STEP = 1 + 12 + 3 + 6 + 2 + 1 + 3 + 1 + 1 + 1   # separate K4b and K5; the fused single-GPU step: one less
+OWN_KERNELS_PER_STEP = 1 + 1 + 12 + 3 + 6 + 2 + 1 + 3 + 1 + 1 + 1   # separate K4b and K5; the fused single-GPU step: one less
 LAMBDA_DSSIM = 0.2   # lambda_dssim_ default (src/arguments/params.h:62)
 LOSS_NAME = "0.8*L1 + 0.2*(1-SSIM)"
 LIB_KERNELS_PER_STEP = 0   # no library kernels on the path (the radix sort and scans are this repo's own)
