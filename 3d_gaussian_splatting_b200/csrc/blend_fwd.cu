@@ -1,15 +1,13 @@
 // blend_fwd.cu — K3: forward alpha compositing.
 //
-// One 256-thread block per 16x16 tile (one pixel per thread: the per-tile critical path is the
-// number of list entries a pixel walks, so a tile gets the maximum parallelism); each warp owns an
-// 8x4 pixel sub-block.  Tiles are launched heaviest-first (tile_order, binning.cu) because per-tile
-// work is extremely skewed.  Gaussian records (48 B AoS) are gathered in sorted order 256 at a time
-// into shared memory and broadcast-read; entries are evaluated four at a time (power/alpha of four
-// entries are independent, only the short transmittance chain is sequential) so one warp keeps
-// several FMA/MUFU operations in flight.  The block stops once every pixel has terminated.
-// Warp-level culling: while staging, every loading thread tests its entry against the eight 8x4 pixel boxes
-// of the tile (the conservative alpha-reach test of the exact tile cull, gs_common.cuh) and the block
-// publishes one bit list per pixel warp; a warp then walks only the entries that can touch its box.
+// A 16x16 tile is eight 8x4-pixel boxes; ONE WARP owns a box (one pixel per lane) and walks the tile's list on its
+// own, 32 entries at a time, until its 32 pixels have terminated -- there is no block barrier (a block is only a
+// scheduling unit: BF_WARPS boxes of one tile, default one).  Tiles are launched heaviest-first (tile_order,
+// binning.cu) because per-tile work is extremely skewed.  The 48-B records of the next chunk travel global -> shared
+// as cp.async copies while the current chunk is walked.  Warp-level culling: the loading lane tests its entry against
+// the warp's box (the conservative alpha-reach test of the exact tile cull, gs_common.cuh); one ballot gives the
+// entries the warp walks.  Entries are evaluated four at a time (power / alpha of four entries are independent) and
+// the short transmittance chain behind them is branch-free.
 //
 // For the segmented backward (blend_bwd.cu) the kernel also leaves, per tile:
 //   * a checkpoint (T, C.rgb) of every live pixel at each GS_SEG-entry boundary of the tile list,
