@@ -305,10 +305,12 @@ cudaError_t gs_launch_blend_backward(const GsDims& d, const uint2* ranges, const
                                      const uint32_t* n_contrib,
                                      const float* dL_dpixels, const float4* ckpt, const uint2* work_items,
                                      const uint32_t* work_count, uint32_t* work_cursor, const uint32_t* tile_last,
-                                     float4* grad_geom, int num_sms, cudaStream_t stream) {
+                                     float4* grad_geom, int num_sms, bool cursor_zeroed, cudaStream_t stream) {
   if (d.ntiles == 0) return cudaSuccess;
-  cudaError_t e = cudaMemsetAsync(work_cursor, 0, sizeof(uint32_t), stream);
-  if (e != cudaSuccess) return e;
+  if (!cursor_zeroed) {  // (the forward's counter clear covers the first backward after it)
+    cudaError_t e = cudaMemsetAsync(work_cursor, 0, sizeof(uint32_t), stream);
+    if (e != cudaSuccess) return e;
+  }
   const int blocks = num_sms * BB_BLOCKS_PER_SM;  // persistent: 96 regs x 64 threads -> 10 blocks per SM
   blend_backward_kernel<<<blocks, BB_THREADS, 0, stream>>>(d, ranges, point_list, geom, bg[0], bg[1], bg[2],
                                                           final_state, n_contrib,

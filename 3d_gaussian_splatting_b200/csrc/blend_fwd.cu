@@ -195,10 +195,12 @@ cudaError_t gs_launch_blend_forward(const GsDims& d, const uint32_t* tile_order,
                                     const uint32_t* point_list, const GsGeom* geom, const float bg[3],
                                     float* out_color, float4* final_state, uint32_t* n_contrib, float4* ckpt,
                                     uint2* work_items, uint32_t* work_count, uint32_t* tile_last,
-                                    cudaStream_t stream) {
+                                    bool tile_last_zeroed, cudaStream_t stream) {
   if (d.ntiles == 0) return cudaSuccess;
-  cudaError_t e = cudaMemsetAsync(tile_last, 0, (size_t)d.ntiles * 8, stream);
-  if (e != cudaSuccess) return e;
+  if (!tile_last_zeroed) {  // (the forward clears it on its second stream, off the critical path, when it forks one)
+    cudaError_t e = cudaMemsetAsync(tile_last, 0, (size_t)d.ntiles * 8, stream);
+    if (e != cudaSuccess) return e;
+  }
   static int warps = 0;
   if (warps == 0) {
     const char* env = getenv("GS_BF_WARPS");  // tuning switch: boxes of a tile per block (1, 2, 4 or 8)

@@ -14,7 +14,7 @@
 
 // ---- launchers implemented in the other translation units ----
 cudaError_t gs_launch_preprocess(const gs_settings&, const gs_gaussians&, int, GsGeom*, float*, int*, uint32_t*,
-                                 uint4*, uint8_t*, cudaStream_t);
+                                 uint4*, uint8_t*, int*, cudaStream_t);
 cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, int,
                                  cudaStream_t);
 int gs_dup_num_blocks(int N);
@@ -29,10 +29,10 @@ cudaError_t gs_launch_depth_keys(const gs_settings&, const float*, int, uint32_t
 cudaError_t gs_launch_order_tiles(int, const uint2*, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_blend_forward(const GsDims&, const uint32_t*, const uint2*, const uint32_t*, const GsGeom*,
                                     const float[3], float*, float4*, uint32_t*, float4*, uint2*, uint32_t*, uint32_t*,
-                                    cudaStream_t);
+                                    bool, cudaStream_t);
 cudaError_t gs_launch_blend_backward(const GsDims&, const uint2*, const uint32_t*, const GsGeom*, const float[3],
                                      const float4*, const uint32_t*, const float*, const float4*, const uint2*,
-                                     const uint32_t*, uint32_t*, const uint32_t*, float4*, int, cudaStream_t);
+                                     const uint32_t*, uint32_t*, const uint32_t*, float4*, int, bool, cudaStream_t);
 cudaError_t gs_launch_preprocess_backward(const gs_settings&, const gs_gaussians&, const gs_gradients&, int, int,
                                           const int*, const uint8_t*, const float4*, cudaStream_t);
 cudaError_t gs_launch_preprocess_backward_adam(const gs_settings&, const gs_gaussians&, float*, int, const int*,
@@ -98,6 +98,7 @@ struct gs_ctx {
   uint32_t* d_host_mapped = nullptr;  // device address of the same buffer
   cudaEvent_t ev_zero = nullptr;      // grad_geom cleared on the side stream during the forward
   bool grad_geom_zeroed = false;
+  bool work_cursor_zeroed = false;    // counters[1] still zero from the forward's clear
   uint64_t dup_cap_fixed = 0;         // > 0: caller-fixed pair capacity, no host synchronisation in gs_forward
   float* overflow_mirror = nullptr;   // optional caller-owned device float raised to 1.0 on overflow
   bool D_pending = false;             // D of the last forward not yet read back
@@ -374,7 +375,11 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   while ((1u << tile_bits) < (uint32_t)d.ntiles) ++tile_bits;
 
   uint64_t D = 0;
+  bool tile_last_zeroed = false;
+  // K1 stores the radii into the caller's array as well (a copy operation less on the stream) when it is 16-byte aligned
+  int* radii_user = (radii && (((uintptr_t)radii) & 15) == 0) ? radii : nullptr;
   GS_CUDA_CHECK(c, cudaMemsetAsync(c->counters.ptr, 0, 64, stream));
+  c->work_cursor_zeroed = true;
   if (N > 0) {
     // The depth argsort reads only the view depth, so it is forked onto the context's second stream and runs
     // beside K1 (the latency-bound N-sized sort fills the issue slots K1 leaves); the scan joins the two.
@@ -383,11 +388,14 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
     if (overlap) {
       GS_CUDA_CHECK(c, cudaEventRecord(c->ev_fork, stream));
       GS_CUDA_CHECK(c, cudaStreamWaitEvent(c->side, c->ev_fork, 0));
+      // K3's per-tile running maximum + arrival counters, cleared off the critical path (joined with the sort)
+      GS_CUDA_CHECK(c, cudaMemsetAsync(c->tile_last.ptr, 0, (size_t)d.ntiles * 8, c->side));
+      tile_last_zeroed = true;
     } else {
       StageTimer t(c, 0, stream);
       GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
                                             (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint4*)c->rects.ptr,
-                                            (uint8_t*)c->clamped.ptr, stream));
+                                            (uint8_t*)c->clamped.ptr, radii_user, stream));
     }
     {
       StageTimer t(c, 1, sort_stream);
@@ -407,7 +415,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
         StageTimer t(c, 0, stream);
         GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
                                               (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint4*)c->rects.ptr,
-                                              (uint8_t*)c->clamped.ptr, stream));
+                                              (uint8_t*)c->clamped.ptr, radii_user, stream));
       }
       GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->ev_join, 0));
     }
@@ -475,9 +483,9 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
                                              c->point_list, (const GsGeom*)c->geom.ptr, st->bg,
                                              out_color, (float4*)c->final_state.ptr, (uint32_t*)c->n_contrib.ptr,
                                              (float4*)c->ckpt.ptr, (uint2*)c->work_items.ptr,
-                                             (uint32_t*)c->counters.ptr, (uint32_t*)c->tile_last.ptr, stream));
+                                             (uint32_t*)c->counters.ptr, (uint32_t*)c->tile_last.ptr, tile_last_zeroed, stream));
   }
-  if (radii && N > 0)
+  if (radii && !radii_user && N > 0)
     GS_CUDA_CHECK(c, cudaMemcpyAsync(radii, c->radii.ptr, (size_t)N * 4, cudaMemcpyDeviceToDevice, stream));
   if (st->debug) {
     GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
@@ -517,13 +525,15 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
     } else {
       GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
     }
+    const bool cursor_fresh = c->work_cursor_zeroed;  // cleared with the counters by the forward, consumed once
+    c->work_cursor_zeroed = false;
     GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, c->point_list,
                                               (const GsGeom*)c->geom.ptr, st->bg, (const float4*)c->final_state.ptr,
                                               (const uint32_t*)c->n_contrib.ptr, dL_dout_color,
                                               (const float4*)c->ckpt.ptr, (const uint2*)c->work_items.ptr,
                                               (const uint32_t*)c->counters.ptr, (uint32_t*)c->counters.ptr + 1,
                                               (const uint32_t*)c->tile_last.ptr, (float4*)c->grad_geom.ptr,
-                                              c->num_sms, stream));
+                                              c->num_sms, cursor_fresh, stream));
   }
   {
     StageTimer t(c, 7, stream);
@@ -598,13 +608,15 @@ int gs_backward_adam_step(gs_ctx* c, const gs_settings* st, int N, const gs_gaus
     } else {
       GS_CUDA_CHECK(c, cudaMemsetAsync(c->grad_geom.ptr, 0, (size_t)N * 48, stream));
     }
+    const bool cursor_fresh = c->work_cursor_zeroed;  // cleared with the counters by the forward, consumed once
+    c->work_cursor_zeroed = false;
     GS_CUDA_CHECK(c, gs_launch_blend_backward(d, (const uint2*)c->ranges.ptr, c->point_list,
                                               (const GsGeom*)c->geom.ptr, st->bg, (const float4*)c->final_state.ptr,
                                               (const uint32_t*)c->n_contrib.ptr, dL_dout_color,
                                               (const float4*)c->ckpt.ptr, (const uint2*)c->work_items.ptr,
                                               (const uint32_t*)c->counters.ptr, (uint32_t*)c->counters.ptr + 1,
                                               (const uint32_t*)c->tile_last.ptr, (float4*)c->grad_geom.ptr,
-                                              c->num_sms, stream));
+                                              c->num_sms, cursor_fresh, stream));
   }
   {
     StageTimer t(c, 7, stream);

@@ -26,6 +26,7 @@ struct PreprocessArgs {
   GsGeom* geom;
   float* depths;
   int* radii;
+  int* radii_user;  // optional second copy straight into the caller's radii array (16-byte aligned), or nullptr
   uint32_t* tiles_touched;
   uint4* rects;  // {x0 | y0 << 16, x1 | y1 << 16, alive-tile mask lo, hi}; zeros when culled (mask unused when area > 64)
   uint8_t* clamped;
@@ -370,6 +371,7 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
   a.geom[i] = o.g;
   a.depths[i] = o.depth;
   a.radii[i] = o.radius;
+  if (a.radii_user) a.radii_user[i] = o.radius;
   a.tiles_touched[i] = o.tiles;
   a.rects[i] = o.rect;
   a.clamped[i] = (uint8_t)o.cmask;
@@ -439,6 +441,7 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
     tma::store(a.geom + row0, s_buf + PPB_OFF_GEOM, PPB_ROWS * 48u);
     tma::store(a.depths + row0, s_buf + PPB_OFF_DEPTH, PPB_ROWS * 4u);
     tma::store(a.radii + row0, s_buf + PPB_OFF_RADII, PPB_ROWS * 4u);
+    if (a.radii_user) tma::store(a.radii_user + row0, s_buf + PPB_OFF_RADII, PPB_ROWS * 4u);
     tma::store(a.tiles_touched + row0, s_buf + PPB_OFF_TILES, PPB_ROWS * 4u);
     tma::store(a.rects + row0, s_buf + PPB_OFF_RECT, PPB_ROWS * 16u);
     tma::store(a.clamped + row0, s_buf + PPB_OFF_CLAMP, PPB_ROWS);
@@ -475,7 +478,7 @@ static bool pp_aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 
 cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, int N, GsGeom* geom, float* depths,
                                  int* radii, uint32_t* tiles_touched, uint4* rects, uint8_t* clamped,
-                                 cudaStream_t stream) {
+                                 int* radii_user, cudaStream_t stream) {
   if (N == 0) return cudaSuccess;
   PreprocessArgs a;
   a.in = in;
@@ -483,6 +486,7 @@ cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, 
   a.geom = geom;
   a.depths = depths;
   a.radii = radii;
+  a.radii_user = radii_user;
   a.tiles_touched = tiles_touched;
   a.rects = rects;
   a.clamped = clamped;
