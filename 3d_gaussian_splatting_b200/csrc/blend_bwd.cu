@@ -20,7 +20,7 @@
 // gs_common.cuh and are identical to the forward's and the oracle's.
 #include "gs_common.cuh"
 
-#define BB_THREADS 64
+#define BB_THREADS 32
 #define BB_WARPS (BB_THREADS / 32)
 #define BB_PER_LANE (GS_SEG / 32)
 // pixel rows per lane: a lane owns BB_QR rows of two x-adjacent pixels, a warp a 16 x (4 BB_QR) box, a tile has
@@ -30,7 +30,7 @@
 #endif
 #define BB_NP (2 * BB_QR)
 #define BB_PARTS (4 / BB_QR)
-#define BB_BLOCKS_PER_SM (BB_QR == 1 ? 16 : 10)
+#define BB_BLOCKS_PER_SM ((BB_QR == 1 ? 32 : 20) / BB_WARPS)
 
 // Every WARP is autonomous: it pulls its own work item -- (tile, segment, one of the tile's BB_PARTS pixel boxes) --
 // stages the segment's records into its own shared-memory slice and never meets a block barrier.  (The first
