@@ -172,9 +172,9 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
       float s[3] = {scl[0], scl[1], scl[2]};
       float q[4] = {q4.x, q4.y, q4.z, q4.w};
       if (a.in.raw_params) {
-        s[0] = expf(s[0]);
-        s[1] = expf(s[1]);
-        s[2] = expf(s[2]);
+        s[0] = gs_exp_any(s[0]);
+        s[1] = gs_exp_any(s[1]);
+        s[2] = gs_exp_any(s[2]);
       }
       cov3d_from_scale_rot(s, st.scale_modifier, q, c6);
     }
@@ -215,7 +215,7 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
             sh_to_rgb(st.sh_degree, p, st.campos, dc, srow, rgb, cmask);
           }
           float opac = opac_in;
-          if (a.in.raw_params) opac = 1.0f / (1.0f + expf(-opac));
+          if (a.in.raw_params) opac = gs_sigmoid(opac);
           // exact tile culling (gs_common.cuh): which tiles of the rectangle can receive alpha >= 1/255
           uint32_t mlo = 0xFFFFFFFFu, mhi = 0xFFFFFFFFu;
           const GsCull cs = gs_cull_setup(0.5f * con_x, con_y, 0.5f * con_z, opac);

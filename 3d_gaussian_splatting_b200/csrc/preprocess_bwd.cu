@@ -96,7 +96,7 @@ __device__ __forceinline__ void pb_compute(const gs_settings& st, const PreBwdAr
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
         float sv = scl[c];
-        if (a.in.raw_params) sv = expf(sv);
+        if (a.in.raw_params) sv = gs_exp_any(sv);
         sact[c] = sv;
         sm[c] = st.scale_modifier * sv;
       }
@@ -284,7 +284,7 @@ __device__ __forceinline__ void pb_compute(const gs_settings& st, const PreBwdAr
       for (int k = 0; k < 4; ++k) gq[k] = (gn[k] - qn[k] * dotq) / qlen;
     }
     if (a.in.raw_params) {
-      const float sg = 1.0f / (1.0f + expf(-opac_in));
+      const float sg = gs_sigmoid(opac_in);
       gop *= sg * (1.0f - sg);
     }
     o.gop = gop;

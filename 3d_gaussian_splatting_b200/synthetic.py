@@ -13,7 +13,8 @@ from dataclasses import dataclass
 
 import numpy as np
 
-from .camera import Camera, look_at_camera
+# (the camera module is imported lazily: it binds libgsplat_b200.so, and bench.py's CPU reference arm loads this
+#  file on its own -- scene generation is pure numpy -- with a camera factory built on the oracle's conventions)
 
 # name -> (N, W, H, focal_px, sh_degree, n_cameras)   [BASELINE.json configs 0..4]
 CONFIGS = {
@@ -66,8 +67,12 @@ def make_scene(N: int, max_sh_degree: int = 3, seed: int = 1234, radius: float =
     return SyntheticScene(xyz, log_scales, raw_rot, opacity_logits, f_dc, f_rest, max_sh_degree)
 
 
-def orbit_cameras(n: int, W: int, H: int, focal_px: float, radius: float = 4.0, elevation_deg: float = 30.0):
-    """n cameras on a sphere of radius 4R looking at the origin, up = +y, elevation swinging +-30 deg."""
+def orbit_cameras(n: int, W: int, H: int, focal_px: float, radius: float = 4.0, elevation_deg: float = 30.0,
+                  look_at_camera=None):
+    """n cameras on a sphere of radius 4R looking at the origin, up = +y, elevation swinging +-30 deg.
+    look_at_camera: camera factory (eye, target, up, focal_px, H, W, uid=) -- default: camera.look_at_camera."""
+    if look_at_camera is None:
+        from .camera import look_at_camera
     cams = []
     for k in range(n):
         az = 2.0 * math.pi * k / max(n, 1)
@@ -77,10 +82,17 @@ def orbit_cameras(n: int, W: int, H: int, focal_px: float, radius: float = 4.0, 
     return cams
 
 
-def make_config(name: str, n_cameras: int | None = None, N: int | None = None):
-    """(scene, cameras, sh_degree) for one of the BASELINE.json configs; seed = 1234 + config index."""
+def make_config(name: str, n_cameras: int | None = None, N: int | None = None, look_at_camera=None,
+                variant: str = "default"):
+    """(scene, cameras, sh_degree) for one of the BASELINE.json configs; seed = 1234 + config index.
+    variant "stress": the same scene with the opacity logits shifted by -2 (N(-3, 1.5^2): faint Gaussians, long
+    blend lists, little early termination) -- the second workload bench.py reports beside the default one."""
     n, W, H, focal, deg, ncam = CONFIGS[name]
     idx = list(CONFIGS).index(name)
     scene = make_scene(N if N is not None else n, max_sh_degree=deg, seed=1234 + idx)
-    cams = orbit_cameras(n_cameras if n_cameras is not None else ncam, W, H, focal)
+    if variant == "stress":
+        scene.opacity_logits -= np.float32(2.0)
+    elif variant != "default":
+        raise ValueError(f"unknown workload variant {variant!r}")
+    cams = orbit_cameras(n_cameras if n_cameras is not None else ncam, W, H, focal, look_at_camera=look_at_camera)
     return scene, cams, deg

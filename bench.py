@@ -2,11 +2,15 @@
 """bench.py — the headline benchmark of BASELINE.json on B200.
 
 A "step" is ONE training iteration of the reference's (missing) loop body on one camera view
-per rank: render (K1-K3) -> L1 loss -> backward (K4a, K4b) -> fused Adam + densification stats
+per rank: render (K1-K3) -> L1 + D-SSIM loss -> backward (K4a, K4b) -> fused Adam + densification stats
 (K5), on the synthetic 1.6M-Gaussian / 1246x825 / SH3 scene (BASELINE.json configs[2], the
 configuration the metric is quoted on).  metric = views/s (= train it/s at N=1).  With N>1 each
-rank renders its own camera (camera sharding, replicated Gaussians) and the per-Gaussian
-gradients are combined by ONE NCCL all-reduce before the identical Adam step on every rank.
+rank renders its own camera (camera sharding, replicated Gaussians); by default (--dp-mode peer) the
+gradient exchange is fused into the kernels on either side over NVLink peer memory (K4b stores into
+the owner ranks' slots, the sharded Adam kernel sums them and stores the new parameters into every
+replica); --dp-mode allreduce is the library baseline (one NCCL all-reduce + replicated Adam).
+The headline runs with WARM Adam state (every moment non-zero: the kernels' exact skip of
+never-touched vectors cannot fire); `best_case` reports the cold-state step beside it.
 
 Printed JSON keys follow the driver contract; see DESIGN.md "Measurement" for the definitions
 of roofline / cpu_baseline / e2e / gpu_launches.
@@ -51,6 +55,17 @@ def parse_args():
                     help="e2e leg: Trainer.train (pipelined Python loop, default), one synchronous Trainer.train_step per "
                          "step, or the native C++ loop gs_trainer_run (N=1 only; wall-clock timed)")
     ap.add_argument("--N", type=int, default=None, help="override the Gaussian count (debugging only)")
+    ap.add_argument("--adam-state", default="warm", choices=["warm", "cold"],
+                    help="warm (default, the headline): every Adam moment non-zero before the timed region, as in a "
+                         "scene whose Gaussians have all received a gradient at some point -- the kernels' exact skip "
+                         "of never-touched vectors cannot fire (adam_idle_frac 0).  cold: moments start at zero, the "
+                         "Gaussians this synthetic ball hides from every view stay idle and are skipped (best case)")
+    ap.add_argument("--variant", default="default", choices=["default", "stress"],
+                    help="stress: opacity logits shifted by -2 (long blend lists, little early termination)")
+    ap.add_argument("--sustain-seconds", type=float, default=2.0,
+                    help="length of the continuous run behind the `sustained` key (0: skip)")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the secondary measurements (best_case, stress, sustained, north-star batch)")
     ap.add_argument("--mode", default="train", choices=["train", "render"],
                     help="train: the headline train step (default).  render: forward-only render throughput sweep over "
                          "the config's cameras (BASELINE.json configs[3]: Mpix/s with the sort / blend breakdown)")
@@ -115,7 +130,12 @@ class ClockSampler:
 
 
 # ---- algorithmic bytes ---------------------------------------------------
-def stage_bytes(N, N_vis, D, D_eff, P, T, K):
+def stage_bytes(N, N_vis, D, D_eff, P, T, K, active_floats=None):
+    """active_floats: parameter floats whose Adam vector is NOT at the exact fixed point g = m = v = 0 (counted on the
+    device after the timed loop); only those are written back (moments + parameter, 12 B).  None: all of them."""
+    w = 11 + 3 * K
+    if active_floats is None:
+        active_floats = w * N
     tile_bits = max(1, int(np.ceil(np.log2(max(T, 2)))))
     passes = int(np.ceil(tile_bits / 8))
     kb = 2 if T <= 65536 else 4
@@ -130,10 +150,11 @@ def stage_bytes(N, N_vis, D, D_eff, P, T, K):
         "blend_fwd": 40 * D_eff + 20 * P,
         "blend_bwd": 40 * D_eff + 20 * P + 36 * N_vis,
         "preprocess_bwd": (44 + 12 * K) * N_vis + 36 * N_vis + 4 * N + (44 + 12 * K) * N,
-        "adam_stats": 28 * (11 + 3 * K) * N + 36 * N_vis,
-        # K4b + K5 fused (single GPU): record 48 + parameters 4w in; moments 8w in, 8w out; parameters 4w out;
-        # radii / clamp mask / statistics ~ 24 B  (w = 11 + 3K floats per Gaussian)
-        "preprocess_bwd_adam": (48 + 24 * (11 + 3 * K) + 24) * N,
+        # p, g, m, v read for every float; m, v, p written for the active ones only
+        "adam_stats": 16 * w * N + 12 * active_floats + 36 * N_vis,
+        # K4b + K5 fused (single GPU): record 48 + parameters 4w + moments 8w in for every Gaussian; moments 8w +
+        # parameters 4w out for the ACTIVE vectors only; radii / clamp mask / statistics ~ 24 B  (w = 11 + 3K)
+        "preprocess_bwd_adam": (48 + 12 * w + 24) * N + 12 * active_floats,
         # (1-lambda) L1 + lambda D-SSIM: fwd reads image + target, writes 3 partial maps; bwd reads them + both images,
         # writes dL/dimage (12 B per pixel each)
         "loss": 12 * P * (2 + 3 + 5 + 1),
@@ -159,9 +180,59 @@ def measured_traffic(stage):
 
 
 # ---- CPU leg: the oracle port timed on the host cores ------------------------------------------
+class OracleCamera:
+    """A camera built on the ORACLE's restatement of the reference conventions (orc_camera_tensors,
+    src/scene/camera.cpp:44-45,66-71), so that the CPU reference arm never loads libgsplat_b200.so.  Same fields
+    as 3d_gaussian_splatting_b200.camera.Camera (tests/test_conventions_golden.py pins both to the same vectors)."""
+
+    def __init__(self, lib, eye, target, up, focal_px, H, W, uid=0):
+        import ctypes as C
+        eye = np.asarray(eye, np.float64); target = np.asarray(target, np.float64); up = np.asarray(up, np.float64)
+        fwd = target - eye
+        fwd /= np.linalg.norm(fwd)
+        right = np.cross(fwd, up)
+        right /= np.linalg.norm(right)
+        down = np.cross(fwd, right)
+        Rw2c = np.stack([right, down, fwd], axis=0)
+        t = -Rw2c @ eye
+        lib.orc_focal2fov.restype = C.c_double
+        lib.orc_focal2fov.argtypes = [C.c_double, C.c_double]
+        fovx, fovy = lib.orc_focal2fov(float(focal_px), float(W)), lib.orc_focal2fov(float(focal_px), float(H))
+        d = lambda a: np.ascontiguousarray(a, np.float64)
+        R, tt, tr = d(Rw2c.T), d(t), d(np.zeros(3))
+        wv, pj, fp, cp = np.zeros(16), np.zeros(16), np.zeros(16), np.zeros(3)
+        P = lambda a: a.ctypes.data_as(C.c_void_p)
+        lib.orc_camera_tensors(P(R), P(tt), P(tr), C.c_double(1.0), C.c_double(0.01), C.c_double(100.0),
+                               C.c_double(fovx), C.c_double(fovy), P(wv), P(pj), P(fp), P(cp))
+        self.uid, self.image_height, self.image_width = uid, int(H), int(W)
+        self.FoVx, self.FoVy = fovx, fovy
+        self.world_view_transform = wv.astype(np.float32).reshape(4, 4)
+        self.full_proj_transform = fp.astype(np.float32).reshape(4, 4)
+        self.camera_center = cp.astype(np.float32)
+        self.tanfovx, self.tanfovy = float(np.float32(np.tan(fovx * 0.5))), float(np.float32(np.tan(fovy * 0.5)))
+
+
+def load_synthetic_standalone():
+    """synthetic.py loaded from its file, WITHOUT the package __init__ (which binds libgsplat_b200.so): scene
+    generation is pure numpy; the cameras come from OracleCamera."""
+    import importlib.util
+    path = os.path.join(ROOT, "3d_gaussian_splatting_b200", "synthetic.py")
+    spec = importlib.util.spec_from_file_location("_gs_synthetic_standalone", path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[spec.name] = mod      # (dataclasses resolves the module of a class through sys.modules)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 class CpuStep:
-    """One full train step (render, L1, backward, Adam + stats) of the CPU oracle on the same scene.
-    oracle/ is the checker; this is the one place bench.py executes it (cpu_baseline / --impl reference)."""
+    """One full train step (render, loss, backward, Adam + stats) of the CPU oracle on the same scene, stated on the
+    RAW parameters exactly as the GPU path runs it (orc_activate_raw: specified exp / sigmoid, quaternion normalised
+    once inside the covariance construction; activation Jacobians of src/scene/gaussian_model.cpp:54-59 applied to the
+    oracle's gradients; xyz learning rate from the reference's schedule, gaussian_model.cpp:355-361).
+    oracle/ is the checker; this is the one place bench.py executes it (cpu_baseline / --impl reference), and
+    tests/test_gpu_raw_path.py compares Trainer.train_step with it."""
+
+    LR = [1.6e-4, 2.5e-3, 2.5e-3 / 20, 0.05, 5e-3, 1e-3]   # src/arguments/params.h:52-60
 
     def __init__(self, scene, cams, deg, views):
         from oracle.oracle_lib import Oracle, RasterSettings
@@ -172,11 +243,10 @@ class CpuStep:
                     scene.opacity_logits.copy(), scene.log_scales.copy(), scene.raw_rotations.copy()]
         self.m = [np.zeros_like(p) for p in self.raw]
         self.v = [np.zeros_like(p) for p in self.raw]
-        self.lr = [1.6e-4, 2.5e-3, 2.5e-3 / 20, 0.05, 5e-3, 1e-3]
+        self.lr = list(self.LR)
         N = scene.N
         self.maxr = np.zeros(N, np.int32); self.acc = np.zeros(N, np.float32); self.den = np.zeros(N, np.float32)
         self.step = 0
-        self.gts = {}
         self.views = views
         # all host cores, whatever OMP_NUM_THREADS the launcher exported (torchrun sets it to 1)
         want = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
@@ -188,31 +258,33 @@ class CpuStep:
                        cam.world_view_transform.reshape(-1), cam.full_proj_transform.reshape(-1), cam.camera_center,
                        self.deg, self.deg)
 
-    def activated(self):
+    def forward_backward(self, cam, dL=None, gt=None):
+        """(loss or None, gradients w.r.t. the six raw parameter groups, pre, g) for one view."""
+        o = self.o
+        s = self.settings(cam)
         xyz, dc, rest, opl, ls, rq = self.raw
-        sc = np.exp(ls); rot = rq / np.linalg.norm(rq, axis=1, keepdims=True); op = 1.0 / (1.0 + np.exp(-opl))
-        return sc.astype(np.float32), rot.astype(np.float32), op.astype(np.float32), \
-            np.ascontiguousarray(np.concatenate([dc, rest], axis=1))
+        sc, rot, op = o.activate_raw(ls, rq, opl)
+        shs = np.ascontiguousarray(np.concatenate([dc, rest], axis=1))
+        pre, b, fwd = o.forward(s, xyz, sc, rot, op, shs)
+        loss = None
+        if dL is None:
+            if gt is None:
+                gt = np.zeros_like(fwd["out_color"])
+            loss, dL, _, _ = o.photometric_loss(fwd["out_color"], gt, LAMBDA_DSSIM)
+        g = o.backward(s, xyz, sc, rot, shs, pre, b, fwd, dL)
+        g_ls = (g["dL_dscales"] * sc).astype(np.float32)
+        g_op = (g["dL_dopacities"].reshape(-1, 1) * (op * (1 - op))).astype(np.float32)
+        grads = [g["dL_dmeans3D"], np.ascontiguousarray(g["dL_dshs"][:, :1]), np.ascontiguousarray(g["dL_dshs"][:, 1:]),
+                 g_op, g_ls, np.ascontiguousarray(g["dL_drotations"], dtype=np.float32)]
+        return loss, grads, pre, g
 
     def run(self, gt=None):
         o = self.o
         cam = self.cams[self.step % self.views]
-        s = self.settings(cam)
-        xyz = self.raw[0]
-        sc, rot, op, shs = self.activated()
-        pre, b, fwd = o.forward(s, xyz, sc, rot, op, shs)
-        if gt is None:
-            gt = np.zeros_like(fwd["out_color"])
-        loss, dL, _, _ = o.photometric_loss(fwd["out_color"], gt, LAMBDA_DSSIM)
-        g = o.backward(s, xyz, sc, rot, shs, pre, b, fwd, dL)
-        # activation Jacobians of the getters (gaussian_model.cpp:54-59)
-        g_ls = g["dL_dscales"] * sc
-        g_op = (g["dL_dopacities"].reshape(-1, 1) * op * (1 - op)).astype(np.float32)
-        qn = np.linalg.norm(self.raw[5], axis=1, keepdims=True)
-        g_rq = ((g["dL_drotations"] - rot * (rot * g["dL_drotations"]).sum(1, keepdims=True)) / qn).astype(np.float32)
-        grads = [g["dL_dmeans3D"], np.ascontiguousarray(g["dL_dshs"][:, :1]), np.ascontiguousarray(g["dL_dshs"][:, 1:]),
-                 g_op, g_ls.astype(np.float32), g_rq]
         self.step += 1
+        # update_learning_rate(iteration): position_lr_init -> position_lr_final over position_lr_max_steps
+        self.lr[0] = float(o.lib.orc_expon_lr(1.6e-4, 1.6e-6, 0, 0.01, 30_000, self.step))
+        loss, grads, pre, g = self.forward_backward(cam, gt=gt)
         for k in range(6):
             if self.raw[k].size:
                 o.adam_step(self.raw[k], np.ascontiguousarray(grads[k], dtype=np.float32), self.m[k], self.v[k],
@@ -221,13 +293,22 @@ class CpuStep:
         return loss
 
 
+def cpu_scene(args, n_cameras):
+    """(scene, cameras, degree, CpuStep-ready) built without touching the product library."""
+    from oracle.oracle_lib import Oracle
+    lib = Oracle().lib
+    syn = load_synthetic_standalone()
+    factory = lambda eye, target, up, focal, H, W, uid=0: OracleCamera(lib, eye, target, up, focal, H, W, uid)
+    return syn.make_config(args.config, n_cameras=n_cameras, N=args.N, look_at_camera=factory)
+
+
 def run_reference(args, rank, world):
     """--impl reference: the reference has no implementation of this path, so the CPU
-    arm is the oracle port on all host cores, one full step of the same workload per step."""
+    arm is the oracle port on all host cores, one full step of the same workload per step.  Nothing of the product
+    is loaded here (no libgsplat_b200.so): scene generation is numpy, cameras come from the oracle's conventions."""
     if rank != 0:
         return
-    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
-    scene, cams, deg = syn.make_config(args.config, n_cameras=max(args.views, 1), N=args.N)
+    scene, cams, deg = cpu_scene(args, max(args.views, 1))
     cpu = CpuStep(scene, cams, deg, args.views)
     steps, warm = max(1, min(args.steps, 6)), max(0, min(args.warmup, 1))
     for _ in range(warm):
@@ -244,7 +325,8 @@ def run_reference(args, rank, world):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.config, "N": scene.N, "W": cam.image_width, "H": cam.image_height,
                    "sh_degree": deg, "views_per_rank_per_step": 1, "loss": LOSS_NAME,
-                   "note": "reference repo has no render path; CPU arm = this repo's oracle port (OpenMP)"},
+                   "note": "reference repo has no render path; CPU arm = this repo's oracle port (OpenMP), built for "
+                           "accuracy (float64 accumulators, serial per-pair gradient reduction), not for speed"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cpu.cores, "kind": "port",
                          "sample": f"{steps} full train steps of the same workload (steps capped at 6)"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -261,72 +343,123 @@ LOSS_NAME = "0.8*L1 + 0.2*(1-SSIM)"
 LIB_KERNELS_PER_STEP = 0   # no library kernels on the path (the radix sort and scans are this repo's own)
 
 
-def run_ours(args, rank, world, local_rank):
+def warm_adam_state(model):
+    """Every Adam moment non-zero (m = 1e-8, v = 1e-14: the size a gradient of ~1e-7 leaves behind): the state of a
+    scene in which every Gaussian has received a gradient at some point.  exp_avg_sq decays by 0.999 per step, so in a
+    real training run a vector that has been touched once stays active for the rest of the run."""
+    for t in model.exp_avg:
+        if t is not None and t.numel():
+            t.fill_(1e-8)
+    for t in model.exp_avg_sq:
+        if t is not None and t.numel():
+            t.fill_(1e-14)
+
+
+class Setup:
+    pass
+
+
+def setup_trainer(args, scene, my_cams, deg, rank, world, local_rank, adam_state, dp_mode):
+    """Model + trainer + ground-truth images (device and pinned host) + fixed pair capacity for one workload."""
     import torch
-    import torch.distributed as dist
-
-    pkg = importlib.import_module("3d_gaussian_splatting_b200")
-    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
     gm = importlib.import_module("3d_gaussian_splatting_b200.gaussian_model")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-
-    scene, cams, deg = syn.make_config(args.config, n_cameras=max(args.views * world, 1), N=args.N)
     par = importlib.import_module("3d_gaussian_splatting_b200.parallel")
-    my_cams = par.shard_cameras(cams, rank, world)[:args.views]
-    H, W = my_cams[0].image_height, my_cams[0].image_width
-    P, T, K, N = H * W, ((H + 15) // 16) * ((W + 15) // 16), (deg + 1) ** 2, scene.N
-
+    dev = torch.device("cuda", local_rank)
+    u = Setup()
+    u.dp_mode = dp_mode
     model = gm.GaussianModel(deg, local_rank).load_scene(scene)
     opt = gm.OptimizationParams()
     trainer = gm.Trainer(model, opt, bg=(0.0, 0.0, 0.0), lambda_dssim=LAMBDA_DSSIM)
     trainer.fused_step = not args.no_fused
-    g = model
-    sharded = None
-    grad_mb = 4e-6 * sum(p.numel() for p in g.params())
-    if world > 1 and args.dp_mode == "peer":
+    u.model, u.opt, u.trainer = model, opt, trainer
+    u.sharded, u.gslab = None, None
+    u.grad_mb = 4e-6 * sum(p.numel() for p in model.params())
+    guard = None
+    if world > 1 and u.dp_mode == "peer":
         # K4b stores gradient rows into the owner's slots over NVLink; K5 sums them, updates the owned shard and
         # stores the parameters into every replica; two one-float NCCL all-reduces order the ranks
         try:
-            sharded = trainer.shard_optimizer_peer(rank, world)
-            slab, guard = None, sharded.guard
+            u.sharded = trainer.shard_optimizer_peer(rank, world)
+            guard = u.sharded.guard
         except RuntimeError as e:       # raised on every rank alike (PeerShardedAdam): fall back to the NCCL mode
             if rank == 0:
                 print(f"[bench] {e}; falling back to --dp-mode sharded", file=sys.stderr)
-            args.dp_mode = "sharded"
-    if world > 1 and args.dp_mode == "peer":
+            u.dp_mode = "sharded"
+    if world > 1 and u.dp_mode == "peer":
         pass
-    elif world > 1 and args.dp_mode == "sharded":
+    elif world > 1 and u.dp_mode == "sharded":
         # gradients reduce-scattered, Adam on the 1/world slice this rank owns, parameters all-gathered
-        sharded = trainer.shard_optimizer(rank, world)
-        slab, guard = sharded.grad_slab, sharded.guard
+        u.sharded = trainer.shard_optimizer(rank, world)
+        guard = u.sharded.guard
     else:
         # one contiguous gradient slab (a single all-reduce per step when world > 1)
-        gslab = par.GradientSlab(g.params())
-        slab, guard = gslab.flat, gslab.guard
-        g.grads = gslab.views
+        u.gslab = par.GradientSlab(model.params())
+        guard = u.gslab.guard
+        model.grads = u.gslab.views
+    if adam_state == "warm":
+        if world > 1 and u.dp_mode == "sharded":
+            u.sharded.exp_avg.fill_(1e-8)
+            u.sharded.exp_avg_sq.fill_(1e-14)
+        else:
+            warm_adam_state(model)
 
     # ground truth = render of the scene with SH perturbed by N(0, 0.05^2)  (SURVEY.md §8d)
     rng = np.random.Generator(np.random.Philox(99))
     gt_model = gm.GaussianModel(deg, local_rank).load_scene(scene)
     gt_model.features_dc_ += torch.from_numpy((0.05 * rng.standard_normal(scene.features_dc.shape)).astype(np.float32)).to(dev)
-    gts_dev, gts_host = [], []
+    u.gts_dev, u.gts_host = [], []
     max_pairs = 0
     for cam in my_cams:
         out = gm.render(cam, gt_model, gm.PipelineParams(), (0.0, 0.0, 0.0), trainer.rast)
-        gts_dev.append(out["render"].clone())
-        gts_host.append(out["render"].cpu().pin_memory())
+        u.gts_dev.append(out["render"].clone())
+        u.gts_host.append(out["render"].cpu().pin_memory())
         max_pairs = max(max_pairs, trainer.rast.forward_status()[0])   # (synchronised by the .cpu() above)
     del gt_model
     torch.cuda.synchronize()
     # fixed (tile, Gaussian) pair capacity: the forward then never waits for the host (include/gsplat_b200.h);
     # an overflowing iteration would be skipped on the device and is reported below
     trainer.reserve_pairs(int(1.3 * max_pairs) + 1024, guard=guard if world > 1 else None)
+    if world > 1 and u.sharded is None:
+        trainer.grad_sync = u.gslab.all_reduce     # ONE NCCL all-reduce of the gradient slab per iteration
+    return u
 
-    if world > 1 and sharded is None:
-        trainer.grad_sync = gslab.all_reduce     # ONE NCCL all-reduce of the gradient slab per iteration
+
+def adam_activity(model, sharded=None):
+    """(idle fraction, active floats): share of parameter floats whose Adam vector is at the exact fixed point
+    (second moment still 0: never received a gradient).  Counted on the device."""
+    if model.exp_avg_sq is None:
+        ts = [sharded.exp_avg_sq] if sharded is not None and hasattr(sharded, "exp_avg_sq") else []
+    else:
+        ts = [t for t in model.exp_avg_sq if t is not None and t.numel()]
+    if not ts:
+        return None, None
+    nz = sum(int((t != 0).sum().item()) for t in ts)
+    tot = sum(t.numel() for t in ts)
+    return round(1.0 - nz / max(1, tot), 4), nz
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
+    gm = importlib.import_module("3d_gaussian_splatting_b200.gaussian_model")
+    par = importlib.import_module("3d_gaussian_splatting_b200.parallel")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    scene, cams, deg = syn.make_config(args.config, n_cameras=max(args.views * world, 1), N=args.N, variant=args.variant)
+    my_cams = par.shard_cameras(cams, rank, world)[:args.views]
+    H, W = my_cams[0].image_height, my_cams[0].image_width
+    P, T, K, N = H * W, ((H + 15) // 16) * ((W + 15) // 16), (deg + 1) ** 2, scene.N
+
+    u = setup_trainer(args, scene, my_cams, deg, rank, world, local_rank, args.adam_state, args.dp_mode)
+    args.dp_mode = u.dp_mode
+    model, opt, trainer, sharded, gslab = u.model, u.opt, u.trainer, u.sharded, u.gslab
+    gts_dev, gts_host, grad_mb = u.gts_dev, u.gts_host, u.grad_mb
+    g = model
 
     def step_device(i):
         return trainer.train_step_device(my_cams[i % args.views], gts_dev[i % args.views])
@@ -395,47 +528,103 @@ def run_ours(args, rank, world, local_rank):
     e2e_value = world * 1.0 / (e2e_ms / args.steps * 1e-3)
 
     # ---- per-stage device times (CUDA events recorded by the library around each stage) ----
-    trainer.rast.set_profiling(True)
-    acc = {}
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
-    extra = {"loss": [], "adam_stats": []}
-    fused = world == 1 and trainer.fused_step
-    for i in range(8):
-        cam, gt = my_cams[i % args.views], gts_dev[i % args.views]
-        out = gm.render(cam, g, trainer.pipe, trainer.bg, trainer.rast)
-        ev[0].record(); loss, dL = trainer.rast.loss(out["render"], gt, LAMBDA_DSSIM); ev[1].record()
-        if fused:     # K4b and K5 are one kernel: its time is the library's stage 7
-            g.step_count = [s + 1 for s in g.step_count]
-            trainer.rast.backward_adam_step(dL, g.exp_avg, g.exp_avg_sq, g.lr, g.step_count,
-                                            max_radii2D=g.max_radii2D_, xyz_grad_accum=g.xyz_gradient_accum_,
-                                            denom=g.denom_, skip_guard=trainer.skip_guard)
-        else:
-            trainer.rast.backward(dL, grads=g.grad_sinks())
-        ev[2].record()
-        if not fused:
-            trainer.optimizer_step(out["radii"])
-        ev[3].record()
-        torch.cuda.synchronize()
-        if i >= 2:
-            for k, v in trainer.rast.stage_ms().items():
-                acc.setdefault(k, []).append(v)
-            extra["loss"].append(ev[0].elapsed_time(ev[1]))
+    def profile_stages(tr, gts):
+        """Median stage times of 6 steady iterations + workload counters of the last view."""
+        m = tr.g
+        tr.rast.set_profiling(True)
+        acc = {}
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        extra = {"loss": [], "adam_stats": []}
+        fused = world == 1 and tr.fused_step
+        for i in range(8):
+            cam, gt = my_cams[i % args.views], gts[i % args.views]
+            out = gm.render(cam, m, tr.pipe, tr.bg, tr.rast)
+            ev[0].record(); loss, dL = tr.rast.loss(out["render"], gt, LAMBDA_DSSIM); ev[1].record()
+            if fused:     # K4b and K5 are one kernel: its time is the library's stage 7
+                m.step_count = [s + 1 for s in m.step_count]
+                tr.rast.backward_adam_step(dL, m.exp_avg, m.exp_avg_sq, m.lr, m.step_count,
+                                           max_radii2D=m.max_radii2D_, xyz_grad_accum=m.xyz_gradient_accum_,
+                                           denom=m.denom_, skip_guard=tr.skip_guard)
+            else:
+                tr.rast.backward(dL, grads=m.grad_sinks())
+            ev[2].record()
             if not fused:
-                extra["adam_stats"].append(ev[2].elapsed_time(ev[3]))
-    trainer.rast.set_profiling(False)
-    stage_ms = {k: float(np.median(v)) for k, v in acc.items()}
-    stage_ms.update({k: float(np.median(v)) for k, v in extra.items() if v})
-    if fused:
-        stage_ms["preprocess_bwd_adam"] = stage_ms.pop("preprocess_bwd")
-    radii = out["radii"]
-    N_vis = int((radii > 0).sum().item())
-    D = int(trainer.rast.debug_get("NUM_RENDERED")[0])
-    ncon = torch.from_numpy(trainer.rast.debug_get("N_CONTRIB").astype(np.int64)).reshape(H, W)
-    pad = torch.zeros(((H + 15) // 16 * 16, (W + 15) // 16 * 16), dtype=torch.int64)
-    pad[:H, :W] = ncon
-    D_eff = int(pad.reshape(pad.shape[0] // 16, 16, pad.shape[1] // 16, 16).amax(dim=(1, 3)).sum().item())
-    interactions = int(ncon.sum().item())
-    by = stage_bytes(N, N_vis, D, D_eff, P, T, K)
+                tr.optimizer_step(out["radii"])
+            ev[3].record()
+            torch.cuda.synchronize()
+            if i >= 2:
+                for k, v in tr.rast.stage_ms().items():
+                    acc.setdefault(k, []).append(v)
+                extra["loss"].append(ev[0].elapsed_time(ev[1]))
+                if not fused:
+                    extra["adam_stats"].append(ev[2].elapsed_time(ev[3]))
+        tr.rast.set_profiling(False)
+        st = {k: float(np.median(v)) for k, v in acc.items()}
+        st.update({k: float(np.median(v)) for k, v in extra.items() if v})
+        if fused:
+            st["preprocess_bwd_adam"] = st.pop("preprocess_bwd")
+        n_vis = int((out["radii"] > 0).sum().item())
+        d_pairs = int(tr.rast.debug_get("NUM_RENDERED")[0])
+        ncon = torch.from_numpy(tr.rast.debug_get("N_CONTRIB").astype(np.int64)).reshape(H, W)
+        pad = torch.zeros(((H + 15) // 16 * 16, (W + 15) // 16 * 16), dtype=torch.int64)
+        pad[:H, :W] = ncon
+        d_eff = int(pad.reshape(pad.shape[0] // 16, 16, pad.shape[1] // 16, 16).amax(dim=(1, 3)).sum().item())
+        return st, n_vis, d_pairs, d_eff, int(ncon.sum().item()), fused
+
+    stage_ms, N_vis, D, D_eff, interactions, fused = profile_stages(trainer, gts_dev)
+    adam_idle_frac, active_floats = adam_activity(g, sharded)
+
+    # ---- sustained: one continuous run of >= sustain_seconds (the 20-step region above lasts ~30 ms; this one says
+    # what the clocks do when the step runs for seconds) ----
+    sustained = None
+    if args.sustain_seconds > 0 and not args.no_extras:
+        n_sus = max(args.steps, int(args.sustain_seconds * 1e3 / ms_per_step) + 1)
+        sus_ms, sus_clocks = timed(step_device, n_sus, 0, ClockSampler(local_rank) if rank == 0 else None)
+        sustained = {"ms_per_step": sus_ms / n_sus, "value": world * 1e3 / (sus_ms / n_sus), "unit": UNIT,
+                     "steps": n_sus, "seconds": round(sus_ms * 1e-3, 3), "clocks": sus_clocks}
+
+    # ---- secondary workloads (single GPU): the same step with (a) cold Adam state -- the synthetic ball hides ~70 %
+    # of its Gaussians from every view, their vectors stay at the exact fixed point and are skipped: the best case;
+    # (b) the stress variant of the scene (faint Gaussians: long blend lists, little early termination) ----
+    def secondary(adam_state, variant):
+        sc2 = scene if variant == args.variant else syn.make_config(args.config, n_cameras=max(args.views, 1), N=args.N,
+                                                                    variant=variant)[0]
+        u2 = setup_trainer(args, sc2, my_cams, deg, rank, world, local_rank, adam_state, args.dp_mode)
+        t2 = u2.trainer
+        ms2, _ = timed(lambda i: t2.train_step_device(my_cams[i % args.views], u2.gts_dev[i % args.views]),
+                       args.steps, warm)
+        ok = not t2.rast.forward_status()[1]
+        st2, nv2, d2, de2, ia2, _ = profile_stages(t2, u2.gts_dev)
+        idle2, act2 = adam_activity(u2.model, u2.sharded)
+        by2 = stage_bytes(N, nv2, d2, de2, P, T, K, act2)
+        dom2 = "preprocess_bwd_adam" if "preprocess_bwd_adam" in st2 else max(st2, key=lambda k: st2[k])
+        pk = peaks()[0]
+        res = {"ms_per_step": ms2 / args.steps, "value": 1e3 / (ms2 / args.steps), "unit": UNIT,
+               "adam_idle_frac": idle2, "D": d2, "D_eff": de2, "pixel_gaussian_interactions": ia2,
+               "capacity_ok": ok,
+               "stages_ms": {k: round(v, 4) for k, v in st2.items()},
+               "roofline_frac": {dom2: round(by2[dom2] / (st2[dom2] * 1e-3) / 1e9 / pk, 4)}}
+        t2.rast.close()
+        del u2, t2
+        torch.cuda.empty_cache()
+        return res
+
+    best_case = stress = None
+    if world == 1 and not args.no_extras:
+        if args.adam_state == "warm":
+            best_case = secondary("cold", args.variant)
+        if args.variant == "default":
+            stress = secondary(args.adam_state, "stress")
+
+    by = stage_bytes(N, N_vis, D, D_eff, P, T, K, active_floats if world == 1 else None)
+    if world > 1 and args.dp_mode == "peer" and active_floats is not None:
+        # adam_peer_kernel, local HBM bytes of one rank: the `world` gradient slots + m, v, p of its R-row shard read;
+        # m, v, p of the active vectors written; plus what the other ranks' kernels store into this replica
+        wfl, R = 11 + 3 * K, sharded.R
+        by["adam_stats"] = (4 * world + 12) * wfl * R + 12 * active_floats + 4 * active_floats * (world - 1) + 36 * N_vis
+    elif world > 1 and args.dp_mode == "sharded":
+        wfl = 11 + 3 * K
+        by["adam_stats"] = 28 * wfl * N // world + 36 * N_vis
     peak, peak_kind = peaks()
     dom = max(stage_ms, key=lambda k: stage_ms[k])
     ach = by[dom] / (stage_ms[dom] * 1e-3) / 1e9
@@ -486,10 +675,18 @@ def run_ours(args, rank, world, local_rank):
                   "what": "gs_forward + gs_backward (K1-K3, K4a, K4b with the six gradient tensors written to HBM), "
                           "dL/dimage = seeded U(-1,1)/P, median of 9 after 3 warm-ups, CUDA events"}
 
-    adam_idle_frac = None
-    if g.exp_avg_sq is not None:
-        nz = sum(int((t != 0).sum().item()) for t in g.exp_avg_sq if t is not None)
-        adam_idle_frac = round(1.0 - nz / max(1, sum(t.numel() for t in g.exp_avg_sq if t is not None)), 4)
+    # ---- N > 1: the replicas must be bit-identical after the timed loops (every rank holds the same model) ----
+    replicas_identical = last_loss = None
+    if world > 1:
+        torch.cuda.synchronize()
+        cs = torch.zeros(1, dtype=torch.int64, device=dev)
+        for t in g.params():
+            if t.numel():
+                cs += t.contiguous().view(torch.int32).to(torch.int64).sum()
+        allcs = [torch.zeros_like(cs) for _ in range(world)]
+        dist.all_gather(allcs, cs)
+        replicas_identical = all(int(c.item()) == int(allcs[0].item()) for c in allcs)
+        last_loss = float(e2e_losses[-1]) if e2e_losses else None
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = CpuStep(scene, cams, deg, args.views)
@@ -509,7 +706,11 @@ def run_ours(args, rank, world, local_rank):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.config, "N": N, "W": W, "H": H, "sh_degree": deg, "tiles": T,
-                       "views_per_rank_per_step": 1, "loss": LOSS_NAME, "N_vis": N_vis, "D": D, "D_eff": D_eff,
+                       "views_per_rank_per_step": 1, "loss": LOSS_NAME, "variant": args.variant,
+                       "adam_state": ("warm: every Adam moment non-zero before the timed region, so no vector is at the "
+                                      "kernels' exact skip point (steady state of a trained scene)" if args.adam_state == "warm"
+                                      else "cold: moments start at zero; never-touched vectors are skipped"),
+                       "N_vis": N_vis, "D": D, "D_eff": D_eff,
                        "pixel_gaussian_interactions": interactions,
                        "l2_policy": "inputs larger than L2 (params+Adam state 1.13 GB per step vs 126 MB L2)",
                        "parallelism": (f"camera-sharded dp{world}, {grad_mb:.0f} MB of gradients per rank: "
@@ -523,6 +724,12 @@ def run_ours(args, rank, world, local_rank):
             # share of parameter floats whose Adam moments are still exactly 0 (never received a gradient): the Adam
             # kernels skip those vectors (an exact fixed point of the update), so K5's time depends on it
             "adam_idle_frac": adam_idle_frac,
+            # the same step over >= sustain_seconds of continuous running, with its own clock record
+            "sustained": sustained,
+            # the same step with cold Adam state (this scene hides ~70 % of its Gaussians from every view: their
+            # vectors are skipped) and on the stress variant of the scene (long blend lists)
+            "best_case": best_case, "stress": stress,
+            "replicas_identical": replicas_identical, "last_loss": last_loss,
             "raster": raster,
             "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,
@@ -604,7 +811,15 @@ def run_render_sweep(args, local_rank):
     pad = torch.zeros(((H + 15) // 16 * 16, (W + 15) // 16 * 16), dtype=torch.int64)
     pad[:H, :W] = ncon
     D_eff = int(pad.reshape(pad.shape[0] // 16, 16, pad.shape[1] // 16, 16).amax(dim=(1, 3)).sum().item())
-    by = stage_bytes(N, N_vis, D, D_eff, P, T, K)
+    by = stage_bytes(N, N_vis, D, D_eff, P, T, K, active_floats if world == 1 else None)
+    if world > 1 and args.dp_mode == "peer" and active_floats is not None:
+        # adam_peer_kernel, local HBM bytes of one rank: the `world` gradient slots + m, v, p of its R-row shard read;
+        # m, v, p of the active vectors written; plus what the other ranks' kernels store into this replica
+        wfl, R = 11 + 3 * K, sharded.R
+        by["adam_stats"] = (4 * world + 12) * wfl * R + 12 * active_floats + 4 * active_floats * (world - 1) + 36 * N_vis
+    elif world > 1 and args.dp_mode == "sharded":
+        wfl = 11 + 3 * K
+        by["adam_stats"] = 28 * wfl * N // world + 36 * N_vis
     peak, peak_kind = peaks()
     fwd_bytes = sum(by[k] for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd"))
     binning = sum(stage_ms.get(k, 0.0) for k in ("depth_sort", "scan_duplicate", "sort", "ranges"))

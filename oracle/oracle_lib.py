@@ -111,6 +111,15 @@ class Oracle:
         flat = shs.reshape(N, K * 3)
         return flat, 3 * K, (flat[:, 3:] if K > 1 else None), 3 * K
 
+    def activate_raw(self, log_scales, raw_rotations, opacity_logits):
+        """The activations as the RAW-parameter path of the kernels evaluates them (orc_activate_raw): specified exp /
+        sigmoid; the quaternion stays un-normalised (the covariance construction normalises it, once)."""
+        ls = self.arr(log_scales); rq = self.arr(raw_rotations); ol = self.arr(opacity_logits).reshape(-1)
+        N = ls.shape[0]
+        sc = np.zeros((N, 3), self.dt); rot = np.zeros((N, 4), self.dt); op = np.zeros(N, self.dt)
+        self.lib.orc_activate_raw(C.c_int(N), self.p(ls), self.p(rq), self.p(ol), self.p(sc), self.p(rot), self.p(op))
+        return sc, rot, op.reshape(-1, 1)
+
     # ---- stages --------------------------------------------------------------------
     def preprocess(self, s, means3D, scales, rotations, opacities, shs, colors_precomp=None, cov3D_precomp=None):
         st = self.settings(s)

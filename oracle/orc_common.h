@@ -137,6 +137,38 @@ static inline real orc_exp(real x) {
   return p * scale;
 }
 #endif
+/*
+ * Activations of the RAW parameter path (raw_params = 1: the kernels apply exp / sigmoid themselves,
+ * src/scene/gaussian_model.cpp:54-59, :270-298).  exp over the whole float range with the same specified
+ * numerics as orc_exp (identical bits for x <= 0): t = x*log2(e), 0 below 2^-126, +inf above 2^128,
+ * else 2^rint(t) * P6(t - rint(t)).  Shared by definition with csrc/gs_common.cuh gs_exp_any, so radii and
+ * tile counts of the raw path stay bit-exact.  sigmoid(x) = 1 / (1 + exp_any(-x)), one IEEE division.
+ */
+#ifdef ORC_DOUBLE
+static inline real orc_exp_any(real x) { return exp(x); }
+#else
+static inline real orc_exp_any(real x) {
+  float t = x * 1.44269504088896340736f;
+  if (!(t >= -126.0f)) return 0.0f;
+  if (t > 128.0f) return HUGE_VALF;
+  float n = rintf(t);
+  float f = t - n;
+  float p = 1.5403530393381608e-4f;
+  p = fmaf(p, f, 1.3333558146428443e-3f);
+  p = fmaf(p, f, 9.6181291076284772e-3f);
+  p = fmaf(p, f, 5.5504108664821580e-2f);
+  p = fmaf(p, f, 2.4022650695910071e-1f);
+  p = fmaf(p, f, 6.9314718055994531e-1f);
+  p = fmaf(p, f, 1.0f);
+  int32_t e = (int32_t)n;
+  uint32_t bits = (uint32_t)(e + 127) << 23;
+  float scale;
+  memcpy(&scale, &bits, 4);
+  return p * scale;
+}
+#endif
+static inline real orc_sigmoid(real x) { return RC(1) / (RC(1) + orc_exp_any(-x)); }
+
 static inline real orc_power(real hA, real B, real hC, real dx, real dy) {
   /* hA = 0.5*A, hC = 0.5*C (exact scalings) */
   real u = R_FMA(hA, dx, B * dy);

@@ -92,6 +92,19 @@ void orc_activate(int N, const real *log_scales, const real *raw_rot, const real
   }
 }
 
+/* The same activations as the RAW-parameter path of the kernels evaluates them (raw_params = 1): scaling and
+ * opacity through the specified exp (orc_common.h orc_exp_any / orc_sigmoid); the quaternion is handed on
+ * un-normalised, because the covariance construction normalises it itself (src/utils/general_utils.cpp:14-19),
+ * exactly once -- as K1 does. */
+void orc_activate_raw(int N, const real *log_scales, const real *raw_rot, const real *logit_opacity,
+                      real *scales, real *rot, real *opacity) {
+  for (int i = 0; i < N; ++i) {
+    for (int c = 0; c < 3; ++c) scales[3 * i + c] = orc_exp_any(log_scales[3 * i + c]);
+    for (int c = 0; c < 4; ++c) rot[4 * i + c] = raw_rot[4 * i + c];
+    opacity[i] = orc_sigmoid(logit_opacity[i]);
+  }
+}
+
 /* ---- camera conventions (float64 on the host, as in the reference) ---- */
 
 /* focal2fov.  Follows src/utils/graphics_utils.cpp:4-7. */

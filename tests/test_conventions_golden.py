@@ -150,3 +150,25 @@ def test_camera_tensors_match_oracle(oracle, pkg):
     V = cam.world_view_transform.T  # row-major V
     np.testing.assert_allclose(V[:3, :3], Q.T, atol=1e-6); np.testing.assert_allclose(V[:3, 3], t, atol=1e-6)
     assert cam.tanfovx == pytest.approx(math.tan(fx / 2), rel=1e-6)
+
+
+def test_reference_arm_cameras_match_product_cameras(oracle):
+    """bench.py --impl reference builds its cameras on the oracle's conventions (so that the CPU arm never loads
+    libgsplat_b200.so); they must be the product's cameras (to rounding of the float64 intermediate)."""
+    import importlib
+    import sys
+    argv, sys.argv = sys.argv, ["bench.py"]
+    try:
+        import bench
+    finally:
+        sys.argv = argv
+    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
+    a = syn.orbit_cameras(5, 1246, 825, 1000.0)
+    b = syn.orbit_cameras(5, 1246, 825, 1000.0, look_at_camera=lambda e, t, u, f, H, W, uid=0:
+                          bench.OracleCamera(oracle.lib, e, t, u, f, H, W, uid))
+    for x, y in zip(a, b):
+        np.testing.assert_allclose(x.world_view_transform, y.world_view_transform, rtol=0, atol=1e-7)
+        np.testing.assert_allclose(x.full_proj_transform, y.full_proj_transform, rtol=1e-6, atol=1e-7)
+        np.testing.assert_allclose(x.camera_center, y.camera_center, rtol=1e-6, atol=1e-7)
+        assert x.tanfovx == y.tanfovx and x.tanfovy == y.tanfovy
+        assert (x.image_height, x.image_width) == (y.image_height, y.image_width)

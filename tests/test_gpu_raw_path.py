@@ -1,0 +1,135 @@
+"""GPU parity of the path the training step and bench.py actually run (-m gpu): RAW parameters in (log-scales,
+un-normalised quaternions, opacity logits, features_dc_/features_rest_ as separate dense tensors), activations fused
+into K1 / K4b (raw_params = 1, src/scene/gaussian_model.cpp:54-59, :270-298), TMA-staged kernels -- against the oracle's
+statement of the same path (helpers.raw_reference: orc_activate_raw -> orc_preprocess -> ... with the activation
+Jacobians applied on the oracle side).  Bars are north_star's: radii / tile counts / sort keys / point lists / ranges
+bit-exact, image 1e-4 max-abs, gradients 1e-3 -- and the gradient bar is PER ELEMENT (helpers.elem_err: an element
+1000x below the array maximum must still be right to 1e-3 of itself) plus a per-Gaussian cosine bound.
+Then whole train steps: Trainer (fused K4b+K5, capacity mode) against the CPU oracle step (bench.CpuStep)."""
+import importlib
+
+import numpy as np
+import pytest
+
+from helpers import elem_err, gpu_settings, min_row_cosine, raw_reference, rel_err, small_scene, syn
+from test_gpu_parity import check_forward, dev, seeded_dL, GRAD_TOL
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+COS_TOL = 1e-5     # 1 - cosine similarity of a Gaussian's gradient row (rows above 1e-3 of the largest row norm)
+
+
+def run_raw(oracle, rast, scene, cam, deg, maxdeg, bg=(0.0, 0.0, 0.0), dL=None):
+    r = raw_reference(oracle, scene, cam, deg, maxdeg, bg, dL)
+    sg = gpu_settings(cam, deg, maxdeg, bg, debug=True)
+    K = (maxdeg + 1) ** 2
+    P = [dev(scene.xyz), dev(scene.features_dc), dev(np.ascontiguousarray(scene.features_rest[:, :K - 1])),
+         dev(scene.opacity_logits), dev(scene.log_scales), dev(scene.raw_rotations)]
+    color, radii = rast.forward(sg, P[0], P[4], P[5], P[3], sh_dc=P[1], sh_rest=P[2] if K > 1 else None,
+                                raw_params=True)
+    r.update(color=color.cpu().numpy(), radii=radii.cpu().numpy(), sg=sg)
+    if dL is not None:
+        g = {k: v.cpu().numpy() for k, v in rast.backward(dev(dL)).items()}
+        rest = g.pop("sh_rest", None)
+        dc = g.pop("sh_dc")
+        g["shs"] = dc if rest is None else np.concatenate([dc, rest], axis=1)
+        r["g_gpu"] = g
+    return r
+
+
+def check_raw_backward(r, report=None):
+    gr, gg = r["g_ref"], r["g_gpu"]
+    pairs = dict(means3D="dL_dmeans3D", opacities="dL_dopacities", means2D="dL_dmeans2D", scales="dL_dscales",
+                 rotations="dL_drotations", shs="dL_dshs")
+    worst = {}
+    for k, kr in pairs.items():
+        ref = gr[kr].reshape(gg[k].shape)
+        assert np.isfinite(gg[k]).all(), k
+        worst[k] = (rel_err(gg[k], ref), elem_err(gg[k], ref), 1.0 - min_row_cosine(gg[k], ref))
+    if report is not None:
+        report.update(worst)
+    for k, (e_max, e_elem, e_cos) in worst.items():
+        assert e_max <= GRAD_TOL, f"grad {k}: error relative to the array maximum {e_max}"
+        assert e_elem <= GRAD_TOL, f"grad {k}: per-element relative error {e_elem} (floor 1e-3 of the maximum)"
+        assert e_cos <= COS_TOL, f"grad {k}: 1 - min row cosine {e_cos}"
+
+
+@pytest.mark.parametrize("deg,maxdeg,N,seed", [(0, 0, 3000, 3), (1, 3, 3000, 4), (3, 3, 4100, 5), (2, 2, 2048, 6)])
+def test_raw_path_small(oracle, rasterizer, deg, maxdeg, N, seed):
+    scene, cam = small_scene(N=N, H=96, W=128, deg=maxdeg, seed=seed, scale_boost=0.5)
+    r = run_raw(oracle, rasterizer, scene, cam, deg, maxdeg, bg=(0.2, 0.5, 0.9), dL=seeded_dL(96, 128, seed))
+    check_forward(rasterizer, r)
+    check_raw_backward(r)
+
+
+def test_raw_path_extreme_parameters(oracle, rasterizer):
+    """Log-scales and opacity logits far outside the synthetic distribution (the specified exp's whole range matters:
+    tiny / huge scales, saturated sigmoids), quaternions of very different lengths."""
+    scene, cam = small_scene(N=2500, H=80, W=112, deg=1, seed=23, scale_boost=0.3)
+    rng = np.random.default_rng(1)
+    scene.log_scales[::7] -= 6.0
+    scene.log_scales[3::11] += 2.0
+    scene.opacity_logits[::5] = rng.uniform(-20, 20, scene.opacity_logits[::5].shape).astype(np.float32)
+    scene.raw_rotations *= (10.0 ** rng.uniform(-3, 3, (scene.N, 1))).astype(np.float32)
+    r = run_raw(oracle, rasterizer, scene, cam, 1, 1, dL=seeded_dL(80, 112, 2))
+    check_forward(rasterizer, r)
+    check_raw_backward(r)
+
+
+@pytest.mark.parametrize("name", ["cfg0_10k_256_sh0", "cfg1_100k_800_sh3", "cfg2_1p6m_1246x825_sh3"])
+def test_raw_path_baseline_configs_full_size(oracle, rasterizer, name):
+    """BASELINE.json configs[0..2] at full size on the raw path (cfg2 = the configuration bench.py's headline runs)."""
+    scene, cams, deg = syn.make_config(name, n_cameras=3)
+    cam = cams[1]
+    H, W = cam.image_height, cam.image_width
+    r = run_raw(oracle, rasterizer, scene, cam, deg, deg, dL=seeded_dL(H, W, 9))
+    check_forward(rasterizer, r, termination_flips=H * W // 100_000)
+    rep = {}
+    try:
+        check_raw_backward(r, rep)
+    finally:
+        print(f"\n[{name}] gradient errors (max-relative, per-element, 1-cos): " +
+              ", ".join(f"{k} {a:.1e}/{b:.1e}/{c:.1e}" for k, (a, b, c) in rep.items()))
+
+
+def test_train_steps_match_cpu_oracle(oracle):
+    """Three full train steps on cfg1 (100 k Gaussians, 800x800, SH3): Trainer.train_step -- fused K4b+K5 kernel,
+    fixed pair capacity, D-SSIM loss, the path bench.py times -- against the CPU oracle's step (bench.CpuStep: the
+    same raw-path statement, orc_adam_step).  Losses to 1e-5 relative.  Parameters: an Adam step moves a parameter by
+    at most ~lr, and its first steps are sign-like (g / (|g| + eps)), which turns the blend backward's atomic-order
+    noise on a gradient that is itself ~eps-sized into a different step; so the bound is statistical: at least 99.9 %
+    of every group's elements agree to 1e-3 of the step size lr, and no element is further than the sign-flip
+    bound 2 lr per step."""
+    import bench
+    gm = importlib.import_module("3d_gaussian_splatting_b200.gaussian_model")
+    scene, cams, deg = syn.make_config("cfg1_100k_800_sh3", n_cameras=3)
+    steps = 3
+    model = gm.GaussianModel(deg, 0).load_scene(scene)
+    tr = gm.Trainer(model, gm.OptimizationParams(), lambda_dssim=0.2)
+    gt_model = gm.GaussianModel(deg, 0).load_scene(scene)
+    gt_model.features_dc_ += 0.05
+    gts = [gm.render(c, gt_model, gm.PipelineParams(), (0., 0., 0.), tr.rast)["render"].cpu().pin_memory() for c in cams]
+    tr.reserve_pairs(6_000_000)
+    assert tr.fused_step
+    cpu = bench.CpuStep(scene, cams, deg, views=len(cams))
+    lg, lc = [], []
+    for i in range(steps):
+        lg.append(tr.train_step(cams[i], gts[i]))
+        lc.append(cpu.run(gts[i].numpy()))
+    assert tr.retries == 0
+    np.testing.assert_allclose(lg, lc, rtol=1e-5)
+    lr = cpu.lr
+    names = gm.GaussianModel.GROUPS
+    for k, (p, q) in enumerate(zip(model.params(), cpu.raw)):
+        d = np.abs(p.cpu().numpy().reshape(q.shape).astype(np.float64) - q)
+        close = float((d <= 1e-3 * lr[k] * steps).mean())
+        assert close >= 0.999, f"{names[k]}: only {close:.5f} of the elements within 1e-3 lr"
+        assert d.max() <= 2.05 * lr[k] * steps, f"{names[k]}: max deviation {d.max()} vs lr {lr[k]}"
+    # the Adam moments of a well-conditioned group (f_dc: gradients far above eps) agree element-wise
+    m_gpu = model.exp_avg[1].cpu().numpy().reshape(cpu.m[1].shape)
+    assert elem_err(m_gpu, cpu.m[1]) <= GRAD_TOL
+    # densification statistics ride along in the fused kernel
+    np.testing.assert_array_equal(model.max_radii2D_.cpu().numpy(), cpu.maxr)
+    np.testing.assert_array_equal(model.denom_.cpu().numpy().reshape(-1), cpu.den)
+    assert rel_err(model.xyz_gradient_accum_.cpu().numpy().reshape(-1), cpu.acc) <= GRAD_TOL

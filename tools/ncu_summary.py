@@ -16,6 +16,9 @@ WANT = {
     "launch__occupancy_limit_shared_mem": "lim_smem",
     "smsp__issue_active.avg.pct_of_peak_sustained_active": "issue_pct",
     "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active": "xu_pct",
+    "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active": "fma_pct",
+    "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active": "alu_pct",
+    "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active": "lsu_pct",
     "smsp__inst_executed.sum": "inst_M",
     "lts__t_sectors_op_red.sum": "l2_red_sect_M",
     "lts__t_sectors_op_atom.sum": "l2_atom_sect_M",
@@ -59,8 +62,8 @@ def main():
         d["grid"] = r[idx["Grid Size"]] if "Grid Size" in idx else ""
         d["block"] = r[idx["Block Size"]] if "Block Size" in idx else ""
         lines.append((name, d))
-    cols = ["dur_us", "dram_rd_MB", "dram_wr_MB", "dram_pct", "l2_pct", "l1_pct", "sm_pct", "issue_pct", "occ_pct", "regs",
-            "inst_M", "l2_red_sect_M"]
+    cols = ["dur_us", "dram_rd_MB", "dram_wr_MB", "dram_pct", "l2_pct", "l1_pct", "sm_pct", "issue_pct", "fma_pct", "alu_pct",
+            "xu_pct", "lsu_pct", "occ_pct", "regs", "inst_M", "l2_red_sect_M"]
     txt = ["| kernel | grid | block | " + " | ".join(cols) + " | top stalls (warps stalled per issue) |", "|" + "---|" * (len(cols) + 4)]
     for name, d in lines:
         txt.append(f"| {name} | {d['grid']} | {d['block']} | " + " | ".join(
