@@ -79,13 +79,30 @@ __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_
       v[k] = __ldcs(vp + k * AD_THREADS);
       p[k] = __ldcs(pp + k * AD_THREADS);
     }
+    // packed fast path when the whole warp's vectors are inside its range, scalar path otherwise (gs_common.cuh)
+    const GsAdamConst kc = {b1, b2, omb1, omb2, eps};
+    GsAdamQuad q[AD_VEC_PER_THREAD];
+    bool idle[AD_VEC_PER_THREAD];
+    bool fast = true, any_active = false;
 #pragma unroll
     for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
-      if (gs_adam_idle(g[k], m[k], v[k])) continue;  // exact fixed point (gs_common.cuh): nothing to write
-      gs_adam_one(p[k].x, g[k].x, m[k].x, v[k].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-      gs_adam_one(p[k].y, g[k].y, m[k].y, v[k].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-      gs_adam_one(p[k].z, g[k].z, m[k].z, v[k].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-      gs_adam_one(p[k].w, g[k].w, m[k].w, v[k].w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      idle[k] = gs_adam_idle(g[k], m[k], v[k]);  // exact fixed point (gs_common.cuh): nothing to write
+      const bool ok = gs_adam_quad_moments(g[k], m[k], v[k], kc, q[k]);
+      fast = fast && (idle[k] || ok);
+      any_active = any_active || !idle[k];
+    }
+    if (!__any_sync(0xffffffffu, any_active)) return;
+    if (__all_sync(0xffffffffu, fast)) {
+#pragma unroll
+      for (int k = 0; k < AD_VEC_PER_THREAD; ++k) gs_adam_quad_step(p[k], m[k], v[k], q[k], eps, neg_step, inv_bc2_sqrt);
+    } else {
+#pragma unroll
+      for (int k = 0; k < AD_VEC_PER_THREAD; ++k)
+        if (!idle[k]) gs_adam_quad_scalar(p[k], g[k], m[k], v[k], kc, neg_step, inv_bc2_sqrt);
+    }
+#pragma unroll
+    for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
+      if (idle[k]) continue;
       __stcs(mp + k * AD_THREADS, m[k]);
       __stcs(vp + k * AD_THREADS, v[k]);
       __stcs(pp + k * AD_THREADS, p[k]);
@@ -234,7 +251,7 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
     float4 gs[G];
 #pragma unroll
     for (int r = 0; r < G; ++r) gs[r] = __ldcs(reinterpret_cast<const float4*>(s.src[r]) + v0);
-    float4 m, v, p;
+    float4 m = make_float4(0.f, 0.f, 0.f, 0.f), v = m, p = m;
     if (!skip) {
       m = __ldcs(reinterpret_cast<const float4*>(s.m) + v0);
       v = __ldcs(reinterpret_cast<const float4*>(s.v) + v0);
@@ -247,7 +264,6 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
                              __float_as_uint(gs[r].w)) & 0x7fffffffu))
           reinterpret_cast<float4*>(const_cast<float*>(s.src[r]))[v0] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    if (skip) return;
     float4 g = gs[0];
 #pragma unroll
     for (int r = 1; r < G; ++r) {
@@ -256,11 +272,17 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
       g.z = __fadd_rn(g.z, gs[r].z);
       g.w = __fadd_rn(g.w, gs[r].w);
     }
-    if (gs_adam_idle(g, m, v)) return;  // exact fixed point: every replica already holds this p, nothing crosses NVLink
-    gs_adam_one(p.x, g.x, m.x, v.x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-    gs_adam_one(p.y, g.y, m.y, v.y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-    gs_adam_one(p.z, g.z, m.z, v.z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-    gs_adam_one(p.w, g.w, m.w, v.w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+    // exact fixed point: every replica already holds this p, nothing crosses NVLink
+    const bool idle = skip || gs_adam_idle(g, m, v);
+    if (!__any_sync(0xffffffffu, !idle)) return;
+    {
+      const GsAdamConst kc = {b1, b2, omb1, omb2, eps};
+      GsAdamQuad q;
+      const bool ok = gs_adam_quad_moments(g, m, v, kc, q);
+      if (__all_sync(0xffffffffu, idle || ok)) gs_adam_quad_step(p, m, v, q, eps, neg_step, inv_bc2_sqrt);
+      else if (!idle) gs_adam_quad_scalar(p, g, m, v, kc, neg_step, inv_bc2_sqrt);
+    }
+    if (idle) return;
 #pragma unroll
     for (int r = 0; r < G - 1; ++r) reinterpret_cast<float4*>(s.dst[r])[v0] = p;  // NVLink stores first
     __stcs(reinterpret_cast<float4*>(s.m) + v0, m);

@@ -597,41 +597,94 @@ struct FusedAdamArgs {
   float* denom;
 };
 
-#define PBF_UNROLL 4
 
 // The block's 128 x (11 + 3K) gradient floats as chunks of 32 float4 (512 B), every chunk inside ONE group because
 // each group's slice is 128 rows x C floats = C chunks: chunk index -> (group, offset).  A warp walks chunks
-// warp, warp + 4, ... four at a time, so every round has 12 independent 16-byte loads per thread in flight
-// whatever the group sizes (a per-group loop would spend a latency round on each of the five small groups).
-struct PbfChunk {
-  const float4* g;  // shared memory
-  float4* p;
-  float4* m;
-  float4* v;
-  int k;
+// warp, warp + 4, ... in rounds of PBF_UNROLL, DOUBLE-BUFFERED: the moments and parameters of the next round are
+// requested (3 x PBF_UNROLL independent 16-byte loads per thread) before the current round is computed, so the L2
+// latency of the Adam phase's loads -- 35 % of the kernel's stall samples when every round waited for its own loads,
+// profiles/r02a -- is spent under arithmetic.  Only the group and one 32-bit vector index are kept per chunk.
+// the 14 chunks behind the W f_rest chunks: xyz 3, f_dc 3, opacity 1, scaling 3, rotation 4
+__constant__ int c_pbf_group[14] = {0, 0, 0, 1, 1, 1, 3, 4, 4, 4, 5, 5, 5, 5};
+__constant__ int c_pbf_sub[14] = {0, 1, 2, 0, 1, 2, 0, 0, 1, 2, 0, 1, 2, 3};
+__constant__ int c_pbf_width[14] = {3, 3, 3, 3, 3, 3, 1, 3, 3, 3, 4, 4, 4, 4};
+__constant__ int c_pbf_soff[14] = {PBB_OFF_XYZ, PBB_OFF_XYZ, PBB_OFF_XYZ, PBB_OFF_DC, PBB_OFF_DC, PBB_OFF_DC, PBB_OFF_OP,
+                                   PBB_OFF_SCL, PBB_OFF_SCL, PBB_OFF_SCL, PBB_OFF_ROT, PBB_OFF_ROT, PBB_OFF_ROT, PBB_OFF_ROT};
+
+template <int PBF_UNROLL>
+struct PbfRound {
+  float4 p[PBF_UNROLL], m[PBF_UNROLL], v[PBF_UNROLL];
+  uint32_t vec[PBF_UNROLL];   // float4 index of this lane's vector inside the group's arrays
+  uint32_t gvec[PBF_UNROLL];  // float4 index of its gradient inside the block's shared memory
+  int k[PBF_UNROLL];          // group (-1: no such chunk)
 };
 
-__device__ __forceinline__ PbfChunk pbf_chunk(const float* s_buf, const FusedAdamArgs& f, const size_t row0, const int W,
-                                              int c) {
-  // chunk order: f_rest (W of them), xyz 3, f_dc 3, opacity 1, scaling 3, rotation 4
-  int k, soff, cw;  // group, smem slice offset, floats per row
-  if (c < W) { k = 2; soff = PBB_OFF_SH; cw = W; }
-  else if ((c -= W) < 3) { k = 0; soff = PBB_OFF_XYZ; cw = 3; }
-  else if ((c -= 3) < 3) { k = 1; soff = PBB_OFF_DC; cw = 3; }
-  else if ((c -= 3) < 1) { k = 3; soff = PBB_OFF_OP; cw = 1; }
-  else if ((c -= 1) < 3) { k = 4; soff = PBB_OFF_SCL; cw = 3; }
-  else { c -= 3; k = 5; soff = PBB_OFF_ROT; cw = 4; }
-  const size_t goff = row0 * cw + (size_t)c * 128;  // floats
-  PbfChunk r;
-  r.g = reinterpret_cast<const float4*>(s_buf + soff + c * 128);
-  r.p = reinterpret_cast<float4*>(f.p[k] + goff);
-  r.m = reinterpret_cast<float4*>(f.m[k] + goff);
-  r.v = reinterpret_cast<float4*>(f.v[k] + goff);
-  r.k = k;
-  return r;
+template <int PBF_UNROLL>
+__device__ __forceinline__ void pbf_request(PbfRound<PBF_UNROLL>& R, const FusedAdamArgs& f, const size_t row0, const int W,
+                                            const int nchunks, const int c0, const int lane) {
+#pragma unroll
+  for (int u = 0; u < PBF_UNROLL; ++u) {
+    const int c = c0 + 4 * u;
+    R.k[u] = -1;
+    if (c < nchunks) {
+      const bool rest = c < W;
+      const int t = rest ? 0 : c - W;
+      const int k = rest ? 2 : c_pbf_group[t];
+      const int sub = rest ? c : c_pbf_sub[t];
+      const int cw = rest ? W : c_pbf_width[t];
+      const int soff = rest ? PBB_OFF_SH : c_pbf_soff[t];
+      R.k[u] = k;
+      R.gvec[u] = (uint32_t)(soff / 4 + sub * 32 + lane);                    // (every slice offset is a multiple of 4)
+      R.vec[u] = (uint32_t)((row0 * cw) / 4 + (size_t)sub * 32 + lane);      // (row0 is a multiple of 128)
+      R.m[u] = __ldcs(reinterpret_cast<const float4*>(f.m[k]) + R.vec[u]);
+      R.v[u] = __ldcs(reinterpret_cast<const float4*>(f.v[k]) + R.vec[u]);
+      R.p[u] = reinterpret_cast<const float4*>(f.p[k])[R.vec[u]];
+    }
+  }
 }
 
-__global__ void __launch_bounds__(PBB_ROWS, 5)
+template <int PBF_UNROLL>
+__device__ __forceinline__ void pbf_update(PbfRound<PBF_UNROLL>& R, const float* s_buf, const FusedAdamArgs& f, const GsAdamConst& kc) {
+  float4 g[PBF_UNROLL];
+  GsAdamQuad q[PBF_UNROLL];
+  bool idle[PBF_UNROLL];
+  bool any_active = false, fast = true;
+#pragma unroll
+  for (int u = 0; u < PBF_UNROLL; ++u) {
+    idle[u] = true;
+    if (R.k[u] >= 0) {
+      g[u] = reinterpret_cast<const float4*>(s_buf)[R.gvec[u]];
+      idle[u] = gs_adam_idle(g[u], R.m[u], R.v[u]);  // exact fixed point (gs_common.cuh): nothing to write
+      const bool ok = gs_adam_quad_moments(g[u], R.m[u], R.v[u], kc, q[u]);
+      fast = fast && (idle[u] || ok);
+      any_active = any_active || !idle[u];
+    }
+  }
+  if (!__any_sync(0xffffffffu, any_active)) return;
+  if (__all_sync(0xffffffffu, fast)) {
+    // packed path (gs_common.cuh): both chunks' pairs in one basic block -- four independent dependency chains
+#pragma unroll
+    for (int u = 0; u < PBF_UNROLL; ++u)
+      if (R.k[u] >= 0)
+        gs_adam_quad_step(R.p[u], R.m[u], R.v[u], q[u], kc.eps, f.neg_step[R.k[u]], f.inv_bc2_sqrt[R.k[u]]);
+  } else {
+#pragma unroll
+    for (int u = 0; u < PBF_UNROLL; ++u)
+      if (R.k[u] >= 0 && !idle[u])
+        gs_adam_quad_scalar(R.p[u], g[u], R.m[u], R.v[u], kc, f.neg_step[R.k[u]], f.inv_bc2_sqrt[R.k[u]]);
+  }
+#pragma unroll
+  for (int u = 0; u < PBF_UNROLL; ++u)
+    if (R.k[u] >= 0 && !idle[u]) {
+      const int k = R.k[u];
+      __stcs(reinterpret_cast<float4*>(f.m[k]) + R.vec[u], R.m[u]);
+      __stcs(reinterpret_cast<float4*>(f.v[k]) + R.vec[u], R.v[u]);
+      reinterpret_cast<float4*>(f.p[k])[R.vec[u]] = R.p[u];  // read again by the next forward
+    }
+}
+
+template <int PBF_UNROLL, int MIN_BLOCKS>
+__global__ void __launch_bounds__(PBB_ROWS, MIN_BLOCKS)
 preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a,
                                 const __grid_constant__ FusedAdamArgs f) {
   if (f.skip_guard && __ldg(f.skip_guard) != 0.0f) return;  // overflowed forward: the whole step is void
@@ -671,6 +724,14 @@ preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __
   const int radius = a.radii[i];
   const bool visible = radius > 0;
   const uint32_t cm = a.clamped[i];
+  // the three statistics are read-modify-write: request them now, consume them after the gradient math
+  int stat_maxr = 0;
+  float stat_acc = 0.f, stat_den = 0.f;
+  if (f.max_radii2D && visible) {
+    stat_maxr = f.max_radii2D[i];
+    stat_acc = f.xyz_grad_accum[i];
+    stat_den = f.denom[i];
+  }
   __syncthreads();
   tma::mbar_wait(bar, 0);
 
@@ -704,47 +765,27 @@ preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __
         for (int ch = 0; ch < 3; ++ch) srow[3 * k + ch] = o.basis[k] * o.gr[ch];
       }
   }
+  // first Adam round's moments / parameters: requested before the block's gradients are complete in shared memory
+  const int nchunks = W + 14;
+  const int warp = tid >> 5, lane = tid & 31;
+  PbfRound<PBF_UNROLL> RA, RB;
+  pbf_request(RA, f, row0, W, nchunks, warp, lane);
   // densification statistics of this row (K5's second half) and the optional dL_dmeans2D sink
   if (f.max_radii2D && visible) {
-    if (radius > f.max_radii2D[i]) f.max_radii2D[i] = radius;
-    f.xyz_grad_accum[i] += __fsqrt_rn(__fadd_rn(__fmul_rn(o.g2x, o.g2x), __fmul_rn(o.g2y, o.g2y)));
-    f.denom[i] += 1.0f;
+    if (radius > stat_maxr) f.max_radii2D[i] = radius;
+    f.xyz_grad_accum[i] = __fadd_rn(stat_acc, __fsqrt_rn(__fadd_rn(__fmul_rn(o.g2x, o.g2x), __fmul_rn(o.g2y, o.g2y))));
+    f.denom[i] = __fadd_rn(stat_den, 1.0f);
   }
   if (a.out.dL_dmeans2D) reinterpret_cast<float2*>(a.out.dL_dmeans2D)[i] = make_float2(o.g2x, o.g2y);
   __syncthreads();
-  // ---- Adam over the block's rows (chunked, see pbf_chunk) ----
-  const int nchunks = W + 14;
-  const int warp = tid >> 5, lane = tid & 31;
-  const float b1 = f.b1, b2 = f.b2, omb1 = f.omb1, omb2 = f.omb2, eps = f.eps;
-  for (int c0 = warp; c0 < nchunks; c0 += 4 * PBF_UNROLL) {
-    PbfChunk ch[PBF_UNROLL];
-    float4 p[PBF_UNROLL], m[PBF_UNROLL], v[PBF_UNROLL];
-#pragma unroll
-    for (int u = 0; u < PBF_UNROLL; ++u) {
-      const int c = c0 + 4 * u;
-      if (c < nchunks) {
-        ch[u] = pbf_chunk(s_buf, f, row0, W, c);
-        m[u] = __ldcs(ch[u].m + lane);
-        v[u] = __ldcs(ch[u].v + lane);
-        p[u] = ch[u].p[lane];
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < PBF_UNROLL; ++u) {
-      const int c = c0 + 4 * u;
-      if (c < nchunks) {
-        const float4 g = ch[u].g[lane];
-        if (gs_adam_idle(g, m[u], v[u])) continue;  // exact fixed point (gs_common.cuh): nothing to write
-        const float neg_step = f.neg_step[ch[u].k], inv_bc2_sqrt = f.inv_bc2_sqrt[ch[u].k];
-        gs_adam_one(p[u].x, g.x, m[u].x, v[u].x, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-        gs_adam_one(p[u].y, g.y, m[u].y, v[u].y, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-        gs_adam_one(p[u].z, g.z, m[u].z, v[u].z, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-        gs_adam_one(p[u].w, g.w, m[u].w, v[u].w, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
-        __stcs(ch[u].m + lane, m[u]);
-        __stcs(ch[u].v + lane, v[u]);
-        ch[u].p[lane] = p[u];  // read again by the next forward
-      }
-    }
+  // ---- Adam over the block's rows (chunked and double-buffered, see pbf_chunk) ----
+  const GsAdamConst kc = {f.b1, f.b2, f.omb1, f.omb2, f.eps};
+  constexpr int STRIDE = 4 * PBF_UNROLL;  // chunks one round of this warp covers
+  for (int c0 = warp; c0 < nchunks; c0 += 2 * STRIDE) {
+    pbf_request(RB, f, row0, W, nchunks, c0 + STRIDE, lane);
+    pbf_update(RA, s_buf, f, kc);
+    pbf_request(RA, f, row0, W, nchunks, c0 + 2 * STRIDE, lane);
+    pbf_update(RB, s_buf, f, kc);
   }
 }
 
@@ -861,15 +902,28 @@ cudaError_t gs_launch_preprocess_backward_adam(const gs_settings& st, const gs_g
   f.max_radii2D = stats ? max_radii2D : nullptr;
   f.xyz_grad_accum = stats ? xyz_grad_accum : nullptr;
   f.denom = stats ? denom : nullptr;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(preprocess_backward_adam_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         PBB_SMEM_BYTES);
-    if (e != cudaSuccess) return e;
-    attr_set = true;
+  // tuning switch (measurement only): GS_FUSED_VARIANT = chunks per Adam round x resident blocks per SM
+  static int variant = -1;
+  if (variant < 0) {
+    const char* env = getenv("GS_FUSED_VARIANT");
+    variant = env ? atoi(env) : 0;
+    if (variant < 0 || variant > 3) variant = 0;
   }
   const int blocks = N / PBB_ROWS;
-  preprocess_backward_adam_kernel<<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, f);
+#define PBF_LAUNCH(U, B)                                                                                           \
+  do {                                                                                                             \
+    cudaError_t e = cudaFuncSetAttribute(preprocess_backward_adam_kernel<U, B>,                                    \
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, PBB_SMEM_BYTES);             \
+    if (e != cudaSuccess) return e;                                                                                \
+    preprocess_backward_adam_kernel<U, B><<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, f);                 \
+  } while (0)
+  switch (variant) {
+    case 1: PBF_LAUNCH(2, 5); break;
+    case 2: PBF_LAUNCH(2, 4); break;
+    case 3: PBF_LAUNCH(1, 6); break;
+    default: PBF_LAUNCH(1, 5); break;
+  }
+#undef PBF_LAUNCH
   *covered = blocks * PBB_ROWS;
   return cudaGetLastError();
 }

@@ -68,6 +68,7 @@ struct gs_trainer {
   float* slots = nullptr;  // pinned: RING x {loss, overflow flag}
   cudaEvent_t done[RING] = {};
   int iteration = 0, active_sh_degree = 0;
+  int sh_degree_at_0 = 0;  // the active SH degree is a function of the iteration number: sh_degree_at_0 + iteration / 1000
   long long step_count[6] = {0, 0, 0, 0, 0, 0};
   unsigned long long pair_capacity = 0;
   int retries = 0;
@@ -146,6 +147,7 @@ int gs_trainer_create(gs_trainer** out, int device, const gs_train_config* cfg, 
   {
     const int maxdeg = (int)lround(sqrt((double)sh_coeffs)) - 1;
     t->active_sh_degree = cfg->active_sh_degree < 0 ? 0 : (cfg->active_sh_degree > maxdeg ? maxdeg : cfg->active_sh_degree);
+    t->sh_degree_at_0 = t->active_sh_degree;
   }
   const float* src[6] = {xyz, f_dc, f_rest, opacity, scaling, rotation};
   auto fail = [&](int code) {
@@ -234,6 +236,12 @@ int gs_trainer_num_gaussians(const gs_trainer* t) { return t ? t->N : -1; }
 int gs_trainer_iteration(const gs_trainer* t) { return t ? t->iteration : -1; }
 int gs_trainer_retries(const gs_trainer* t) { return t ? t->retries : -1; }
 
+int gs_trainer_set_pair_capacity(gs_trainer* t, unsigned long long pairs) {
+  if (!t || pairs == 0) return GS_EINVAL;
+  t->pair_capacity = pairs;
+  return gs_set_duplicate_capacity(t->ctx, pairs);
+}
+
 int gs_trainer_get_params(gs_trainer* t, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling,
                           float* rotation) {
   if (!t) return GS_EINVAL;
@@ -277,11 +285,16 @@ int next_view(gs_trainer* t, int sampling) {
   return v;
 }
 
-// one iteration, enqueued on t->stream; its loss and overflow flag land in pinned slot `slot`
-int enqueue_iteration(gs_trainer* t, int view, int slot) {
+// Iteration number `iter_no`, enqueued on t->stream; its loss and overflow flag land in pinned slot `slot`.  Learning
+// rate and SH degree are functions of iter_no, so an iteration repeated after a capacity overflow runs under the
+// schedule of its own number (one more SH degree every 1000 iterations: src/utils/train_utils.cpp:133-136).
+int enqueue_iteration(gs_trainer* t, int iter_no, int view, int slot) {
   const gs_train_config& c = t->cfg;
-  t->iteration += 1;
-  if (t->iteration % 1000 == 0 && t->active_sh_degree < (int)lround(sqrt((double)t->K)) - 1) t->active_sh_degree += 1;
+  {
+    const int maxdeg = (int)lround(sqrt((double)t->K)) - 1;
+    const int deg = t->sh_degree_at_0 + iter_no / 1000;
+    t->active_sh_degree = deg > maxdeg ? maxdeg : deg;
+  }
   const View& v = t->views[(size_t)view];
   gs_settings st = v.st;
   st.sh_degree = t->active_sh_degree;
@@ -297,7 +310,7 @@ int enqueue_iteration(gs_trainer* t, int view, int slot) {
   TR_CUDA(t, cudaEventRecord(t->gt_free, t->stream));
   double lr[6] = {0, c.feature_lr, c.feature_lr / 20.0, c.opacity_lr, c.scaling_lr, c.rotation_lr};
   lr[0] = (double)gs_expon_lr((float)(c.position_lr_init * c.spatial_lr_scale), (float)(c.position_lr_final * c.spatial_lr_scale),
-                              0, (float)c.position_lr_delay_mult, c.position_lr_max_steps, t->iteration);
+                              0, (float)c.position_lr_delay_mult, c.position_lr_max_steps, iter_no);
   for (int k = 0; k < 6; ++k) t->step_count[k] += 1;
   TR_CHECK(gs_backward_adam_step(t->ctx, &st, t->N, &in, t->dL, nullptr, t->M, t->V, lr, t->step_count, 0.9, 0.999, 1e-8,
                                  t->max_radii2D, t->accum, t->denom, gs_overflow_guard(t->ctx), t->stream));
@@ -337,6 +350,11 @@ int densify_if_due(gs_trainer* t, float extent) {
       t->M[k] = nM[k];
       t->V[k] = nV[k];
     }
+    if (t->pair_capacity > 0 && n_new > t->N) {
+      // the (tile, Gaussian) pair count grows with N: keep the fixed capacity ahead of it
+      t->pair_capacity = (unsigned long long)((double)t->pair_capacity * ((double)n_new / (double)(t->N > 0 ? t->N : 1)) * 1.1) + 1024;
+      TR_CHECK(gs_set_duplicate_capacity(t->ctx, t->pair_capacity));
+    }
     t->N = n_new;
     TR_CHECK(trainer_alloc_stats(t, n_new));
   }
@@ -370,7 +388,7 @@ extern "C" int gs_trainer_run(gs_trainer* t, int n_iterations, float* losses, in
     TR_CHECK(gs_set_duplicate_capacity(t->ctx, t->pair_capacity));
   }
   struct Pending {
-    int j, view, slot;
+    int j, view, slot, iter_no;
   };
   std::vector<Pending> pending, redo;
   const int depth = 2;
@@ -382,12 +400,37 @@ extern "C" int gs_trainer_run(gs_trainer* t, int n_iterations, float* losses, in
     else losses[p.j] = t->slots[2 * p.slot];
     return GS_OK;
   };
+  // An overflowed iteration was void on the device (parameters, moments, statistics untouched).  Recover AT ONCE:
+  // drain, take back the void attempts' step counters, grow the capacity, repeat those iterations under their own
+  // iteration numbers -- before anything new is enqueued, so an outgrown capacity never voids the rest of a run.
+  auto recover = [&]() -> int {
+    while (!pending.empty()) TR_CHECK(retire());
+    while (!redo.empty()) {
+      std::vector<Pending> batch;
+      batch.swap(redo);
+      unsigned long long D = 0;
+      int ov = 0;
+      TR_CHECK(gs_get_forward_status(t->ctx, &D, &ov));
+      t->pair_capacity = std::max(2 * t->pair_capacity, (unsigned long long)(1.25 * (double)D));
+      TR_CHECK(gs_set_duplicate_capacity(t->ctx, t->pair_capacity));
+      t->retries += (int)batch.size();
+      for (const Pending& p : batch) {
+        for (int k = 0; k < 6; ++k) t->step_count[k] -= 1;
+        TR_CHECK(enqueue_iteration(t, p.iter_no, p.view, 0));
+        pending.push_back({p.j, p.view, 0, p.iter_no});
+        TR_CHECK(retire());
+      }
+    }
+    return GS_OK;
+  };
   for (int j = 0; j < n_iterations; ++j) {
     if ((int)pending.size() >= depth) TR_CHECK(retire());
+    if (!redo.empty()) TR_CHECK(recover());
     const int view = next_view(t, sampling);
     const int slot = j % gs_trainer::RING;
-    TR_CHECK(enqueue_iteration(t, view, slot));
-    pending.push_back({j, view, slot});
+    t->iteration += 1;
+    TR_CHECK(enqueue_iteration(t, t->iteration, view, slot));
+    pending.push_back({j, view, slot, t->iteration});
     if (densify_extent > 0.0f) {
       const gs_train_config& c = t->cfg;
       const int it = t->iteration;
@@ -395,26 +438,11 @@ extern "C" int gs_trainer_run(gs_trainer* t, int n_iterations, float* losses, in
                        ((it > c.densify_from_iter && c.densification_interval > 0 && it % c.densification_interval == 0) ||
                         (c.opacity_reset_interval > 0 && it % c.opacity_reset_interval == 0));
       if (due) {
-        while (!pending.empty()) TR_CHECK(retire());
+        TR_CHECK(recover());
         TR_CHECK(densify_if_due(t, densify_extent));
       }
     }
   }
-  while (!pending.empty()) TR_CHECK(retire());
-  while (!redo.empty()) {  // rare: grow the capacity, repeat the skipped views one at a time
-    std::vector<Pending> batch;
-    batch.swap(redo);
-    unsigned long long D = 0;
-    int ov = 0;
-    TR_CHECK(gs_get_forward_status(t->ctx, &D, &ov));
-    t->pair_capacity = std::max(2 * t->pair_capacity, (unsigned long long)(1.25 * (double)D));
-    TR_CHECK(gs_set_duplicate_capacity(t->ctx, t->pair_capacity));
-    t->retries += (int)batch.size();
-    for (const Pending& p : batch) {
-      TR_CHECK(enqueue_iteration(t, p.view, 0));
-      pending.push_back({p.j, p.view, 0});
-      TR_CHECK(retire());
-    }
-  }
+  TR_CHECK(recover());
   return GS_OK;
 }

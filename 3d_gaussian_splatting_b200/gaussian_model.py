@@ -203,6 +203,10 @@ class NativeTrainer:
                                                float(densify_extent)), "gs_trainer_run")
         return losses.tolist()
 
+    def set_pair_capacity(self, pairs: int):
+        """Fixed (tile, Gaussian) pair capacity (default: probed by the first run with one forward per view)."""
+        self._check(self._L.lib.gs_trainer_set_pair_capacity(self._t, int(pairs)), "set_pair_capacity")
+
     @property
     def N(self):
         return int(self._L.lib.gs_trainer_num_gaussians(self._t))
@@ -288,6 +292,11 @@ class Trainer:
             gaussians.setup(opt)
         self.lambda_dssim = opt.lambda_dssim if lambda_dssim is None else lambda_dssim
         self.iteration = 0
+        # active SH degree as a FUNCTION of the iteration number (one more every 1000 iterations,
+        # src/utils/train_utils.cpp:133-136 / gaussian_model.cpp:307-313), so that repeating an iteration after a
+        # capacity overflow cannot raise it twice
+        self._sh_degree_at_0 = gaussians.active_sh_degree
+        self.scale_capacity_on_densify = True
         self._gt_dev = None
         self._loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
         # capacity mode (no host round-trip inside the forward): enabled by reserve_pairs()
@@ -415,8 +424,13 @@ class Trainer:
                     old.detach_model()
                     old.close()
                     g.exp_avg, g.exp_avg_sq = m_full, v_full
+                n_before = g.N
                 done = g.densify_and_prune(self.rast, o.densify_grad_threshold, 0.005, extent, size_threshold,
                                            seed=iteration)
+                if self.pair_capacity and self.scale_capacity_on_densify and g.N > n_before:
+                    # the (tile, Gaussian) pair count grows with N: keep the fixed capacity ahead of it
+                    self.pair_capacity = int(self.pair_capacity * (g.N / max(n_before, 1)) * 1.1) + 1024
+                    self.rast.set_duplicate_capacity(self.pair_capacity)
                 if self.peer is not None:
                     from . import parallel
                     self.peer = parallel.PeerShardedAdam(g, self.rast, old.rank, old.world, group=old.group,
@@ -453,12 +467,19 @@ class Trainer:
             self.rast.set_duplicate_capacity(self.pair_capacity)
         return overflow
 
-    def train_step_device(self, cam, gt_dev: torch.Tensor, gt_host=None):
-        """Device-resident step: ground truth already in HBM; returns the loss as a device tensor."""
-        self.iteration += 1
-        self.g.update_learning_rate(self.iteration)
-        if self.iteration % 1000 == 0:
-            self.g.oneup_SH_degree()
+    def apply_schedules(self, iteration: int):
+        """Position learning rate and active SH degree of iteration `iteration` (idempotent)."""
+        self.g.update_learning_rate(iteration)
+        self.g.active_sh_degree = min(self.g.max_sh_degree, self._sh_degree_at_0 + iteration // 1000)
+
+    def train_step_device(self, cam, gt_dev: torch.Tensor, gt_host=None, iteration: int | None = None):
+        """Device-resident step: ground truth already in HBM; returns the loss as a device tensor.
+        iteration: run the step AS iteration number `iteration` (a repeated iteration after a capacity overflow keeps
+        its own number and with it its learning rate and SH degree); default: the next one."""
+        if iteration is None:
+            self.iteration += 1
+            iteration = self.iteration
+        self.apply_schedules(iteration)
         if self.fused_step and self.grad_sync is None and self.peer is None and self.sharded is None:
             # single GPU: K4b and K5 fused (gs_backward_adam_step) -- the gradient tensors never reach HBM
             loss, out = self.forward_backward(cam, gt_dev, gt_host=gt_host, fused_optimizer=True)
@@ -494,14 +515,18 @@ class Trainer:
         losses (floats, in order); on_loss(i, loss) is called as each arrives.
 
         Fixed pair capacity (reserve_pairs) is required -- the synchronous forward would stall the pipeline.  An
-        iteration whose forward overflows the capacity is skipped on the device (Adam guard); the host learns of
-        it `depth - 1` iterations late, drains the pipeline, doubles the capacity and runs that view again at the
-        end (the Adam bias-correction counters of the iterations that were already in flight stay one ahead).
+        iteration whose forward overflows the capacity is skipped on the device (Adam guard: parameters, moments and
+        densification statistics untouched).  The host learns of it `depth - 1` iterations late and recovers AT ONCE:
+        it drains the pipeline, takes back the step counters of the void iterations, grows the capacity and runs
+        those iterations again under their ORIGINAL iteration numbers (learning rate, SH degree) before it enqueues
+        anything new -- so a capacity outgrown in the middle of a long run (densification) costs a few repeated
+        iterations, never the rest of the schedule.  (Iterations that were already in flight behind a void one and
+        did fit have run with a bias-correction counter one ahead.)
 
         densify_extent (the scene extent): run the densification schedule of the published loop
-        (densification_step) -- the pipeline is drained first, since N changes.  Unlike the published loop, whose
-        freshly concatenated parameters carry no gradient in that iteration, the iteration's optimiser step has
-        already been applied when the model is densified."""
+        (densification_step) -- the pipeline is drained first, since N changes, and the pair capacity follows N.
+        Unlike the published loop, whose freshly concatenated parameters carry no gradient in that iteration, the
+        iteration's optimiser step has already been applied when the model is densified."""
         assert self.pair_capacity, "Trainer.train needs reserve_pairs() (capacity mode)"
         dev = self.g.device
         shape = gts_host[0].shape
@@ -511,17 +536,16 @@ class Trainer:
         if getattr(self, "_ring", None) is None or self._ring[0].shape[0] != ring:
             self._ring = (torch.zeros(ring, 2, dtype=torch.float32).pin_memory(),
                           [torch.cuda.Event() for _ in range(ring)])
-            gp = self.skip_guard if isinstance(self.skip_guard, int) else None
-            self._guard_view = self._guard_tensor if self._guard_tensor is not None else self.rast.wrap(gp, 1)
+        ctx_guard = self.rast.wrap(self.rast.overflow_guard_ptr(), 1)   # the context's own flag (stable address)
         slots, events = self._ring
         stream = torch.cuda.current_stream(dev)
-        losses, pending, redo = [None] * n_steps, [], []
+        losses, pending, void = [None] * n_steps, [], []
 
         def retire():
-            j, slot = pending.pop(0)
+            j, slot, it_no = pending.pop(0)
             events[slot].synchronize()
             if slots[slot, 1] != 0.0:      # iteration j overflowed: skipped on the device
-                redo.append(j)
+                void.append((j, it_no))
                 return
             losses[j] = float(slots[slot, 0])
             if on_loss is not None:
@@ -529,34 +553,42 @@ class Trainer:
 
         drawn = {}
 
-        def enqueue(j, slot):
+        def enqueue(j, slot, it_no):
             if j not in drawn:      # (a repeated iteration after an overflow keeps its view)
                 drawn[j] = sampler() if sampler is not None else (first + j) % len(cams)
             v = drawn[j]
-            loss = self.train_step_device(cams[v], self._gt_dev, gt_host=gts_host[v])
+            loss = self.train_step_device(cams[v], self._gt_dev, gt_host=gts_host[v], iteration=it_no)
             slots[slot, 0:1].copy_(loss.reshape(1), non_blocking=True)
-            guard = self._guard_tensor if self._guard_tensor is not None else self._guard_view
-            slots[slot, 1:2].copy_(guard, non_blocking=True)
+            # (looked up per iteration: a densification step in peer mode installs a new caller-owned guard)
+            slots[slot, 1:2].copy_(self._guard_tensor if self._guard_tensor is not None else ctx_guard, non_blocking=True)
             events[slot].record(stream)
-            pending.append((j, slot))
+            pending.append((j, slot, it_no))
+
+        def recover():
+            """Drain, then repeat every void iteration (one at a time, growing the capacity until it fits)."""
+            while pending:
+                retire()
+            while void:
+                batch = list(void)
+                del void[:]
+                D, _ = self.rast.forward_status()
+                self.pair_capacity = max(2 * self.pair_capacity, int(1.25 * D))
+                self.rast.set_duplicate_capacity(self.pair_capacity)
+                self.retries += len(batch)
+                for j, it_no in batch:
+                    self.g.step_count = [s - 1 for s in self.g.step_count]   # the void attempt's increment
+                    enqueue(j, 0, it_no)
+                    retire()
 
         for i in range(n_steps):
             if len(pending) >= depth:
                 retire()
-            enqueue(i, i % ring)
+            if void:
+                recover()
+            self.iteration += 1
+            enqueue(i, i % ring, self.iteration)
             if densify_extent is not None and self.densification_due(self.iteration):
-                while pending:
-                    retire()
+                recover()
                 self.densification_step(self.iteration, densify_extent)
-        while pending:
-            retire()
-        while redo:      # rare: overflowed views, one at a time with a grown capacity
-            batch, redo = redo, []
-            D, _ = self.rast.forward_status()
-            self.pair_capacity = max(2 * self.pair_capacity, int(1.25 * D))
-            self.rast.set_duplicate_capacity(self.pair_capacity)
-            self.retries += len(batch)
-            for j in batch:
-                enqueue(j, 0)
-                retire()
+        recover()
         return losses

@@ -342,6 +342,11 @@ GS_API int gs_trainer_run(gs_trainer *t, int n_iterations, float *losses, int sa
 GS_API int gs_trainer_num_gaussians(const gs_trainer *t);
 GS_API int gs_trainer_iteration(const gs_trainer *t);
 GS_API int gs_trainer_retries(const gs_trainer *t); /* iterations repeated after a pair-capacity overflow */
+/* Fix the (tile, Gaussian) pair capacity of the trainer's forwards instead of letting the first gs_trainer_run probe
+ * it with one synchronous forward per view.  Too small a value is not an error: an overflowing iteration is void on
+ * the device, and the loop repeats it at once under its own iteration number with a grown capacity (and after a
+ * densification step the capacity follows N). */
+GS_API int gs_trainer_set_pair_capacity(gs_trainer *t, unsigned long long pairs);
 GS_API int gs_trainer_get_params(gs_trainer *t, float *xyz, float *features_dc, float *features_rest,
                                  float *opacity, float *scaling, float *rotation); /* any may be NULL */
 

@@ -44,6 +44,15 @@ def elem_err(a, b, floor=1e-3):
     return float((np.abs(a - b) / scale).max())
 
 
+def frac_elem_beyond(a, b, tol=1e-3, floor=1e-3):
+    """Share of the elements whose floored per-element relative error (elem_err's measure) exceeds tol."""
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    if b.size == 0:
+        return 0.0
+    scale = np.maximum(np.abs(b), floor * max(np.abs(b).max(), 1e-300))
+    return float((np.abs(a - b) / scale > tol).mean())
+
+
 def min_row_cosine(a, b, floor=1e-3):
     """Smallest cosine similarity between matching per-Gaussian rows (rows whose reference norm is above floor * the
     largest row norm; the others are covered by elem_err's absolute floor).  1.0 when no row qualifies."""

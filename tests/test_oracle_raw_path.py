@@ -39,3 +39,26 @@ def test_raw_reference_equals_activated_path_with_manual_jacobians(oracle):
     assert rel_err(gr["dL_dscales"][same], (g["dL_dscales"] * sc)[same]) < 5e-3
     assert rel_err(gr["dL_dopacities"][same], (g["dL_dopacities"].reshape(-1, 1) * op * (1 - op))[same]) < 5e-3
     assert rel_err(gr["dL_dmeans3D"][same], g["dL_dmeans3D"][same]) < 5e-3
+
+
+def test_fp32_conditioning_of_the_gradients(oracle, oracle64):
+    """The bars of the GPU gradient tests (tests/test_gpu_raw_path.py) are set where the ALGORITHM sits in fp32: on
+    cfg0 (no decision differs between the two builds) the fp32 oracle is within 1e-4 of its float64 build relative
+    to the array maximum, but only within ~1e-3 per element (floor 1e-3 of the maximum) for the covariance gradients
+    -- differences of products that no fp32 evaluation order gets closer to."""
+    from helpers import elem_err, syn
+    scene, cams, deg = syn.make_config("cfg0_10k_256_sh0", n_cameras=3)
+    cam = cams[1]
+    rng = np.random.default_rng(9)
+    dL = ((rng.random((3, 256, 256)) * 2 - 1) / 65536).astype(np.float32)
+    r32 = raw_reference(oracle, scene, cam, deg, deg, dL=dL)
+    r64 = raw_reference(oracle64, scene, cam, deg, deg, dL=dL)
+    assert np.array_equal(r32["pre"]["radii"], r64["pre"]["radii"])
+    assert np.array_equal(r32["fwd"]["n_contrib"], r64["fwd"]["n_contrib"])
+    worst = {}
+    for k in ("dL_dmeans3D", "dL_dscales", "dL_drotations", "dL_dopacities", "dL_dshs"):
+        a, b = r32["g_ref"][k], r64["g_ref"][k]
+        assert rel_err(a, b) < 2e-4, k
+        worst[k] = elem_err(a, b)
+    assert max(worst.values()) < 5e-3
+    assert max(worst["dL_dscales"], worst["dL_drotations"]) > 3e-4      # ... and it really is that large in fp32
