@@ -83,18 +83,22 @@ __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_
     const GsAdamConst kc = {b1, b2, omb1, omb2, eps};
     GsAdamQuad q[AD_VEC_PER_THREAD];
     bool idle[AD_VEC_PER_THREAD];
-    bool fast = true, any_active = false;
+    bool any_active = false;
+    int mode = GS_ADAM_FAST;
 #pragma unroll
     for (int k = 0; k < AD_VEC_PER_THREAD; ++k) {
       idle[k] = gs_adam_idle(g[k], m[k], v[k]);  // exact fixed point (gs_common.cuh): nothing to write
-      const bool ok = gs_adam_quad_moments(g[k], m[k], v[k], kc, q[k]);
-      fast = fast && (idle[k] || ok);
+      const int ok = gs_adam_quad_moments(g[k], m[k], v[k], kc, q[k]);
+      if (!idle[k]) mode = min(mode, ok);
       any_active = any_active || !idle[k];
     }
     if (!__any_sync(0xffffffffu, any_active)) return;
-    if (__all_sync(0xffffffffu, fast)) {
+    if (__all_sync(0xffffffffu, mode == GS_ADAM_FAST)) {
 #pragma unroll
-      for (int k = 0; k < AD_VEC_PER_THREAD; ++k) gs_adam_quad_step(p[k], m[k], v[k], q[k], eps, neg_step, inv_bc2_sqrt);
+      for (int k = 0; k < AD_VEC_PER_THREAD; ++k) gs_adam_quad_step<false>(p[k], m[k], v[k], q[k], eps, neg_step, inv_bc2_sqrt);
+    } else if (__all_sync(0xffffffffu, mode >= GS_ADAM_FAST_Z)) {
+#pragma unroll
+      for (int k = 0; k < AD_VEC_PER_THREAD; ++k) gs_adam_quad_step<true>(p[k], m[k], v[k], q[k], eps, neg_step, inv_bc2_sqrt);
     } else {
 #pragma unroll
       for (int k = 0; k < AD_VEC_PER_THREAD; ++k)
@@ -278,8 +282,9 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
     {
       const GsAdamConst kc = {b1, b2, omb1, omb2, eps};
       GsAdamQuad q;
-      const bool ok = gs_adam_quad_moments(g, m, v, kc, q);
-      if (__all_sync(0xffffffffu, idle || ok)) gs_adam_quad_step(p, m, v, q, eps, neg_step, inv_bc2_sqrt);
+      const int ok = idle ? GS_ADAM_FAST : gs_adam_quad_moments(g, m, v, kc, q);
+      if (__all_sync(0xffffffffu, ok == GS_ADAM_FAST)) gs_adam_quad_step<false>(p, m, v, q, eps, neg_step, inv_bc2_sqrt);
+      else if (__all_sync(0xffffffffu, ok >= GS_ADAM_FAST_Z)) gs_adam_quad_step<true>(p, m, v, q, eps, neg_step, inv_bc2_sqrt);
       else if (!idle) gs_adam_quad_scalar(p, g, m, v, kc, neg_step, inv_bc2_sqrt);
     }
     if (idle) return;

@@ -648,25 +648,31 @@ __device__ __forceinline__ void pbf_update(PbfRound<PBF_UNROLL>& R, const float*
   float4 g[PBF_UNROLL];
   GsAdamQuad q[PBF_UNROLL];
   bool idle[PBF_UNROLL];
-  bool any_active = false, fast = true;
+  bool any_active = false;
+  int mode = GS_ADAM_FAST;  // the weakest path any of this lane's live vectors needs
 #pragma unroll
   for (int u = 0; u < PBF_UNROLL; ++u) {
     idle[u] = true;
     if (R.k[u] >= 0) {
       g[u] = reinterpret_cast<const float4*>(s_buf)[R.gvec[u]];
       idle[u] = gs_adam_idle(g[u], R.m[u], R.v[u]);  // exact fixed point (gs_common.cuh): nothing to write
-      const bool ok = gs_adam_quad_moments(g[u], R.m[u], R.v[u], kc, q[u]);
-      fast = fast && (idle[u] || ok);
+      const int ok = gs_adam_quad_moments(g[u], R.m[u], R.v[u], kc, q[u]);
+      if (!idle[u]) mode = min(mode, ok);
       any_active = any_active || !idle[u];
     }
   }
   if (!__any_sync(0xffffffffu, any_active)) return;
-  if (__all_sync(0xffffffffu, fast)) {
-    // packed path (gs_common.cuh): both chunks' pairs in one basic block -- four independent dependency chains
+  // packed paths (gs_common.cuh): the round's pairs in one basic block -- independent dependency chains
+  if (__all_sync(0xffffffffu, mode == GS_ADAM_FAST)) {
 #pragma unroll
     for (int u = 0; u < PBF_UNROLL; ++u)
       if (R.k[u] >= 0)
-        gs_adam_quad_step(R.p[u], R.m[u], R.v[u], q[u], kc.eps, f.neg_step[R.k[u]], f.inv_bc2_sqrt[R.k[u]]);
+        gs_adam_quad_step<false>(R.p[u], R.m[u], R.v[u], q[u], kc.eps, f.neg_step[R.k[u]], f.inv_bc2_sqrt[R.k[u]]);
+  } else if (__all_sync(0xffffffffu, mode >= GS_ADAM_FAST_Z)) {
+#pragma unroll
+    for (int u = 0; u < PBF_UNROLL; ++u)
+      if (R.k[u] >= 0)
+        gs_adam_quad_step<true>(R.p[u], R.m[u], R.v[u], q[u], kc.eps, f.neg_step[R.k[u]], f.inv_bc2_sqrt[R.k[u]]);
   } else {
 #pragma unroll
     for (int u = 0; u < PBF_UNROLL; ++u)

@@ -13,10 +13,12 @@
 // Views are drawn without replacement from a stack refilled when empty (the published loop's viewpoint_stack), by
 // a specified counter-based generator; GS_SAMPLE_CYCLIC walks them in order instead.
 #include <math.h>
+#include <stdio.h>
 #include <string.h>
 
 #include <algorithm>
 #include <new>
+#include <string>
 #include <vector>
 
 #include "gs_common.cuh"
@@ -240,6 +242,179 @@ int gs_trainer_set_pair_capacity(gs_trainer* t, unsigned long long pairs) {
   if (!t || pairs == 0) return GS_EINVAL;
   t->pair_capacity = pairs;
   return gs_set_duplicate_capacity(t->ctx, pairs);
+}
+
+// ---- checkpoint of the live training state (the start_checkpoint hook of src/utils/train_utils.cpp:110-113) ----
+// One file in the flat container of 3d_gaussian_splatting_b200/checkpoint.py (libgsplat_b200.so does not link
+// libtorch; checkpoint.native_to_libtorch converts it into the reference's torch::save archives):
+//   magic "GSB200CK" | u32 version 1 | u32 n_entries | entry*;  entry := u8 dtype (0 f32, 1 i32, 2 i64) | u8 ndim |
+//   u16 0 | u64 dims[ndim] | raw bytes.
+// Entries: [0] i64[8] {iteration, active_sh_degree, sh_degree_at_0, N, K, draws, pair_capacity, 0}; [1] i64[6] Adam
+// step counters; [2..7] parameters, [8..13] exp_avg, [14..19] exp_avg_sq (group order of GaussianModel::setup);
+// [20] max_radii2D i32; [21] xyz_gradient_accum; [22] denom; [23] i32 views not yet drawn in this pass.
+namespace {
+struct FlatWriter {
+  FILE* f;
+  bool ok;
+  void entry(int dtype, const std::vector<unsigned long long>& dims, const void* data, size_t bytes) {
+    const unsigned char head[4] = {(unsigned char)dtype, (unsigned char)dims.size(), 0, 0};
+    ok = ok && fwrite(head, 1, 4, f) == 4;
+    for (unsigned long long d : dims) ok = ok && fwrite(&d, 8, 1, f) == 1;
+    if (bytes) ok = ok && fwrite(data, 1, bytes, f) == bytes;
+  }
+};
+}  // namespace
+
+int gs_trainer_save(gs_trainer* t, const char* path) {
+  if (!t || !path) return GS_EINVAL;
+  TR_CUDA(t, cudaSetDevice(t->device));
+  TR_CUDA(t, cudaStreamSynchronize(t->stream));
+  const std::string tmp = std::string(path) + ".tmp";
+  FILE* f = fopen(tmp.c_str(), "wb");
+  if (!f) {
+    gs_set_error(t->ctx, "gs_trainer_save: cannot open %s", tmp.c_str());
+    return GS_EINVAL;
+  }
+  FlatWriter w{f, true};
+  const unsigned int ver = 1, n_entries = 24;
+  w.ok = fwrite("GSB200CK", 1, 8, f) == 8 && fwrite(&ver, 4, 1, f) == 1 && fwrite(&n_entries, 4, 1, f) == 1;
+  const long long head[8] = {t->iteration, t->active_sh_degree, t->sh_degree_at_0, t->N, t->K, (long long)t->draws,
+                             (long long)t->pair_capacity, 0};
+  w.entry(2, {8}, head, sizeof(head));
+  w.entry(2, {6}, t->step_count, sizeof(t->step_count));
+  std::vector<char> host;
+  auto dev_entry = [&](int dtype, const void* dptr, unsigned long long rows, unsigned long long cols) -> int {
+    const size_t bytes = (size_t)rows * cols * 4;
+    host.resize(bytes ? bytes : 1);
+    if (bytes) TR_CUDA(t, cudaMemcpy(host.data(), dptr, bytes, cudaMemcpyDeviceToHost));
+    w.entry(dtype, {rows, cols}, host.data(), bytes);
+    return GS_OK;
+  };
+  float* const* slabs[3] = {t->P, t->M, t->V};
+  for (int a = 0; a < 3; ++a)
+    for (int k = 0; k < 6; ++k) {
+      const int rc = dev_entry(0, slabs[a][k], (unsigned long long)t->N, (unsigned long long)t->widths[k]);
+      if (rc != GS_OK) {
+        fclose(f);
+        remove(tmp.c_str());
+        return rc;
+      }
+    }
+  int rc = dev_entry(1, t->max_radii2D, (unsigned long long)t->N, 1);
+  if (rc == GS_OK) rc = dev_entry(0, t->accum, (unsigned long long)t->N, 1);
+  if (rc == GS_OK) rc = dev_entry(0, t->denom, (unsigned long long)t->N, 1);
+  if (rc != GS_OK) {
+    fclose(f);
+    remove(tmp.c_str());
+    return rc;
+  }
+  w.entry(1, {(unsigned long long)t->stack.size()}, t->stack.data(), t->stack.size() * 4);
+  const bool closed = fclose(f) == 0;
+  if (!w.ok || !closed || rename(tmp.c_str(), path) != 0) {  // a crash never leaves a truncated file under the final name
+    remove(tmp.c_str());
+    gs_set_error(t->ctx, "gs_trainer_save: writing %s failed", path);
+    return GS_EINVAL;
+  }
+  return GS_OK;
+}
+
+int gs_trainer_load(gs_trainer* t, const char* path) {
+  if (!t || !path) return GS_EINVAL;
+  TR_CUDA(t, cudaSetDevice(t->device));
+  TR_CUDA(t, cudaStreamSynchronize(t->stream));
+  FILE* f = fopen(path, "rb");
+  if (!f) {
+    gs_set_error(t->ctx, "gs_trainer_load: cannot open %s", path);
+    return GS_EINVAL;
+  }
+  struct Entry {
+    int dtype;
+    std::vector<unsigned long long> dims;
+    std::vector<char> data;
+  };
+  std::vector<Entry> e;
+  bool ok = true;
+  char magic[8];
+  unsigned int ver = 0, n = 0;
+  ok = fread(magic, 1, 8, f) == 8 && memcmp(magic, "GSB200CK", 8) == 0 && fread(&ver, 4, 1, f) == 1 && ver == 1 &&
+       fread(&n, 4, 1, f) == 1 && n == 24;
+  for (unsigned int i = 0; ok && i < n; ++i) {
+    unsigned char head[4];
+    ok = fread(head, 1, 4, f) == 4 && head[0] <= 3 && head[1] <= 4;
+    if (!ok) break;
+    Entry en;
+    en.dtype = head[0];
+    size_t count = 1;
+    for (int d = 0; ok && d < head[1]; ++d) {
+      unsigned long long v = 0;
+      ok = fread(&v, 8, 1, f) == 1 && v < (1ull << 40);
+      en.dims.push_back(v);
+      count *= (size_t)v;
+    }
+    const size_t bytes = count * ((en.dtype == 2 || en.dtype == 3) ? 8 : 4);
+    if (ok && bytes > ((size_t)1 << 40)) ok = false;
+    if (ok) {
+      en.data.resize(bytes ? bytes : 1);
+      ok = bytes == 0 || fread(en.data.data(), 1, bytes, f) == bytes;
+    }
+    e.push_back(std::move(en));
+  }
+  fclose(f);
+  if (!ok || e.size() != 24 || e[0].data.size() < 64 || e[1].data.size() < 48) {
+    gs_set_error(t->ctx, "gs_trainer_load: %s is not a gs_trainer checkpoint (or is truncated)", path);
+    return GS_EINVAL;
+  }
+  const long long* head = (const long long*)e[0].data.data();
+  const int N = (int)head[3], K = (int)head[4];
+  if (K != t->K || N < 0) {
+    gs_set_error(t->ctx, "gs_trainer_load: checkpoint has %d SH coefficients, the trainer %d", K, t->K);
+    return GS_EINVAL;
+  }
+  for (int a = 0; a < 3; ++a)
+    for (int k = 0; k < 6; ++k)
+      if (e[2 + 6 * a + k].data.size() < (size_t)N * t->widths[k] * 4) {
+        gs_set_error(t->ctx, "gs_trainer_load: entry %d is too short", 2 + 6 * a + k);
+        return GS_EINVAL;
+      }
+  if (e[20].data.size() < (size_t)N * 4 || e[21].data.size() < (size_t)N * 4 || e[22].data.size() < (size_t)N * 4) {
+    gs_set_error(t->ctx, "gs_trainer_load: statistics entries are too short");
+    return GS_EINVAL;
+  }
+  float** slabs[3] = {t->P, t->M, t->V};
+  for (int a = 0; a < 3; ++a)
+    for (int k = 0; k < 6; ++k) {
+      const size_t bytes = (size_t)N * t->widths[k] * 4;
+      cudaFree(slabs[a][k]);
+      slabs[a][k] = nullptr;
+      TR_CUDA(t, cudaMalloc(&slabs[a][k], bytes > 16 ? bytes : 16));
+      if (bytes) TR_CUDA(t, cudaMemcpy(slabs[a][k], e[2 + 6 * a + k].data.data(), bytes, cudaMemcpyHostToDevice));
+    }
+  t->N = N;
+  TR_CHECK(trainer_alloc_stats(t, N));
+  TR_CUDA(t, cudaStreamSynchronize(t->stream));
+  if (N > 0) {
+    TR_CUDA(t, cudaMemcpy(t->max_radii2D, e[20].data.data(), (size_t)N * 4, cudaMemcpyHostToDevice));
+    TR_CUDA(t, cudaMemcpy(t->accum, e[21].data.data(), (size_t)N * 4, cudaMemcpyHostToDevice));
+    TR_CUDA(t, cudaMemcpy(t->denom, e[22].data.data(), (size_t)N * 4, cudaMemcpyHostToDevice));
+  }
+  t->iteration = (int)head[0];
+  t->active_sh_degree = (int)head[1];
+  t->sh_degree_at_0 = (int)head[2];
+  t->draws = (uint32_t)head[5];
+  if (head[6] > 0 && (unsigned long long)head[6] > t->pair_capacity) {
+    t->pair_capacity = (unsigned long long)head[6];
+    TR_CHECK(gs_set_duplicate_capacity(t->ctx, t->pair_capacity));
+  }
+  memcpy(t->step_count, e[1].data.data(), sizeof(t->step_count));
+  const int* st = (const int*)e[23].data.data();
+  const size_t ns = e[23].dims.empty() ? 0 : (size_t)e[23].dims[0];
+  t->stack.assign(st, st + ns);
+  for (int v : t->stack)
+    if (v < 0 || v >= (int)t->views.size()) {
+      t->stack.clear();  // the views of this trainer differ from the checkpoint's: start a fresh pass
+      break;
+    }
+  return GS_OK;
 }
 
 int gs_trainer_get_params(gs_trainer* t, float* xyz, float* f_dc, float* f_rest, float* opacity, float* scaling,

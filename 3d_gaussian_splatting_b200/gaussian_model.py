@@ -151,6 +151,24 @@ class GaussianModel:
         """opacity <- logit(min(sigmoid(opacity), 0.01)), fresh Adam state for the group (opacity_reset_interval_)."""
         rast.reset_opacity(self.opacity_, self.exp_avg[3], self.exp_avg_sq[3])
 
+    # ---- checkpoint (src/scene/gaussian_model.cpp:228-262; files: checkpoint.py) ----
+    def capture(self, tensors_path, opt_path_for_xyz=None, opt_path_for_f_dc=None, opt_path_for_f_rest=None,
+                opt_path_for_opacity=None, opt_path_for_scaling=None, opt_path_for_rotation=None, fmt="libtorch",
+                moments=None):
+        """GaussianModel::capture: the eleven tensors + one Adam archive per parameter group, in the reference's own
+        torch::save format by default."""
+        from . import checkpoint
+        checkpoint.capture(self, tensors_path, opt_path_for_xyz, opt_path_for_f_dc, opt_path_for_f_rest,
+                           opt_path_for_opacity, opt_path_for_scaling, opt_path_for_rotation, fmt=fmt, moments=moments)
+
+    def restore(self, params: OptimizationParams, tensors_path, opt_path_for_xyz=None, opt_path_for_f_dc=None,
+                opt_path_for_f_rest=None, opt_path_for_opacity=None, opt_path_for_scaling=None,
+                opt_path_for_rotation=None):
+        """GaussianModel::restore (gaussian_model.cpp:247-262): setup(params), then every file that exists."""
+        from . import checkpoint
+        checkpoint.restore(self, tensors_path, opt_path_for_xyz, opt_path_for_f_dc, opt_path_for_f_rest,
+                           opt_path_for_opacity, opt_path_for_scaling, opt_path_for_rotation, opt_params=params)
+
     def grad_sinks(self):
         g = self.grads
         return dict(means3D=g[0], sh_dc=g[1], sh_rest=g[2], opacities=g[3], scales=g[4], rotations=g[5],
@@ -202,6 +220,14 @@ class NativeTrainer:
         self._check(self._L.lib.gs_trainer_run(self._t, int(n), losses.ctypes.data_as(C.c_void_p), int(cyclic),
                                                float(densify_extent)), "gs_trainer_run")
         return losses.tolist()
+
+    def save(self, path: str):
+        """gs_trainer_save: the live training state into one flat-container file (checkpoint.native_to_libtorch
+        converts it into the reference's torch::save archives)."""
+        self._check(self._L.lib.gs_trainer_save(self._t, str(path).encode()), "gs_trainer_save")
+
+    def load(self, path: str):
+        self._check(self._L.lib.gs_trainer_load(self._t, str(path).encode()), "gs_trainer_load")
 
     def set_pair_capacity(self, pairs: int):
         """Fixed (tile, Gaussian) pair capacity (default: probed by the first run with one forward per view)."""
@@ -392,6 +418,55 @@ class Trainer:
                                     radii=radii, dL_dmeans2D=g.grad_means2D, max_radii2D=g.max_radii2D_,
                                     xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_,
                                     skip_guard=self.skip_guard if self.pair_capacity else None)
+
+    # ---- checkpoint of the LIVE training state (the start_checkpoint hook of src/utils/train_utils.cpp:110-113) ----
+    def capture(self, folder: str, fmt: str = "libtorch"):
+        """Write the seven files of a checkpoint of the model being trained into `folder`, named *_<iteration>
+        (search_for_max_iteration finds the newest).  Drains nothing: call between iterations.  In peer mode the
+        sharded Adam moments are gathered first (every rank gets the full state; rank 0 writes)."""
+        from . import checkpoint
+        torch.cuda.synchronize(self.g.device)
+        moments = None
+        if self.peer is not None:
+            moments = self.peer.gather_moments()
+            import torch.distributed as dist
+            if dist.is_initialized() and dist.get_rank(self.peer.group) != 0:
+                return None
+        assert self.sharded is None, "checkpointing the NCCL-sharded optimiser is not wired (use the peer mode)"
+        paths = checkpoint.checkpoint_paths(folder, self.iteration)
+        self.g.capture(*paths, fmt=fmt, moments=moments)
+        return paths
+
+    def restore(self, folder: str, iteration: int | None = None):
+        """Load the checkpoint of `iteration` (default: the newest in `folder`) into the live model: parameters,
+        statistics, Adam moments and step counters, learning rates, the iteration counter and the SH-degree
+        schedule.  Returns the iteration restored."""
+        from . import checkpoint
+        assert self.sharded is None, "restoring into the NCCL-sharded optimiser is not wired (use the peer mode)"
+        if iteration is None:
+            iteration = checkpoint.search_for_max_iteration(folder)
+            if iteration < 0:
+                raise FileNotFoundError(f"no checkpoint in {folder}")
+        paths = checkpoint.checkpoint_paths(folder, iteration)
+        torch.cuda.synchronize(self.g.device)
+        g = self.g
+        old = self.peer
+        if old is not None:            # the parameters are views of the peer buffer: release it, re-shard afterwards
+            old.detach_model()
+            old.close()
+            self.peer = None
+        g.restore(self.opt, *paths)
+        self.iteration = int(iteration)
+        self._sh_degree_at_0 = g.active_sh_degree - self.iteration // 1000
+        if old is not None:
+            from . import parallel
+            self.peer = parallel.PeerShardedAdam(g, self.rast, old.rank, old.world, group=old.group,
+                                                 moments=(g.exp_avg, g.exp_avg_sq))
+            if self.pair_capacity:
+                self.reserve_pairs(self.pair_capacity, guard=self.peer.guard)
+        elif self.on_resize is not None:
+            self.on_resize()
+        return self.iteration
 
     def densification_due(self, iteration: int) -> bool:
         o = self.opt

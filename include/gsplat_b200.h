@@ -347,6 +347,15 @@ GS_API int gs_trainer_retries(const gs_trainer *t); /* iterations repeated after
  * the device, and the loop repeats it at once under its own iteration number with a grown capacity (and after a
  * densification step the capacity follows N). */
 GS_API int gs_trainer_set_pair_capacity(gs_trainer *t, unsigned long long pairs);
+/* Checkpoint of the LIVE training state -- parameters, Adam moments and step counters, densification statistics,
+ * iteration, SH-degree schedule, pair capacity, the sampler's position -- the start_checkpoint hook the reference's
+ * train() leaves commented out (src/utils/train_utils.cpp:110-113; what it would save:
+ * GaussianModel::capture, src/scene/gaussian_model.cpp:228-262).  One file in the dependency-free flat container of
+ * 3d_gaussian_splatting_b200/checkpoint.py (this library does not link libtorch); checkpoint.native_to_libtorch turns
+ * it into the seven torch::save archives CoreParams::restore reads (gaussian_model.cpp:152-202).  Call between
+ * gs_trainer_run calls.  gs_trainer_load replaces the model (N may differ) and resumes exactly where save left. */
+GS_API int gs_trainer_save(gs_trainer *t, const char *path);
+GS_API int gs_trainer_load(gs_trainer *t, const char *path);
 GS_API int gs_trainer_get_params(gs_trainer *t, float *xyz, float *features_dc, float *features_rest,
                                  float *opacity, float *scaling, float *rotation); /* any may be NULL */
 

@@ -43,11 +43,12 @@ FIELDS = ["xyz_", "features_dc_", "features_rest_", "scaling_", "rotation_", "op
           "xyz_gradient_accum_", "denom_"]
 
 
-def test_capture_restore_roundtrip(tmp_path):
+@pytest.mark.parametrize("fmt", ["libtorch", "flat"])
+def test_capture_restore_roundtrip(tmp_path, fmt):
     a = Model(N=1234, seed=1)
     paths = ck.checkpoint_paths(str(tmp_path), 7000)
     assert len(paths) == 7
-    ck.capture(a, *paths)
+    ck.capture(a, *paths, fmt=fmt)
     b = Model(N=10, seed=2)                 # different N: restore re-shapes the optimiser state
     ck.restore(b, *paths)
     for f in FIELDS:
@@ -57,7 +58,7 @@ def test_capture_restore_roundtrip(tmp_path):
         assert torch.equal(a.exp_avg[k], b.exp_avg[k]) and torch.equal(a.exp_avg_sq[k], b.exp_avg_sq[k])
     assert b.step_count == a.step_count and b.lr == a.lr
     # entry order of the tensors file == the reference's vector (gaussian_model.cpp:85-97)
-    e = ck.read_entries(paths[0])
+    e = ck.read_entries(paths[0]) if fmt == "flat" else [x.numpy() for x in ck.read_tensor_archive(paths[0])]
     assert len(e) == 11 and int(e[0]) == 2 and e[1].shape == (1234, 3) and e[3].shape == (1234, 15, 3)
     assert e[4].shape == (1234, 3) and e[5].shape == (1234, 4) and e[6].shape == (1234, 1) and e[7].dtype == np.int32
     assert float(e[10]) == 1.25
@@ -80,7 +81,7 @@ def test_restore_tolerates_missing_files_like_the_reference(tmp_path):
 def test_empty_model_and_corruption(tmp_path):
     a = Model(N=0, seed=1)
     p = ck.checkpoint_paths(str(tmp_path), 1)
-    ck.capture(a, *p)
+    ck.capture(a, *p, fmt="flat")
     b = Model(N=3, seed=2)
     ck.restore(b, *p)
     assert b.N == 0
@@ -90,7 +91,7 @@ def test_empty_model_and_corruption(tmp_path):
         ck.restore(b, *p)
     blob = open(p[1], "rb").read()
     open(p[1], "wb").write(blob[:-1] if len(blob) > 40 else blob[:20])
-    ck.capture(Model(N=5, seed=1), *ck.checkpoint_paths(str(tmp_path / "t"), 2))
+    ck.capture(Model(N=5, seed=1), *ck.checkpoint_paths(str(tmp_path / "t"), 2), fmt="flat")
     q = ck.checkpoint_paths(str(tmp_path / "t"), 2)
     blob = open(q[1], "rb").read()
     open(q[1], "wb").write(blob[:-4])
@@ -127,3 +128,57 @@ def test_ply_roundtrip(tmp_path):
     # f_rest is stored channel-major, as the published exporter does (transpose(1, 2) before flattening)
     raw = np.frombuffer(open(path, "rb").read()[-321 * 62 * 4:], dtype="<f4").reshape(321, 62)
     np.testing.assert_array_equal(raw[:, 9:9 + 15], a.features_rest_[:, :, 0].numpy())
+
+
+def _libtorch():
+    """tests/ckpt/ckpt_module.cpp: libtorch's own torch::save / torch::load, the calls the reference makes."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "ckpt"))
+    import build_ckpt
+    return build_ckpt.build()
+
+
+def test_checkpoints_are_libtorch_archives_both_ways(tmp_path):
+    """The default container IS the reference's: the tensors file written here loads with
+    torch::load(std::vector<torch::Tensor>&) into the 11 entries of CoreParams::restore (gaussian_model.cpp:163-176),
+    each optimiser file loads into a torch::optim::Adam set up as GaussianModel::setup does (:323-345) -- and files
+    written by libtorch's torch::save restore into this model."""
+    ext = _libtorch()
+    a = Model(N=321, seed=6)
+    paths = ck.checkpoint_paths(str(tmp_path), 30000)
+    ck.capture(a, *paths)
+    t = ext.load_tensors(paths[0])
+    assert len(t) == 11 and int(t[0]) == a.active_sh_degree and abs(float(t[10]) - a.spatial_lr_scale) < 1e-7
+    order = [a.xyz_, a.features_dc_, a.features_rest_, a.scaling_, a.rotation_, a.opacity_, a.max_radii2D_,
+             a.xyz_gradient_accum_, a.denom_]
+    for got, want in zip(t[1:10], order):
+        assert got.dtype == want.dtype and torch.equal(got, want)
+    for k, p in enumerate(a.params()):
+        step, lr, m, v = ext.load_adam(paths[1 + k], p.clone(), 0.5)      # lr 0.5: must be overwritten by the file's
+        assert int(step) == a.step_count[k] and abs(float(lr) - a.lr[k]) < 1e-15
+        assert torch.equal(m, a.exp_avg[k]) and torch.equal(v, a.exp_avg_sq[k])
+    # the other direction: libtorch writes, this package restores
+    q = [str(tmp_path / f"cpp_{i}") for i in range(7)]
+    ext.save_tensors(q[0], [torch.tensor(a.active_sh_degree, dtype=torch.int32)] + order +
+                     [torch.tensor(a.spatial_lr_scale, dtype=torch.float32)])
+    for k, p in enumerate(a.params()):
+        ext.save_adam(q[1 + k], p.clone(), a.lr[k], a.step_count[k], a.exp_avg[k], a.exp_avg_sq[k])
+    b = Model(N=7, seed=8)
+    ck.restore(b, *q)
+    for f in FIELDS:
+        assert torch.equal(getattr(a, f), getattr(b, f)), f
+    assert b.active_sh_degree == a.active_sh_degree and b.step_count == a.step_count
+    assert all(abs(x - y) < 1e-15 for x, y in zip(b.lr, a.lr))
+    for k in range(6):
+        assert torch.equal(a.exp_avg[k], b.exp_avg[k]) and torch.equal(a.exp_avg_sq[k], b.exp_avg_sq[k])
+
+
+def test_search_for_max_iteration_sign_handling(tmp_path):
+    """std::stoi accepts ONE sign character (src/utils/system_utils.cpp:7-31 parses the suffix with it)."""
+    d = tmp_path / "pc"
+    d.mkdir()
+    (d / "iteration_+15").write_text("")
+    assert ck.search_for_max_iteration(str(d)) == 15
+    (d / "iteration_+-5").write_text("")
+    with pytest.raises(RuntimeError):
+        ck.search_for_max_iteration(str(d))
