@@ -592,6 +592,7 @@ struct FusedAdamArgs {
   float neg_step[6], inv_bc2_sqrt[6];
   float b1, b2, omb1, omb2, eps;
   const float* skip_guard;
+  int l2_prefetch;   // pull the block's moments into L2 at block start (cp.async.bulk.prefetch.L2)
   int* max_radii2D;  // the three statistics: all or none
   float* xyz_grad_accum;
   float* denom;
@@ -689,7 +690,7 @@ __device__ __forceinline__ void pbf_update(PbfRound<PBF_UNROLL>& R, const float*
     }
 }
 
-template <int PBF_UNROLL, int MIN_BLOCKS>
+template <int PBF_UNROLL, int MIN_BLOCKS, int DEPTH>
 __global__ void __launch_bounds__(PBB_ROWS, MIN_BLOCKS)
 preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ PreBwdArgs a,
                                 const __grid_constant__ FusedAdamArgs f) {
@@ -717,15 +718,17 @@ preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __
     // the Adam phase below reads the moments (and the one parameter slice not staged above) with plain loads:
     // pull them into L2 now, underneath the gradient math
     const int cw[6] = {3, 3, W, 1, 3, 4};
+    if (f.l2_prefetch) {
 #pragma unroll
-    for (int k = 0; k < 6; ++k)
-      if (cw[k] > 0) {
-        tma::prefetch_l2(f.m[k] + row0 * cw[k], PBB_ROWS * 4u * cw[k]);
-        tma::prefetch_l2(f.v[k] + row0 * cw[k], PBB_ROWS * 4u * cw[k]);
-      }
-    tma::prefetch_l2(f.p[1] + 3 * row0, PBB_ROWS * 12u);
-    if (!load_sh && W > 0) tma::prefetch_l2(f.p[2] + row0 * W, (uint32_t)(PBB_ROWS * W * 4));
-    if (!a.in.raw_params) tma::prefetch_l2(f.p[3] + row0, PBB_ROWS * 4u);
+      for (int k = 0; k < 6; ++k)
+        if (cw[k] > 0) {
+          tma::prefetch_l2(f.m[k] + row0 * cw[k], PBB_ROWS * 4u * cw[k]);
+          tma::prefetch_l2(f.v[k] + row0 * cw[k], PBB_ROWS * 4u * cw[k]);
+        }
+      tma::prefetch_l2(f.p[1] + 3 * row0, PBB_ROWS * 12u);
+      if (!load_sh && W > 0) tma::prefetch_l2(f.p[2] + row0 * W, (uint32_t)(PBB_ROWS * W * 4));
+      if (!a.in.raw_params) tma::prefetch_l2(f.p[3] + row0, PBB_ROWS * 4u);
+    }
   }
   const int radius = a.radii[i];
   const bool visible = radius > 0;
@@ -774,8 +777,10 @@ preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __
   // first Adam round's moments / parameters: requested before the block's gradients are complete in shared memory
   const int nchunks = W + 14;
   const int warp = tid >> 5, lane = tid & 31;
-  PbfRound<PBF_UNROLL> RA, RB;
-  pbf_request(RA, f, row0, W, nchunks, warp, lane);
+  constexpr int STRIDE = 4 * PBF_UNROLL;  // chunks one round of this warp covers
+  PbfRound<PBF_UNROLL> R[DEPTH];         // ring of rounds in flight: DEPTH - 1 rounds are requested ahead of the one computed
+#pragma unroll
+  for (int d = 0; d < DEPTH - 1; ++d) pbf_request(R[d], f, row0, W, nchunks, warp + d * STRIDE, lane);
   // densification statistics of this row (K5's second half) and the optional dL_dmeans2D sink
   if (f.max_radii2D && visible) {
     if (radius > stat_maxr) f.max_radii2D[i] = radius;
@@ -786,12 +791,12 @@ preprocess_backward_adam_kernel(const __grid_constant__ gs_settings st, const __
   __syncthreads();
   // ---- Adam over the block's rows (chunked and double-buffered, see pbf_chunk) ----
   const GsAdamConst kc = {f.b1, f.b2, f.omb1, f.omb2, f.eps};
-  constexpr int STRIDE = 4 * PBF_UNROLL;  // chunks one round of this warp covers
-  for (int c0 = warp; c0 < nchunks; c0 += 2 * STRIDE) {
-    pbf_request(RB, f, row0, W, nchunks, c0 + STRIDE, lane);
-    pbf_update(RA, s_buf, f, kc);
-    pbf_request(RA, f, row0, W, nchunks, c0 + 2 * STRIDE, lane);
-    pbf_update(RB, s_buf, f, kc);
+  for (int c0 = warp; c0 < nchunks; c0 += DEPTH * STRIDE) {
+#pragma unroll
+    for (int d = 0; d < DEPTH; ++d) {
+      pbf_request(R[(d + DEPTH - 1) % DEPTH], f, row0, W, nchunks, c0 + (d + DEPTH - 1) * STRIDE, lane);
+      pbf_update(R[d], s_buf, f, kc);
+    }
   }
 }
 
@@ -913,21 +918,30 @@ cudaError_t gs_launch_preprocess_backward_adam(const gs_settings& st, const gs_g
   if (variant < 0) {
     const char* env = getenv("GS_FUSED_VARIANT");
     variant = env ? atoi(env) : 0;
-    if (variant < 0 || variant > 3) variant = 0;
+    if (variant < 0 || variant > 7) variant = 0;
   }
+  static int no_pf = -1;
+  if (no_pf < 0) {
+    const char* env = getenv("GS_FUSED_NO_L2_PREFETCH");
+    no_pf = env && env[0] == '1';
+  }
+  f.l2_prefetch = !no_pf;
   const int blocks = N / PBB_ROWS;
-#define PBF_LAUNCH(U, B)                                                                                           \
+#define PBF_LAUNCH(U, B, D)                                                                                        \
   do {                                                                                                             \
-    cudaError_t e = cudaFuncSetAttribute(preprocess_backward_adam_kernel<U, B>,                                    \
+    cudaError_t e = cudaFuncSetAttribute(preprocess_backward_adam_kernel<U, B, D>,                                 \
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, PBB_SMEM_BYTES);             \
     if (e != cudaSuccess) return e;                                                                                \
-    preprocess_backward_adam_kernel<U, B><<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, f);                 \
+    preprocess_backward_adam_kernel<U, B, D><<<blocks, PBB_ROWS, PBB_SMEM_BYTES, stream>>>(st, a, f);              \
   } while (0)
   switch (variant) {
-    case 1: PBF_LAUNCH(2, 5); break;
-    case 2: PBF_LAUNCH(2, 4); break;
-    case 3: PBF_LAUNCH(1, 6); break;
-    default: PBF_LAUNCH(1, 5); break;
+    case 2: PBF_LAUNCH(2, 4, 2); break;
+    case 3: PBF_LAUNCH(1, 6, 2); break;
+    case 4: PBF_LAUNCH(1, 5, 4); break;
+    case 5: PBF_LAUNCH(1, 4, 4); break;
+    case 6: PBF_LAUNCH(1, 5, 3); break;
+    case 7: PBF_LAUNCH(2, 4, 3); break;
+    default: PBF_LAUNCH(1, 5, 2); break;
   }
 #undef PBF_LAUNCH
   *covered = blocks * PBB_ROWS;
