@@ -126,7 +126,7 @@ def _load() -> C.CDLL:
     lib.gs_reset_opacity.argtypes = [vp, i, vp, vp, vp, vp]
     lib.gs_set_gradient_routing.argtypes = [vp, i, i, i, C.POINTER(vp)]
     lib.gs_adam_step_peer.argtypes = [vp, i, i, i, i, C.POINTER(vp), C.POINTER(vp), vp * 6, vp * 6, i * 6, d * 6,
-                                      C.c_longlong * 6, d, d, d, vp, vp, vp, vp, vp, vp, vp]
+                                      C.c_longlong * 6, d, d, d, vp, vp, vp, vp, vp, vp, i, vp]
     lib.gs_peer_alloc.argtypes = [vp, C.c_ulonglong, C.POINTER(vp), C.c_char_p]
     lib.gs_peer_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
     lib.gs_peer_close.argtypes = [vp, vp]

@@ -20,18 +20,27 @@
 #include "radix_sort.cuh"
 
 // ---- 1. depth sort ----------------------------------------------------------------------------
+// hist: the four digit histograms taken by depth_key_kernel; status / tickets / tag: one-sweep bookkeeping
+// (radix_sort.cuh).  Four launches; the result (Gaussian ids in depth order) lands in v1.
 cudaError_t gs_launch_depth_sort(int N, const uint32_t* depth_bits, uint32_t* k0, uint32_t* k1, uint32_t* v0,
-                                 uint32_t* v1, uint32_t* counts, int grid_unused, cudaStream_t stream) {
+                                 uint32_t* v1, const uint32_t* hist, unsigned long long* status, uint32_t* tickets,
+                                 uint32_t tag, int max_grid, int items, uint32_t sleep_ns, cudaStream_t stream) {
   if (N == 0) return cudaSuccess;
-  (void)grid_unused;
-  // one 2048-pair tile per block when that fits the grid limit: the N-sized sort is latency-bound
-  int grid = (N + 2047) / 2048;
-  if (grid > RS_MAX_GRID) grid = RS_MAX_GRID;
-  // result (Gaussian ids in depth order) lands in v1
-  radix_pass<uint32_t, 8>(depth_bits, k0, nullptr, v0, (uint32_t)N, nullptr, 0, counts, grid, stream);
-  radix_pass<uint32_t, 8>(k0, k1, v0, v1, (uint32_t)N, nullptr, 8, counts, grid, stream);
-  radix_pass<uint32_t, 8>(k1, k0, v1, v0, (uint32_t)N, nullptr, 16, counts, grid, stream);
-  return radix_pass<uint32_t, 8>(k0, nullptr, v0, v1, (uint32_t)N, nullptr, 24, counts, grid, stream);
+  const uint32_t n = (uint32_t)N;
+#define GS_DEPTH_PASSES(IT)                                                                                              \
+  do {                                                                                                                   \
+    onesweep_pass<uint32_t, IT>(depth_bits, k0, nullptr, v0, n, nullptr, n, 0, hist, status, tickets + 0, tag + 0,      \
+                                max_grid, sleep_ns, stream);                                                             \
+    onesweep_pass<uint32_t, IT>(k0, k1, v0, v1, n, nullptr, n, 8, hist + 256, status, tickets + 1, tag + 1, max_grid,    \
+                                sleep_ns, stream);                                                                       \
+    onesweep_pass<uint32_t, IT>(k1, k0, v1, v0, n, nullptr, n, 16, hist + 512, status, tickets + 2, tag + 2, max_grid,   \
+                                sleep_ns, stream);                                                                       \
+    return onesweep_pass<uint32_t, IT>(k0, nullptr, v0, v1, n, nullptr, n, 24, hist + 768, status, tickets + 3, tag + 3, \
+                                       max_grid, sleep_ns, stream);                                                      \
+  } while (0)
+  if (items == 16) GS_DEPTH_PASSES(16);
+  GS_DEPTH_PASSES(8);
+#undef GS_DEPTH_PASSES
 }
 
 // ---- 2. scan of tiles_touched along the depth order + duplicate ---------------------------------
@@ -167,7 +176,12 @@ template <typename KeyT>
 __global__ void __launch_bounds__(DUP_THREADS)
 duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint4* __restrict__ rects,
                            const uint32_t* __restrict__ block_base, KeyT* __restrict__ tile_ids,
-                           uint32_t* __restrict__ values, int gx, uint32_t cap, uint32_t* __restrict__ overflow) {
+                           uint32_t* __restrict__ values, int gx, uint32_t cap, uint32_t* __restrict__ overflow,
+                           uint32_t* __restrict__ hist /* [sizeof(KeyT)][256]: digit histograms of the tile ids */) {
+  // the tile sort's one-sweep passes take their digit histograms from here (radix_sort.cuh): the pairs are counted
+  // by the kernel that writes them
+  constexpr int NDIG = (int)sizeof(KeyT);
+  __shared__ uint32_t s_hist[NDIG][256];
   __shared__ uint32_t s_warp[DUP_THREADS / 32];
   __shared__ uint32_t s_wmax[DUP_THREADS / 32];
   __shared__ uint32_t s_off[DUP_BLOCK];
@@ -175,6 +189,8 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
   __shared__ uint4 s_rect[DUP_BLOCK];
   __shared__ __align__(16) uint16_t s_owner[DUP_ROUND];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+  for (int d = 0; d < NDIG; ++d) s_hist[d][tid] = 0;  // (ordered before the first use by the scan's barrier)
   const int r0 = blockIdx.x * DUP_BLOCK + tid * DUP_ITEMS;
   uint32_t cnt[DUP_ITEMS], myoff[DUP_ITEMS];
   uint32_t sum = 0;
@@ -248,7 +264,9 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
     for (int i = 0; i < DUP_SLOTS; ++i) {
       const uint32_t jr = (uint32_t)tid + (uint32_t)i * DUP_THREADS;
       const uint32_t j = lo + jr;
-      if (j < limit) {
+      const bool valid = j < limit;
+      uint32_t tile = 0;
+      if (valid) {
         const uint32_t owner = (uint32_t)s_owner[jr] - 1u;
         const uint4 rc = s_rect[owner];
         uint32_t k = j - s_off[owner];
@@ -262,11 +280,22 @@ duplicate_with_keys_kernel(int N, const uint32_t* __restrict__ order, const uint
           row = __float2uint_rz(__fdividef((float)k + 0.5f, (float)w));
         }
         const uint32_t col = k - row * w;
-        tile_ids[base + j] = (KeyT)((y0 + row) * (uint32_t)gx + x0 + col);
+        tile = (y0 + row) * (uint32_t)gx + x0 + col;
+        tile_ids[base + j] = (KeyT)tile;
         values[base + j] = s_id[owner];
       }
+      // digit histograms (slots, hence valid lanes, increase with the lane; a rectangle row is a run of high bytes)
+      if (valid) atomicAdd(&s_hist[0][tile & 0xFFu], 1u);
+#pragma unroll
+      for (int d = 1; d < NDIG; ++d) warp_run_hist(s_hist[d], (tile >> (8 * d)) & 0xFFu, valid, lane);
     }
     __syncthreads();  // the next round clears s_owner
+  }
+  __syncthreads();
+#pragma unroll
+  for (int d = 0; d < NDIG; ++d) {
+    const uint32_t c = s_hist[d][tid];
+    if (c) atomicAdd(hist + d * 256 + tid, c);
   }
 }
 
@@ -285,43 +314,51 @@ cudaError_t gs_launch_dup_scan(int N, const uint32_t* order, const uint32_t* til
 
 cudaError_t gs_launch_duplicate(int N, const uint32_t* order, const uint4* rects, const uint32_t* block_base,
                                 void* tile_ids, int key_bytes, uint32_t* values, int gx, uint32_t cap,
-                                uint32_t* overflow, cudaStream_t stream) {
+                                uint32_t* overflow, uint32_t* hist, cudaStream_t stream) {
   if (N == 0) return cudaSuccess;
   const int nb = gs_dup_num_blocks(N);
   if (key_bytes == 2)
     duplicate_with_keys_kernel<uint16_t><<<nb, DUP_THREADS, 0, stream>>>(N, order, rects, block_base, (uint16_t*)tile_ids,
-                                                                        values, gx, cap, overflow);
+                                                                        values, gx, cap, overflow, hist);
   else
     duplicate_with_keys_kernel<uint32_t><<<nb, DUP_THREADS, 0, stream>>>(N, order, rects, block_base, (uint32_t*)tile_ids,
-                                                                        values, gx, cap, overflow);
+                                                                        values, gx, cap, overflow, hist);
   return cudaGetLastError();
 }
 
-#ifndef RS_TILE_SORT_ITEMS
-#define RS_TILE_SORT_ITEMS 8
-#endif
 // ---- 3. tile sort -------------------------------------------------------------------------------
 // Sorts the D pairs by tile id.  Buffers a = input; the result is in `a` after an even number of
 // passes and in `b` after an odd number (returned through *result_in_b).
-cudaError_t gs_launch_tile_sort(const uint32_t* D_dev, int tile_bits, int key_bytes, void* keys_a, void* keys_b,
-                                uint32_t* vals_a, uint32_t* vals_b, uint32_t* counts, int grid, int* result_in_b,
-                                cudaStream_t stream) {
+cudaError_t gs_launch_tile_sort(const uint32_t* D_dev, uint32_t D_max, int tile_bits, int key_bytes, void* keys_a,
+                                void* keys_b, uint32_t* vals_a, uint32_t* vals_b, const uint32_t* hist,
+                                unsigned long long* status, uint32_t* tickets, uint32_t tag, int max_grid, int items,
+                                uint32_t sleep_ns, int* result_in_b, cudaStream_t stream) {
   const int passes = (tile_bits + 7) / 8;
   bool in_a = true;
   for (int p = 0; p < passes; ++p) {
+    uint32_t* vi = in_a ? vals_a : vals_b;
+    uint32_t* vo = in_a ? vals_b : vals_a;
+#define GS_TILE_PASS(KeyT, IT)                                                                                         \
+  onesweep_pass<KeyT, IT>((const KeyT*)(in_a ? keys_a : keys_b), (KeyT*)(in_a ? keys_b : keys_a), vi, vo, 0u, D_dev,   \
+                          D_max, 8 * p, hist + 256 * p, status, tickets + p, tag + (uint32_t)p, max_grid, sleep_ns, stream)
     if (key_bytes == 2) {
-      uint16_t* ki = (uint16_t*)(in_a ? keys_a : keys_b);
-      uint16_t* ko = (uint16_t*)(in_a ? keys_b : keys_a);
-      radix_pass<uint16_t, RS_TILE_SORT_ITEMS>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
+      if (items == 16) GS_TILE_PASS(uint16_t, 16);
+      else GS_TILE_PASS(uint16_t, 8);
     } else {
-      uint32_t* ki = (uint32_t*)(in_a ? keys_a : keys_b);
-      uint32_t* ko = (uint32_t*)(in_a ? keys_b : keys_a);
-      radix_pass<uint32_t, RS_TILE_SORT_ITEMS>(ki, ko, in_a ? vals_a : vals_b, in_a ? vals_b : vals_a, 0u, D_dev, 8 * p, counts, grid, stream);
+      if (items == 16) GS_TILE_PASS(uint32_t, 16);
+      else GS_TILE_PASS(uint32_t, 8);
     }
+#undef GS_TILE_PASS
     in_a = !in_a;
   }
   *result_in_b = in_a ? 0 : 1;
   return cudaGetLastError();
+}
+
+// 64-bit status words the one-sweep passes need for a list of up to n pairs in tiles of 256 * items pairs
+size_t gs_onesweep_status_words(size_t n, int items) {
+  const size_t tile = (size_t)RS_THREADS * items;
+  return ((n + tile - 1) / tile + 1) * RS_BINS;
 }
 
 // ---- 4. tile ranges -----------------------------------------------------------------------------

@@ -15,17 +15,18 @@
 // ---- launchers implemented in the other translation units ----
 cudaError_t gs_launch_preprocess(const gs_settings&, const gs_gaussians&, int, GsGeom*, float*, int*, uint32_t*,
                                  uint4*, uint8_t*, int*, cudaStream_t);
-cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, int,
-                                 cudaStream_t);
+cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, const uint32_t*,
+                                 unsigned long long*, uint32_t*, uint32_t, int, int, uint32_t, cudaStream_t);
+size_t gs_onesweep_status_words(size_t n, int items);
 int gs_dup_num_blocks(int N);
 cudaError_t gs_launch_dup_scan(int, const uint32_t*, const uint32_t*, uint32_t*, unsigned long long*, uint32_t*,
                                unsigned long long, uint32_t*, float*, float*, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_duplicate(int, const uint32_t*, const uint4*, const uint32_t*, void*, int, uint32_t*, int,
-                                uint32_t, uint32_t*, cudaStream_t);
-cudaError_t gs_launch_tile_sort(const uint32_t*, int, int, void*, void*, uint32_t*, uint32_t*, uint32_t*, int, int*,
-                                cudaStream_t);
+                                uint32_t, uint32_t*, uint32_t*, cudaStream_t);
+cudaError_t gs_launch_tile_sort(const uint32_t*, uint32_t, int, int, void*, void*, uint32_t*, uint32_t*, const uint32_t*,
+                                unsigned long long*, uint32_t*, uint32_t, int, int, uint32_t, int*, cudaStream_t);
 cudaError_t gs_launch_ranges(const uint32_t*, const void*, int, uint2*, int, cudaStream_t);
-cudaError_t gs_launch_depth_keys(const gs_settings&, const float*, int, uint32_t*, cudaStream_t);
+cudaError_t gs_launch_depth_keys(const gs_settings&, const float*, int, uint32_t*, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_order_tiles(int, const uint2*, uint32_t*, cudaStream_t);
 cudaError_t gs_launch_blend_forward(const GsDims&, const uint32_t*, const uint2*, const uint32_t*, const GsGeom*,
                                     const float[3], float*, float4*, uint32_t*, float4*, uint2*, uint32_t*, uint32_t*,
@@ -50,7 +51,7 @@ cudaError_t gs_launch_preprocess_backward_routed(const gs_settings&, const gs_ga
                                                  cudaStream_t);
 cudaError_t gs_launch_adam_peer(int, int, int, int, float* const[], const float* const[], float* const[6],
                                 float* const[6], const int[6], const double[6], const long long[6], double, double,
-                                double, const int*, const float*, int*, float*, float*, const float*, cudaStream_t);
+                                double, const int*, const float*, int*, float*, float*, const float*, int, cudaStream_t);
 cudaError_t gs_launch_adam(int, float* const[6], float* const[6], float* const[6], float* const[6], const int[6],
                            const double[6], const long long[6], double, double, double, const int*, const float*, int*,
                            float*, float*, int, const float*, cudaStream_t);
@@ -82,6 +83,14 @@ struct gs_ctx {
   // per-duplicate: tile ids (u16, u32 beyond 65536 tiles) and Gaussian ids, ping-pong
   DevBuf keys_a, keys_b, vals_a, vals_b;
   DevBuf radix_counts;
+  // one-sweep radix passes (radix_sort.cuh): 16 ticket counters + the digit histograms of the depth argsort (4 x 256)
+  // and of the tile sort (4 x 256), cleared at the start of every forward; per-tile status words (tagged, never
+  // cleared after the allocation); the next unused tag
+  DevBuf sort_meta, sort_status;
+  uint32_t sort_tag = 8;
+  // tuning (environment, read at gs_create): pairs per thread of a tile (8 / 16), persistent grids, poll back-off
+  int depth_sort_items = 8, tile_sort_items = 8, depth_sort_grid = 592;
+  uint32_t sort_sleep_ns = 0;
   int radix_grid = 296;
   int key_bytes = 2;
   const void* sorted_tiles = nullptr;    // tile ids of the sorted list
@@ -235,6 +244,17 @@ int gs_create(gs_ctx** out, int device) {
     return GS_ECUDA;
   }
   {
+    const char* e1 = getenv("GS_DEPTH_SORT_ITEMS");
+    const char* e2 = getenv("GS_TILE_SORT_ITEMS");
+    const char* e3 = getenv("GS_DEPTH_SORT_GRID");
+    const char* e4 = getenv("GS_SORT_SLEEP_NS");
+    if (e1 && atoi(e1) == 16) c->depth_sort_items = 16;
+    if (e2 && atoi(e2) == 16) c->tile_sort_items = 16;
+    c->depth_sort_grid = c->radix_grid;
+    if (e3 && atoi(e3) >= 1 && atoi(e3) <= 1024) c->depth_sort_grid = atoi(e3);
+    if (e4 && atoi(e4) >= 0 && atoi(e4) <= 10000) c->sort_sleep_ns = (uint32_t)atoi(e4);
+  }
+  {
     const char* env = getenv("GS_NO_SORT_OVERLAP");  // measurement switch: run the depth argsort after K1 on the caller's stream
     if (env && env[0] == '1') c->overlap_depth_sort = false;
   }
@@ -246,7 +266,7 @@ void gs_destroy(gs_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   DevBuf* bufs[] = {&c->geom,   &c->depths, &c->radii,  &c->tiles,   &c->rects, &c->clamped,   &c->grad_geom, &c->sort_k0,
-                    &c->sort_k1, &c->sort_v0, &c->sort_v1, &c->dup_sums, &c->radix_counts, &c->depth_keys,
+                    &c->sort_k1, &c->sort_v0, &c->sort_v1, &c->dup_sums, &c->radix_counts, &c->depth_keys, &c->sort_meta, &c->sort_status,
                     &c->keys_a, &c->keys_b, &c->vals_a, &c->vals_b,  &c->ranges,    &c->final_state,  &c->n_contrib,
                     &c->tile_order, &c->tile_last, &c->ckpt, &c->work_items, &c->counters, &c->loss_acc, &c->ssim_work,
                     &c->tail_grads, &c->dz_codes,
@@ -355,7 +375,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   GS_ENSURE(c, c->sort_v0, Nn * 4);
   GS_ENSURE(c, c->sort_v1, Nn * 4);
   GS_ENSURE(c, c->dup_sums, (size_t)(gs_dup_num_blocks(N > 0 ? N : 1) + 1) * 4);
-  GS_ENSURE(c, c->radix_counts, (size_t)256 * (1024 + 1) * 4);  // RS_MAX_GRID
+  GS_ENSURE(c, c->sort_meta, 64 + 8 * 256 * 4);
   GS_ENSURE(c, c->ranges, (size_t)d.ntiles * sizeof(uint2));
   GS_ENSURE(c, c->final_state, P * 16);
   GS_ENSURE(c, c->tile_order, (size_t)d.ntiles * 4);
@@ -380,6 +400,25 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   int* radii_user = (radii && (((uintptr_t)radii) & 15) == 0) ? radii : nullptr;
   GS_CUDA_CHECK(c, cudaMemsetAsync(c->counters.ptr, 0, 64, stream));
   c->work_cursor_zeroed = true;
+  // one-sweep sorts: tickets and digit histograms start at zero; eight fresh tags (depth passes, tile passes)
+  GS_CUDA_CHECK(c, cudaMemsetAsync(c->sort_meta.ptr, 0, 64 + 8 * 256 * 4, stream));
+  uint32_t* sort_tickets = (uint32_t*)c->sort_meta.ptr;
+  uint32_t* depth_hist = sort_tickets + 16;
+  uint32_t* tile_hist = depth_hist + 4 * 256;
+  const uint32_t tag0 = c->sort_tag;
+  c->sort_tag = c->sort_tag + 8 >= (1u << 30) ? 8u : c->sort_tag + 8;
+  auto ensure_status = [&](size_t words) -> int {
+    if (words * 8 <= c->sort_status.cap) return GS_OK;
+    const int r = ensure(c, c->sort_status, words * 8);
+    if (r != GS_OK) return r;
+    // a status word is valid only if it carries the tag of the launch reading it: fresh memory must not by accident
+    if (cudaMemsetAsync(c->sort_status.ptr, 0, c->sort_status.cap, stream) != cudaSuccess) return GS_ECUDA;
+    return GS_OK;
+  };
+  {
+    const int r = ensure_status(gs_onesweep_status_words(Nn, 8));
+    if (r != GS_OK) return r;
+  }
   if (N > 0) {
     // The depth argsort reads only the view depth, so it is forked onto the context's second stream and runs
     // beside K1 (the latency-bound N-sized sort fills the issue slots K1 leaves); the scan joins the two.
@@ -399,11 +438,12 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
     }
     {
       StageTimer t(c, 1, sort_stream);
-      GS_CUDA_CHECK(c, gs_launch_depth_keys(*st, in->means3D, N, (uint32_t*)c->depth_keys.ptr, sort_stream));
+      GS_CUDA_CHECK(c, gs_launch_depth_keys(*st, in->means3D, N, (uint32_t*)c->depth_keys.ptr, depth_hist, sort_stream));
       GS_CUDA_CHECK(c, gs_launch_depth_sort(N, (const uint32_t*)c->depth_keys.ptr, (uint32_t*)c->sort_k0.ptr,
                                             (uint32_t*)c->sort_k1.ptr, (uint32_t*)c->sort_v0.ptr,
-                                            (uint32_t*)c->sort_v1.ptr, (uint32_t*)c->radix_counts.ptr, c->radix_grid,
-                                            sort_stream));
+                                            (uint32_t*)c->sort_v1.ptr, depth_hist,
+                                            (unsigned long long*)c->sort_status.ptr, sort_tickets, tag0,
+                                            c->depth_sort_grid, c->depth_sort_items, c->sort_sleep_ns, sort_stream));
     }
     if (overlap) {
       GS_CUDA_CHECK(c, cudaEventRecord(c->ev_join, c->side));
@@ -445,17 +485,23 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
       GS_ENSURE(c, c->keys_b, Dn * c->key_bytes);
       GS_ENSURE(c, c->vals_a, Dn * 4);
       GS_ENSURE(c, c->vals_b, Dn * 4);
+      {
+        const int r = ensure_status(gs_onesweep_status_words(Dn, 8));  // (the depth argsort has joined)
+        if (r != GS_OK) return r;
+      }
       if (D > 0)
         GS_CUDA_CHECK(c, gs_launch_duplicate(N, (const uint32_t*)c->sort_v1.ptr, (const uint4*)c->rects.ptr,
                                              (const uint32_t*)c->dup_sums.ptr, c->keys_a.ptr, c->key_bytes,
-                                             (uint32_t*)c->vals_a.ptr, d.gx, (uint32_t)D, overflow_dev, stream));
+                                             (uint32_t*)c->vals_a.ptr, d.gx, (uint32_t)D, overflow_dev, tile_hist,
+                                             stream));
     }
     {
       StageTimer t(c, 3, stream);
       int in_b = 0;
-      GS_CUDA_CHECK(c, gs_launch_tile_sort(D_dev, tile_bits, c->key_bytes, c->keys_a.ptr, c->keys_b.ptr,
-                                           (uint32_t*)c->vals_a.ptr, (uint32_t*)c->vals_b.ptr,
-                                           (uint32_t*)c->radix_counts.ptr, c->radix_grid, &in_b, stream));
+      GS_CUDA_CHECK(c, gs_launch_tile_sort(D_dev, (uint32_t)D, tile_bits, c->key_bytes, c->keys_a.ptr, c->keys_b.ptr,
+                                           (uint32_t*)c->vals_a.ptr, (uint32_t*)c->vals_b.ptr, tile_hist,
+                                           (unsigned long long*)c->sort_status.ptr, sort_tickets + 8, tag0 + 4,
+                                           c->radix_grid, c->tile_sort_items, c->sort_sleep_ns, &in_b, stream));
       c->sorted_tiles = in_b ? c->keys_b.ptr : c->keys_a.ptr;
       c->point_list = (const uint32_t*)(in_b ? c->vals_b.ptr : c->vals_a.ptr);
     }
@@ -844,7 +890,7 @@ int gs_adam_step_peer(gs_ctx* c, int nranks, int rank, int N, int rows_per_shard
                       const float* const slots[], float* const exp_avg[6], float* const exp_avg_sq[6],
                       const int widths[6], const double lr[6], const long long step[6], double beta1, double beta2,
                       double eps, const int* radii, const float* dL_dmeans2D, int* max_radii2D,
-                      float* xyz_grad_accum, float* denom, const float* skip_guard, void* stream_) {
+                      float* xyz_grad_accum, float* denom, const float* skip_guard, int flags, void* stream_) {
   if (!c || nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks || N < 0 || rows_per_shard <= 0 ||
       rows_per_shard % 128 || !params || !slots || !exp_avg || !exp_avg_sq || !widths || !lr || !step) {
     gs_set_error(c, "gs_adam_step_peer: bad argument (1..8 ranks, rows_per_shard a positive multiple of 128)");
@@ -872,7 +918,7 @@ int gs_adam_step_peer(gs_ctx* c, int nranks, int rank, int N, int rows_per_shard
   GS_CUDA_CHECK(c, cudaSetDevice(c->device));
   GS_CUDA_CHECK(c, gs_launch_adam_peer(nranks, rank, N, rows_per_shard, params, slots, exp_avg, exp_avg_sq, widths, lr,
                                        step, beta1, beta2, eps, radii, dL_dmeans2D, max_radii2D, xyz_grad_accum,
-                                       denom, skip_guard, (cudaStream_t)stream_));
+                                       denom, skip_guard, (flags & GS_PEER_PULL) ? 0 : 1, (cudaStream_t)stream_));
   return GS_OK;
 }
 

@@ -321,7 +321,7 @@ cudaError_t gs_launch_adam_peer(int nranks, int rank, int N, int R, float* const
                                 const int widths[6], const double lr[6], const long long step[6], double beta1,
                                 double beta2, double eps, const int* radii, const float* dL_dmeans2D,
                                 int* max_radii2D, float* xyz_grad_accum, float* denom, const float* skip_guard,
-                                cudaStream_t stream) {
+                                int sparse_rest, cudaStream_t stream) {
   AdamPeerArgs a;
   const long long row0 = (long long)rank * R;
   const long long rows = row0 >= N ? 0 : ((long long)N - row0 < R ? (long long)N - row0 : (long long)R);
@@ -358,7 +358,7 @@ cudaError_t gs_launch_adam_peer(int nranks, int rank, int N, int R, float* const
   a.eps = (float)eps;
   a.skip_guard = skip_guard;
   a.rank = rank;
-  a.sparse_seg = 2;  // f_rest: 76% of the gradient bytes at SH degree 3
+  a.sparse_seg = sparse_rest ? 2 : -1;  // f_rest: 76% of the gradient bytes at SH degree 3 (push layout only)
   a.N = N;
   a.radii = radii;
   a.dL_dmeans2D = dL_dmeans2D;

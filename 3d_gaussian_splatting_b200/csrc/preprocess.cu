@@ -16,6 +16,7 @@
 // Generic fallback (preprocess_kernel: strided / unaligned tensors, precomputed cov3D or colours,
 // ragged tail): direct loads, SH rows staged through shared memory with coalesced loops.
 #include "gs_common.cuh"
+#include "radix_sort.cuh"
 #include "tma_bulk.cuh"
 
 #define PP_THREADS 256
@@ -457,20 +458,51 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
 // contraction: the same bits) and the sort runs beside K1 on the context's second stream (capi.cu).  A Gaussian
 // behind the near plane gets key 0 like in K1; one that K1 culls later (degenerate covariance, empty rectangle)
 // keeps its depth here -- it emits no (tile, Gaussian) pair, so its place in the order is immaterial.
+// The kernel also takes the digit histograms of all four radix passes of the depth argsort (a digit histogram does
+// not depend on the order of the keys, so the one-sweep passes need no histogram launches of their own,
+// radix_sort.cuh): per-block shared-memory counters, then one global atomic per non-empty bin.  The two high bytes
+// of a depth are nearly constant over a scene, so a warp whose 32 keys agree on a digit adds 32 with one atomic.
+#define DK_ITEMS 8
 __global__ void __launch_bounds__(256)
 depth_key_kernel(const __grid_constant__ gs_settings st, const float* __restrict__ means3D, int N,
-                 uint32_t* __restrict__ keys) {
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= N) return;
+                 uint32_t* __restrict__ keys, uint32_t* __restrict__ hist /* [4][256] */) {
+  __shared__ uint32_t s_hist[4][256];
+  const int tid = threadIdx.x, lane = tid & 31;
+#pragma unroll
+  for (int d = 0; d < 4; ++d) s_hist[d][tid] = 0;
+  __syncthreads();
   const float* V = st.viewmatrix;
-  const float p[3] = {__ldg(means3D + 3 * (size_t)i), __ldg(means3D + 3 * (size_t)i + 1), __ldg(means3D + 3 * (size_t)i + 2)};
-  const float z = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
-  keys[i] = z > GS_NEAR_Z ? __float_as_uint(z) : 0u;
+  const int base = blockIdx.x * (256 * DK_ITEMS);
+#pragma unroll
+  for (int k = 0; k < DK_ITEMS; ++k) {
+    const int i = base + k * 256 + tid;
+    const bool valid = i < N;
+    uint32_t key = 0;
+    if (valid) {
+      const float p[3] = {__ldg(means3D + 3 * (size_t)i), __ldg(means3D + 3 * (size_t)i + 1), __ldg(means3D + 3 * (size_t)i + 2)};
+      const float z = V[2] * p[0] + V[6] * p[1] + V[10] * p[2] + V[14];
+      key = z > GS_NEAR_Z ? __float_as_uint(z) : 0u;
+      keys[i] = key;
+    }
+    if (valid) {
+      atomicAdd(&s_hist[0][key & 0xFFu], 1u);
+      atomicAdd(&s_hist[1][(key >> 8) & 0xFFu], 1u);
+    }
+    warp_run_hist(s_hist[2], (key >> 16) & 0xFFu, valid, lane);  // (i increases with the lane: valid lanes are a prefix)
+    warp_run_hist(s_hist[3], key >> 24, valid, lane);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int d = 0; d < 4; ++d) {
+    const uint32_t c = s_hist[d][tid];
+    if (c) atomicAdd(hist + d * 256 + tid, c);
+  }
 }
 
-cudaError_t gs_launch_depth_keys(const gs_settings& st, const float* means3D, int N, uint32_t* keys, cudaStream_t stream) {
+cudaError_t gs_launch_depth_keys(const gs_settings& st, const float* means3D, int N, uint32_t* keys, uint32_t* hist,
+                                 cudaStream_t stream) {
   if (N == 0) return cudaSuccess;
-  depth_key_kernel<<<(N + 255) / 256, 256, 0, stream>>>(st, means3D, N, keys);
+  depth_key_kernel<<<(N + 256 * DK_ITEMS - 1) / (256 * DK_ITEMS), 256, 0, stream>>>(st, means3D, N, keys, hist);
   return cudaGetLastError();
 }
 

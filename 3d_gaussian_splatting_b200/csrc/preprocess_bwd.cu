@@ -371,11 +371,9 @@ preprocess_backward_kernel(const __grid_constant__ gs_settings st, const __grid_
       float* o = a.out.dL_dopacities + i;
       *o = acc ? *o + gop : gop;
     }
-    if (a.out.dL_dmeans2D) {
+    if (a.out.dL_dmeans2D) {  // a per-VIEW quantity (densification statistics): never accumulated
       float2* o = reinterpret_cast<float2*>(a.out.dL_dmeans2D + 2 * (size_t)i);
-      float2 v = make_float2(g2x, g2y);
-      if (acc) { const float2 u = *o; v.x += u.x; v.y += u.y; }
-      *o = v;
+      *o = make_float2(g2x, g2y);
     }
     if (a.out.dL_dcov3D) {
       float* o = a.out.dL_dcov3D + 6 * (size_t)i;
@@ -557,7 +555,7 @@ preprocess_backward_bulk_kernel(const __grid_constant__ gs_settings st, const __
     PBB_OUT(o_scl ? o_scl + 3 * row0 : nullptr, PBB_OFF_SCL, PBB_ROWS * 12u);
     PBB_OUT(o_rot ? o_rot + 4 * row0 : nullptr, PBB_OFF_ROT, PBB_ROWS * 16u);
     PBB_OUT(o_op ? o_op + row0 : nullptr, PBB_OFF_OP, PBB_ROWS * 4u);
-    PBB_OUT(a.out.dL_dmeans2D ? a.out.dL_dmeans2D + 2 * row0 : nullptr, PBB_OFF_M2D, PBB_ROWS * 8u);
+    if (a.out.dL_dmeans2D) tma::store(a.out.dL_dmeans2D + 2 * row0, s_buf + PBB_OFF_M2D, PBB_ROWS * 8u);  // per view: never accumulated
     PBB_OUT(o_dc ? o_dc + 3 * row0 : nullptr, PBB_OFF_DC, PBB_ROWS * 12u);
 #undef PBB_OUT
     tma::commit_group();
@@ -937,10 +935,7 @@ cudaError_t gs_launch_preprocess_backward_adam(const gs_settings& st, const gs_g
   switch (variant) {
     case 2: PBF_LAUNCH(2, 4, 2); break;
     case 3: PBF_LAUNCH(1, 6, 2); break;
-    case 4: PBF_LAUNCH(1, 5, 4); break;
-    case 5: PBF_LAUNCH(1, 4, 4); break;
     case 6: PBF_LAUNCH(1, 5, 3); break;
-    case 7: PBF_LAUNCH(2, 4, 3); break;
     default: PBF_LAUNCH(1, 5, 2); break;
   }
 #undef PBF_LAUNCH

@@ -1,16 +1,15 @@
-// radix_sort.cuh — this library's own stable LSD radix-sort pass (8-bit digits) for (key, value)
-// pairs, used twice by the binning stage (binning.cu):
+// radix_sort.cuh — this library's own stable LSD radix sort (8-bit digits) for (key, value) pairs, used twice by the
+// binning stage (binning.cu):
 //   * Gaussians by view depth   (u32 keys = fp32 bits of the depth, 4 passes over N pairs)
 //   * duplicates by tile id     (u16/u32 keys, ceil(log2(T)/8) passes over D pairs)
-// One pass = three launches on a fixed persistent grid (so the element count may live in device
-// memory and no host round-trip is needed):
-//   radix_hist_kernel    per-block digit histograms of the block's contiguous chunk -> counts[256][B]
-//   radix_scan_kernel    exclusive scan of every digit's row of counts (one block per digit)
-//   radix_scatter_kernel re-reads the chunk tile by tile (4096 pairs), ranks every pair stably
-//                        (ballot-built peer masks + per-warp counters, then a prefix over warps), reorders the
-//                        tile by digit in shared memory and writes digit-contiguous runs, so global
-//                        stores coalesce.
+// ONE launch per pass ("one-sweep": chained scan with decoupled look-back, below); the digit histograms of all
+// passes are taken by the kernels that write the keys.  The element count may live in device memory (fixed-capacity
+// mode: no host round-trip).  A tile of 2048 / 4096 pairs is ranked stably (ballot-built peer masks + per-warp
+// counters, then a prefix over warps -- match.any is avoided on purpose: measured at ~64 SM cycles per instruction on
+// sm_100), reordered by digit in shared memory and written as digit-contiguous runs, so global stores coalesce.
 // Stability is what makes the two-level scheme exact: pairs that compare equal keep their input order.
+// (Round 1 ran three launches per pass -- per-block histograms, a scan kernel, the scatter: 13 launches for the depth
+//  argsort, 6 for the tile sort, each bound by launch latency on data that fits in L2.)
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -18,119 +17,84 @@
 #define RS_THREADS 256
 #define RS_WARPS (RS_THREADS / 32)
 #define RS_BINS 256
-#define RS_MAX_GRID 1024  // persistent grid size limit (the scan kernel has one thread per chunk)
-// pairs per thread and tile: 16 (4096-pair tiles) for the multi-million pair lists; 8 (2048-pair tiles, twice the
-// blocks, half the serial ranking rounds per block) for the N-sized depth argsort, which is latency-bound
+#define RS_MAX_GRID 1024  // persistent grid size limit
 
-struct RadixChunk {
-  uint32_t begin, end;  // element range of this block
-};
-
-__device__ __forceinline__ RadixChunk radix_chunk(uint32_t n, uint32_t tile) {
-  const uint32_t tiles = (n + tile - 1) / tile;
-  const uint32_t tpb = (tiles + gridDim.x - 1) / gridDim.x;
-  RadixChunk c;
-  const uint64_t b = (uint64_t)blockIdx.x * tpb * tile;
-  const uint64_t e = b + (uint64_t)tpb * tile;
-  c.begin = (uint32_t)(b < n ? b : n);
-  c.end = (uint32_t)(e < n ? e : n);
-  return c;
+// ---- one-sweep pass: chained scan with decoupled look-back (no separate histogram / scan launches) -------------
+// The per-pass digit histograms of ALL passes are produced by the kernels that WRITE the keys (depth_key_kernel for
+// the depth argsort, duplicate_with_keys_kernel for the tile sort): a digit histogram does not depend on the order of
+// the keys, so it can be taken before the first pass.  One pass is then ONE launch: a block takes the next 2048- or
+// 4096-pair tile by ticket (so that every tile it will wait for has been started before it), ranks the tile stably as
+// above, publishes its per-digit counts, looks back over the preceding tiles' published counts until it meets one
+// that carries an inclusive prefix, publishes its own inclusive prefix, and scatters.  A status word is 64 bits --
+// {tag << 2 | flag, value} -- written and read with single 8-byte accesses, and the tag (a fresh number per launch)
+// means the status array never has to be cleared.
+#define OS_FLAG_AGGREGATE 1u
+#define OS_FLAG_INCLUSIVE 2u
+__device__ __forceinline__ unsigned long long os_load(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void os_store(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// Per-block digit histogram of the block's chunk.  16-byte loads (8 u16 / 4 u32 keys per lane), per-warp
-// private shared-memory histograms, and run-length aggregation inside each lane's vector: tile ids of one
-// Gaussian's rectangle and the high bytes of depths come in runs, which would otherwise serialise the
-// shared-memory atomics on a single bin.  (match.any is avoided on purpose: measured at ~64 SM cycles
-// per instruction on sm_100, it alone cost 60% of the SM's time in the first version of this kernel.)
-template <typename KeyT>
-__global__ void __launch_bounds__(RS_THREADS)
-radix_hist_kernel(const KeyT* __restrict__ keys, uint32_t n_host, const uint32_t* __restrict__ n_dev, int shift,
-                  uint32_t tile, uint32_t* __restrict__ counts) {
-  __shared__ uint32_t s_hist[RS_WARPS][RS_BINS];
-  constexpr int VEC = 16 / sizeof(KeyT);
-  const uint32_t n = n_dev ? *n_dev : n_host;
-  const RadixChunk c = radix_chunk(n, tile);
-  const int warp = threadIdx.x >> 5;
-  for (int k = threadIdx.x; k < RS_WARPS * RS_BINS; k += RS_THREADS) (&s_hist[0][0])[k] = 0;
-  __syncthreads();
-  uint32_t* h = s_hist[warp];
-  const uint32_t nvec = (c.end - c.begin) / VEC;  // c.begin is a multiple of the tile size: 16-byte aligned
-  const uint4* vp = reinterpret_cast<const uint4*>(keys + c.begin);
-  for (uint32_t v = threadIdx.x; v < nvec; v += RS_THREADS) {
-    const uint4 q = __ldg(vp + v);
-    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-    uint32_t prev = 0xFFFFFFFFu, run = 0;
-#pragma unroll
-    for (int k = 0; k < VEC; ++k) {
-      const uint32_t key = sizeof(KeyT) == 2 ? ((w[k >> 1] >> (16 * (k & 1))) & 0xFFFFu) : w[k & 3];
-      const uint32_t d = (key >> shift) & 0xFFu;
-      if (d != prev) {
-        if (run) atomicAdd(&h[prev], run);
-        prev = d;
-        run = 0;
-      }
-      ++run;
-    }
-    atomicAdd(&h[prev], run);
+// Histogram update of one warp-wide batch of digits with run aggregation: a lane whose digit differs from its left
+// neighbour's heads a run and adds the run's length with ONE shared-memory atomic.  Digits that come in runs (the
+// high bytes of depths, the high byte of a rectangle's tile ids) would otherwise serialise 32 atomics on one bin.
+// The valid lanes must form a prefix of the warp; every lane of the warp calls.
+__device__ __forceinline__ void warp_run_hist(uint32_t* h, uint32_t dig, bool valid, int lane) {
+  const uint32_t prev = __shfl_up_sync(0xffffffffu, dig, 1);
+  const bool head = valid && (lane == 0 || prev != dig);
+  const uint32_t heads = __ballot_sync(0xffffffffu, head);
+  const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+  if (head) {
+    const uint32_t after = (heads | ~vmask) & ~((2u << lane) - 1u);  // next head, or first invalid lane, above this one
+    const int end = after ? __ffs(after) - 1 : 32;
+    atomicAdd(&h[dig], (uint32_t)(end - lane));
   }
-  for (uint32_t i = c.begin + nvec * VEC + threadIdx.x; i < c.end; i += RS_THREADS)
-    atomicAdd(&h[((uint32_t)keys[i] >> shift) & 0xFFu], 1u);
-  __syncthreads();
-  uint32_t tot = 0;
-#pragma unroll
-  for (int w = 0; w < RS_WARPS; ++w) tot += s_hist[w][threadIdx.x];
-  counts[threadIdx.x * gridDim.x + blockIdx.x] = tot;
 }
 
-// Block d scans row d of counts[256][B] in place (exclusive) and leaves the row total in
-// counts[256*B + d]; the scatter kernel scans those 256 totals itself.
-#define RS_SCAN_THREADS RS_MAX_GRID
-__global__ void __launch_bounds__(RS_SCAN_THREADS) radix_scan_kernel(uint32_t* __restrict__ counts, uint32_t B) {
-  __shared__ uint32_t s_w[RS_SCAN_THREADS / 32];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  uint32_t* row = counts + (size_t)blockIdx.x * B;
-  const uint32_t v = threadIdx.x < B ? row[threadIdx.x] : 0u;
-  uint32_t incl = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += t;
-  }
-  if (lane == 31) s_w[warp] = incl;
-  __syncthreads();
-  uint32_t off = 0, tot = 0;
-#pragma unroll
-  for (int w = 0; w < RS_SCAN_THREADS / 32; ++w) {
-    const uint32_t t = s_w[w];
-    off += (w < warp) ? t : 0u;
-    tot += t;
-  }
-  if (threadIdx.x < B) row[threadIdx.x] = off + incl - v;
-  if (threadIdx.x == 0) counts[(size_t)RS_BINS * B + blockIdx.x] = tot;
-}
-
-// vals_in == nullptr: the value of element i is i (first pass of an argsort)
 template <typename KeyT, int RS_ITEMS>
 __global__ void __launch_bounds__(RS_THREADS, 4)
-radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out, const uint32_t* __restrict__ vals_in,
-                     uint32_t* __restrict__ vals_out, uint32_t n_host, const uint32_t* __restrict__ n_dev, int shift,
-                     const uint32_t* __restrict__ counts) {
+onesweep_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_out, const uint32_t* __restrict__ vals_in,
+                        uint32_t* __restrict__ vals_out, uint32_t n_host, const uint32_t* __restrict__ n_dev, int shift,
+                        const uint32_t* __restrict__ digit_hist, unsigned long long* __restrict__ status,
+                        uint32_t* __restrict__ ticket, uint32_t tag, uint32_t sleep_ns) {
   constexpr uint32_t RS_TILE = RS_THREADS * RS_ITEMS;
   __shared__ KeyT s_keys[RS_TILE];
   __shared__ uint32_t s_vals[RS_TILE];
   __shared__ uint32_t s_whist[RS_WARPS][RS_BINS + 1];
-  __shared__ uint32_t s_run[RS_BINS];    // next global slot of every digit for this block
-  __shared__ uint32_t s_gbase[RS_BINS];  // global slot - position in the reordered tile (mod 2^32)
-  __shared__ uint32_t s_start[RS_BINS];  // first position of every digit in the reordered tile
+  __shared__ uint32_t s_dstart[RS_BINS];  // first global slot of every digit (exclusive scan of the pass's histogram)
+  __shared__ uint32_t s_gbase[RS_BINS];   // global slot - position in the reordered tile (mod 2^32)
+  __shared__ uint32_t s_start[RS_BINS];   // first position of every digit in the reordered tile
   __shared__ uint32_t s_wsum[RS_WARPS];
+  __shared__ uint32_t s_tile;
 
   const uint32_t n = n_dev ? *n_dev : n_host;
-  const RadixChunk c = radix_chunk(n, RS_TILE);
+  const uint32_t ntiles = (n + RS_TILE - 1) / RS_TILE;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
-  {  // first global slot of (digit tid, this block) = all smaller digits + this digit in earlier blocks
-    const uint32_t rowtot = counts[RS_BINS * gridDim.x + tid];
-    uint32_t incl = rowtot;
+  const uint32_t cnt0 = digit_hist[tid];
+  if (__syncthreads_or(cnt0 == n && n > 0)) {
+    // every key carries the same digit (the top byte of the depths of a scene a few octaves deep, the high byte of
+    // the tile ids of a small image): a stable pass over it is the identity -- copy the tiles through
+    while (true) {
+      if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+      __syncthreads();
+      const uint32_t tile = s_tile;
+      __syncthreads();
+      if (tile >= ntiles) return;
+      const uint32_t t0 = tile * RS_TILE, tile_n = min(RS_TILE, n - t0);
+      for (uint32_t i = tid; i < tile_n; i += RS_THREADS) {
+        if (keys_out) keys_out[t0 + i] = keys_in[t0 + i];
+        vals_out[t0 + i] = vals_in ? vals_in[t0 + i] : t0 + i;
+      }
+    }
+  }
+  {  // exclusive scan over the digits of this pass's histogram
+    const uint32_t cnt = cnt0;
+    uint32_t incl = cnt;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
@@ -141,16 +105,20 @@ radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     uint32_t off = 0;
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w) off += (w < warp) ? s_wsum[w] : 0u;
-    s_run[tid] = counts[tid * gridDim.x + blockIdx.x] + off + incl - rowtot;
+    s_dstart[tid] = off + incl - cnt;
     __syncthreads();
   }
 
-  for (uint32_t t0 = c.begin; t0 < c.end; t0 += RS_TILE) {
-    const uint32_t tile_n = min(RS_TILE, c.end - t0);
+  while (true) {
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
     for (int k = tid; k < RS_WARPS * (RS_BINS + 1); k += RS_THREADS) (&s_whist[0][0])[k] = 0;
     __syncthreads();
+    const uint32_t tile = s_tile;
+    if (tile >= ntiles) return;
+    const uint32_t t0 = tile * RS_TILE;
+    const uint32_t tile_n = min(RS_TILE, n - t0);
 
-    // ---- load (warp w owns items [w*512, w*512+512) of the tile, 32 consecutive per round) + rank ----
+    // ---- load (warp w owns items [w*32*ITEMS, (w+1)*32*ITEMS) of the tile, 32 consecutive per round) + rank ----
     KeyT key[RS_ITEMS];
     uint32_t val[RS_ITEMS];
     uint16_t rank[RS_ITEMS];
@@ -166,7 +134,6 @@ radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     for (int j = 0; j < RS_ITEMS; ++j) {
       const bool valid = wbase + j * 32 < tile_n;
       const uint32_t d = valid ? (((uint32_t)key[j] >> shift) & 0xFFu) : 256u;
-      // lanes holding the same digit, from 9 ballots (8 digit bits + validity)
       uint32_t peers = __ballot_sync(0xffffffffu, valid);
       peers = valid ? peers : ~peers;
 #pragma unroll
@@ -187,13 +154,31 @@ radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     }
     __syncthreads();
 
-    // ---- per digit: exclusive prefix over warps, tile total, exclusive scan over digits ----
+    // ---- per digit (thread = digit): prefix over warps, tile total; publish, look back, publish ----
     uint32_t total = 0;
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w) {
       const uint32_t t = s_whist[w][tid];
       s_whist[w][tid] = total;
       total += t;
+    }
+    unsigned long long* my = status + (size_t)tile * RS_BINS + tid;
+    const unsigned long long hi = (unsigned long long)tag << 34;
+    uint32_t excl = 0;
+    if (tile == 0) {
+      os_store(my, hi | ((unsigned long long)OS_FLAG_INCLUSIVE << 32) | total);
+    } else {
+      os_store(my, hi | ((unsigned long long)OS_FLAG_AGGREGATE << 32) | total);
+      const unsigned long long* look = my - RS_BINS;
+      while (true) {
+        unsigned long long sv;
+        while (((sv = os_load(look)) >> 34) != (unsigned long long)tag)
+          if (sleep_ns) __nanosleep(sleep_ns);  // (polling 256 words per waiting tile competes with K1 for L2 slots)
+        excl += (uint32_t)sv;
+        if (((uint32_t)(sv >> 32) & 3u) == OS_FLAG_INCLUSIVE) break;
+        look -= RS_BINS;
+      }
+      os_store(my, hi | ((unsigned long long)OS_FLAG_INCLUSIVE << 32) | (unsigned long long)(excl + total));
     }
     uint32_t incl = total;
 #pragma unroll
@@ -208,9 +193,7 @@ radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
     for (int w = 0; w < RS_WARPS; ++w) woff += (w < warp) ? s_wsum[w] : 0u;
     const uint32_t start = woff + incl - total;
     s_start[tid] = start;
-    const uint32_t run = s_run[tid];
-    s_gbase[tid] = run - start;
-    s_run[tid] = run + total;
+    s_gbase[tid] = s_dstart[tid] + excl - start;
     __syncthreads();
 
     // ---- reorder the tile by digit in shared memory ----
@@ -237,15 +220,19 @@ radix_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ keys_o
   }
 }
 
-// One full pass.  `counts` must hold 256 * (grid + 1) uint32.  keys_out may be null on the last pass when the
-// sorted keys are not needed.
+// One one-sweep pass = one launch.  digit_hist: the 256 counts of this pass's digit over all n keys; status: 256
+// 64-bit words per tile of RS_THREADS * ITEMS pairs (never cleared, see above; zeroed once when allocated);
+// ticket: one zeroed counter per launch; tag: a number no earlier launch on this status array has used.
 template <typename KeyT, int ITEMS>
-static cudaError_t radix_pass(const KeyT* keys_in, KeyT* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
-                              uint32_t n_host, const uint32_t* n_dev, int shift, uint32_t* counts, int grid,
-                              cudaStream_t stream) {
-  radix_hist_kernel<KeyT><<<grid, RS_THREADS, 0, stream>>>(keys_in, n_host, n_dev, shift, RS_THREADS * ITEMS, counts);
-  radix_scan_kernel<<<RS_BINS, RS_SCAN_THREADS, 0, stream>>>(counts, (uint32_t)grid);
-  radix_scatter_kernel<KeyT, ITEMS><<<grid, RS_THREADS, 0, stream>>>(keys_in, keys_out, vals_in, vals_out, n_host, n_dev,
-                                                                     shift, counts);
+static cudaError_t onesweep_pass(const KeyT* keys_in, KeyT* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                                 uint32_t n_host, const uint32_t* n_dev, uint32_t n_max, int shift,
+                                 const uint32_t* digit_hist, unsigned long long* status, uint32_t* ticket, uint32_t tag,
+                                 int max_grid, uint32_t sleep_ns, cudaStream_t stream) {
+  const uint32_t tile = RS_THREADS * ITEMS;
+  long long grid = ((long long)n_max + tile - 1) / tile;
+  if (grid > max_grid) grid = max_grid;
+  if (grid < 1) grid = 1;
+  onesweep_scatter_kernel<KeyT, ITEMS><<<(int)grid, RS_THREADS, 0, stream>>>(keys_in, keys_out, vals_in, vals_out, n_host,
+                                                                            n_dev, shift, digit_hist, status, ticket, tag, sleep_ns);
   return cudaGetLastError();
 }

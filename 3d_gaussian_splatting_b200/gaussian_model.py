@@ -345,10 +345,11 @@ class Trainer:
         self.sharded = parallel.ShardedAdam(self.g, rank, world, adam, group=group)
         return self.sharded
 
-    def shard_optimizer_peer(self, rank: int, world: int, group=None):
-        """Fused multi-GPU step over peer memory (parallel.PeerShardedAdam).  Call before reserve_pairs()."""
+    def shard_optimizer_peer(self, rank: int, world: int, group=None, pull: bool = False):
+        """Fused multi-GPU step over peer memory (parallel.PeerShardedAdam).  Call before reserve_pairs().
+        pull=True: the layout for train_batch_device (several views per rank and step, one exchange)."""
         from . import parallel
-        self.peer = parallel.PeerShardedAdam(self.g, self.rast, rank, world, group=group)
+        self.peer = parallel.PeerShardedAdam(self.g, self.rast, rank, world, group=group, pull=pull)
         return self.peer
 
     def reserve_pairs(self, pairs: int, guard: torch.Tensor | None = None):
@@ -564,6 +565,39 @@ class Trainer:
             self.grad_sync()
         self.optimizer_step(out["radii"])
         return loss
+
+    def train_batch_device(self, cams, gts_dev, gts_host=None, exchange_events=None):
+        """ONE optimiser step on a batch of views (north_star's multi-view step): render + loss +
+        backward per view with the parameter gradients ACCUMULATED over the views (the gradient of the summed
+        per-view losses), the densification statistics taken view by view (xyz_gradient_accum += |dL/dmean2D| and
+        denom += 1 are per-view sums, src/scene/gaussian_model.h:18-20), then ONE gradient exchange and ONE Adam.
+        Data parallel: every rank passes ITS views of the batch; exchange = the trainer's mode (all-reduce of the
+        gradient slab, or the pull layout of the peer optimiser: shard_optimizer_peer(pull=True)).
+        Needs a caller-owned overflow guard (reserve_pairs(pairs, guard=tensor)): the context's own flag is reset by
+        every forward, the caller's stays raised for the rest of the step.  exchange_events: two CUDA events recorded
+        around the exchange + Adam part (benchmarks report it separately).  Returns the mean loss (device tensor)."""
+        assert self.pair_capacity and self._guard_tensor is not None, "train_batch_device: reserve_pairs(pairs, guard=...)"
+        assert self.sharded is None and (self.peer is None or self.peer.pull), "batch steps: all-reduce or pull layout"
+        g = self.g
+        self.iteration += 1
+        self.apply_schedules(self.iteration)
+        none6 = [None] * 6
+        total = None
+        for v, cam in enumerate(cams):
+            loss, out = self.forward_backward(cam, gts_dev[v], accumulate=v > 0,
+                                              gt_host=None if gts_host is None else gts_host[v])
+            self.rast.adam_densify_step(g.N, none6, none6, none6, none6, g.widths, g.lr, [1] * 6, radii=out["radii"],
+                                        dL_dmeans2D=g.grad_means2D, max_radii2D=g.max_radii2D_,
+                                        xyz_grad_accum=g.xyz_gradient_accum_, denom=g.denom_, skip_guard=self.skip_guard)
+            total = loss if total is None else total + loss
+        if exchange_events is not None:
+            exchange_events[0].record()
+        if self.grad_sync is not None:
+            self.grad_sync()
+        self.optimizer_step(None)
+        if exchange_events is not None:
+            exchange_events[1].record()
+        return total / len(cams)
 
     def train_step(self, cam, gt_host: torch.Tensor) -> float:
         """End-to-end step with HOST buffers: pinned ground-truth image H2D (overlapped with the render, see

@@ -160,10 +160,18 @@ class PeerShardedAdam:
     rast: the rank's Rasterizer.  exchange(handle) -> list of all ranks' handles (default: all_gather_object).
     """
 
-    def __init__(self, model, rast, rank: int, world: int, group=None, moments=None):
+    def __init__(self, model, rast, rank: int, world: int, group=None, moments=None, pull: bool = False):
         """moments: optional (exp_avg[6], exp_avg_sq[6]) FULL (N, C) arrays to start the owned shards from (after a
-        densification step, which needs and produces the full optimiser state); default: zeros."""
+        densification step, which needs and produces the full optimiser state); default: zeros.
+
+        pull=True -- the layout for steps that render SEVERAL views per rank (north_star's 64-view batch): every rank
+        accumulates the gradients of all its views into ONE local full-size slab (plain local reduce-adds, no
+        routing), and after a barrier the owner's Adam kernel reads rows [r*R, (r+1)*R) of EVERY rank's slab straight
+        over NVLink (peer loads), sums them in rank order, updates, and stores the parameters into every replica:
+        one exchange per step, however many views went into it.  The buffer is the same size as in the push layout
+        (world slots of R rows == one slab of N rows)."""
         self.model, self.rast, self.rank, self.world, self.group = model, rast, rank, world, group
+        self.pull = bool(pull)
         params = model.params()
         N = self.N = int(params[0].shape[0])
         self.widths = [int(p.numel() // max(N, 1)) for p in params]
@@ -174,12 +182,19 @@ class PeerShardedAdam:
             self.p_off.append(off)
             off += (N * c + 3) // 4 * 4
         self.s_off = []
-        for s in range(world):
-            row = []
+        if self.pull:
+            # ONE gradient slab of world * R rows per group (rows past N are never written nor read)
+            self.g_off = []
             for c in self.widths:
-                row.append(off)
-                off += R * c
-            self.s_off.append(row)
+                self.g_off.append(off)
+                off += world * R * c
+        else:
+            for s in range(world):
+                row = []
+                for c in self.widths:
+                    row.append(off)
+                    off += R * c
+                self.s_off.append(row)
         self.total = off
         self.base, handle = rast.peer_alloc(self.total * 4)
         handles = [None] * world
@@ -212,7 +227,10 @@ class PeerShardedAdam:
             v.copy_(p)
             views.append(v)
         (model.xyz_, model.features_dc_, model.features_rest_, model.opacity_, model.scaling_, model.rotation_) = views
-        model.grads = [None] * 6
+        if self.pull:   # the model's gradient sinks ARE the local slab
+            model.grads = [self.flat[o:o + N * c].view_as(p) for o, c, p in zip(self.g_off, self.widths, params)]
+        else:
+            model.grads = [None] * 6
         lo, hi = min(rank * R, N), min((rank + 1) * R, N)
         shard = []
         for full in (moments if moments is not None else (None, None)):
@@ -227,9 +245,14 @@ class PeerShardedAdam:
         self.sync = torch.zeros(1, dtype=torch.float32, device=self.flat.device)
         # params[r][k]: rank r's replica; slots[s][k]: MY slot for source s; routing[q][k]: my slot INSIDE rank q
         self.param_ptrs = [[self.bases[r] + 4 * self.p_off[k] for k in range(6)] for r in range(world)]
-        self.slot_ptrs = [[self.base + 4 * self.s_off[s][k] for k in range(6)] for s in range(world)]
-        routing = [[self.bases[q] + 4 * self.s_off[rank][k] for k in range(6)] for q in range(world)]
-        rast.set_gradient_routing(world, rank, R, routing)
+        if self.pull:
+            # source s of my shard = rows [rank*R, ...) of rank s's slab (peer-mapped for s != rank)
+            self.slot_ptrs = [[self.bases[s] + 4 * (self.g_off[k] + rank * R * self.widths[k]) for k in range(6)]
+                              for s in range(world)]
+        else:
+            self.slot_ptrs = [[self.base + 4 * self.s_off[s][k] for k in range(6)] for s in range(world)]
+            routing = [[self.bases[q] + 4 * self.s_off[rank][k] for k in range(6)] for q in range(world)]
+            rast.set_gradient_routing(world, rank, R, routing)
         self.barrier()   # every replica initialised and every mapping in place before anyone stores remotely
 
     def barrier(self):
@@ -238,7 +261,8 @@ class PeerShardedAdam:
             dist.all_reduce(self.sync, op=dist.ReduceOp.MAX, group=self.group)
 
     def slot(self, src: int, k: int) -> torch.Tensor:
-        """The gradient rows source rank `src` stored for my shard, group k: (R, widths[k])."""
+        """The gradient rows source rank `src` stored for my shard, group k: (R, widths[k]) (push layout)."""
+        assert not self.pull
         o = self.s_off[src][k]
         return self.flat[o:o + self.R * self.widths[k]].view(self.R, self.widths[k])
 
@@ -251,7 +275,7 @@ class PeerShardedAdam:
         self.rast.adam_step_peer(self.world, self.rank, self.N, self.R, self.param_ptrs, self.slot_ptrs, m.exp_avg,
                                  m.exp_avg_sq, self.widths, lr, step, radii=radii, dL_dmeans2D=dL_dmeans2D,
                                  max_radii2D=max_radii2D, xyz_grad_accum=xyz_grad_accum, denom=denom,
-                                 skip_guard=self.guard if use_guard else None)
+                                 skip_guard=self.guard if use_guard else None, sparse_rest=not self.pull)
         self.barrier()   # barrier 2: every replica complete before the next forward reads it
 
     def gather_moments(self):
@@ -282,7 +306,8 @@ class PeerShardedAdam:
     def close(self):
         torch.cuda.synchronize(self.flat.device)
         self.barrier()                        # nobody is still storing into a peer's buffer
-        self.rast.set_gradient_routing(0)
+        if not self.pull:
+            self.rast.set_gradient_routing(0)
         for r, b in enumerate(self.bases):
             if r != self.rank:
                 self.rast.peer_close(b)

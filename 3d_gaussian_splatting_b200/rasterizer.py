@@ -357,8 +357,9 @@ class Rasterizer:
 
     def adam_step_peer(self, nranks, rank, N, rows_per_shard, params, slots, exp_avg, exp_avg_sq, widths, lr, step,
                        beta1=0.9, beta2=0.999, eps=1e-8, radii=None, dL_dmeans2D=None, max_radii2D=None,
-                       xyz_grad_accum=None, denom=None, skip_guard=None):
-        """params[r][k] / slots[s][k]: device pointers (ints); exp_avg / exp_avg_sq: six shard-local tensors."""
+                       xyz_grad_accum=None, denom=None, skip_guard=None, sparse_rest=True):
+        """params[r][k] / slots[s][k]: device pointers (ints); exp_avg / exp_avg_sq: six shard-local tensors.
+        sparse_rest=False: the pull layout (GS_PEER_PULL): slots point into the ranks' full gradient slabs."""
         if isinstance(skip_guard, torch.Tensor):
             skip_guard = skip_guard.data_ptr()
         tab = lambda t: (C.c_void_p * (nranks * 6))(*[int(t[r][k]) for r in range(nranks) for k in range(6)])
@@ -369,7 +370,7 @@ class Rasterizer:
             VP6(*[t.data_ptr() for t in exp_avg]), VP6(*[t.data_ptr() for t in exp_avg_sq]), (C.c_int * 6)(*widths),
             (C.c_double * 6)(*[float(x) for x in lr]), (C.c_longlong * 6)(*[int(x) for x in step]), float(beta1),
             float(beta2), float(eps), _ptr(radii), _ptr(dL_dmeans2D), _ptr(max_radii2D), _ptr(xyz_grad_accum),
-            _ptr(denom), C.c_void_p(skip_guard) if skip_guard else None, C.c_void_p(stream)))
+            _ptr(denom), C.c_void_p(skip_guard) if skip_guard else None, 0 if sparse_rest else 1, C.c_void_p(stream)))
 
     def loss(self, image, gt, lambda_dssim=0.0, want_grad=True):
         """(1-lambda)*L1 + lambda*(1-SSIM); returns (loss 1-element device tensor, dL/dimage)."""

@@ -66,6 +66,10 @@ def parse_args():
                     help="length of the continuous run behind the `sustained` key (0: skip)")
     ap.add_argument("--no-extras", action="store_true",
                     help="skip the secondary measurements (best_case, stress, sustained, north-star batch)")
+    ap.add_argument("--batch-views", type=int, default=0,
+                    help="> 0: north_star's multi-view step (BASELINE.json configs[4]): ONE optimiser step per batch of this "
+                         "many views, split V/g per GPU, gradients accumulated locally over a rank's views, ONE exchange "
+                         "(strong scaling: the batch is the same at every GPU count).  Default config for it: cfg4")
     ap.add_argument("--mode", default="train", choices=["train", "render"],
                     help="train: the headline train step (default).  render: forward-only render throughput sweep over "
                          "the config's cameras (BASELINE.json configs[3]: Mpix/s with the sort / blend breakdown)")
@@ -335,9 +339,9 @@ def run_reference(args, rank, world):
 
 
 # ---- GPU arm -----------------------------------------------------------------------------------
-# depth keys, preprocess, depth sort 4 x (hist, scan, scatter), dup block sums + scan + duplicate, tile sort 2 x 3, tile
+# depth keys (+ histograms), preprocess, depth sort 4 one-sweep passes, dup block sums + scan + duplicate, tile sort 2 passes, tile
 # ranges, tile order, blend_forward, ssim forward + backward + finalize, blend_backward, preprocess_backward, adam_stats
-OWN_KERNELS_PER_STEP = 1 + 1 + 12 + 3 + 6 + 2 + 1 + 3 + 1 + 1 + 1   # separate K4b and K5; the fused single-GPU step: one less
+OWN_KERNELS_PER_STEP = 1 + 1 + 4 + 3 + 2 + 2 + 1 + 3 + 1 + 1 + 1   # separate K4b and K5; the fused single-GPU step: one less
 LAMBDA_DSSIM = 0.2   # lambda_dssim_ default (src/arguments/params.h:62)
 LOSS_NAME = "0.8*L1 + 0.2*(1-SSIM)"
 LIB_KERNELS_PER_STEP = 0   # no library kernels on the path (the radix sort and scans are this repo's own)
@@ -616,6 +620,15 @@ def run_ours(args, rank, world, local_rank):
         if args.variant == "default":
             stress = secondary(args.adam_state, "stress")
 
+    # ---- north_star's multi-view step (BASELINE.json configs[4]): 6 M Gaussians, ONE optimiser step per 64-view
+    # batch split over the GPUs (strong scaling), gradients accumulated per rank, one exchange per step ----
+    north = None
+    if not args.no_extras and args.variant == "default":
+        try:
+            north = measure_batch(args, rank, world, local_rank, "cfg4_6m_1246x825_sh3", 64, 2, 1, args.dp_mode)
+        except Exception as e:      # (reported, never fatal for the headline)
+            north = {"error": f"{type(e).__name__}: {e}"}
+
     by = stage_bytes(N, N_vis, D, D_eff, P, T, K, active_floats if world == 1 else None)
     if world > 1 and args.dp_mode == "peer" and active_floats is not None:
         # adam_peer_kernel, local HBM bytes of one rank: the `world` gradient slots + m, v, p of its R-row shard read;
@@ -729,6 +742,8 @@ def run_ours(args, rank, world, local_rank):
             # the same step with cold Adam state (this scene hides ~70 % of its Gaussians from every view: their
             # vectors are skipped) and on the stress variant of the scene (long blend lists)
             "best_case": best_case, "stress": stress,
+            # north_star's 64-view batch on the 6 M-Gaussian scene: views/s, exchange time reported separately
+            "north_star_batch": north,
             "replicas_identical": replicas_identical, "last_loss": last_loss,
             "raster": raster,
             "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
@@ -753,6 +768,155 @@ def run_ours(args, rank, world, local_rank):
             "library_launches": LIB_KERNELS_PER_STEP * args.steps,
             "clocks": clocks,
         }), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def measure_batch(args, rank, world, local_rank, config, V, steps, warm, dp_mode):
+    """north_star's multi-view step on `config`: V views per optimiser step, V/world per rank.  Returns the fields of
+    the result (every rank must call; values are maxima over ranks)."""
+    import torch
+    import torch.distributed as dist
+    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
+    gm = importlib.import_module("3d_gaussian_splatting_b200.gaussian_model")
+    par = importlib.import_module("3d_gaussian_splatting_b200.parallel")
+    dev = torch.device("cuda", local_rank)
+    assert V % world == 0, "--batch-views must be a multiple of the GPU count"
+    scene, cams, deg = syn.make_config(config, n_cameras=V, N=args.N)
+    my_cams = par.shard_cameras(cams, rank, world)          # V / world views
+    H, W = my_cams[0].image_height, my_cams[0].image_width
+    model = gm.GaussianModel(deg, local_rank).load_scene(scene)
+    trainer = gm.Trainer(model, gm.OptimizationParams(), bg=(0.0, 0.0, 0.0), lambda_dssim=LAMBDA_DSSIM)
+    mode = dp_mode if world > 1 else "single"
+    gslab = None
+    if mode == "peer":
+        try:
+            peer = trainer.shard_optimizer_peer(rank, world, pull=True)
+            guard = peer.guard
+        except RuntimeError as e:
+            if rank == 0:
+                print(f"[bench] {e}; batch mode falls back to --dp-mode allreduce", file=sys.stderr)
+            mode = "allreduce"
+    if mode != "peer":
+        gslab = par.GradientSlab(model.params())
+        model.grads = gslab.views
+        guard = gslab.guard
+        if world > 1:
+            trainer.grad_sync = gslab.all_reduce
+    warm_adam_state(model)
+    rng = np.random.Generator(np.random.Philox(99))
+    gt_model = gm.GaussianModel(deg, local_rank).load_scene(scene)
+    gt_model.features_dc_ += torch.from_numpy((0.05 * rng.standard_normal(scene.features_dc.shape)).astype(np.float32)).to(dev)
+    gts_dev, gts_host, max_pairs = [], [], 0
+    for cam in my_cams:
+        out = gm.render(cam, gt_model, gm.PipelineParams(), (0.0, 0.0, 0.0), trainer.rast)
+        gts_dev.append(out["render"].clone())
+        gts_host.append(out["render"].cpu().pin_memory())
+        max_pairs = max(max_pairs, trainer.rast.forward_status()[0])
+    del gt_model
+    torch.cuda.synchronize()
+    trainer.reserve_pairs(int(1.3 * max_pairs) + 1024, guard=guard)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ex_ms = []
+
+    def step(timed):
+        loss = trainer.train_batch_device(my_cams, gts_dev, exchange_events=ev if timed else None)
+        return loss
+
+    def run(n, host=False):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for _ in range(n):
+            if host:      # end to end: every view's ground truth comes from pinned host memory, the loss goes back
+                last = trainer.train_batch_device(my_cams, [trainer._gt_dev] * len(my_cams), gts_host=gts_host)
+                trainer._loss_host.copy_(last, non_blocking=True)
+            else:
+                last = step(True)
+        e1.record()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / n, last
+
+    trainer._gt_dev = torch.empty_like(gts_dev[0])
+    for _ in range(warm):
+        step(False)
+    ms_step, last = run(steps)
+    torch.cuda.synchronize()
+    ex = torch.tensor([ev[0].elapsed_time(ev[1])], device=dev, dtype=torch.float64)      # (the last step's)
+    if world > 1:
+        dist.all_reduce(ex, op=dist.ReduceOp.MAX)
+    e2e_ms, last_e2e = run(max(1, steps), host=True)
+    torch.cuda.synchronize()
+    ok = float(guard.item()) == 0.0
+    cs = torch.zeros(1, dtype=torch.int64, device=dev)
+    for t in model.params():
+        if t.numel():
+            cs += t.contiguous().view(torch.int32).to(torch.int64).sum()
+    identical = None
+    if world > 1:
+        allcs = [torch.zeros_like(cs) for _ in range(world)]
+        dist.all_gather(allcs, cs)
+        identical = all(int(c.item()) == int(allcs[0].item()) for c in allcs)
+    res = {"workload": config, "N": scene.N, "W": W, "H": H, "sh_degree": deg, "batch_views": V,
+           "views_per_rank": len(my_cams), "steps": steps, "warmup": warm,
+           "ms_per_step": ms_step, "views_per_s": V / (ms_step * 1e-3),
+           "exchange_ms": float(ex.item()),
+           "exchange": {"single": "none (one GPU): Adam + statistics only",
+                        "peer": "pull over NVLink peer memory: the owner's Adam kernel reads its rows of every rank's "
+                                "gradient slab, updates its 1/%d of the model and stores the parameters into every "
+                                "replica (2 one-float NCCL all-reduces as barriers)" % world,
+                        "allreduce": "one NCCL all-reduce of the gradient slab, replicated Adam"}[mode],
+           "exchange_bytes_per_rank": (0 if world == 1 else int(2 * (world - 1) / world * 4 * sum(p.numel() for p in model.params()))),
+           "e2e_ms_per_step": e2e_ms, "e2e_views_per_s": V / (e2e_ms * 1e-3),
+           "h2d_bytes_per_step": int(len(my_cams) * gts_host[0].numel() * 4), "d2h_bytes_per_step": 4,
+           "capacity_ok": ok, "replicas_identical": identical, "last_loss": float(last.item()),
+           "adam_state": "warm", "scaling": "strong"}
+    if mode == "peer":
+        trainer.peer.detach_model()
+        trainer.peer.close()
+    trainer.rast.close()
+    del trainer, model, gts_dev, gts_host
+    torch.cuda.empty_cache()
+    return res
+
+
+def run_batch(args, rank, world, local_rank):
+    """--batch-views V: the multi-view step as the headline of its own line (strong scaling over the GPU count)."""
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    config = args.config if args.config != DEFAULT_CONFIG else "cfg4_6m_1246x825_sh3"
+    warm = max(args.warmup, 3)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    r = measure_batch(args, rank, world, local_rank, config, args.batch_views, args.steps, warm, args.dp_mode)
+    clocks = sampler.stop() if sampler else None
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": r["views_per_s"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
+            "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {k: r[k] for k in ("workload", "N", "W", "H", "sh_degree", "batch_views", "views_per_rank", "adam_state",
+                                         "exchange")},
+            "exchange_ms": r["exchange_ms"], "exchange_bytes_per_rank": r["exchange_bytes_per_rank"],
+            "e2e": {"value": r["e2e_views_per_s"], "unit": UNIT, "ms_per_step": r["e2e_ms_per_step"],
+                    "h2d_bytes_per_step": r["h2d_bytes_per_step"], "d2h_bytes_per_step": r["d2h_bytes_per_step"],
+                    "api": "Trainer.train_batch_device with pinned host ground truth per view, loss D2H per step"},
+            "capacity_ok": r["capacity_ok"], "replicas_identical": r["replicas_identical"], "last_loss": r["last_loss"],
+            "clocks": clocks}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -851,6 +1015,8 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+    elif args.batch_views > 0:
+        run_batch(args, rank, world, local_rank)
     elif args.mode == "render":
         if rank == 0:
             run_render_sweep(args, local_rank)

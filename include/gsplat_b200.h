@@ -100,7 +100,8 @@ typedef struct {
 /* Gradient sinks (device pointers, same layouts as the inputs; any may be NULL to skip).
  * dL_dmeans2D is (N,2): the screen-space gradient whose norm feeds xyz_gradient_accum_
  * (src/scene/gaussian_model.h:19).  accumulate != 0 adds into the buffers instead of
- * overwriting them (gradient accumulation over several views). */
+ * overwriting them (gradient accumulation over several views) -- except dL_dmeans2D, which is a
+ * per-VIEW quantity (the statistics take its norm view by view) and is always overwritten. */
 typedef struct {
   float *dL_dmeans3D;
   float *dL_dscales;
@@ -236,6 +237,11 @@ GS_API int gs_peer_free(gs_ctx *ctx, void *ptr);
  * gs_adam_densify_step to them and stores the new parameters into the replica of every rank: params[r*6 + k] is
  * rank r's (N, widths[k]) array (r == rank: local).  slots[s*6 + k]: the local slot of source rank s.
  * exp_avg / exp_avg_sq: (R, widths[k]) shard-local moments.  Statistics as in gs_adam_densify_step (per rank).
+ * flags: 0 -- the PUSH layout above (remote f_rest slots are written sparsely by the routed backward and re-zeroed
+ * by this call).  GS_PEER_PULL -- the layout for steps of several views per rank: no routing; every rank accumulates
+ * all its views into one LOCAL (nranks*R, widths[k]) gradient slab, and slots[s*6 + k] points at rows [rank*R, ..)
+ * of rank s's slab (peer-mapped for s != rank), which this call reads over NVLink: ONE exchange per step.  Nothing
+ * is re-zeroed (the next step's first backward overwrites).
  *
  * Ordering is the caller's: every rank's gs_backward must have completed before any rank's gs_adam_step_peer
  * runs, and every gs_adam_step_peer before the next gs_forward -- two stream-ordered barriers per step (the
@@ -246,7 +252,8 @@ GS_API int gs_adam_step_peer(gs_ctx *ctx, int nranks, int rank, int N, int rows_
                              const int widths[6], const double lr[6], const long long step[6], double beta1,
                              double beta2, double eps, const int *radii, const float *dL_dmeans2D,
                              int *max_radii2D, float *xyz_grad_accum, float *denom, const float *skip_guard,
-                             void *stream);
+                             int flags, void *stream);
+#define GS_PEER_PULL 1
 
 /* ---- running without the host round-trip ----------------------------------------------------
  * By default gs_forward synchronises the stream once, to size the (tile, Gaussian) pair lists from

@@ -12,8 +12,11 @@ for path in sys.argv[1:]:
               f"  raster {d.get('raster_fwd_bwd_ms')}")
         st = d.get("stages") or {}
         print("   " + "  ".join(f"{k}={v['ms']:.3f}" for k, v in st.items()))
-        for key in ("sustained", "best_case", "stress"):
+        for key in ("sustained", "best_case", "stress", "north_star_batch"):
             v = d.get(key)
             if v:
                 print(f"   {key}: {v.get('ms_per_step', 0):.4f} ms/step  " + json.dumps({k: v[k] for k in v if k not in ('clocks',)})[:600])
-        print("   roofline:", json.dumps(d.get("roofline")), " idle", d.get("adam_idle_frac"), " clocks", d.get("clocks"))
+        try:
+            print("   roofline:", json.dumps(d.get("roofline")), " idle", d.get("adam_idle_frac"), " clocks", d.get("clocks"))
+        except BrokenPipeError:
+            pass
