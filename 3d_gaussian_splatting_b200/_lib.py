@@ -12,7 +12,8 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libgsplat_b200.so")
 
-GS_OK, GS_EINVAL, GS_ENOMEM, GS_ECUDA, GS_EOVERFLOW, GS_ESTATE = 0, -1, -2, -3, -4, -5
+GS_OK, GS_EINVAL, GS_ENOMEM, GS_ECUDA, GS_EOVERFLOW, GS_ESTATE, GS_ENUMERIC = 0, -1, -2, -3, -4, -5, -6
+GS_DEBUG_CHECKS, GS_PUBLISHED_CLAMP_GRAD = 1, 2
 GS_NUM_STAGES = 8
 STAGE_NAMES = ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")
 
@@ -62,7 +63,7 @@ class GsTrainConfig(C.Structure):
         ("densification_interval", C.c_int), ("opacity_reset_interval", C.c_int), ("densify_from_iter", C.c_int),
         ("densify_until_iter", C.c_int),
         ("densify_grad_threshold", C.c_double), ("spatial_lr_scale", C.c_double),
-        ("bg", C.c_float * 3), ("seed", C.c_uint), ("active_sh_degree", C.c_int),
+        ("bg", C.c_float * 3), ("seed", C.c_uint), ("active_sh_degree", C.c_int), ("random_background", C.c_int),
     ]
 
 

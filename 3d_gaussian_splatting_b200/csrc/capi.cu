@@ -59,6 +59,7 @@ cudaError_t gs_launch_adam_counts(int, int, float* const[], float* const[], floa
                                   const size_t[], const double[], const long long[], double, double, double,
                                   const int*, const float*, int*, float*, float*, int, const float*, cudaStream_t);
 cudaError_t gs_launch_l1_loss(size_t, const float*, const float*, float, float*, double*, float*, cudaStream_t);
+cudaError_t gs_launch_count_nonfinite(const float*, size_t, uint32_t*, cudaStream_t);
 size_t gs_ssim_workspace_bytes(int H, int W);
 cudaError_t gs_launch_photometric_loss(int, int, const float*, const float*, float, float*, double*, float*, float*,
                                        cudaStream_t);
@@ -533,7 +534,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   }
   if (radii && !radii_user && N > 0)
     GS_CUDA_CHECK(c, cudaMemcpyAsync(radii, c->radii.ptr, (size_t)N * 4, cudaMemcpyDeviceToDevice, stream));
-  if (st->debug) {
+  if (st->debug & GS_DEBUG_CHECKS) {
     GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
     GS_CUDA_CHECK(c, cudaGetLastError());
   }
@@ -543,6 +544,23 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   c->ntiles = d.ntiles;
   c->D = D;
   c->have_forward = true;
+  return GS_OK;
+}
+
+// debug: count NaN / inf in a device array; GS_ENUMERIC with a message naming it when there are any
+static int scan_nonfinite(gs_ctx* c, const float* p, size_t n, const char* name, cudaStream_t stream) {
+  if (!p || n == 0) return GS_OK;
+  GS_ENSURE(c, c->loss_acc, 64);
+  uint32_t* cnt = (uint32_t*)c->loss_acc.ptr + 8;
+  GS_CUDA_CHECK(c, cudaMemsetAsync(cnt, 0, 4, stream));
+  GS_CUDA_CHECK(c, gs_launch_count_nonfinite(p, n, cnt, stream));
+  uint32_t h = 0;
+  GS_CUDA_CHECK(c, cudaMemcpyAsync(&h, cnt, 4, cudaMemcpyDeviceToHost, stream));
+  GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
+  if (h) {
+    gs_set_error(c, "debug: %u non-finite values (NaN / inf) in %s", h, name);
+    return GS_ENUMERIC;
+  }
   return GS_OK;
 }
 
@@ -599,9 +617,30 @@ int gs_backward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in,
                                                             (const float4*)c->grad_geom.ptr, stream));
     }
   }
-  if (st->debug) {
+  if (st->debug & GS_DEBUG_CHECKS) {
     GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
     GS_CUDA_CHECK(c, cudaGetLastError());
+    // anomaly scan (the role of --detect_anomaly, src/train.cpp:39): the blend-gradient records and every sink
+    const int kmax = (st->max_sh_degree + 1) * (st->max_sh_degree + 1);
+    const struct { const float* p; size_t n; const char* name; } sinks[] = {
+        {(const float*)c->grad_geom.ptr, (size_t)N * 12, "blend gradients (dL/dmean2D, conic, opacity, colour)"},
+        {c->route_shards ? nullptr : grads->dL_dmeans3D, (size_t)N * 3, "dL_dmeans3D"},
+        {c->route_shards ? nullptr : grads->dL_dscales, (size_t)N * 3, "dL_dscales"},
+        {c->route_shards ? nullptr : grads->dL_drotations, (size_t)N * 4, "dL_drotations"},
+        {c->route_shards ? nullptr : grads->dL_dopacities, (size_t)N, "dL_dopacities"},
+        {grads->dL_dmeans2D, (size_t)N * 2, "dL_dmeans2D"},
+        {grads->dL_dcov3D, (size_t)N * 6, "dL_dcov3D"},
+        {grads->dL_dcolors, (size_t)N * 3, "dL_dcolors"},
+        {(!c->route_shards && grads->sh_dc_stride == 3) ? grads->dL_dsh_dc : nullptr, (size_t)N * 3, "dL_dsh_dc"},
+        {(!c->route_shards && kmax > 1 && grads->sh_rest_stride == 3 * (kmax - 1)) ? grads->dL_dsh_rest : nullptr,
+         (size_t)N * 3 * (kmax - 1), "dL_dsh_rest"},
+        {(!c->route_shards && grads->dL_dsh_dc && grads->sh_dc_stride == 3 * kmax && grads->sh_dc_stride != 3) ? grads->dL_dsh_dc : nullptr,
+         (size_t)N * 3 * kmax, "dL_dshs"},
+    };
+    for (const auto& s : sinks) {
+      const int r = scan_nonfinite(c, s.p, s.n, s.name, stream);
+      if (r != GS_OK) return r;
+    }
   }
   c->have_backward = true;
   return GS_OK;
@@ -721,9 +760,17 @@ int gs_backward_adam_step(gs_ctx* c, const gs_settings* st, int N, const gs_gaus
                                              stats ? denom + b : nullptr, 0, skip_guard, stream));
     }
   }
-  if (st->debug) {
+  if (st->debug & GS_DEBUG_CHECKS) {
     GS_CUDA_CHECK(c, cudaStreamSynchronize(stream));
     GS_CUDA_CHECK(c, cudaGetLastError());
+    // the parameter gradients never reach HBM here: scan what feeds them, and the updated parameters
+    int r = scan_nonfinite(c, (const float*)c->grad_geom.ptr, (size_t)N * 12,
+                           "blend gradients (dL/dmean2D, conic, opacity, colour)", stream);
+    if (r == GS_OK) r = scan_nonfinite(c, in->means3D, (size_t)N * 3, "means3D after the fused Adam step", stream);
+    if (r == GS_OK) r = scan_nonfinite(c, in->scales, (size_t)N * 3, "scales after the fused Adam step", stream);
+    if (r == GS_OK) r = scan_nonfinite(c, in->rotations, (size_t)N * 4, "rotations after the fused Adam step", stream);
+    if (r == GS_OK) r = scan_nonfinite(c, in->opacities, (size_t)N, "opacities after the fused Adam step", stream);
+    if (r != GS_OK) return r;
   }
   c->have_backward = true;
   return GS_OK;

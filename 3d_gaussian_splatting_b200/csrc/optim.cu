@@ -409,3 +409,17 @@ cudaError_t gs_launch_l1_loss(size_t n, const float* img, const float* gt, float
   loss_finalize_kernel<<<1, 1, 0, stream>>>(acc, (double)weight / (double)n, loss_out);
   return cudaGetLastError();
 }
+
+// ---- debug: NaN / inf count (gs_settings.debug & GS_DEBUG_CHECKS; the role of --detect_anomaly) ----
+__global__ void __launch_bounds__(256) count_nonfinite_kernel(const float* __restrict__ p, size_t n, uint32_t* __restrict__ count) {
+  uint32_t bad = 0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    bad += ((__float_as_uint(p[i]) & 0x7f800000u) == 0x7f800000u) ? 1u : 0u;
+  bad = __reduce_add_sync(0xffffffffu, bad);
+  if ((threadIdx.x & 31) == 0 && bad) atomicAdd(count, bad);
+}
+cudaError_t gs_launch_count_nonfinite(const float* p, size_t n, uint32_t* count, cudaStream_t stream) {
+  const size_t want = (n + 255) / 256;
+  count_nonfinite_kernel<<<(int)(want < 1184 ? (want ? want : 1) : 1184), 256, 0, stream>>>(p, n, count);
+  return cudaGetLastError();
+}

@@ -166,7 +166,10 @@ __device__ __forceinline__ void pb_compute(const gs_settings& st, const PreBwdAr
     const float tz2 = 1.0f / (tz * tz), tz3 = tz2 / tz;
     const float gtx = x_free ? -fx * tz2 * gJ02 : 0.f;
     const float gty = y_free ? -fy * tz2 * gJ12 : 0.f;
-    const float kx = x_free ? 2.f : 1.f, ky = y_free ? 2.f : 1.f;
+    // GS_PUBLISHED_CLAMP_GRAD (settings.debug bit 1): the widely used implementation's factor 2 for a clamped
+    // component too; default: the true derivative of the clamped forward (factor 1), which finite differences confirm
+    const bool published = (st.debug & GS_PUBLISHED_CLAMP_GRAD) != 0;
+    const float kx = (x_free || published) ? 2.f : 1.f, ky = (y_free || published) ? 2.f : 1.f;
     const float gtz = -fx * tz2 * gJ00 - fy * tz2 * gJ11 + kx * fx * tx * tz3 * gJ02 + ky * fy * ty * tz3 * gJ12;
 #pragma unroll
     for (int c = 0; c < 3; ++c) gm[c] = W0[c] * gtx + W1[c] * gty + W2[c] * gtz;

@@ -473,6 +473,12 @@ int enqueue_iteration(gs_trainer* t, int iter_no, int view, int slot) {
   const View& v = t->views[(size_t)view];
   gs_settings st = v.st;
   st.sh_degree = t->active_sh_degree;
+  if (c.random_background) {
+    // random_background_ (src/arguments/params.h:68): a function of (seed, iteration), so a repeated iteration draws
+    // the same colour; the same generator as Trainer.background_for in gaussian_model.py
+    for (int ch = 0; ch < 3; ++ch)
+      st.bg[ch] = (float)(mix32((uint32_t)c.seed ^ mix32((uint32_t)iter_no * 3u + (uint32_t)ch + 0x51ed270bu)) >> 8) * (1.0f / 16777216.0f);
+  }
   const gs_gaussians in = model_view(t);
   TR_CHECK(gs_forward(t->ctx, &st, t->N, &in, t->image, t->radii, t->stream));
   // ground truth: host -> device on the copy stream, underneath the render that was just enqueued

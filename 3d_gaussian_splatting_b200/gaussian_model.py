@@ -281,17 +281,20 @@ class ViewSampler:
 
 
 def render(viewpoint_camera, pc: GaussianModel, pipe: PipelineParams, bg_color, rast: Rasterizer,
-           scaling_modifier: float = 1.0, fused_activations: bool = True, with_visibility: bool = True):
+           scaling_modifier: float = 1.0, fused_activations: bool = True, with_visibility: bool = True,
+           cache_settings: bool = True):
     """The missing render(viewpoint_cam, gaussians, pipe, background) call.  Returns
     dict(render=(3,H,W), radii=(N) int32, visibility_filter=radii>0).
     fused_activations=True feeds the RAW parameters (activations fused in the kernels);
     False reproduces the getter chain of the reference (exp / normalise / sigmoid / cat)."""
     key = (tuple(bg_color), pc.active_sh_degree, pc.max_sh_degree, scaling_modifier, pipe.debug)
     cache = viewpoint_camera.__dict__.setdefault("_raster_settings", {})
-    st = cache.get(key)
+    st = cache.get(key) if cache_settings else None
     if st is None:   # raster settings of a camera are fixed (src/scene/camera.cpp:56-71): build them once
-        st = cache[key] = GaussianRasterizationSettings.from_camera(
+        st = GaussianRasterizationSettings.from_camera(
             viewpoint_camera, bg_color, pc.active_sh_degree, pc.max_sh_degree, scaling_modifier, pipe.debug)
+        if cache_settings:      # (a random background changes every iteration: not cached)
+            cache[key] = st
     if fused_activations:
         color, radii = rast.forward(st, pc.xyz_, pc.scaling_, pc.rotation_, pc.opacity_, sh_dc=pc.features_dc_,
                                     sh_rest=pc.features_rest_, raw_params=True)
@@ -323,6 +326,8 @@ class Trainer:
         # capacity overflow cannot raise it twice
         self._sh_degree_at_0 = gaussians.active_sh_degree
         self.scale_capacity_on_densify = True
+        self.bg_seed = 0                # random_background: colour = f(bg_seed, iteration)
+        self._cur_bg = self.bg
         self._gt_dev = None
         self._loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
         # capacity mode (no host round-trip inside the forward): enabled by reserve_pairs()
@@ -337,6 +342,25 @@ class Trainer:
         self.on_resize = None           # callable run after a densification step changed N (e.g. rebuild a gradient slab)
         self.peer = None                # multi-GPU: parallel.PeerShardedAdam (exchange fused into K4b / K5)
         self.sharded = None             # multi-GPU: parallel.ShardedAdam (reduce-scatter / sharded Adam / all-gather)
+
+    @staticmethod
+    def _mix32(x: int) -> int:
+        x &= 0xFFFFFFFF
+        x ^= x >> 16
+        x = (x * 0x7feb352d) & 0xFFFFFFFF
+        x ^= x >> 15
+        x = (x * 0x846ca68b) & 0xFFFFFFFF
+        x ^= x >> 16
+        return x
+
+    def background_for(self, iteration: int):
+        """The background colour of iteration `iteration`: the fixed one, or with opt.random_background
+        (random_background_, src/arguments/params.h:68) a fresh uniform colour per iteration -- a function of (seed,
+        iteration), the same counter-based generator as the native trainer's."""
+        if not self.opt.random_background:
+            return self.bg
+        m = self._mix32
+        return tuple((m(self.bg_seed ^ m(iteration * 3 + ch + 0x51ed270b)) >> 8) / 16777216.0 for ch in range(3))
 
     def shard_optimizer(self, rank: int, world: int, group=None):
         """Shard the Adam state over the ranks (parallel.ShardedAdam).  Call before reserve_pairs()."""
@@ -374,7 +398,8 @@ class Trainer:
         stream only waits for it in front of the loss kernel."""
         if self._guard_tensor is not None and not accumulate:
             self._guard_tensor.zero_()   # caller-owned guard: lowered at the start of every iteration
-        out = render(cam, self.g, self.pipe, self.bg, self.rast, with_visibility=False)
+        out = render(cam, self.g, self.pipe, self._cur_bg, self.rast, with_visibility=False,
+                     cache_settings=not self.opt.random_background)
         if gt_host is not None:
             main = torch.cuda.current_stream(self.g.device)
             if self._copy_stream is None:
@@ -547,6 +572,7 @@ class Trainer:
         """Position learning rate and active SH degree of iteration `iteration` (idempotent)."""
         self.g.update_learning_rate(iteration)
         self.g.active_sh_degree = min(self.g.max_sh_degree, self._sh_degree_at_0 + iteration // 1000)
+        self._cur_bg = self.background_for(iteration)
 
     def train_step_device(self, cam, gt_dev: torch.Tensor, gt_host=None, iteration: int | None = None):
         """Device-resident step: ground truth already in HBM; returns the loss as a device tensor.

@@ -34,7 +34,8 @@ class GaussianRasterizationSettings:
     sh_degree: int
     max_sh_degree: int = 3
     prefiltered: bool = False
-    debug: bool = False         # PipelineParams::debug_ (src/arguments/params.h:97)
+    debug: bool = False         # PipelineParams::debug_ (src/arguments/params.h:97): sync + error + NaN/inf checks
+    published_clamp_grad: bool = False   # GS_PUBLISHED_CLAMP_GRAD: the widely used derivative of the 1.3 tanfov guard
 
     def to_c(self) -> GsSettings:
         cached = self.__dict__.get("_c")
@@ -54,16 +55,18 @@ class GaussianRasterizationSettings:
             st.projmatrix[k] = float(pm[k])
         st.scale_modifier = float(self.scale_modifier)
         st.sh_degree, st.max_sh_degree = int(self.sh_degree), int(self.max_sh_degree)
-        st.prefiltered, st.debug = int(self.prefiltered), int(self.debug)
+        st.prefiltered = int(self.prefiltered)
+        st.debug = (_lib.GS_DEBUG_CHECKS if self.debug else 0) | (_lib.GS_PUBLISHED_CLAMP_GRAD if self.published_clamp_grad else 0)
         self.__dict__["_c"] = st
         return st
 
     @staticmethod
-    def from_camera(cam, bg=(0.0, 0.0, 0.0), sh_degree=3, max_sh_degree=3, scale_modifier=1.0, debug=False):
+    def from_camera(cam, bg=(0.0, 0.0, 0.0), sh_degree=3, max_sh_degree=3, scale_modifier=1.0, debug=False,
+                    published_clamp_grad=False):
         return GaussianRasterizationSettings(
             cam.image_height, cam.image_width, cam.tanfovx, cam.tanfovy, tuple(bg), scale_modifier,
             cam.world_view_transform.reshape(-1), cam.full_proj_transform.reshape(-1), cam.camera_center,
-            sh_degree, max_sh_degree, False, debug)
+            sh_degree, max_sh_degree, False, debug, published_clamp_grad)
 
 
 def _ptr(t: Optional[torch.Tensor]):

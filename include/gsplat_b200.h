@@ -36,7 +36,8 @@ enum {
   GS_ENOMEM = -2,    /* device allocation failed */
   GS_ECUDA = -3,     /* CUDA runtime / launch error, or no usable device */
   GS_EOVERFLOW = -4, /* duplicate (Gaussian,tile) list exceeds the 32-bit index space */
-  GS_ESTATE = -5     /* backward without a matching forward, etc. */
+  GS_ESTATE = -5,    /* backward without a matching forward, etc. */
+  GS_ENUMERIC = -6   /* debug: a gradient is NaN or infinite (the role of --detect_anomaly, src/train.cpp:39) */
 };
 
 typedef struct gs_ctx gs_ctx;
@@ -65,8 +66,15 @@ typedef struct {
   float projmatrix[16];
   float campos[3];
   int sh_degree, max_sh_degree;
-  int prefiltered, debug;
+  int prefiltered, debug; /* debug: bit flags, below */
 } gs_settings;
+/* gs_settings.debug bits.  GS_DEBUG_CHECKS = PipelineParams::debug_ (src/arguments/params.h:97): every compute call
+ * synchronises and reports CUDA errors at once, and the backward scans its gradients for NaN / inf (GS_ENUMERIC: the
+ * role of --detect_anomaly, src/train.cpp:39).  GS_PUBLISHED_CLAMP_GRAD: differentiate the 1.3 * tanfov guard of the
+ * EWA projection the way the widely used implementation does (factor 2 in dJ/dt.z for a clamped component too)
+ * instead of the true derivative of the clamped forward; gradients differ only for Gaussians outside the guard. */
+#define GS_DEBUG_CHECKS 1
+#define GS_PUBLISHED_CLAMP_GRAD 2
 
 /*
  * Per-Gaussian inputs (device pointers) = the GaussianModel getters
@@ -329,6 +337,8 @@ typedef struct gs_train_config {
   float bg[3];             /* background colour (white_background_ ? 1 : 0) */
   unsigned int seed;       /* view sampling */
   int active_sh_degree;    /* SH degree at the first iteration (the reference starts at 0 and adds one every 1000) */
+  int random_background;   /* random_background_ (src/arguments/params.h:68): a fresh uniform background colour every
+                              iteration (counter-based, from `seed` and the iteration number) instead of bg */
 } gs_train_config;
 typedef struct gs_trainer gs_trainer;
 #define GS_SAMPLE_SHUFFLE 0 /* without replacement: a stack of all views, one popped at random, refilled when empty */

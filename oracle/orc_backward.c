@@ -10,7 +10,8 @@
  *
  * Deviation from the widely used implementation, chosen because finite differences are this
  * oracle's independent check: when x/z (y/z) is clamped by the 1.3*tanfov guard, the forward
- * is J02 = -fx*lim/tz, so dJ02/dtz carries a factor 1 (not 2) and dJ02/dtx = 0.
+ * is J02 = -fx*lim/tz, so dJ02/dtz carries a factor 1 (not 2) and dJ02/dtx = 0.  Setting bit 1 of
+ * settings.debug selects the widely used form (factor 2 always) -- the compatibility switch of the product.
  */
 #include "orc_common.h"
 
@@ -111,7 +112,10 @@ void orc_preprocess_backward(const orc_settings *st, int N, const real *means3D,
       const real tz2 = RC(1) / (tz * tz), tz3 = tz2 / tz;
       const real gtx = x_free ? -focal_x * tz2 * gJ02 : RC(0);
       const real gty = y_free ? -focal_y * tz2 * gJ12 : RC(0);
-      const real kx = x_free ? RC(2) : RC(1), ky = y_free ? RC(2) : RC(1);
+      /* debug bit 1 (GS_PUBLISHED_CLAMP_GRAD of include/gsplat_b200.h): the widely used implementation's factor 2
+       * for a clamped component as well (its dJ02/dtz treats the clamped t.x as independent of t.z) */
+      const int published = (st->debug & 2) != 0;
+      const real kx = (x_free || published) ? RC(2) : RC(1), ky = (y_free || published) ? RC(2) : RC(1);
       const real gtz = -focal_x * tz2 * gJ00 - focal_y * tz2 * gJ11 + kx * focal_x * tx * tz3 * gJ02 +
                        ky * focal_y * ty * tz3 * gJ12;
       gm[0] = W0[0] * gtx + W1[0] * gty + W2[0] * gtz;

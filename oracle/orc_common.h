@@ -10,7 +10,7 @@
  * PARITY STATUS: "parity unpinned" downstream of the 3D covariance.  The reference
  * contains no rasterizer and does not declare the third-party one it would call
  * (SURVEY.md §0, §8c).  What the reference DOES fix is restated here line by line and
- * pinned against the reference's own known-answer tests (tests/test_oracle_conventions.py):
+ * pinned against the reference's own known-answer tests (tests/test_conventions_golden.py):
  *   quaternion -> R           src/utils/general_utils.cpp:12-40
  *   L = R*diag(s)             src/utils/general_utils.cpp:88-99
  *   Sigma = L*L^T, packing    src/scene/gaussian_model.cpp:18-28, general_utils.cpp:49-62
@@ -105,7 +105,7 @@ typedef struct {
 
 
 /*
- * Specified numerics of the blend inner loop (shared definition: csrc/blend_common.cuh
+ * Specified numerics of the blend inner loop (shared definition: csrc/gs_common.cuh
  * restates the same two functions with __fmaf_rn so the GPU's skip decisions are the oracle's).
  *  - orc_power: power = -(dx*(0.5*A*dx + B*dy) + 0.5*C*dy*dy), evaluated with two explicit
  *    fused multiply-adds in this exact order.
