@@ -62,3 +62,21 @@ def test_fp32_conditioning_of_the_gradients(oracle, oracle64):
         worst[k] = elem_err(a, b)
     assert max(worst.values()) < 5e-3
     assert max(worst["dL_dscales"], worst["dL_drotations"]) > 3e-4      # ... and it really is that large in fp32
+
+
+def test_fp32_oracle_against_float64_build_at_100k(oracle, oracle64):
+    """cfg1 (100 k Gaussians, 800x800): between the fp32 oracle and its float64 build a handful of early-termination /
+    alpha-threshold decisions flip, and the covariance-derived gradients then differ by more than 1e-3 of the array
+    maximum -- the reason the GPU tests allow scales / rotations 3e-3 on the large scenes while every other gradient
+    keeps north_star's 1e-3."""
+    from helpers import syn
+    scene, cams, deg = syn.make_config("cfg1_100k_800_sh3", n_cameras=3)
+    cam = cams[1]
+    rng = np.random.default_rng(9)
+    dL = ((rng.random((3, 800, 800)) * 2 - 1) / 640000).astype(np.float32)
+    r32 = raw_reference(oracle, scene, cam, deg, deg, dL=dL)
+    r64 = raw_reference(oracle64, scene, cam, deg, deg, dL=dL)
+    same = r32["pre"]["radii"] == r64["pre"]["radii"]
+    assert same.mean() > 0.9999
+    e = {k: rel_err(r32["g_ref"][k][same], r64["g_ref"][k][same]) for k in ("dL_dscales", "dL_drotations", "dL_dshs")}
+    assert max(e["dL_dscales"], e["dL_drotations"]) > 1e-3 and e["dL_dscales"] < 1e-2
