@@ -70,9 +70,10 @@ def parse_args():
                     help="> 0: north_star's multi-view step (BASELINE.json configs[4]): ONE optimiser step per batch of this "
                          "many views, split V/g per GPU, gradients accumulated locally over a rank's views, ONE exchange "
                          "(strong scaling: the batch is the same at every GPU count).  Default config for it: cfg4")
-    ap.add_argument("--mode", default="train", choices=["train", "render"],
+    ap.add_argument("--mode", default="train", choices=["train", "render", "raster"],
                     help="train: the headline train step (default).  render: forward-only render throughput sweep over "
-                         "the config's cameras (BASELINE.json configs[3]: Mpix/s with the sort / blend breakdown)")
+                         "the config's cameras (BASELINE.json configs[3]: Mpix/s with the sort / blend breakdown).  raster: "
+                         "one forward + backward of the render path, GPU beside the CPU oracle (BASELINE.json configs[0])")
     return ap.parse_args()
 
 
@@ -551,6 +552,8 @@ def run_ours(args, rank, world, local_rank):
                                            denom=m.denom_, skip_guard=tr.skip_guard)
             else:
                 tr.rast.backward(dL, grads=m.grad_sinks())
+                if tr.grad_sync is not None:      # (all-reduce mode: the replicas must keep receiving the SUMMED gradient;
+                    tr.grad_sync()                #  its time lands in neither the backward's nor the Adam stage)
             ev[2].record()
             if not fused:
                 tr.optimizer_step(out["radii"])
@@ -921,6 +924,67 @@ def run_batch(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_raster(args, local_rank):
+    """--mode raster: ONE forward + backward of the render path (BASELINE.json configs[0]: 10 k Gaussians, one 256x256
+    camera, SH degree 0 -- the mandated CPU measurement), the CUDA path beside the CPU oracle on the host cores, same
+    seeded inputs, dL/dimage = seeded U(-1,1)/P; medians of >= 5 repetitions after warm-up."""
+    import torch
+    pkg = importlib.import_module("3d_gaussian_splatting_b200")
+    syn = importlib.import_module("3d_gaussian_splatting_b200.synthetic")
+    torch.cuda.set_device(local_rank)
+    scene, cams, deg = syn.make_config(args.config, n_cameras=1, N=args.N)
+    cam = cams[0]
+    H, W = cam.image_height, cam.image_width
+    P = H * W
+    rs = np.random.Generator(np.random.Philox(4321))
+    dL = ((2.0 * rs.random((3, H, W)) - 1.0) / P).astype(np.float32)
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda()
+    Pm = [d(scene.xyz), d(scene.features_dc), d(scene.features_rest), d(scene.opacity_logits), d(scene.log_scales),
+          d(scene.raw_rotations)]
+    rast = pkg.Rasterizer(local_rank)
+    sg = pkg.GaussianRasterizationSettings.from_camera(cam, (0.0, 0.0, 0.0), deg, deg)
+    dLd = d(dL)
+    reps = max(args.steps, 9)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(reps + 3)]
+    for e in evs:
+        e[0].record()
+        rast.forward(sg, Pm[0], Pm[4], Pm[5], Pm[3], sh_dc=Pm[1], sh_rest=Pm[2] if Pm[2].numel() else None, raw_params=True)
+        e[1].record()
+        rast.backward(dLd)
+        e[2].record()
+    torch.cuda.synchronize()
+    gf = float(np.median([e[0].elapsed_time(e[1]) for e in evs[3:]]))
+    gb = float(np.median([e[1].elapsed_time(e[2]) for e in evs[3:]]))
+    gfb = float(np.median([e[0].elapsed_time(e[2]) for e in evs[3:]]))
+    D = int(rast.debug_get("NUM_RENDERED")[0])
+    cpu = CpuStep(scene, cams, deg, 1)
+    cf, cb = [], []
+    for i in range(1 + max(5, min(args.steps, 9))):
+        t0 = time.perf_counter()
+        s = cpu.settings(cam)
+        xyz, dc, rest, opl, ls, rq = cpu.raw
+        sc, rot, op = cpu.o.activate_raw(ls, rq, opl)
+        shs = np.ascontiguousarray(np.concatenate([dc, rest], axis=1))
+        pre, b, fwd = cpu.o.forward(s, xyz, sc, rot, op, shs)
+        t1 = time.perf_counter()
+        cpu.o.backward(s, xyz, sc, rot, shs, pre, b, fwd, dL)
+        t2 = time.perf_counter()
+        if i:
+            cf.append((t1 - t0) * 1e3); cb.append((t2 - t1) * 1e3)
+    print(json.dumps({
+        "metric": "raster_fwd_bwd_ms", "value": gfb, "unit": "ms", "n_gpus": 1, "steps": reps, "warmup": 3,
+        "higher_is_better": False, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.config, "mode": "one forward + backward of the render path", "N": scene.N, "W": W,
+                   "H": H, "sh_degree": deg, "D": D},
+        "gpu": {"fwd_ms": round(gf, 4), "bwd_ms": round(gb, 4), "fwd_bwd_ms": round(gfb, 4),
+                "what": "gs_forward + gs_backward through the C ABI (raw parameters), CUDA events, median"},
+        "cpu_baseline": {"fwd_ms": round(float(np.median(cf)), 3), "bwd_ms": round(float(np.median(cb)), 3),
+                         "value": round(float(np.median(cf) + np.median(cb)), 3), "unit": "ms", "cores": cpu.cores,
+                         "kind": "port", "sample": f"median of {len(cf)} forward + backward passes of the same inputs "
+                                                   "(oracle port, OpenMP; built for accuracy, not speed)"},
+    }), flush=True)
+
+
 def run_render_sweep(args, local_rank):
     """--mode render: forward-only render throughput over the config's cameras (BASELINE.json configs[3]: 4 M
     Gaussians at 1920x1080), Mpix/s with the per-stage breakdown.  One JSON line; not the headline metric."""
@@ -1020,6 +1084,9 @@ def main():
     elif args.mode == "render":
         if rank == 0:
             run_render_sweep(args, local_rank)
+    elif args.mode == "raster":
+        if rank == 0:
+            run_raster(args, local_rank)
     else:
         run_ours(args, rank, world, local_rank)
 

@@ -23,6 +23,10 @@ namespace gsplat_b200 {
 // One context per (thread, device), destroyed with the handle.
 struct Context {
   gs_ctx* ctx = nullptr;
+  // stamped by every Rasterize::forward: the gs_ctx keeps the state of its LAST forward only, so a backward whose
+  // stamp is stale (another render ran on this context in between) must fail loudly instead of differentiating the
+  // wrong view
+  uint64_t generation = 0;
   explicit Context(int device = 0) {
     if (gs_create(&ctx, device) != GS_OK) throw std::runtime_error(std::string("gs_create: ") + gs_last_error(nullptr));
   }
@@ -72,12 +76,15 @@ inline gs_settings make_settings(int H, int W, double FoVx, double FoVy, const t
 // {image (3,H,W), radii (N) int32}.  The six inputs are the RAW parameter tensors (the activations of
 // get_scaling / get_rotation / get_opacity / get_features, gaussian_model.cpp:270-304, are fused in the kernels),
 // so loss.backward() deposits .grad on exactly the tensors the reference's optimisers own.
+// means2D (optional): an (N,2) zero tensor with requires_grad, the "screenspace points" of the published API --
+// its .grad receives dL/dmean2D, whose per-Gaussian norm feeds xyz_gradient_accum_ (src/scene/gaussian_model.h:19).
 class Rasterize : public torch::autograd::Function<Rasterize> {
  public:
   static torch::autograd::variable_list forward(torch::autograd::AutogradContext* actx, std::shared_ptr<Context> gs,
                                                 gs_settings st, torch::Tensor xyz, torch::Tensor features_dc,
                                                 torch::Tensor features_rest, torch::Tensor opacity,
-                                                torch::Tensor scaling, torch::Tensor rotation) {
+                                                torch::Tensor scaling, torch::Tensor rotation,
+                                                torch::Tensor means2D = torch::Tensor()) {
     TORCH_CHECK(xyz.is_cuda() && xyz.scalar_type() == torch::kFloat32, "parameters must be float32 CUDA tensors");
     xyz = xyz.contiguous();
     features_dc = features_dc.contiguous();
@@ -103,8 +110,13 @@ class Rasterize : public torch::autograd::Function<Rasterize> {
     check(gs->ctx, gs_forward(gs->ctx, &st, N, &in, image.data_ptr<float>(), radii.data_ptr<int>(), stream), "gs_forward");
     actx->save_for_backward({xyz, features_dc, features_rest, opacity, scaling, rotation});
     actx->saved_data["K"] = (int64_t)K;
-    // (the context and the settings travel as opaque blobs: autograd only stores IValues)
-    actx->saved_data["gs"] = (int64_t)(intptr_t) new std::shared_ptr<Context>(gs);
+    // The context and the settings travel as opaque blobs (autograd only stores IValues).  The context handle lives
+    // in a one-byte tensor whose DELETER releases it: freed with the autograd node whether or not backward ever
+    // runs (an evaluation render with requires_grad), and never twice (retain_graph, a second backward).
+    auto* handle = new std::shared_ptr<Context>(gs);
+    actx->saved_data["gs"] = torch::from_blob(handle, {1}, [handle](void*) { delete handle; }, torch::kUInt8);
+    actx->saved_data["generation"] = (int64_t)(++gs->generation);
+    actx->saved_data["has_means2D"] = means2D.defined();
     actx->saved_data["st"] = torch::from_blob(&st, {(int64_t)sizeof(gs_settings)}, torch::kUInt8).clone();
     actx->mark_non_differentiable({radii});
     return {image, radii};
@@ -115,9 +127,12 @@ class Rasterize : public torch::autograd::Function<Rasterize> {
     auto saved = actx->get_saved_variables();
     auto xyz = saved[0], features_dc = saved[1], features_rest = saved[2], opacity = saved[3], scaling = saved[4],
          rotation = saved[5];
-    std::unique_ptr<std::shared_ptr<Context>> holder(
-        reinterpret_cast<std::shared_ptr<Context>*>((intptr_t)actx->saved_data["gs"].toInt()));
-    gs_ctx* ctx = (*holder)->ctx;
+    const std::shared_ptr<Context>& gs =
+        *reinterpret_cast<std::shared_ptr<Context>*>(actx->saved_data["gs"].toTensor().data_ptr());
+    TORCH_CHECK((int64_t)gs->generation == actx->saved_data["generation"].toInt(),
+                "gsplat_b200::Rasterize: another render ran on this context between this forward and its backward; "
+                "the context keeps the state of its last forward only (use one Context per in-flight render)");
+    gs_ctx* ctx = gs->ctx;
     gs_settings st;
     std::memcpy(&st, actx->saved_data["st"].toTensor().data_ptr<uint8_t>(), sizeof(gs_settings));
     const int K = (int)actx->saved_data["K"].toInt();
@@ -148,8 +163,9 @@ class Rasterize : public torch::autograd::Function<Rasterize> {
     g.dL_dmeans2D = g_m2d.data_ptr<float>();
     void* stream = c10::cuda::getCurrentCUDAStream().stream();
     check(ctx, gs_backward(ctx, &st, N, &in, dL.data_ptr<float>(), &g, stream), "gs_backward");
-    // inputs of forward(): gs, st, then the six parameter tensors
-    return {torch::Tensor(), torch::Tensor(), g_xyz, g_dc, g_rest, g_op, g_scl, g_rot};
+    // inputs of forward(): gs, st, the six parameter tensors, means2D
+    return {torch::Tensor(), torch::Tensor(), g_xyz, g_dc, g_rest, g_op, g_scl, g_rot,
+            actx->saved_data["has_means2D"].toBool() ? g_m2d : torch::Tensor()};
   }
 };
 
