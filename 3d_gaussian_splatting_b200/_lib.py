@@ -74,7 +74,7 @@ EXPORTS = (
     "gs_focal2fov", "gs_get_world2view2", "gs_get_projection_matrix", "gs_camera_settings", "gs_expon_lr",
     "gs_adam_step_flat", "gs_trainer_create", "gs_trainer_destroy", "gs_trainer_last_error", "gs_trainer_add_view", "gs_trainer_run",
     "gs_trainer_num_gaussians", "gs_trainer_iteration", "gs_trainer_retries", "gs_trainer_get_params",
-    "gs_trainer_set_pair_capacity", "gs_trainer_save", "gs_trainer_load",
+    "gs_trainer_set_pair_capacity", "gs_trainer_save", "gs_trainer_load", "gs_peer_barrier",
     "gs_backward_adam_step", "gs_densify_plan", "gs_densify_apply", "gs_reset_opacity", "gs_debug_reuse_blend_gradients", "gs_set_gradient_routing", "gs_adam_step_peer", "gs_peer_alloc", "gs_peer_open", "gs_peer_close", "gs_peer_free", "gs_set_duplicate_capacity", "gs_set_overflow_mirror", "gs_overflow_guard", "gs_get_forward_status",
 )
 
@@ -128,6 +128,7 @@ def _load() -> C.CDLL:
     lib.gs_set_gradient_routing.argtypes = [vp, i, i, i, C.POINTER(vp)]
     lib.gs_adam_step_peer.argtypes = [vp, i, i, i, i, C.POINTER(vp), C.POINTER(vp), vp * 6, vp * 6, i * 6, d * 6,
                                       C.c_longlong * 6, d, d, d, vp, vp, vp, vp, vp, vp, i, vp]
+    lib.gs_peer_barrier.argtypes = [vp, i, i, C.POINTER(vp), C.c_uint, vp, vp, vp]
     lib.gs_peer_alloc.argtypes = [vp, C.c_ulonglong, C.POINTER(vp), C.c_char_p]
     lib.gs_peer_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
     lib.gs_peer_close.argtypes = [vp, vp]

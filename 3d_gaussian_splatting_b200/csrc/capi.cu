@@ -60,6 +60,7 @@ cudaError_t gs_launch_adam_counts(int, int, float* const[], float* const[], floa
                                   const int*, const float*, int*, float*, float*, int, const float*, cudaStream_t);
 cudaError_t gs_launch_l1_loss(size_t, const float*, const float*, float, float*, double*, float*, cudaStream_t);
 cudaError_t gs_launch_count_nonfinite(const float*, size_t, uint32_t*, cudaStream_t);
+cudaError_t gs_launch_peer_barrier(int, int, uint32_t* const[], uint32_t, const float*, float*, cudaStream_t);
 size_t gs_ssim_workspace_bytes(int H, int W);
 cudaError_t gs_launch_photometric_loss(int, int, const float*, const float*, float, float*, double*, float*, float*,
                                        cudaStream_t);
@@ -966,6 +967,25 @@ int gs_adam_step_peer(gs_ctx* c, int nranks, int rank, int N, int rows_per_shard
   GS_CUDA_CHECK(c, gs_launch_adam_peer(nranks, rank, N, rows_per_shard, params, slots, exp_avg, exp_avg_sq, widths, lr,
                                        step, beta1, beta2, eps, radii, dL_dmeans2D, max_radii2D, xyz_grad_accum,
                                        denom, skip_guard, (flags & GS_PEER_PULL) ? 0 : 1, (cudaStream_t)stream_));
+  return GS_OK;
+}
+
+int gs_peer_barrier(gs_ctx* c, int nranks, int rank, void* const flag_blocks[], unsigned int epoch, const float* guard_in,
+                    float* guard_out, void* stream_) {
+  if (!c || nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks || !flag_blocks) {
+    gs_set_error(c, "gs_peer_barrier: bad argument (1..8 ranks)");
+    return GS_EINVAL;
+  }
+  uint32_t* f[8] = {};
+  for (int r = 0; r < nranks; ++r) {
+    if (!flag_blocks[r] || ((uintptr_t)flag_blocks[r] & 3)) {
+      gs_set_error(c, "gs_peer_barrier: flag block %d null or unaligned", r);
+      return GS_EINVAL;
+    }
+    f[r] = (uint32_t*)flag_blocks[r];
+  }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  GS_CUDA_CHECK(c, gs_launch_peer_barrier(nranks, rank, f, epoch, guard_in, guard_out, (cudaStream_t)stream_));
   return GS_OK;
 }
 

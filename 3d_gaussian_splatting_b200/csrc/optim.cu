@@ -423,3 +423,61 @@ cudaError_t gs_launch_count_nonfinite(const float* p, size_t n, uint32_t* count,
   count_nonfinite_kernel<<<(int)(want < 1184 ? (want ? want : 1) : 1184), 256, 0, stream>>>(p, n, count);
   return cudaGetLastError();
 }
+
+// ---- barrier across the ranks of the peer-memory step, in one small kernel (no NCCL, no host) ----
+// Every rank owns a flag block {uint32 epoch[8]; float guard[8]; uint32 timeouts} inside its peer-mapped buffer.
+// Rank r signals by storing (its guard, then `epoch` with release semantics at system scope) into slot r of EVERY
+// rank's block, then waits until every slot of its OWN block has reached `epoch` (acquire loads).  Stream order
+// puts the call after the kernel whose peer stores it publishes (K4b's rows in the owners' slots, the Adam kernel's
+// parameters in the replicas): a kernel boundary completes those stores, the fence orders them before the flag.
+// The guards ride along: guard_out = max over the ranks' guard_in (a pair-capacity overflow on ANY rank voids the
+// step on EVERY rank).  Epochs only grow, and no rank can be more than one barrier ahead of another, so `>=` is the
+// test.  A rank that does not arrive within ~2 s (a crashed peer) is reported in the block's timeout counter and the
+// kernel returns instead of hanging the GPU.
+struct PeerBarrierArgs {
+  uint32_t* flags[ADP_MAX_RANKS];  // flag block of every rank (own: local memory)
+  int G, rank;
+  uint32_t epoch;
+  const float* guard_in;
+  float* guard_out;
+};
+__global__ void __launch_bounds__(32) peer_barrier_kernel(const __grid_constant__ PeerBarrierArgs a) {
+  const int r = threadIdx.x;
+  float g = 0.0f;
+  if (r < a.G) {
+    const float mine = a.guard_in ? *a.guard_in : 0.0f;
+    __threadfence_system();
+    float* gslot = reinterpret_cast<float*>(a.flags[r] + 8) + a.rank;
+    uint32_t* eslot = a.flags[r] + a.rank;
+    asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(gslot), "f"(mine) : "memory");
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(eslot), "r"(a.epoch) : "memory");
+    const uint32_t* wait = a.flags[a.rank] + r;
+    const long long t0 = clock64();
+    uint32_t seen;
+    while (true) {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(wait) : "memory");
+      if ((int32_t)(seen - a.epoch) >= 0) break;
+      if (clock64() - t0 > 4000000000ll) {  // ~2 s
+        atomicAdd(a.flags[a.rank] + 16, 1u);
+        break;
+      }
+      __nanosleep(100);
+    }
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(g) : "l"(reinterpret_cast<const float*>(a.flags[a.rank] + 8) + r) : "memory");
+  }
+#pragma unroll
+  for (int o = 4; o > 0; o >>= 1) g = fmaxf(g, __shfl_xor_sync(0xffffffffu, g, o));
+  if (r == 0 && a.guard_out) *a.guard_out = g;
+}
+cudaError_t gs_launch_peer_barrier(int G, int rank, uint32_t* const flags[], uint32_t epoch, const float* guard_in,
+                                   float* guard_out, cudaStream_t stream) {
+  PeerBarrierArgs a;
+  for (int r = 0; r < ADP_MAX_RANKS; ++r) a.flags[r] = r < G ? flags[r] : nullptr;
+  a.G = G;
+  a.rank = rank;
+  a.epoch = epoch;
+  a.guard_in = guard_in;
+  a.guard_out = guard_out;
+  peer_barrier_kernel<<<1, 32, 0, stream>>>(a);
+  return cudaGetLastError();
+}

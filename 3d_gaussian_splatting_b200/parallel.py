@@ -195,7 +195,14 @@ class PeerShardedAdam:
                     row.append(off)
                     off += R * c
                 self.s_off.append(row)
+        # the flag block of the kernel barriers (gs_peer_barrier): 32 words, zeroed with the buffer
+        off = (off + 31) // 32 * 32
+        self.f_off = off
+        off += 32
         self.total = off
+        self.epoch = 0
+        import os
+        self.flag_barriers = os.environ.get("GS_PEER_NCCL_BARRIER", "0") != "1"
         self.base, handle = rast.peer_alloc(self.total * 4)
         handles = [None] * world
         if world > 1:
@@ -244,6 +251,7 @@ class PeerShardedAdam:
         self.guard = torch.zeros(1, dtype=torch.float32, device=self.flat.device)
         self.sync = torch.zeros(1, dtype=torch.float32, device=self.flat.device)
         # params[r][k]: rank r's replica; slots[s][k]: MY slot for source s; routing[q][k]: my slot INSIDE rank q
+        self.flag_ptrs = [self.bases[r] + 4 * self.f_off for r in range(world)]
         self.param_ptrs = [[self.bases[r] + 4 * self.p_off[k] for k in range(6)] for r in range(world)]
         if self.pull:
             # source s of my shard = rows [rank*R, ...) of rank s's slab (peer-mapped for s != rank)
@@ -255,10 +263,24 @@ class PeerShardedAdam:
             rast.set_gradient_routing(world, rank, R, routing)
         self.barrier()   # every replica initialised and every mapping in place before anyone stores remotely
 
-    def barrier(self):
-        """Stream-ordered barrier across the ranks (one-float NCCL all-reduce)."""
-        if dist.is_initialized() and self.world > 1:
-            dist.all_reduce(self.sync, op=dist.ReduceOp.MAX, group=self.group)
+    def barrier(self, with_guard: bool = False, nccl: bool = False):
+        """Stream-ordered barrier across the ranks.  Default: gs_peer_barrier -- one 32-thread kernel per rank that
+        stores an epoch flag into every rank's flag block over NVLink and waits for the others' (a few microseconds,
+        against ~25 for a one-float NCCL all-reduce).  with_guard: the overflow guards ride along, self.guard becomes
+        their maximum over the ranks.  nccl=True (or GS_PEER_NCCL_BARRIER=1): the collective instead."""
+        if not (dist.is_initialized() and self.world > 1):
+            return
+        if nccl or not self.flag_barriers:
+            dist.all_reduce(self.guard if with_guard else self.sync, op=dist.ReduceOp.MAX, group=self.group)
+            return
+        self.epoch += 1
+        g = self.guard if with_guard else None
+        self.rast.peer_barrier(self.world, self.rank, self.flag_ptrs, self.epoch, guard_in=g, guard_out=g)
+
+    def barrier_timeouts(self) -> int:
+        """Barriers of this rank that gave up waiting for a peer (~2 s each); 0 in a healthy run.  Synchronises."""
+        torch.cuda.synchronize(self.flat.device)
+        return int(self.flat[self.f_off + 16:self.f_off + 17].view(torch.int32).item())
 
     def slot(self, src: int, k: int) -> torch.Tensor:
         """The gradient rows source rank `src` stored for my shard, group k: (R, widths[k]) (push layout)."""
@@ -270,8 +292,7 @@ class PeerShardedAdam:
              use_guard: bool = False):
         m = self.model
         # barrier 1: every rank's backward has landed in the slots; carries the overflow guard along
-        if dist.is_initialized() and self.world > 1:
-            dist.all_reduce(self.guard, op=dist.ReduceOp.MAX, group=self.group)
+        self.barrier(with_guard=True)
         self.rast.adam_step_peer(self.world, self.rank, self.N, self.R, self.param_ptrs, self.slot_ptrs, m.exp_avg,
                                  m.exp_avg_sq, self.widths, lr, step, radii=radii, dL_dmeans2D=dL_dmeans2D,
                                  max_radii2D=max_radii2D, xyz_grad_accum=xyz_grad_accum, denom=denom,
@@ -305,14 +326,14 @@ class PeerShardedAdam:
 
     def close(self):
         torch.cuda.synchronize(self.flat.device)
-        self.barrier()                        # nobody is still storing into a peer's buffer
+        self.barrier(nccl=True)               # nobody is still storing into a peer's buffer
         if not self.pull:
             self.rast.set_gradient_routing(0)
         for r, b in enumerate(self.bases):
             if r != self.rank:
                 self.rast.peer_close(b)
         torch.cuda.synchronize(self.flat.device)
-        self.barrier()                        # every mapping is gone before any owner frees
+        self.barrier(nccl=True)               # every mapping is gone before any owner frees (the flag blocks too)
         torch.cuda.synchronize(self.flat.device)
         self.flat = None
         self.rast.peer_free(self.base)

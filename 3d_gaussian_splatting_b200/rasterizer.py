@@ -338,6 +338,13 @@ class Rasterizer:
     def peer_free(self, ptr: int):
         check(self._ctx, lib.gs_peer_free(self._ctx, C.c_void_p(ptr)))
 
+    def peer_barrier(self, nranks: int, rank: int, flag_blocks, epoch: int, guard_in=None, guard_out=None):
+        """gs_peer_barrier: flag-based barrier across the ranks of the peer-memory step (one 32-thread kernel)."""
+        tab = (C.c_void_p * nranks)(*[int(p) for p in flag_blocks])
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._ctx, lib.gs_peer_barrier(self._ctx, nranks, rank, tab, int(epoch) & 0xFFFFFFFF, _ptr(guard_in),
+                                             _ptr(guard_out), C.c_void_p(stream)))
+
     def wrap(self, ptr: int, nfloats: int) -> torch.Tensor:
         """A float32 torch view of raw device memory (no copy, no ownership)."""
         class _Raw:

@@ -692,7 +692,7 @@ def run_ours(args, rank, world, local_rank):
                           "dL/dimage = seeded U(-1,1)/P, median of 9 after 3 warm-ups, CUDA events"}
 
     # ---- N > 1: the replicas must be bit-identical after the timed loops (every rank holds the same model) ----
-    replicas_identical = last_loss = None
+    replicas_identical = last_loss = barrier_timeouts = None
     if world > 1:
         torch.cuda.synchronize()
         cs = torch.zeros(1, dtype=torch.int64, device=dev)
@@ -703,6 +703,8 @@ def run_ours(args, rank, world, local_rank):
         dist.all_gather(allcs, cs)
         replicas_identical = all(int(c.item()) == int(allcs[0].item()) for c in allcs)
         last_loss = float(e2e_losses[-1]) if e2e_losses else None
+        if args.dp_mode == "peer":
+            barrier_timeouts = sharded.barrier_timeouts()
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = CpuStep(scene, cams, deg, args.views)
@@ -732,7 +734,8 @@ def run_ours(args, rank, world, local_rank):
                        "parallelism": (f"camera-sharded dp{world}, {grad_mb:.0f} MB of gradients per rank: "
                                        + {"peer": "K4b stores them into the owner ranks' slots over NVLink, K5 sums the "
                                                   "slots, updates the owned 1/%d of the rows and stores the parameters "
-                                                  "into every replica (2 one-float NCCL all-reduces as barriers)" % world,
+                                                  "into every replica (2 flag barriers per step: gs_peer_barrier, one 32-thread "
+                                                  "kernel each, no collective)" % world,
                                           "sharded": "NCCL reduce-scatter -> Adam on the owned 1/%d slice -> NCCL "
                                                      "all-gather" % world,
                                           "allreduce": "one NCCL all-reduce, replicated Adam"}[args.dp_mode])
@@ -747,7 +750,7 @@ def run_ours(args, rank, world, local_rank):
             "best_case": best_case, "stress": stress,
             # north_star's 64-view batch on the 6 M-Gaussian scene: views/s, exchange time reported separately
             "north_star_batch": north,
-            "replicas_identical": replicas_identical, "last_loss": last_loss,
+            "replicas_identical": replicas_identical, "last_loss": last_loss, "barrier_timeouts": barrier_timeouts,
             "raster": raster,
             "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,
@@ -877,7 +880,7 @@ def measure_batch(args, rank, world, local_rank, config, V, steps, warm, dp_mode
            "exchange": {"single": "none (one GPU): Adam + statistics only",
                         "peer": "pull over NVLink peer memory: the owner's Adam kernel reads its rows of every rank's "
                                 "gradient slab, updates its 1/%d of the model and stores the parameters into every "
-                                "replica (2 one-float NCCL all-reduces as barriers)" % world,
+                                "replica (2 flag barriers per step: gs_peer_barrier)" % world,
                         "allreduce": "one NCCL all-reduce of the gradient slab, replicated Adam"}[mode],
            "exchange_bytes_per_rank": (0 if world == 1 else int(2 * (world - 1) / world * 4 * sum(p.numel() for p in model.params()))),
            "e2e_ms_per_step": e2e_ms, "e2e_views_per_s": V / (e2e_ms * 1e-3),
@@ -885,6 +888,7 @@ def measure_batch(args, rank, world, local_rank, config, V, steps, warm, dp_mode
            "capacity_ok": ok, "replicas_identical": identical, "last_loss": float(last.item()),
            "adam_state": "warm", "scaling": "strong"}
     if mode == "peer":
+        res["barrier_timeouts"] = trainer.peer.barrier_timeouts()
         trainer.peer.detach_model()
         trainer.peer.close()
     trainer.rast.close()

@@ -262,6 +262,17 @@ GS_API int gs_adam_step_peer(gs_ctx *ctx, int nranks, int rank, int N, int rows_
                              int *max_radii2D, float *xyz_grad_accum, float *denom, const float *skip_guard,
                              int flags, void *stream);
 #define GS_PEER_PULL 1
+/* The two barriers of the peer-memory step as ONE small kernel each instead of a collective: every rank owns a
+ * 128-byte flag block inside its peer-mapped buffer (zeroed by gs_peer_alloc); flag_blocks[r] is rank r's block as
+ * mapped here.  The call stores (guard_in, epoch) into this rank's slot of every block and waits until every slot of
+ * its own block has reached `epoch` -- so it returns (in stream order) only after every rank's preceding kernels on
+ * the same barrier have completed and their peer stores are visible.  epoch: a number that grows by one per barrier
+ * (the same sequence on every rank).  guard_out receives the maximum of the ranks' guard_in (the overflow guard of
+ * the step; both may be NULL).  A peer that does not arrive within ~2 s is counted in word 16 of the block and the
+ * kernel returns instead of hanging. */
+GS_API int gs_peer_barrier(gs_ctx *ctx, int nranks, int rank, void *const flag_blocks[], unsigned int epoch,
+                           const float *guard_in, float *guard_out, void *stream);
+#define GS_PEER_FLAG_BYTES 128
 
 /* ---- running without the host round-trip ----------------------------------------------------
  * By default gs_forward synchronises the stream once, to size the (tile, Gaussian) pair lists from
