@@ -192,7 +192,8 @@ class NativeTrainer:
             o.lambda_dssim if lambda_dssim is None else lambda_dssim, o.densification_interval,
             o.opacity_reset_interval, o.densify_from_iter, o.densify_until_iter, o.densify_grad_threshold,
             spatial_lr_scale, (C.c_float * 3)(*bg), seed,
-            scene.max_sh_degree if active_sh_degree is None else active_sh_degree)   # (as GaussianModel.load_scene)
+            scene.max_sh_degree if active_sh_degree is None else active_sh_degree,   # (as GaussianModel.load_scene)
+            int(o.random_background))
         f32 = lambda a: np.ascontiguousarray(a, dtype=np.float32)
         self._init = [f32(scene.xyz), f32(scene.features_dc), f32(scene.features_rest), f32(scene.opacity_logits),
                       f32(scene.log_scales), f32(scene.raw_rotations)]

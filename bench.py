@@ -586,9 +586,26 @@ def run_ours(args, rank, world, local_rank):
     sustained = None
     if args.sustain_seconds > 0 and not args.no_extras:
         n_sus = max(args.steps, int(args.sustain_seconds * 1e3 / ms_per_step) + 1)
-        sus_ms, sus_clocks = timed(step_device, n_sus, 0, ClockSampler(local_rank) if rank == 0 else None)
+        marks, host_t = [], [0.0, 0.0]
+
+        def step_marked(i):
+            if i == 0:
+                host_t[0] = time.perf_counter()
+            if i % 100 == 0:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                marks.append(e)
+            step_device(i)
+            host_t[1] = time.perf_counter()
+
+        sus_ms, sus_clocks = timed(step_marked, n_sus, 0, ClockSampler(local_rank) if rank == 0 else None)
+        per100 = [round(a.elapsed_time(b) / 100.0, 4) for a, b in zip(marks, marks[1:])]
         sustained = {"ms_per_step": sus_ms / n_sus, "value": world * 1e3 / (sus_ms / n_sus), "unit": UNIT,
-                     "steps": n_sus, "seconds": round(sus_ms * 1e-3, 3), "clocks": sus_clocks}
+                     "steps": n_sus, "seconds": round(sus_ms * 1e-3, 3), "clocks": sus_clocks,
+                     # device ms per step over each block of 100 steps, and the HOST time the Python loop needed to
+                     # enqueue a step (when it reaches the device time the loop, not the GPU, sets the pace)
+                     "ms_per_step_by_100": per100,
+                     "host_enqueue_ms_per_step": round((host_t[1] - host_t[0]) * 1e3 / n_sus, 4)}
 
     # ---- secondary workloads (single GPU): the same step with (a) cold Adam state -- the synthetic ball hides ~70 %
     # of its Gaussians from every view, their vectors stay at the exact fixed point and are skipped: the best case;
@@ -1043,7 +1060,7 @@ def run_render_sweep(args, local_rank):
     pad = torch.zeros(((H + 15) // 16 * 16, (W + 15) // 16 * 16), dtype=torch.int64)
     pad[:H, :W] = ncon
     D_eff = int(pad.reshape(pad.shape[0] // 16, 16, pad.shape[1] // 16, 16).amax(dim=(1, 3)).sum().item())
-    by = stage_bytes(N, N_vis, D, D_eff, P, T, K, active_floats if world == 1 else None)
+    by = stage_bytes(N, N_vis, D, D_eff, P, T, K)
     if world > 1 and args.dp_mode == "peer" and active_floats is not None:
         # adam_peer_kernel, local HBM bytes of one rank: the `world` gradient slots + m, v, p of its R-row shard read;
         # m, v, p of the active vectors written; plus what the other ranks' kernels store into this replica
