@@ -169,14 +169,29 @@ onesweep_scatter_kernel(const KeyT* __restrict__ keys_in, KeyT* __restrict__ key
       os_store(my, hi | ((unsigned long long)OS_FLAG_INCLUSIVE << 32) | total);
     } else {
       os_store(my, hi | ((unsigned long long)OS_FLAG_AGGREGATE << 32) | total);
+      // Look back over the predecessors, nearest first, EIGHT status words per round (independent loads: one L2
+      // latency per round instead of one per tile -- tiles that start together see ~sqrt(2 * tiles) aggregate-only
+      // predecessors before the first inclusive one, and the serial walk was most of a pass, profiles/r02g).
       const unsigned long long* look = my - RS_BINS;
-      while (true) {
-        unsigned long long sv;
-        while (((sv = os_load(look)) >> 34) != (unsigned long long)tag)
-          if (sleep_ns) __nanosleep(sleep_ns);  // (polling 256 words per waiting tile competes with K1 for L2 slots)
-        excl += (uint32_t)sv;
-        if (((uint32_t)(sv >> 32) & 3u) == OS_FLAG_INCLUSIVE) break;
-        look -= RS_BINS;
+      int remaining = (int)tile;  // predecessors not yet examined (tile 0 always carries an inclusive prefix)
+      bool done = false;
+      while (!done) {
+        unsigned long long sv[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) sv[k] = k < remaining ? os_load(look - (size_t)k * RS_BINS) : 0ull;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (!done && k < remaining) {
+            while ((sv[k] >> 34) != (unsigned long long)tag) {  // not published yet in this pass
+              if (sleep_ns) __nanosleep(sleep_ns);
+              sv[k] = os_load(look - (size_t)k * RS_BINS);
+            }
+            excl += (uint32_t)sv[k];
+            done = ((uint32_t)(sv[k] >> 32) & 3u) == OS_FLAG_INCLUSIVE;
+          }
+        }
+        look -= 8 * RS_BINS;
+        remaining -= 8;
       }
       os_store(my, hi | ((unsigned long long)OS_FLAG_INCLUSIVE << 32) | (unsigned long long)(excl + total));
     }

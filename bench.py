@@ -1061,14 +1061,6 @@ def run_render_sweep(args, local_rank):
     pad[:H, :W] = ncon
     D_eff = int(pad.reshape(pad.shape[0] // 16, 16, pad.shape[1] // 16, 16).amax(dim=(1, 3)).sum().item())
     by = stage_bytes(N, N_vis, D, D_eff, P, T, K)
-    if world > 1 and args.dp_mode == "peer" and active_floats is not None:
-        # adam_peer_kernel, local HBM bytes of one rank: the `world` gradient slots + m, v, p of its R-row shard read;
-        # m, v, p of the active vectors written; plus what the other ranks' kernels store into this replica
-        wfl, R = 11 + 3 * K, sharded.R
-        by["adam_stats"] = (4 * world + 12) * wfl * R + 12 * active_floats + 4 * active_floats * (world - 1) + 36 * N_vis
-    elif world > 1 and args.dp_mode == "sharded":
-        wfl = 11 + 3 * K
-        by["adam_stats"] = 28 * wfl * N // world + 36 * N_vis
     peak, peak_kind = peaks()
     fwd_bytes = sum(by[k] for k in ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd"))
     binning = sum(stage_ms.get(k, 0.0) for k in ("depth_sort", "scan_duplicate", "sort", "ranges"))
