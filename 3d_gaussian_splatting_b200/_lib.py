@@ -70,7 +70,7 @@ class GsTrainConfig(C.Structure):
 # every symbol include/gsplat_b200.h declares (tests check the library exports all of them)
 EXPORTS = (
     "gs_version", "gs_create", "gs_destroy", "gs_last_error", "gs_forward", "gs_backward",
-    "gs_adam_densify_step", "gs_loss", "gs_debug_size", "gs_debug_get", "gs_set_profiling", "gs_get_stage_ms",
+    "gs_adam_densify_step", "gs_loss", "gs_loss_static", "gs_debug_size", "gs_debug_get", "gs_set_profiling", "gs_get_stage_ms",
     "gs_focal2fov", "gs_get_world2view2", "gs_get_projection_matrix", "gs_camera_settings", "gs_expon_lr",
     "gs_adam_step_flat", "gs_trainer_create", "gs_trainer_destroy", "gs_trainer_last_error", "gs_trainer_add_view", "gs_trainer_run",
     "gs_trainer_num_gaussians", "gs_trainer_iteration", "gs_trainer_retries", "gs_trainer_get_params",
@@ -139,6 +139,7 @@ def _load() -> C.CDLL:
     lib.gs_overflow_guard.restype = vp
     lib.gs_get_forward_status.argtypes = [vp, C.POINTER(C.c_ulonglong), C.POINTER(i)]
     lib.gs_loss.argtypes = [vp, i, i, vp, vp, f, vp, vp, vp]
+    lib.gs_loss_static.argtypes = [i, i, i, vp, vp, f, vp, vp, vp]
     lib.gs_debug_size.argtypes = [vp, i]
     lib.gs_debug_size.restype = C.c_longlong
     lib.gs_debug_get.argtypes = [vp, i, vp, C.c_size_t]

@@ -13,6 +13,8 @@
 //                         window is itself) and combines  dL/dx = w*dmu1 + 2x w*de11 + y w*de12  with the L1 sign.
 #include "gs_common.cuh"
 
+#include <mutex>
+
 #define SS_TX 32
 #define SS_TY 32
 #define SS_R 5
@@ -293,4 +295,60 @@ cudaError_t gs_launch_photometric_loss(int H, int W, const float* img, const flo
                                                      (1.0f - lambda) / (float)n, dL_dimg);
   photometric_finalize_kernel<<<1, 1024, 0, stream>>>(partial, ssim_blocks(H, W), 1.0 / (double)n, (double)lambda, loss_out);
   return cudaGetLastError();
+}
+
+// ---- allocation-free variant of the photometric loss ------------------------------------------------------------
+// gs_loss_static: the same three kernels as gs_loss, with the SSIM workspace (three partial-derivative maps of
+// 3*H*W floats and one float2 per block) in a file-scope device array instead of a cudaMalloc'ed context buffer, for
+// callers that may not allocate (CUDA graph capture, serving loops).  No counterpart in the reference.
+// The array exists once per device that loads the library and is shared by every
+// call: calls that overlap on the GPU (two streams, two host threads) race on it.  Nothing in it has to start at
+// zero: every word a call reads (the maps inside the image, one partial per launched block) is written earlier in
+// the same call, so the contents left by the previous call are never observed.
+#define GS_LOSS_STATIC_MAX_BLOCKS 32768
+static __device__ __align__(256) float g_loss_static_scratch[(size_t)9 * GS_LOSS_STATIC_MAX_PIXELS + 2 * GS_LOSS_STATIC_MAX_BLOCKS];
+
+#define GS_LOSS_STATIC_MAX_DEVICES 64
+static float* s_loss_static_ptr[GS_LOSS_STATIC_MAX_DEVICES];  // device address of the array, per device ordinal
+static std::mutex s_loss_static_mu;
+
+// In host code `g_loss_static_scratch` is only a handle for the runtime, not a device address: resolve it once per
+// device, with that device current.  (The first resolution on a device may make the runtime load this module there;
+// a caller that captures graphs makes one call outside the capture first.)
+static cudaError_t loss_static_scratch(int device, float** out) {
+  std::lock_guard<std::mutex> lk(s_loss_static_mu);
+  if (!s_loss_static_ptr[device]) {
+    float* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_loss_static_scratch);
+    if (e != cudaSuccess) return e;
+    s_loss_static_ptr[device] = p;
+  }
+  *out = s_loss_static_ptr[device];
+  return cudaSuccess;
+}
+
+extern "C" GS_API int gs_loss_static(int device, int H, int W, const float* image, const float* gt, float lambda_dssim,
+                                     float* loss_out, float* dL_dimage, void* stream) {
+  if (device < 0 || device >= GS_LOSS_STATIC_MAX_DEVICES || H <= 0 || W <= 0 || !image || !gt || !loss_out) {
+    gs_set_error(nullptr, "gs_loss_static: bad argument");
+    return GS_EINVAL;
+  }
+  if (!(lambda_dssim >= 0.0f && lambda_dssim <= 1.0f)) {
+    gs_set_error(nullptr, "gs_loss_static: lambda_dssim %g outside [0,1]", (double)lambda_dssim);
+    return GS_EINVAL;
+  }
+  if ((long long)H * W > GS_LOSS_STATIC_MAX_PIXELS || ssim_blocks(H, W) > GS_LOSS_STATIC_MAX_BLOCKS) {
+    gs_set_error(nullptr,
+                 "gs_loss_static: %d x %d = %lld pixels exceeds the static workspace (GS_LOSS_STATIC_MAX_PIXELS = %d, "
+                 "at most %d blocks of 32x32); use gs_loss",
+                 H, W, (long long)H * W, GS_LOSS_STATIC_MAX_PIXELS, GS_LOSS_STATIC_MAX_BLOCKS / 3);
+    return GS_EINVAL;
+  }
+  GS_CUDA_CHECK((gs_ctx*)nullptr, cudaSetDevice(device));
+  float* work = nullptr;
+  GS_CUDA_CHECK((gs_ctx*)nullptr, loss_static_scratch(device, &work));
+  // same layout inside the array as gs_ssim_workspace_bytes() describes for the context's buffer
+  GS_CUDA_CHECK((gs_ctx*)nullptr, gs_launch_photometric_loss(H, W, image, gt, lambda_dssim, work, nullptr, loss_out,
+                                                             dL_dimage, (cudaStream_t)stream));
+  return GS_OK;
 }

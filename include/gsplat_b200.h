@@ -296,6 +296,20 @@ GS_API int gs_get_forward_status(gs_ctx *ctx, unsigned long long *num_duplicates
 GS_API int gs_loss(gs_ctx *ctx, int H, int W, const float *image, const float *gt, float lambda_dssim,
                    float *loss_out, float *dL_dimage, void *stream);
 
+/* gs_loss_static: gs_loss for callers that may not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and result as gs_loss minus the context (`device` = CUDA device ordinal of the buffers); the SSIM
+ * workspace is a file-scope device array inside the library (9 * GS_LOSS_STATIC_MAX_PIXELS floats + block partials
+ * = 9.25 MiB, held by every GPU that loads the library until the process exits), so the call makes no cudaMalloc /
+ * cudaFree and needs no gs_ctx.  H * W > GS_LOSS_STATIC_MAX_PIXELS (or more than 10 922 tiles of 32x32) returns
+ * GS_EINVAL with a message in gs_last_error(NULL).  lambda_dssim = 0 runs the same kernels (gs_loss switches to a
+ * pure-L1 kernel there; equal to rounding).  All calls on a device share the array: calls that overlap on the GPU
+ * (different streams or host threads) race; nothing in it needs clearing between calls.  The array's device address
+ * is resolved once per device on the first call there (cudaGetSymbolAddress): make that call outside a capture. */
+#define GS_LOSS_STATIC_MAX_PIXELS 262144 /* e.g. 512 x 512 */
+GS_API int gs_loss_static(int device, int H, int W, const float *image, const float *gt, float lambda_dssim,
+                          float *loss_out, float *dL_dimage, void *stream);
+
 /* ---- parity harness: read intermediates of the last gs_forward / gs_backward --------------
  * Copies (synchronously) the named workspace array to host memory.  `bytes` must equal the
  * array's size; gs_debug_size returns it (or a negative error). */
