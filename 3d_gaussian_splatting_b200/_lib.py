@@ -14,8 +14,8 @@ LIB_PATH = os.path.join(HERE, "libgsplat_b200.so")
 
 GS_OK, GS_EINVAL, GS_ENOMEM, GS_ECUDA, GS_EOVERFLOW, GS_ESTATE, GS_ENUMERIC = 0, -1, -2, -3, -4, -5, -6
 GS_DEBUG_CHECKS, GS_PUBLISHED_CLAMP_GRAD = 1, 2
-GS_NUM_STAGES = 8
-STAGE_NAMES = ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd")
+GS_NUM_STAGES = 9
+STAGE_NAMES = ("preprocess", "depth_sort", "scan_duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "sh_color")
 
 DBG = dict(MEANS2D=0, DEPTHS=1, CONIC_OPACITY=2, RGB=3, CLAMPED=4, TILES_TOUCHED=5, DEPTH_ORDER=6,
            KEYS_SORTED=7, POINT_LIST=8, RANGES=9, FINAL_T=10, N_CONTRIB=11, DL_DMEAN2D=12, DL_DCONIC=13,
@@ -74,7 +74,7 @@ EXPORTS = (
     "gs_focal2fov", "gs_get_world2view2", "gs_get_projection_matrix", "gs_camera_settings", "gs_expon_lr",
     "gs_adam_step_flat", "gs_trainer_create", "gs_trainer_destroy", "gs_trainer_last_error", "gs_trainer_add_view", "gs_trainer_run",
     "gs_trainer_num_gaussians", "gs_trainer_iteration", "gs_trainer_retries", "gs_trainer_get_params",
-    "gs_trainer_set_pair_capacity", "gs_trainer_save", "gs_trainer_load", "gs_peer_barrier",
+    "gs_trainer_set_pair_capacity", "gs_trainer_save", "gs_trainer_load", "gs_peer_barrier", "gs_set_color_gate", "gs_peer_copy",
     "gs_backward_adam_step", "gs_densify_plan", "gs_densify_apply", "gs_reset_opacity", "gs_debug_reuse_blend_gradients", "gs_set_gradient_routing", "gs_adam_step_peer", "gs_peer_alloc", "gs_peer_open", "gs_peer_close", "gs_peer_free", "gs_set_duplicate_capacity", "gs_set_overflow_mirror", "gs_overflow_guard", "gs_get_forward_status",
 )
 
@@ -139,6 +139,8 @@ def _load() -> C.CDLL:
     lib.gs_overflow_guard.restype = vp
     lib.gs_get_forward_status.argtypes = [vp, C.POINTER(C.c_ulonglong), C.POINTER(i)]
     lib.gs_loss.argtypes = [vp, i, i, vp, vp, f, vp, vp, vp]
+    lib.gs_set_color_gate.argtypes = [vp, vp]
+    lib.gs_peer_copy.argtypes = [vp, vp, vp, C.c_ulonglong, vp]
     lib.gs_loss_static.argtypes = [i, i, i, vp, vp, f, vp, vp, vp]
     lib.gs_debug_size.argtypes = [vp, i]
     lib.gs_debug_size.restype = C.c_longlong

@@ -14,7 +14,9 @@
 
 // ---- launchers implemented in the other translation units ----
 cudaError_t gs_launch_preprocess(const gs_settings&, const gs_gaussians&, int, GsGeom*, float*, int*, uint32_t*,
-                                 uint4*, uint8_t*, int*, cudaStream_t);
+                                 uint4*, uint8_t*, int*, int defer_color, cudaStream_t);
+cudaError_t gs_launch_sh_color(const gs_settings&, const gs_gaussians&, int, const int* radii, GsGeom*, uint8_t* clamped,
+                               cudaStream_t);
 cudaError_t gs_launch_depth_sort(int, const uint32_t*, uint32_t*, uint32_t*, uint32_t*, uint32_t*, const uint32_t*,
                                  unsigned long long*, uint32_t*, uint32_t, int, int, uint32_t, cudaStream_t);
 size_t gs_onesweep_status_words(size_t n, int items);
@@ -51,7 +53,8 @@ cudaError_t gs_launch_preprocess_backward_routed(const gs_settings&, const gs_ga
                                                  cudaStream_t);
 cudaError_t gs_launch_adam_peer(int, int, int, int, float* const[], const float* const[], float* const[6],
                                 float* const[6], const int[6], const double[6], const long long[6], double, double,
-                                double, const int*, const float*, int*, float*, float*, const float*, int, cudaStream_t);
+                                double, const int*, const float*, int*, float*, float*, const float*, int, int max_blocks, int local_mask,
+                                cudaStream_t);
 cudaError_t gs_launch_adam(int, float* const[6], float* const[6], float* const[6], float* const[6], const int[6],
                            const double[6], const long long[6], double, double, double, const int*, const float*, int*,
                            float*, float*, int, const float*, cudaStream_t);
@@ -82,6 +85,14 @@ struct gs_ctx {
   cudaStream_t side = nullptr;
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool overlap_depth_sort = true;
+  // colour gate (gs_set_color_gate): K1 leaves the SH -> RGB evaluation to a kernel that runs just ahead of the
+  // forward blend, after this event -- the multi-GPU step records it once the peers have delivered the new SH
+  // coefficients, so that their all-gather overlaps K1 and the binning stages
+  cudaEvent_t color_gate = nullptr;
+  cudaEvent_t ev_k1 = nullptr, ev_color = nullptr;  // K1 done (the colour kernel needs its radii) / colours complete
+  cudaStream_t color_stream = nullptr;              // default priority (the sort's stream is high priority: a 12 500-block
+                                                    // kernel there would push the duplicate stage aside, not run beside it)
+  int peer_side_grid = 0;  // grid cap of a gs_adam_step_peer call flagged GS_PEER_BESIDE_FORWARD (a third of the SMs)
   // per-duplicate: tile ids (u16, u32 beyond 65536 tiles) and Gaussian ids, ping-pong
   DevBuf keys_a, keys_b, vals_a, vals_b;
   DevBuf radix_counts;
@@ -240,7 +251,10 @@ int gs_create(gs_ctx** out, int device) {
   if (cudaStreamCreateWithPriority(&c->side, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&c->ev_zero, cudaEventDisableTiming) != cudaSuccess) {
+      cudaEventCreateWithFlags(&c->ev_zero, cudaEventDisableTiming) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->color_stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_k1, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&c->ev_color, cudaEventDisableTiming) != cudaSuccess) {
     gs_set_error(nullptr, "cudaStreamCreate/cudaEventCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
     gs_destroy(c);
     return GS_ECUDA;
@@ -255,6 +269,13 @@ int gs_create(gs_ctx** out, int device) {
     c->depth_sort_grid = c->radix_grid;
     if (e3 && atoi(e3) >= 1 && atoi(e3) <= 1024) c->depth_sort_grid = atoi(e3);
     if (e4 && atoi(e4) >= 0 && atoi(e4) <= 10000) c->sort_sleep_ns = (uint32_t)atoi(e4);
+  }
+  // measured at 8 GPUs (profiles/r02k_split_phase.md): 40-64 blocks 1.56 ms/step, 148: 1.63, 296: 1.71 -- the kernel is bound
+  // by NVLink, and the more stores it has queued the longer the loads of the kernels beside it wait
+  c->peer_side_grid = c->num_sms / 3 > 16 ? c->num_sms / 3 : 16;
+  {
+    const char* env = getenv("GS_PEER_ADAM_GRID");  // tuning switch: blocks of an Adam call that runs beside a forward
+    if (env && atoi(env) >= 1) c->peer_side_grid = atoi(env);
   }
   {
     const char* env = getenv("GS_NO_SORT_OVERLAP");  // measurement switch: run the depth argsort after K1 on the caller's stream
@@ -280,6 +301,9 @@ void gs_destroy(gs_ctx* c) {
   if (c->ev_fork) cudaEventDestroy(c->ev_fork);
   if (c->ev_join) cudaEventDestroy(c->ev_join);
   if (c->ev_zero) cudaEventDestroy(c->ev_zero);
+  if (c->color_stream) cudaStreamDestroy(c->color_stream);
+  if (c->ev_k1) cudaEventDestroy(c->ev_k1);
+  if (c->ev_color) cudaEventDestroy(c->ev_color);
   for (int i = 0; i < 2 * GS_NUM_STAGES; ++i)
     if (c->ev[i]) cudaEventDestroy(c->ev[i]);
   delete c;
@@ -421,6 +445,8 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
     const int r = ensure_status(gs_onesweep_status_words(Nn, 8));
     if (r != GS_OK) return r;
   }
+  const int defer_color = (c->color_gate != nullptr && !in->colors_precomp) ? 1 : 0;
+  bool color_on_side = false;
   if (N > 0) {
     // The depth argsort reads only the view depth, so it is forked onto the context's second stream and runs
     // beside K1 (the latency-bound N-sized sort fills the issue slots K1 leaves); the scan joins the two.
@@ -436,7 +462,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
       StageTimer t(c, 0, stream);
       GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
                                             (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint4*)c->rects.ptr,
-                                            (uint8_t*)c->clamped.ptr, radii_user, stream));
+                                            (uint8_t*)c->clamped.ptr, radii_user, defer_color, stream));
     }
     {
       StageTimer t(c, 1, sort_stream);
@@ -457,7 +483,21 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
         StageTimer t(c, 0, stream);
         GS_CUDA_CHECK(c, gs_launch_preprocess(*st, *in, N, (GsGeom*)c->geom.ptr, (float*)c->depths.ptr,
                                               (int*)c->radii.ptr, (uint32_t*)c->tiles.ptr, (uint4*)c->rects.ptr,
-                                              (uint8_t*)c->clamped.ptr, radii_user, stream));
+                                              (uint8_t*)c->clamped.ptr, radii_user, defer_color, stream));
+      }
+      if (defer_color) {
+        // deferred SH -> RGB on a stream of its own, beside the duplicate stage and the tile sort (HBM-bound next to
+        // latency-bound work): after K1 (its radii), after the gate (the caller recorded it BEFORE this call)
+        GS_CUDA_CHECK(c, cudaEventRecord(c->ev_k1, stream));
+        GS_CUDA_CHECK(c, cudaStreamWaitEvent(c->color_stream, c->ev_k1, 0));
+        GS_CUDA_CHECK(c, cudaStreamWaitEvent(c->color_stream, c->color_gate, 0));
+        {
+          StageTimer t(c, 8, c->color_stream);
+          GS_CUDA_CHECK(c, gs_launch_sh_color(*st, *in, N, (const int*)c->radii.ptr, (GsGeom*)c->geom.ptr,
+                                              (uint8_t*)c->clamped.ptr, c->color_stream));
+        }
+        GS_CUDA_CHECK(c, cudaEventRecord(c->ev_color, c->color_stream));
+        color_on_side = true;
       }
       GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->ev_join, 0));
     }
@@ -525,6 +565,15 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   const size_t max_segs = (size_t)(D >> GS_SEG_SHIFT) + (size_t)d.ntiles;
   GS_ENSURE(c, c->work_items, max_segs * sizeof(uint2));
   GS_ENSURE(c, c->ckpt, max_segs * GS_TILE_PIX * sizeof(float4));
+  if (color_on_side) {
+    GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->ev_color, 0));
+  } else if (defer_color && N > 0) {
+    // (GS_NO_SORT_OVERLAP: no second stream) wait for the gate, then fill colours / clamp masks in
+    GS_CUDA_CHECK(c, cudaStreamWaitEvent(stream, c->color_gate, 0));
+    StageTimer t(c, 8, stream);
+    GS_CUDA_CHECK(c, gs_launch_sh_color(*st, *in, N, (const int*)c->radii.ptr, (GsGeom*)c->geom.ptr,
+                                        (uint8_t*)c->clamped.ptr, stream));
+  }
   {
     StageTimer t(c, 5, stream);
     GS_CUDA_CHECK(c, gs_launch_blend_forward(d, (const uint32_t*)c->tile_order.ptr, (const uint2*)c->ranges.ptr,
@@ -966,7 +1015,19 @@ int gs_adam_step_peer(gs_ctx* c, int nranks, int rank, int N, int rows_per_shard
   GS_CUDA_CHECK(c, cudaSetDevice(c->device));
   GS_CUDA_CHECK(c, gs_launch_adam_peer(nranks, rank, N, rows_per_shard, params, slots, exp_avg, exp_avg_sq, widths, lr,
                                        step, beta1, beta2, eps, radii, dL_dmeans2D, max_radii2D, xyz_grad_accum,
-                                       denom, skip_guard, (flags & GS_PEER_PULL) ? 0 : 1, (cudaStream_t)stream_));
+                                       denom, skip_guard, (flags & GS_PEER_PULL) ? 0 : 1,
+                                       (flags & GS_PEER_BESIDE_FORWARD) ? c->peer_side_grid : 0,
+                                       (flags & GS_PEER_SH_LOCAL) ? 0x6 : 0, (cudaStream_t)stream_));
+  return GS_OK;
+}
+
+int gs_peer_copy(gs_ctx* c, void* dst, const void* src, unsigned long long bytes, void* stream_) {
+  if (!c || (bytes && (!dst || !src))) {
+    gs_set_error(c, "gs_peer_copy: bad argument");
+    return GS_EINVAL;
+  }
+  GS_CUDA_CHECK(c, cudaSetDevice(c->device));
+  if (bytes) GS_CUDA_CHECK(c, cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream_));
   return GS_OK;
 }
 
@@ -1045,6 +1106,12 @@ int gs_set_duplicate_capacity(gs_ctx* c, unsigned long long pairs) {
     return GS_EINVAL;
   }
   c->dup_cap_fixed = pairs;
+  return GS_OK;
+}
+
+int gs_set_color_gate(gs_ctx* c, void* cuda_event) {
+  if (!c) return GS_EINVAL;
+  c->color_gate = (cudaEvent_t)cuda_event;
   return GS_OK;
 }
 

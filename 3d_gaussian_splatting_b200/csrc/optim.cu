@@ -209,6 +209,7 @@ struct AdamPeerArgs {
   const float* skip_guard;
   int rank;        // the slot this rank's own backward wrote (local, dense)
   int sparse_seg;  // segment whose REMOTE slots are written sparsely and must be re-zeroed after use (-1: none)
+  int local_mask;  // bit k: segment k is updated in the OWN replica only (the caller distributes it with copy engines)
   int N;
   const int* radii;
   const float* dL_dmeans2D;
@@ -221,7 +222,9 @@ template <int G>
 __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_constant__ AdamPeerArgs a) {
   // an overflowed forward voids the step -- but the SPARSE slots (see below) must still be cleared
   const bool skip = a.skip_guard && __ldg(a.skip_guard) != 0.0f;
-  const int b = blockIdx.x;
+  // grid-stride over the work blocks: the launch may be capped (GS_PEER_ADAM_GRID) so that a call that runs beside the
+  // next forward on a second stream -- bound by NVLink, not by the SMs -- leaves most warp slots to the forward
+  for (int b = blockIdx.x; b < a.total_blocks; b += gridDim.x) {
   if (b >= a.stats_block_start) {
     if (skip) return;
     const int i = (b - a.stats_block_start) * AD_THREADS + threadIdx.x;
@@ -234,7 +237,7 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
         a.denom[i] += 1.0f;
       }
     }
-    return;
+    continue;
   }
   int si = 0;
 #pragma unroll
@@ -245,7 +248,8 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
   // NVLink, preprocess_bwd.cu): a row that is not written must read as zero, so whatever this kernel consumes
   // from a remote f_rest slot it puts back to zero (local stores, non-zero vectors only).
   const bool sparse = si == a.sparse_seg;
-  if (skip && !sparse) return;
+  const bool remote = !((a.local_mask >> si) & 1);
+  if (skip && !sparse) continue;
   const float b1 = a.b1, b2 = a.b2, omb1 = a.omb1, omb2 = a.omb2, eps = a.eps;
   const float neg_step = s.neg_step, inv_bc2_sqrt = s.inv_bc2_sqrt;
   constexpr int FPB = AD_THREADS * 4;  // one float4 per thread: G + 3 vector loads in flight
@@ -278,7 +282,7 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
     }
     // exact fixed point: every replica already holds this p, nothing crosses NVLink
     const bool idle = skip || gs_adam_idle(g, m, v);
-    if (!__any_sync(0xffffffffu, !idle)) return;
+    if (!__any_sync(0xffffffffu, !idle)) continue;
     {
       const GsAdamConst kc = {b1, b2, omb1, omb2, eps};
       GsAdamQuad q;
@@ -287,9 +291,11 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
       else if (__all_sync(0xffffffffu, ok >= GS_ADAM_FAST_Z)) gs_adam_quad_step<true>(p, m, v, q, eps, neg_step, inv_bc2_sqrt);
       else if (!idle) gs_adam_quad_scalar(p, g, m, v, kc, neg_step, inv_bc2_sqrt);
     }
-    if (idle) return;
+    if (idle) continue;
+    if (remote) {
 #pragma unroll
-    for (int r = 0; r < G - 1; ++r) reinterpret_cast<float4*>(s.dst[r])[v0] = p;  // NVLink stores first
+      for (int r = 0; r < G - 1; ++r) reinterpret_cast<float4*>(s.dst[r])[v0] = p;  // NVLink stores first
+    }
     __stcs(reinterpret_cast<float4*>(s.m) + v0, m);
     __stcs(reinterpret_cast<float4*>(s.v) + v0, v);
     reinterpret_cast<float4*>(s.p)[v0] = p;   // read again by the next forward: normal caching
@@ -305,12 +311,15 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
       if (skip) continue;
       float p = s.p[idx], m = s.m[idx], v = s.v[idx];
       gs_adam_one(p, g, m, v, b1, b2, omb1, omb2, eps, neg_step, inv_bc2_sqrt);
+      if (remote) {
 #pragma unroll
-      for (int r = 0; r < G - 1; ++r) s.dst[r][idx] = p;
+        for (int r = 0; r < G - 1; ++r) s.dst[r][idx] = p;
+      }
       s.p[idx] = p;
       s.m[idx] = m;
       s.v[idx] = v;
     }
+  }
   }
 }
 
@@ -321,8 +330,9 @@ cudaError_t gs_launch_adam_peer(int nranks, int rank, int N, int R, float* const
                                 const int widths[6], const double lr[6], const long long step[6], double beta1,
                                 double beta2, double eps, const int* radii, const float* dL_dmeans2D,
                                 int* max_radii2D, float* xyz_grad_accum, float* denom, const float* skip_guard,
-                                int sparse_rest, cudaStream_t stream) {
+                                int sparse_rest, int max_blocks, int local_mask, cudaStream_t stream) {
   AdamPeerArgs a;
+  a.local_mask = local_mask;
   const long long row0 = (long long)rank * R;
   const long long rows = row0 >= N ? 0 : ((long long)N - row0 < R ? (long long)N - row0 : (long long)R);
   int blocks = 0;
@@ -366,6 +376,7 @@ cudaError_t gs_launch_adam_peer(int nranks, int rank, int N, int R, float* const
   a.xyz_grad_accum = xyz_grad_accum;
   a.denom = denom;
   if (blocks == 0) return cudaSuccess;
+  if (max_blocks > 0 && blocks > max_blocks) blocks = max_blocks;
   switch (nranks) {
 #define ADP_CASE(G) case G: adam_peer_kernel<G><<<blocks, AD_THREADS, 0, stream>>>(a); break;
     ADP_CASE(1) ADP_CASE(2) ADP_CASE(3) ADP_CASE(4) ADP_CASE(5) ADP_CASE(6) ADP_CASE(7) ADP_CASE(8)

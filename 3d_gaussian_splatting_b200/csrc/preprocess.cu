@@ -35,6 +35,7 @@ struct PreprocessArgs {
   int gx, gy;
   int rest_width;  // active SH floats per Gaussian beyond dc: 3*((deg+1)^2-1)
   int rest_pitch;  // smem row pitch (odd)
+  int defer_color; // 1: leave colour and clamp mask at zero, the SH rows are not read (sh_color_kernel fills them in later)
 };
 
 __device__ __forceinline__ void cov3d_from_scale_rot(const float s[3], float mod, const float q[4], float c6[6]) {
@@ -211,6 +212,8 @@ __device__ __forceinline__ PpOut pp_compute(const gs_settings& st, const Preproc
             rgb[0] = col_pre[0];
             rgb[1] = col_pre[1];
             rgb[2] = col_pre[2];
+          } else if (a.defer_color) {
+            rgb[0] = rgb[1] = rgb[2] = 0.f;  // sh_color_kernel: same sh_to_rgb, same translation unit, same bits
           } else {
             const float dc[3] = {dcp[0], dcp[1], dcp[2]};
             sh_to_rgb(st.sh_degree, p, st.campos, dc, srow, rgb, cmask);
@@ -340,7 +343,7 @@ preprocess_kernel(const __grid_constant__ gs_settings st, const __grid_constant_
   const int rows = min(PP_THREADS, a.N - row0);
 
   // ---- stage the SH "rest" rows of this block: coalesced global reads, odd-pitch smem ----
-  if (a.rest_width > 0 && a.in.colors_precomp == nullptr) {
+  if (a.rest_width > 0 && a.in.colors_precomp == nullptr && !a.defer_color) {
     const int stride = a.in.sh_rest_stride;
     const float* base = a.in.sh_rest + (size_t)row0 * stride;
     const int total = (rows - 1) * stride + a.rest_width;  // never read past the last row
@@ -406,13 +409,14 @@ preprocess_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_cons
   if (tid == 0) {
     tma::mbar_init(bar, 1);
     tma::fence_mbar_init();
-    const uint32_t sh_bytes = a.rest_width > 0 ? (uint32_t)(PPB_ROWS * W * 4) : 0u;
-    tma::mbar_arrive_expect_tx(bar, sh_bytes + PPB_ROWS * (12u + 12u + 16u + 4u + 12u));
+    const uint32_t sh_bytes = (a.rest_width > 0 && !a.defer_color) ? (uint32_t)(PPB_ROWS * W * 4) : 0u;
+    const uint32_t dc_bytes = a.defer_color ? 0u : PPB_ROWS * 12u;
+    tma::mbar_arrive_expect_tx(bar, sh_bytes + dc_bytes + PPB_ROWS * (12u + 12u + 16u + 4u));
     tma::load(s_buf + PPB_OFF_XYZ, a.in.means3D + 3 * row0, PPB_ROWS * 12u, bar);
     tma::load(s_buf + PPB_OFF_SCL, a.in.scales + 3 * row0, PPB_ROWS * 12u, bar);
     tma::load(s_buf + PPB_OFF_ROT, a.in.rotations + 4 * row0, PPB_ROWS * 16u, bar);
     tma::load(s_buf + PPB_OFF_OP, a.in.opacities + row0, PPB_ROWS * 4u, bar);
-    tma::load(s_buf + PPB_OFF_DC, a.in.sh_dc + 3 * row0, PPB_ROWS * 12u, bar);
+    if (dc_bytes) tma::load(s_buf + PPB_OFF_DC, a.in.sh_dc + 3 * row0, dc_bytes, bar);
     if (sh_bytes) tma::load(s_buf + PPB_OFF_SH, a.in.sh_rest + row0 * W, sh_bytes, bar);
   }
   __syncthreads();
@@ -508,12 +512,128 @@ cudaError_t gs_launch_depth_keys(const gs_settings& st, const float* means3D, in
 
 static bool pp_aligned16(const void* p) { return (((uintptr_t)p) & 15) == 0; }
 
+// ---- deferred colour (multi-GPU step, capi.cu: gs_set_color_gate) -------------------------------------------------
+// With a colour gate the forward runs K1 WITHOUT the SH -> RGB evaluation (defer_color: 44 of a Gaussian's 236 B are
+// read), bins and sorts, and only then -- after the gate event, i.e. once the peers' optimiser kernels have delivered
+// the new SH coefficients into this replica over NVLink -- evaluates the colours with this kernel, just ahead of the
+// forward blend.  The all-gather of the SH coefficients (81 % of the parameter bytes at degree 3) thereby overlaps
+// K1, the depth argsort, the duplicate stage and the tile sort of the next iteration.  Same sh_to_rgb, same
+// translation unit (no contraction): colours and clamp masks are bit-identical to the undeferred K1.
+// A Gaussian gets a colour iff K1 gave it a radius (K1 evaluates the colour under exactly that condition).
+#define SHC_OFF_SH 0                              // rows x 45 floats
+#define SHC_OFF_XYZ (SHC_OFF_SH + PPB_ROWS * 45)  // rows x 3
+#define SHC_OFF_DC (SHC_OFF_XYZ + PPB_ROWS * 3)   // rows x 3
+#define SHC_FLOATS (SHC_OFF_DC + PPB_ROWS * 3)
+#define SHC_SMEM_BYTES (SHC_FLOATS * 4 + 16)
+struct ShColorArgs {
+  gs_gaussians in;
+  int N, first;
+  const int* radii;
+  GsGeom* geom;
+  uint8_t* clamped;
+  int rest_width;
+};
+
+__device__ __forceinline__ void shc_store(const ShColorArgs& a, size_t i, const float rgb[3], uint32_t cmask) {
+  float* rec = reinterpret_cast<float*>(a.geom + i);  // {x,y,hA,B} {hC,opacity,r,g} {b,depth,thr,-}
+  *reinterpret_cast<float2*>(rec + 6) = make_float2(rgb[0], rgb[1]);
+  rec[8] = rgb[2];
+  a.clamped[i] = (uint8_t)cmask;
+}
+
+__global__ void __launch_bounds__(PPB_ROWS)
+sh_color_bulk_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ ShColorArgs a) {
+  extern __shared__ __align__(128) float s_buf[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_buf + SHC_FLOATS);
+  const int tid = threadIdx.x;
+  const size_t row0 = (size_t)blockIdx.x * PPB_ROWS;
+  const int W = a.in.sh_rest_stride;
+  // (the rows are requested before the radii are known: one memory latency per block, as in K1, which cannot know
+  //  the visibility before it has read a row either)
+  if (tid == 0) {
+    tma::mbar_init(bar, 1);
+    tma::fence_mbar_init();
+    const uint32_t sh_bytes = a.rest_width > 0 ? (uint32_t)(PPB_ROWS * W * 4) : 0u;
+    tma::mbar_arrive_expect_tx(bar, sh_bytes + PPB_ROWS * (12u + 12u));
+    tma::load(s_buf + SHC_OFF_XYZ, a.in.means3D + 3 * row0, PPB_ROWS * 12u, bar);
+    tma::load(s_buf + SHC_OFF_DC, a.in.sh_dc + 3 * row0, PPB_ROWS * 12u, bar);
+    if (sh_bytes) tma::load(s_buf + SHC_OFF_SH, a.in.sh_rest + row0 * W, sh_bytes, bar);
+  }
+  const int radius = a.radii[row0 + tid];
+  __syncthreads();
+  tma::mbar_wait(bar, 0);
+  if (radius > 0) {
+    const float p[3] = {s_buf[SHC_OFF_XYZ + 3 * tid], s_buf[SHC_OFF_XYZ + 3 * tid + 1], s_buf[SHC_OFF_XYZ + 3 * tid + 2]};
+    const float dc[3] = {s_buf[SHC_OFF_DC + 3 * tid], s_buf[SHC_OFF_DC + 3 * tid + 1], s_buf[SHC_OFF_DC + 3 * tid + 2]};
+    float rgb[3];
+    uint32_t cmask = 0;
+    sh_to_rgb(st.sh_degree, p, st.campos, dc, s_buf + SHC_OFF_SH + tid * W, rgb, cmask);
+    shc_store(a, row0 + tid, rgb, cmask);
+  }
+}
+
+// generic rows (ragged tail, strided or unaligned tensors): one thread per Gaussian, SH row read in place
+__global__ void __launch_bounds__(PPB_ROWS)
+sh_color_kernel(const __grid_constant__ gs_settings st, const __grid_constant__ ShColorArgs a) {
+  const size_t i = (size_t)a.first + (size_t)blockIdx.x * PPB_ROWS + threadIdx.x;
+  if (i >= (size_t)a.N || a.radii[i] <= 0) return;
+  const float p[3] = {a.in.means3D[3 * i], a.in.means3D[3 * i + 1], a.in.means3D[3 * i + 2]};
+  const float* dcp = a.in.sh_dc + i * a.in.sh_dc_stride;
+  const float dc[3] = {dcp[0], dcp[1], dcp[2]};
+  float srow[45];
+#pragma unroll
+  for (int k = 0; k < 45; ++k) srow[k] = k < a.rest_width ? a.in.sh_rest[i * a.in.sh_rest_stride + k] : 0.f;
+  float rgb[3];
+  uint32_t cmask = 0;
+  sh_to_rgb(st.sh_degree, p, st.campos, dc, srow, rgb, cmask);
+  shc_store(a, i, rgb, cmask);
+}
+
+static bool pp_dense_layout(const gs_settings& st, const gs_gaussians& in, int rest_width) {
+  const int kmax = (st.max_sh_degree + 1) * (st.max_sh_degree + 1);
+  const int Wmax = 3 * (kmax - 1);
+  return !in.colors_precomp && !in.cov3D_precomp && in.sh_dc_stride == 3 &&
+         (Wmax == 0 || in.sh_rest_stride == Wmax) && (rest_width == 0 || in.sh_rest_stride <= 45) &&
+         pp_aligned16(in.means3D) && pp_aligned16(in.scales) && pp_aligned16(in.rotations) &&
+         pp_aligned16(in.opacities) && pp_aligned16(in.sh_dc) && (rest_width == 0 || pp_aligned16(in.sh_rest));
+}
+
+cudaError_t gs_launch_sh_color(const gs_settings& st, const gs_gaussians& in, int N, const int* radii, GsGeom* geom,
+                               uint8_t* clamped, cudaStream_t stream) {
+  if (N == 0 || in.colors_precomp) return cudaSuccess;
+  ShColorArgs a;
+  a.in = in;
+  a.N = N;
+  a.first = 0;
+  a.radii = radii;
+  a.geom = geom;
+  a.clamped = clamped;
+  const int kact = (st.sh_degree + 1) * (st.sh_degree + 1);
+  a.rest_width = 3 * (kact - 1);
+  if (pp_dense_layout(st, in, a.rest_width) && N >= PPB_ROWS) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t e =
+          cudaFuncSetAttribute(sh_color_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SHC_SMEM_BYTES);
+      if (e != cudaSuccess) return e;
+      attr_set = true;
+    }
+    const int blocks = N / PPB_ROWS;
+    sh_color_bulk_kernel<<<blocks, PPB_ROWS, SHC_SMEM_BYTES, stream>>>(st, a);
+    a.first = blocks * PPB_ROWS;
+  }
+  if (a.first < N) sh_color_kernel<<<(N - a.first + PPB_ROWS - 1) / PPB_ROWS, PPB_ROWS, 0, stream>>>(st, a);
+  return cudaGetLastError();
+}
+
+// defer_color: K1 without the SH -> RGB evaluation (colours and clamp masks stay zero until gs_launch_sh_color)
 cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, int N, GsGeom* geom, float* depths,
                                  int* radii, uint32_t* tiles_touched, uint4* rects, uint8_t* clamped,
-                                 int* radii_user, cudaStream_t stream) {
+                                 int* radii_user, int defer_color, cudaStream_t stream) {
   if (N == 0) return cudaSuccess;
   PreprocessArgs a;
   a.in = in;
+  a.defer_color = (defer_color && !in.colors_precomp) ? 1 : 0;
   a.N = N;
   a.geom = geom;
   a.depths = depths;
@@ -531,13 +651,7 @@ cudaError_t gs_launch_preprocess(const gs_settings& st, const gs_gaussians& in, 
   a.rest_pitch = a.rest_width | 1;
   size_t smem = (size_t)PP_THREADS * a.rest_pitch * sizeof(float);
   if (a.rest_width == 0) smem = 0;
-  const int kmax = (st.max_sh_degree + 1) * (st.max_sh_degree + 1);
-  const int Wmax = 3 * (kmax - 1);
-  const bool dense = !in.colors_precomp && !in.cov3D_precomp && in.sh_dc_stride == 3 &&
-                     (Wmax == 0 || in.sh_rest_stride == Wmax) && (a.rest_width == 0 || in.sh_rest_stride <= 45) &&
-                     pp_aligned16(in.means3D) && pp_aligned16(in.scales) && pp_aligned16(in.rotations) &&
-                     pp_aligned16(in.opacities) && pp_aligned16(in.sh_dc) &&
-                     (a.rest_width == 0 || pp_aligned16(in.sh_rest));
+  const bool dense = pp_dense_layout(st, in, a.rest_width);
   int first = 0;
   if (dense && N >= PPB_ROWS) {
     static bool attr_set = false;

@@ -147,10 +147,16 @@ class PeerShardedAdam:
     (include/gsplat_b200.h, "the multi-GPU step over peer memory"):
 
         backward (K4b) : stores the gradient rows of shard q straight into rank q's slot buffer over NVLink
-        barrier 1      : one-float NCCL all-reduce (MAX of the overflow guards)
+        barrier 1      : gs_peer_barrier (flag kernel; carries the MAX of the overflow guards)
         Adam (K5)      : sums the world slots of the owned rows, updates them, stores the new parameters into
-                         every rank's replica over NVLink
-        barrier 2      : one-float NCCL all-reduce
+                         every rank's replica over NVLink -- in TWO phases (split-phase step): the geometry groups
+                         (xyz, opacity, scaling, rotation: 44 of a Gaussian's 236 B) + statistics on the caller's
+                         stream, then barrier 2a and the next forward starts; the two SH groups (192 B) on a second
+                         stream, then barrier 2b on a second flag block and an event -- the colour gate of the next
+                         forward (gs_set_color_gate), which evaluates SH -> RGB only after K1, the depth argsort, the
+                         duplicate stage and the tile sort.  The all-gather of 81 % of the parameter bytes thereby
+                         overlaps the front of the next iteration.  Used from 4 ranks (GS_PEER_SPLIT=sm|ce|off
+                         overrides; GS_PEER_NO_SPLIT=1: one phase, one barrier 2).
 
     Per rank and step the wire carries (world-1)/world of the gradient and parameter bytes once each -- the same
     as reduce-scatter + all-gather -- but no byte is staged, re-read or re-written in HBM for the exchange, and
@@ -199,10 +205,28 @@ class PeerShardedAdam:
         off = (off + 31) // 32 * 32
         self.f_off = off
         off += 32
+        self.f_off2 = off       # second flag block: the barrier of the SH phase, which runs on its own stream
+        off += 32
         self.total = off
         self.epoch = 0
+        self.epoch2 = 0
         import os
         self.flag_barriers = os.environ.get("GS_PEER_NCCL_BARRIER", "0") != "1"
+        # split-phase step (see the class docstring): needs the flag barriers (a collective on a second stream would
+        # have to be ordered against NCCL's own stream use) and a model with SH coefficients
+        self.split = (world > 1 and self.flag_barriers and os.environ.get("GS_PEER_NO_SPLIT", "0") != "1"
+                      and self.widths[1] + self.widths[2] > 0)
+        # GS_PEER_SPLIT: "sm" -- a second Adam kernel on the second stream stores the SH rows into every replica, its
+        # grid capped at a third of the SMs (GS_PEER_BESIDE_FORWARD); "ce" -- the Adam kernel updates the SH rows in
+        # the own replica only and COPY ENGINES distribute them (gs_peer_copy); "off" -- one phase.  Measured (B200,
+        # cfg2, one view per rank per step, ms/step; profiles/r02k_split_phase.md): 8 GPUs sm 1.56 / ce 1.83 / off
+        # 1.71; 4 GPUs sm 1.49 / ce 1.52 / off 1.57; 2 GPUs sm 1.46 / off 1.42 (half the model's SH rows per rank is
+        # HBM work, not NVLink time, and the two-kernel forward costs 45 us).  Default: sm from 4 ranks, else off.
+        default_mode = "sm" if world >= 4 else "off"
+        self.split_mode = os.environ.get("GS_PEER_SPLIT", default_mode) if self.split else "off"
+        if self.split_mode == "off":
+            self.split = False
+        assert self.split_mode in ("off", "ce", "sm"), self.split_mode
         self.base, handle = rast.peer_alloc(self.total * 4)
         handles = [None] * world
         if world > 1:
@@ -252,6 +276,21 @@ class PeerShardedAdam:
         self.sync = torch.zeros(1, dtype=torch.float32, device=self.flat.device)
         # params[r][k]: rank r's replica; slots[s][k]: MY slot for source s; routing[q][k]: my slot INSIDE rank q
         self.flag_ptrs = [self.bases[r] + 4 * self.f_off for r in range(world)]
+        self.flag_ptrs2 = [self.bases[r] + 4 * self.f_off2 for r in range(world)]
+        self.geo_widths = [self.widths[0], 0, 0, self.widths[3], self.widths[4], self.widths[5]]
+        self.sh_widths = [0, self.widths[1], self.widths[2], 0, 0, 0]
+        self.side = self.ev_fork = self.ev_sh = None
+        self.profile_phases, self.phase_events = False, []
+        if self.split:
+            dev = self.flat.device
+            self.copy_streams = [torch.cuda.Stream(device=dev) for _ in range(max(1, world - 1))]
+            self.ev_copy = [torch.cuda.Event() for _ in range(max(1, world - 1))]
+            self.ev_shadam = torch.cuda.Event()
+            self.side = self.copy_streams[0]
+            self.ev_fork = torch.cuda.Event()
+            self.ev_sh = torch.cuda.Event()
+            self.ev_sh.record(torch.cuda.current_stream(dev))     # (creates the handle; nothing to wait for yet)
+            rast.set_color_gate(self.ev_sh)
         self.param_ptrs = [[self.bases[r] + 4 * self.p_off[k] for k in range(6)] for r in range(world)]
         if self.pull:
             # source s of my shard = rows [rank*R, ...) of rank s's slab (peer-mapped for s != rank)
@@ -263,7 +302,14 @@ class PeerShardedAdam:
             rast.set_gradient_routing(world, rank, R, routing)
         self.barrier()   # every replica initialised and every mapping in place before anyone stores remotely
 
-    def barrier(self, with_guard: bool = False, nccl: bool = False):
+    def join(self):
+        """Make the current stream wait for the SH phase of the last step (a no-op without the split).  The forward
+        does this itself through the colour gate; anything ELSE that reads or writes the SH coefficients, the SH
+        moments or the gradient slots on the current stream must call this first."""
+        if self.ev_sh is not None:
+            torch.cuda.current_stream(self.flat.device).wait_event(self.ev_sh)
+
+    def barrier(self, with_guard: bool = False, nccl: bool = False, second: bool = False):
         """Stream-ordered barrier across the ranks.  Default: gs_peer_barrier -- one 32-thread kernel per rank that
         stores an epoch flag into every rank's flag block over NVLink and waits for the others' (a few microseconds,
         against ~25 for a one-float NCCL all-reduce).  with_guard: the overflow guards ride along, self.guard becomes
@@ -273,14 +319,32 @@ class PeerShardedAdam:
         if nccl or not self.flag_barriers:
             dist.all_reduce(self.guard if with_guard else self.sync, op=dist.ReduceOp.MAX, group=self.group)
             return
+        if second:          # the SH phase's own flag block and epoch sequence (it runs on its own stream)
+            self.epoch2 += 1
+            self.rast.peer_barrier(self.world, self.rank, self.flag_ptrs2, self.epoch2)
+            return
         self.epoch += 1
         g = self.guard if with_guard else None
         self.rast.peer_barrier(self.world, self.rank, self.flag_ptrs, self.epoch, guard_in=g, guard_out=g)
 
+    def phase_ms(self):
+        """Median device times of the split-phase step's parts over the steps taken with profile_phases = True, from the
+        end of barrier 1: SH copies (or SH Adam kernel) done on the second stream, + its barrier 2b, Adam kernel of the
+        caller's stream done, + its barrier 2a."""
+        torch.cuda.synchronize(self.flat.device)
+        if not self.phase_events:
+            return None
+        import statistics
+        rows = [[e[0].elapsed_time(e[k]) for k in (1, 2, 3, 4)] for e in self.phase_events]
+        self.phase_events = []
+        names = ("sh_phase_done", "sh_barrier_done", "adam_done", "geo_barrier_done")
+        return {n: round(statistics.median(r[i] for r in rows), 4) for i, n in enumerate(names)}
+
     def barrier_timeouts(self) -> int:
         """Barriers of this rank that gave up waiting for a peer (~2 s each); 0 in a healthy run.  Synchronises."""
         torch.cuda.synchronize(self.flat.device)
-        return int(self.flat[self.f_off + 16:self.f_off + 17].view(torch.int32).item())
+        return int(self.flat[self.f_off + 16:self.f_off + 17].view(torch.int32).item()) + \
+            int(self.flat[self.f_off2 + 16:self.f_off2 + 17].view(torch.int32).item())
 
     def slot(self, src: int, k: int) -> torch.Tensor:
         """The gradient rows source rank `src` stored for my shard, group k: (R, widths[k]) (push layout)."""
@@ -293,15 +357,98 @@ class PeerShardedAdam:
         m = self.model
         # barrier 1: every rank's backward has landed in the slots; carries the overflow guard along
         self.barrier(with_guard=True)
+        guard = self.guard if use_guard else None
+        if not self.split:
+            self.rast.adam_step_peer(self.world, self.rank, self.N, self.R, self.param_ptrs, self.slot_ptrs, m.exp_avg,
+                                     m.exp_avg_sq, self.widths, lr, step, radii=radii, dL_dmeans2D=dL_dmeans2D,
+                                     max_radii2D=max_radii2D, xyz_grad_accum=xyz_grad_accum, denom=denom,
+                                     skip_guard=guard, sparse_rest=not self.pull)
+            self.barrier()   # barrier 2: every replica complete before the next forward reads it
+            return
+        main = torch.cuda.current_stream(self.flat.device)
+        prof = self.phase_events if self.profile_phases else None
+        if prof is not None:      # (measurement only: CUDA events around the two phases of this step)
+            evs = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+            prof.append(evs)
+            evs[0].record(main)
+        if self.split_mode == "ce":
+            # Geometry phase on the caller's stream, stored into every replica by the kernel: what K1 and the binning
+            # stages of the next forward read -- the critical path, so nothing bulky shares NVLink with it for long.
+            self.ev_fork.record(main)
+            self.rast.adam_step_peer(self.world, self.rank, self.N, self.R, self.param_ptrs, self.slot_ptrs, m.exp_avg,
+                                     m.exp_avg_sq, self.geo_widths, lr, step, radii=radii, dL_dmeans2D=dL_dmeans2D,
+                                     max_radii2D=max_radii2D, xyz_grad_accum=xyz_grad_accum, denom=denom,
+                                     skip_guard=guard, sparse_rest=not self.pull)
+            if prof is not None:
+                evs[3].record(main)
+            self.barrier()   # barrier 2a: xyz / opacity / scaling / rotation of every replica complete
+            if prof is not None:
+                evs[4].record(main)
+            # SH phase beside it: the SH groups are updated in the OWN replica only (GS_PEER_SH_LOCAL, second stream),
+            # then the copy engines carry the owned rows to the other replicas -- one stream per peer, several engines
+            # busy at a time, no SM involved -- beside the next forward; then that phase's own barrier (2b) and the
+            # event the next colour kernel waits for
+            self.side.wait_event(self.ev_fork)
+            with torch.cuda.stream(self.side):
+                self.rast.adam_step_peer(self.world, self.rank, self.N, self.R, self.param_ptrs, self.slot_ptrs,
+                                         m.exp_avg, m.exp_avg_sq, self.sh_widths, lr, step, skip_guard=guard,
+                                         sparse_rest=not self.pull, sh_local=True)
+                self.ev_shadam.record(self.side)
+            rows = max(0, min(self.R, self.N - self.rank * self.R))
+            for d in range(1, self.world):
+                r = (self.rank + d) % self.world
+                st = self.copy_streams[d - 1]
+                if d > 1:
+                    st.wait_event(self.ev_shadam)
+                with torch.cuda.stream(st):
+                    for k in (2, 1):
+                        w = self.widths[k]
+                        if w and rows:
+                            off = 4 * self.rank * self.R * w
+                            self.rast.peer_copy(self.param_ptrs[r][k] + off, self.param_ptrs[self.rank][k] + off,
+                                                4 * rows * w)
+                    if d > 1:
+                        self.ev_copy[d - 1].record(st)
+            with torch.cuda.stream(self.side):          # (self.side is copy_streams[0])
+                for d in range(2, self.world):
+                    self.side.wait_event(self.ev_copy[d - 1])
+                if prof is not None:
+                    evs[1].record(self.side)
+                self.barrier(second=True)
+                self.ev_sh.record(self.side)
+                if prof is not None:
+                    evs[2].record(self.side)
+            return
+        # "sm": SH phase as a second Adam kernel on the second stream: f_dc / f_rest (81 % of the bytes), then its own
+        # barrier (2b) and the event the next forward's colour kernel waits for.  (The previous step's SH phase is
+        # complete: this step's forward waited for its event before the colour kernel.)
+        self.ev_fork.record(main)
+        self.side.wait_event(self.ev_fork)
+        with torch.cuda.stream(self.side):
+            self.rast.adam_step_peer(self.world, self.rank, self.N, self.R, self.param_ptrs, self.slot_ptrs, m.exp_avg,
+                                     m.exp_avg_sq, self.sh_widths, lr, step, skip_guard=guard,
+                                     sparse_rest=not self.pull, beside_forward=True)
+            if prof is not None:
+                evs[1].record(self.side)
+            self.barrier(second=True)
+            self.ev_sh.record(self.side)
+            if prof is not None:
+                evs[2].record(self.side)
+        # geometry phase on the caller's stream: what K1 and the binning stages of the next forward read
         self.rast.adam_step_peer(self.world, self.rank, self.N, self.R, self.param_ptrs, self.slot_ptrs, m.exp_avg,
-                                 m.exp_avg_sq, self.widths, lr, step, radii=radii, dL_dmeans2D=dL_dmeans2D,
+                                 m.exp_avg_sq, self.geo_widths, lr, step, radii=radii, dL_dmeans2D=dL_dmeans2D,
                                  max_radii2D=max_radii2D, xyz_grad_accum=xyz_grad_accum, denom=denom,
-                                 skip_guard=self.guard if use_guard else None, sparse_rest=not self.pull)
-        self.barrier()   # barrier 2: every replica complete before the next forward reads it
+                                 skip_guard=guard, sparse_rest=not self.pull)
+        if prof is not None:
+            evs[3].record(main)
+        self.barrier()   # barrier 2a: xyz / opacity / scaling / rotation of every replica complete
+        if prof is not None:
+            evs[4].record(main)
 
     def gather_moments(self):
         """The FULL (N, C) Adam moments on every rank (all-gather of the shards): what a densification step or a
         checkpoint needs.  Rare (once per densification interval), so plain NCCL."""
+        self.join()
         out = []
         for shard in (self.model.exp_avg, self.model.exp_avg_sq):
             full = []
@@ -321,12 +468,15 @@ class PeerShardedAdam:
     def detach_model(self):
         """Give the model private copies of its parameters (they are views of the peer buffer) so that the buffer
         can be released."""
+        self.join()
         m = self.model
         (m.xyz_, m.features_dc_, m.features_rest_, m.opacity_, m.scaling_, m.rotation_) = [p.clone() for p in m.params()]
 
     def close(self):
         torch.cuda.synchronize(self.flat.device)
         self.barrier(nccl=True)               # nobody is still storing into a peer's buffer
+        if self.split:
+            self.rast.set_color_gate(None)
         if not self.pull:
             self.rast.set_gradient_routing(0)
         for r, b in enumerate(self.bases):

@@ -345,6 +345,19 @@ class Rasterizer:
         check(self._ctx, lib.gs_peer_barrier(self._ctx, nranks, rank, tab, int(epoch) & 0xFFFFFFFF, _ptr(guard_in),
                                              _ptr(guard_out), C.c_void_p(stream)))
 
+    def peer_copy(self, dst_ptr: int, src_ptr: int, nbytes: int):
+        """gs_peer_copy: one contiguous copy-engine copy on the current stream (either side may be peer-mapped)."""
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._ctx, lib.gs_peer_copy(self._ctx, C.c_void_p(int(dst_ptr)), C.c_void_p(int(src_ptr)), int(nbytes),
+                                          C.c_void_p(stream)))
+
+    def set_color_gate(self, event=None):
+        """gs_set_color_gate: event = a torch.cuda.Event that has been recorded at least once (its handle exists
+        from then on); later forwards run K1 without the SH -> RGB evaluation and evaluate the colours after the
+        event's most recent record, just ahead of the blend.  None: back to the one-kernel K1."""
+        self._gate_event = event      # keep the event object (and its handle) alive
+        check(self._ctx, lib.gs_set_color_gate(self._ctx, C.c_void_p(event.cuda_event) if event is not None else None))
+
     def wrap(self, ptr: int, nfloats: int) -> torch.Tensor:
         """A float32 torch view of raw device memory (no copy, no ownership)."""
         class _Raw:
@@ -367,7 +380,8 @@ class Rasterizer:
 
     def adam_step_peer(self, nranks, rank, N, rows_per_shard, params, slots, exp_avg, exp_avg_sq, widths, lr, step,
                        beta1=0.9, beta2=0.999, eps=1e-8, radii=None, dL_dmeans2D=None, max_radii2D=None,
-                       xyz_grad_accum=None, denom=None, skip_guard=None, sparse_rest=True):
+                       xyz_grad_accum=None, denom=None, skip_guard=None, sparse_rest=True, beside_forward=False,
+                       sh_local=False):
         """params[r][k] / slots[s][k]: device pointers (ints); exp_avg / exp_avg_sq: six shard-local tensors.
         sparse_rest=False: the pull layout (GS_PEER_PULL): slots point into the ranks' full gradient slabs."""
         if isinstance(skip_guard, torch.Tensor):
@@ -380,7 +394,8 @@ class Rasterizer:
             VP6(*[t.data_ptr() for t in exp_avg]), VP6(*[t.data_ptr() for t in exp_avg_sq]), (C.c_int * 6)(*widths),
             (C.c_double * 6)(*[float(x) for x in lr]), (C.c_longlong * 6)(*[int(x) for x in step]), float(beta1),
             float(beta2), float(eps), _ptr(radii), _ptr(dL_dmeans2D), _ptr(max_radii2D), _ptr(xyz_grad_accum),
-            _ptr(denom), C.c_void_p(skip_guard) if skip_guard else None, 0 if sparse_rest else 1, C.c_void_p(stream)))
+            _ptr(denom), C.c_void_p(skip_guard) if skip_guard else None, (0 if sparse_rest else 1) | (2 if beside_forward else 0) | (4 if sh_local else 0),
+            C.c_void_p(stream)))
 
     def loss(self, image, gt, lambda_dssim=0.0, want_grad=True):
         """(1-lambda)*L1 + lambda*(1-SSIM); returns (loss 1-element device tensor, dL/dimage)."""

@@ -152,6 +152,9 @@ def stage_bytes(N, N_vis, D, D_eff, P, T, K, active_floats=None):
         "scan_duplicate": 2 * 20 * N + (kb + 4) * D,
         "sort": passes * (kb + 2 * (kb + 4)) * D,
         "ranges": 8 * T,
+        # deferred SH -> RGB of the split-phase multi-GPU step (gs_set_color_gate): xyz + dc + rest + radius read,
+        # colour + clamp mask written; K1 then reads 12 K bytes per Gaussian less (subtracted where it is used)
+        "sh_color": (16 + 12 * K) * N + 13 * N_vis,
         "blend_fwd": 40 * D_eff + 20 * P,
         "blend_bwd": 40 * D_eff + 20 * P + 36 * N_vis,
         "preprocess_bwd": (44 + 12 * K) * N_vis + 36 * N_vis + 4 * N + (44 + 12 * K) * N,
@@ -500,6 +503,18 @@ def run_ours(args, rank, world, local_rank):
     warm = max(args.warmup, 3)
     sampler = ClockSampler(local_rank) if rank == 0 else None
     total_ms, clocks = timed(step_device, args.steps, warm, sampler)
+    peer_phases = None
+    if world > 1 and args.dp_mode == "peer" and getattr(sharded, "split", False):
+        # where the split-phase exchange sits inside a pipelined step: a second, instrumented pass (events only)
+        sharded.profile_phases = True
+        trainer.rast.set_profiling(True)
+        timed(step_device, args.steps, 1)
+        sharded.profile_phases = False
+        peer_phases = sharded.phase_ms()
+        # the library's per-stage events of the LAST pipelined iteration: stage durations as they are while the SH
+        # phase of the previous step is still running beside them
+        peer_phases["stages_while_overlapped"] = {k: round(v, 4) for k, v in trainer.rast.stage_ms().items()}
+        trainer.rast.set_profiling(False)
     assert not trainer.rast.forward_status()[1], "pair capacity overflow inside the timed region"
     ms_per_step = total_ms / args.steps
     value = world * 1.0 / (ms_per_step * 1e-3)
@@ -567,6 +582,8 @@ def run_ours(args, rank, world, local_rank):
                     extra["adam_stats"].append(ev[2].elapsed_time(ev[3]))
         tr.rast.set_profiling(False)
         st = {k: float(np.median(v)) for k, v in acc.items()}
+        if st.get("sh_color", 0.0) <= 0.0:      # (only the split-phase multi-GPU step defers the colour evaluation)
+            st.pop("sh_color", None)
         st.update({k: float(np.median(v)) for k, v in extra.items() if v})
         if fused:
             st["preprocess_bwd_adam"] = st.pop("preprocess_bwd")
@@ -669,6 +686,8 @@ def run_ours(args, rank, world, local_rank):
             north = {"error": f"{type(e).__name__}: {e}"}
 
     by = stage_bytes(N, N_vis, D, D_eff, P, T, K, active_floats if world == 1 else None)
+    if "sh_color" in stage_ms:
+        by["preprocess"] -= 12 * K * N
     if world > 1 and args.dp_mode == "peer" and active_floats is not None:
         # adam_peer_kernel, local HBM bytes of one rank: the `world` gradient slots + m, v, p of its R-row shard read;
         # m, v, p of the active vectors written; plus what the other ranks' kernels store into this replica
@@ -795,6 +814,8 @@ def run_ours(args, rank, world, local_rank):
             # north_star's 64-view batch on the 6 M-Gaussian scene: views/s, exchange time reported separately
             "north_star_batch": north,
             "replicas_identical": replicas_identical, "last_loss": last_loss, "barrier_timeouts": barrier_timeouts,
+            # split-phase exchange (N > 1, peer mode): device ms from the end of barrier 1 to the end of each part
+            "peer_phases_ms": peer_phases,
             "raster": raster,
             "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,

@@ -262,6 +262,20 @@ GS_API int gs_adam_step_peer(gs_ctx *ctx, int nranks, int rank, int N, int rows_
                              int *max_radii2D, float *xyz_grad_accum, float *denom, const float *skip_guard,
                              int flags, void *stream);
 #define GS_PEER_PULL 1
+/* GS_PEER_BESIDE_FORWARD: the call runs on a second stream beside the next gs_forward (the SH groups of the
+ * split-phase step, see gs_set_color_gate): it is bound by NVLink, not by the SMs, so its grid is capped at a third
+ * of the SM count (grid-stride loop; GS_PEER_ADAM_GRID overrides).  Measured on 8 GPUs: the more remote stores the
+ * kernel keeps queued, the longer the loads of K1 and the sorts beside it wait (40-64 blocks: 1.56 ms/step, 296:
+ * 1.71, none of the split: 1.71). */
+#define GS_PEER_BESIDE_FORWARD 2
+/* GS_PEER_SH_LOCAL: the two SH groups (f_dc, f_rest) are updated in the rank's OWN replica only; the caller
+ * distributes the owned rows to the other replicas with gs_peer_copy -- copy engines over NVLink, no SM involved --
+ * on a second stream, beside the next gs_forward (see gs_set_color_gate).  The copy engines leave the kernels
+ * beside them alone, but their all-gather is slower than the kernel's stores (8 GPUs: 336 GB/s per rank against
+ * 560 GB/s; 1.83 against 1.56 ms/step, profiles/r02k_split_phase.md), so this is not the default. */
+#define GS_PEER_SH_LOCAL 4
+/* One contiguous device-to-device copy (cudaMemcpyAsync: a copy engine; dst or src may be peer-mapped). */
+GS_API int gs_peer_copy(gs_ctx *ctx, void *dst, const void *src, unsigned long long bytes, void *stream);
 /* The two barriers of the peer-memory step as ONE small kernel each instead of a collective: every rank owns a
  * 128-byte flag block inside its peer-mapped buffer (zeroed by gs_peer_alloc); flag_blocks[r] is rank r's block as
  * mapped here.  The call stores (guard_in, epoch) into this rank's slot of every block and waits until every slot of
@@ -272,6 +286,16 @@ GS_API int gs_adam_step_peer(gs_ctx *ctx, int nranks, int rank, int N, int rows_
  * kernel returns instead of hanging. */
 GS_API int gs_peer_barrier(gs_ctx *ctx, int nranks, int rank, void *const flag_blocks[], unsigned int epoch,
                            const float *guard_in, float *guard_out, void *stream);
+
+/* Colour gate (multi-GPU step; no counterpart in the single-device reference).  With a non-NULL cudaEvent_t set,
+ * gs_forward runs K1 WITHOUT the SH -> RGB evaluation (it reads 44 of a Gaussian's 236 B), bins and sorts, then makes
+ * its stream wait for the event and evaluates colours + clamp masks (bit-identical to the undeferred K1) just ahead
+ * of the forward blend.  The caller records the event -- BEFORE calling gs_forward, on whatever stream -- once the SH
+ * coefficients of its replica are complete, e.g. after a gs_adam_step_peer over the two SH groups + gs_peer_barrier
+ * on a second stream: the all-gather of 81 % of the parameter bytes then overlaps K1 and the binning stages of the
+ * next iteration (parallel.PeerShardedAdam).  xyz / scaling / rotation / opacity must be complete when gs_forward is
+ * called.  NULL restores the one-kernel K1. */
+GS_API int gs_set_color_gate(gs_ctx *ctx, void *cuda_event);
 #define GS_PEER_FLAG_BYTES 128
 
 /* ---- running without the host round-trip ----------------------------------------------------
@@ -338,9 +362,9 @@ GS_API int gs_debug_get(gs_ctx *ctx, int what, void *host_dst, size_t bytes);
 
 /* Per-stage device time of the last forward/backward in milliseconds (CUDA events recorded
  * only when gs_set_profiling(ctx,1)); order: preprocess, depth sort, scan+duplicate, tile sort,
- * ranges, blend, blend_bwd, preprocess_bwd.  The role of the CUDA-event timers the reference says it lacks
+ * ranges, blend, blend_bwd, preprocess_bwd, deferred colour (gs_set_color_gate; 0 otherwise).  The role of the CUDA-event timers the reference says it lacks
  * (src/utils/train_utils.cpp:119-121). */
-#define GS_NUM_STAGES 8
+#define GS_NUM_STAGES 9
 GS_API int gs_set_profiling(gs_ctx *ctx, int enabled);
 GS_API int gs_get_stage_ms(gs_ctx *ctx, float ms[GS_NUM_STAGES]);
 
