@@ -92,7 +92,7 @@ struct gs_ctx {
   cudaEvent_t ev_k1 = nullptr, ev_color = nullptr;  // K1 done (the colour kernel needs its radii) / colours complete
   cudaStream_t color_stream = nullptr;              // default priority (the sort's stream is high priority: a 12 500-block
                                                     // kernel there would push the duplicate stage aside, not run beside it)
-  int peer_side_grid = 0;  // grid cap of a gs_adam_step_peer call flagged GS_PEER_BESIDE_FORWARD (a third of the SMs)
+  int peer_side_grid = 0;  // GS_PEER_ADAM_GRID: grid cap of a gs_adam_step_peer call flagged GS_PEER_BESIDE_FORWARD (0: automatic)
   // per-duplicate: tile ids (u16, u32 beyond 65536 tiles) and Gaussian ids, ping-pong
   DevBuf keys_a, keys_b, vals_a, vals_b;
   DevBuf radix_counts;
@@ -270,9 +270,7 @@ int gs_create(gs_ctx** out, int device) {
     if (e3 && atoi(e3) >= 1 && atoi(e3) <= 1024) c->depth_sort_grid = atoi(e3);
     if (e4 && atoi(e4) >= 0 && atoi(e4) <= 10000) c->sort_sleep_ns = (uint32_t)atoi(e4);
   }
-  // measured at 8 GPUs (profiles/r02k_split_phase.md): 40-64 blocks 1.56 ms/step, 148: 1.63, 296: 1.71 -- the kernel is bound
-  // by NVLink, and the more stores it has queued the longer the loads of the kernels beside it wait
-  c->peer_side_grid = c->num_sms / 3 > 16 ? c->num_sms / 3 : 16;
+  c->peer_side_grid = 0;  // 0: from the rank count (gs_peer_side_grid)
   {
     const char* env = getenv("GS_PEER_ADAM_GRID");  // tuning switch: blocks of an Adam call that runs beside a forward
     if (env && atoi(env) >= 1) c->peer_side_grid = atoi(env);
@@ -983,6 +981,17 @@ int gs_set_gradient_routing(gs_ctx* c, int nranks, int rank, int rows_per_shard,
   return GS_OK;
 }
 
+// Grid of an Adam call that runs beside a forward (GS_PEER_BESIDE_FORWARD).  The kernel is bound by NVLink, and the
+// more stores it keeps queued the longer the loads of the kernels beside it wait; too few blocks and the phase
+// itself is late.  The rows per rank go with 1 / nranks, so does the cap: 3 * SMs / nranks (8 GPUs: 55, measured
+// 40-64 blocks 1.56 ms/step, 24: 1.74, 148: 1.63, 296: 1.71; 4 GPUs: 111, measured 64-128 blocks 1.49-1.50, 49:
+// 1.58, 296: 1.52 -- profiles/r02k_split_phase.md).  GS_PEER_ADAM_GRID overrides.
+static int gs_peer_side_grid(const gs_ctx* c, int nranks) {
+  if (c->peer_side_grid > 0) return c->peer_side_grid;
+  const int g = 3 * c->num_sms / (nranks > 0 ? nranks : 1);
+  return g > 16 ? g : 16;
+}
+
 int gs_adam_step_peer(gs_ctx* c, int nranks, int rank, int N, int rows_per_shard, float* const params[],
                       const float* const slots[], float* const exp_avg[6], float* const exp_avg_sq[6],
                       const int widths[6], const double lr[6], const long long step[6], double beta1, double beta2,
@@ -1016,7 +1025,7 @@ int gs_adam_step_peer(gs_ctx* c, int nranks, int rank, int N, int rows_per_shard
   GS_CUDA_CHECK(c, gs_launch_adam_peer(nranks, rank, N, rows_per_shard, params, slots, exp_avg, exp_avg_sq, widths, lr,
                                        step, beta1, beta2, eps, radii, dL_dmeans2D, max_radii2D, xyz_grad_accum,
                                        denom, skip_guard, (flags & GS_PEER_PULL) ? 0 : 1,
-                                       (flags & GS_PEER_BESIDE_FORWARD) ? c->peer_side_grid : 0,
+                                       (flags & GS_PEER_BESIDE_FORWARD) ? gs_peer_side_grid(c, nranks) : 0,
                                        (flags & GS_PEER_SH_LOCAL) ? 0x6 : 0, (cudaStream_t)stream_));
   return GS_OK;
 }

@@ -217,12 +217,14 @@ class PeerShardedAdam:
         self.split = (world > 1 and self.flag_barriers and os.environ.get("GS_PEER_NO_SPLIT", "0") != "1"
                       and self.widths[1] + self.widths[2] > 0)
         # GS_PEER_SPLIT: "sm" -- a second Adam kernel on the second stream stores the SH rows into every replica, its
-        # grid capped at a third of the SMs (GS_PEER_BESIDE_FORWARD); "ce" -- the Adam kernel updates the SH rows in
+        # grid capped at 3 x SMs / ranks (GS_PEER_BESIDE_FORWARD); "ce" -- the Adam kernel updates the SH rows in
         # the own replica only and COPY ENGINES distribute them (gs_peer_copy); "off" -- one phase.  Measured (B200,
         # cfg2, one view per rank per step, ms/step; profiles/r02k_split_phase.md): 8 GPUs sm 1.56 / ce 1.83 / off
         # 1.71; 4 GPUs sm 1.49 / ce 1.52 / off 1.57; 2 GPUs sm 1.46 / off 1.42 (half the model's SH rows per rank is
         # HBM work, not NVLink time, and the two-kernel forward costs 45 us).  Default: sm from 4 ranks, else off.
-        default_mode = "sm" if world >= 4 else "off"
+        # (pull layout -- several views per rank and step: the exchange is a small share of the step and the split
+        # measured within noise of one phase, 25.2 against 24.7 ms at 8 GPUs: off unless asked for)
+        default_mode = "sm" if (world >= 4 and not self.pull) else "off"
         self.split_mode = os.environ.get("GS_PEER_SPLIT", default_mode) if self.split else "off"
         if self.split_mode == "off":
             self.split = False

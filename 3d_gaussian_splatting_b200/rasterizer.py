@@ -386,7 +386,13 @@ class Rasterizer:
         sparse_rest=False: the pull layout (GS_PEER_PULL): slots point into the ranks' full gradient slabs."""
         if isinstance(skip_guard, torch.Tensor):
             skip_guard = skip_guard.data_ptr()
-        tab = lambda t: (C.c_void_p * (nranks * 6))(*[int(t[r][k]) for r in range(nranks) for k in range(6)])
+        def tab(t):
+            # the pointer tables of the peer optimiser are the same lists every step: build the ctypes array once
+            cache = self.__dict__.setdefault("_peer_tab_cache", {})
+            hit = cache.get(id(t))
+            if hit is None or hit[0] is not t:
+                hit = cache[id(t)] = (t, (C.c_void_p * (nranks * 6))(*[int(t[r][k]) for r in range(nranks) for k in range(6)]))
+            return hit[1]
         VP6 = C.c_void_p * 6
         stream = torch.cuda.current_stream(self.device).cuda_stream
         check(self._ctx, lib.gs_adam_step_peer(

@@ -476,6 +476,8 @@ def run_ours(args, rank, world, local_rank):
         # the public call: pinned host image in, loss (python float) out
         return trainer.train_step(my_cams[i % args.views], gts_host[i % args.views])
 
+    host_ms = [0.0]   # host time the last timed() loop needed to ENQUEUE a step (the queue is empty when it starts)
+
     def timed(fn, steps, warmup, sampler=None):
         for i in range(warmup):
             fn(i)
@@ -487,8 +489,10 @@ def run_ours(args, rank, world, local_rank):
             sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+        h0 = time.perf_counter()
         for i in range(steps):
             fn(warmup + i)
+        host_ms[0] = (time.perf_counter() - h0) * 1e3 / max(steps, 1)
         e1.record()
         torch.cuda.synchronize()
         if world > 1:
@@ -503,6 +507,7 @@ def run_ours(args, rank, world, local_rank):
     warm = max(args.warmup, 3)
     sampler = ClockSampler(local_rank) if rank == 0 else None
     total_ms, clocks = timed(step_device, args.steps, warm, sampler)
+    host_enqueue_ms = host_ms[0]
     peer_phases = None
     if world > 1 and args.dp_mode == "peer" and getattr(sharded, "split", False):
         # where the split-phase exchange sits inside a pipelined step: a second, instrumented pass (events only)
@@ -806,6 +811,9 @@ def run_ours(args, rank, world, local_rank):
             # share of parameter floats whose Adam moments are still exactly 0 (never received a gradient): the Adam
             # kernels skip those vectors (an exact fixed point of the update), so K5's time depends on it
             "adam_idle_frac": adam_idle_frac,
+            # host time per step the Python loop spent enqueuing the timed region (below ms_per_step: the device sets
+            # the pace; at or above it: the host does)
+            "host_enqueue_ms_per_step": round(host_enqueue_ms, 4),
             # the same step over >= sustain_seconds of continuous running, with its own clock record
             "sustained": sustained,
             # the same step with cold Adam state (this scene hides ~70 % of its Gaussians from every view: their

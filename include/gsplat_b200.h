@@ -263,8 +263,8 @@ GS_API int gs_adam_step_peer(gs_ctx *ctx, int nranks, int rank, int N, int rows_
                              int flags, void *stream);
 #define GS_PEER_PULL 1
 /* GS_PEER_BESIDE_FORWARD: the call runs on a second stream beside the next gs_forward (the SH groups of the
- * split-phase step, see gs_set_color_gate): it is bound by NVLink, not by the SMs, so its grid is capped at a third
- * of the SM count (grid-stride loop; GS_PEER_ADAM_GRID overrides).  Measured on 8 GPUs: the more remote stores the
+ * split-phase step, see gs_set_color_gate): it is bound by NVLink, not by the SMs, so its grid is capped at
+ * 3 x SM count / nranks (grid-stride loop; GS_PEER_ADAM_GRID overrides).  Measured on 8 GPUs: the more remote stores the
  * kernel keeps queued, the longer the loads of K1 and the sorts beside it wait (40-64 blocks: 1.56 ms/step, 296:
  * 1.71, none of the split: 1.71). */
 #define GS_PEER_BESIDE_FORWARD 2
