@@ -100,6 +100,9 @@ __global__ void __launch_bounds__(AD_THREADS, 4) adam_stats_kernel(const __grid_
 #pragma unroll
       for (int k = 0; k < AD_VEC_PER_THREAD; ++k) gs_adam_quad_step<true>(p[k], m[k], v[k], q[k], eps, neg_step, inv_bc2_sqrt);
     } else {
+      // (tiny first moments, GS_ADAM_FAST_T, stay on the scalar path in THIS kernel: with eight vectors per thread the
+      //  extra branch costs 10 registers and spills at the 64 that four blocks per SM allow -- 0.44 -> 0.50 ms for
+      //  every state, measured; the fused kernel and the peer kernel, one or two vectors in flight, have the path)
 #pragma unroll
       for (int k = 0; k < AD_VEC_PER_THREAD; ++k)
         if (!idle[k]) gs_adam_quad_scalar(p[k], g[k], m[k], v[k], kc, neg_step, inv_bc2_sqrt);
@@ -289,6 +292,7 @@ __global__ void __launch_bounds__(AD_THREADS, 2) adam_peer_kernel(const __grid_c
       const int ok = idle ? GS_ADAM_FAST : gs_adam_quad_moments(g, m, v, kc, q);
       if (__all_sync(0xffffffffu, ok == GS_ADAM_FAST)) gs_adam_quad_step<false>(p, m, v, q, eps, neg_step, inv_bc2_sqrt);
       else if (__all_sync(0xffffffffu, ok >= GS_ADAM_FAST_Z)) gs_adam_quad_step<true>(p, m, v, q, eps, neg_step, inv_bc2_sqrt);
+      else if (__all_sync(0xffffffffu, ok >= GS_ADAM_FAST_T)) gs_adam_quad_step_tiny(p, g, m, v, q, kc, neg_step, inv_bc2_sqrt, !idle);
       else if (!idle) gs_adam_quad_scalar(p, g, m, v, kc, neg_step, inv_bc2_sqrt);
     }
     if (idle) continue;

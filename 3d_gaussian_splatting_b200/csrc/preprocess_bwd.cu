@@ -675,6 +675,14 @@ __device__ __forceinline__ void pbf_update(PbfRound<PBF_UNROLL>& R, const float*
     for (int u = 0; u < PBF_UNROLL; ++u)
       if (R.k[u] >= 0)
         gs_adam_quad_step<true>(R.p[u], R.m[u], R.v[u], q[u], kc.eps, f.neg_step[R.k[u]], f.inv_bc2_sqrt[R.k[u]]);
+  } else if (__all_sync(0xffffffffu, mode >= GS_ADAM_FAST_T)) {
+    // tiny first moments (Gaussians unseen for ~480 iterations and more): still packed, see gs_common.cuh
+#pragma unroll
+    for (int u = 0; u < PBF_UNROLL; ++u) {
+      const int k = R.k[u] >= 0 ? R.k[u] : 0;
+      gs_adam_quad_step_tiny(R.p[u], g[u], R.m[u], R.v[u], q[u], kc, f.neg_step[k], f.inv_bc2_sqrt[k],
+                             R.k[u] >= 0 && !idle[u]);
+    }
   } else {
 #pragma unroll
     for (int u = 0; u < PBF_UNROLL; ++u)

@@ -172,3 +172,82 @@ def _same_world(a, b):
     for sa, sb in zip(a[4], b[4]):
         for rowa, rowb in zip(sa, sb):
             assert all(torch.equal(x, y) for x, y in zip(rowa, rowb))
+
+
+def test_tiny_first_moments_fused_and_peer_kernels(rasterizer):
+    """First moments below 2^-100 (Gaussians unseen for ~480 iterations and more; they end up stuck at the smallest
+    denormal) have a packed path of their own in the fused K4b+K5 kernel and in the peer Adam kernel
+    (GS_ADAM_FAST_T, csrc/gs_common.cuh).  Both must give the bits of gs_adam_densify_step, whose kernel keeps such
+    vectors on the scalar IEEE path (itself pinned to the oracle by test_adam_packed_fast_path_is_ieee).  Whole row
+    blocks are tiny so that whole warps take the path; large second moments make some quotients denormal (the
+    scalar fallback inside the path), zero gradients exercise the pure decay."""
+    L = importlib.import_module("3d_gaussian_splatting_b200._lib")
+    from test_gpu_parity import seeded_dL
+    N, deg = 3000, 2
+    # (the camera sits inside the cloud: the Gaussians behind it are culled and receive no gradient -- pure decay)
+    scene, cam = small_scene(N=N, H=96, W=128, deg=deg, seed=43, scale_boost=0.5, eye=(0.1, 0.0, 0.2))
+    K = (deg + 1) ** 2
+    widths = [3, 3, 3 * (K - 1), 1, 3, 4]
+    sg = gpu_settings(cam, deg, deg)
+    P = [dev(np.ascontiguousarray(a, dtype=np.float32)) for a in
+         (scene.xyz, scene.features_dc, scene.features_rest[:, :K - 1], scene.opacity_logits, scene.log_scales,
+          scene.raw_rotations)]
+    lr = [1.6e-4, 2.5e-3, 1.25e-4, 0.05, 5e-3, 1e-3]
+    rng = np.random.default_rng(29)
+
+    def moments():
+        M, V = [], []
+        for p in P:
+            shp = tuple(p.shape)
+            m = (rng.standard_normal(shp) * 1e-4).astype(np.float32)
+            v = (rng.random(shp) * 1e-8 + 1e-16).astype(np.float32)
+            tiny = ((10.0 ** rng.uniform(-45, -31, shp)) * rng.choice([-1.0, 1.0], shp)).astype(np.float32)
+            m[:2000] = tiny[:2000]
+            m[:2000:5] = np.float32(1e-45)
+            v[:1000] = (10.0 ** rng.uniform(-18, -13, shp)).astype(np.float32)[:1000]
+            v[1000:1500] = (10.0 ** rng.uniform(-6, 2, shp)).astype(np.float32)[1000:1500]      # denormal quotients
+            M.append(dev(m)); V.append(dev(v))
+        return M, V
+
+    # ---- fused K4b+K5 against gs_backward + gs_adam_densify_step on the same blend-gradient records ----
+    M, V = moments()
+    _, radii = rasterizer.forward(sg, P[0], P[4], P[5], P[3], sh_dc=P[1], sh_rest=P[2], raw_params=True)
+    dL = dev(seeded_dL(96, 128, 5))
+    G = rasterizer.backward(dL)
+    Gk = [G["means3D"], G["sh_dc"], G["sh_rest"], G["opacities"], G["scales"], G["rotations"]]
+    assert sum(int((g[:2000] == 0).all(dim=-1).sum()) for g in Gk) > 0          # pure-decay rows among the tiny ones
+    A, MA, VA = [p.clone() for p in P], [m.clone() for m in M], [v.clone() for v in V]
+    rasterizer.adam_densify_step(N, A, Gk, MA, VA, widths, lr, [7] * 6)
+    PF, MF, VF = [p.clone() for p in P], [m.clone() for m in M], [v.clone() for v in V]
+    L.check(rasterizer._ctx, L.lib.gs_debug_reuse_blend_gradients(rasterizer._ctx, 1))
+    saved = [p.clone() for p in P]
+    try:
+        rasterizer.backward_adam_step(dL, MF, VF, lr, [7] * 6)       # updates P in place
+    finally:
+        L.check(rasterizer._ctx, L.lib.gs_debug_reuse_blend_gradients(rasterizer._ctx, 0))
+    torch.cuda.synchronize()
+    for k in range(6):
+        assert torch.equal(P[k], A[k]), ("fused param", k)
+        assert torch.equal(MF[k], MA[k]) and torch.equal(VF[k], VA[k]), ("fused moments", k)
+        assert not torch.equal(P[k], saved[k])
+        P[k].copy_(saved[k])
+    # ---- peer Adam kernel, one rank: slot 0 holds the gradients ----
+    R = (N + 127) // 128 * 128
+    M, V = moments()
+    A, MA, VA = [p.clone() for p in P], [m.clone() for m in M], [v.clone() for v in V]
+    grads = [dev((rng.standard_normal(tuple(p.shape)) * 1e-3 * (rng.random(tuple(p.shape)) < 0.5)).astype(np.float32)) for p in P]
+    rasterizer.adam_densify_step(N, A, grads, MA, VA, widths, lr, [9] * 6)
+    slots = [torch.zeros(R * w, device="cuda") for w in widths]
+    mp = [torch.zeros(R * w, device="cuda") for w in widths]
+    vp = [torch.zeros(R * w, device="cuda") for w in widths]
+    for k, w in enumerate(widths):
+        slots[k][:N * w] = grads[k].reshape(-1)
+        mp[k][:N * w] = M[k].reshape(-1)
+        vp[k][:N * w] = V[k].reshape(-1)
+    rep = [p.clone() for p in P]
+    rasterizer.adam_step_peer(1, 0, N, R, [[t.data_ptr() for t in rep]], [[t.data_ptr() for t in slots]], mp, vp, widths,
+                              lr, [9] * 6, sparse_rest=False)
+    torch.cuda.synchronize()
+    for k, w in enumerate(widths):
+        assert torch.equal(rep[k], A[k]), ("peer param", k)
+        assert torch.equal(mp[k][:N * w], MA[k].reshape(-1)) and torch.equal(vp[k][:N * w], VA[k].reshape(-1)), ("peer moments", k)
