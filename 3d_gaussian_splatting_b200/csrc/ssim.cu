@@ -3,9 +3,9 @@
 // reference (src/utils/train_utils.cpp:138-145).  SSIM: per channel, 11x11 Gaussian window (sigma 1.5),
 // zero-padded "same" convolution, C1 = 0.01^2, C2 = 0.03^2 -- the oracle's definition (oracle/orc_ssim.c).
 //
-// Two fused kernels over 32x16 pixel tiles of one channel (grid.z = 3), 128 threads each producing 4 outputs per
+// Two fused kernels over 32x32 pixel tiles of one channel (grid.z = 3), 256 threads each producing 4 outputs per
 // pass so every staged value (and, in the forward, its three products) is reused from registers by 4 windows:
-//   ssim_forward_kernel   stages the 42x26 halo of image and target in shared memory, runs the separable
+//   ssim_forward_kernel   stages the 42x42 halo of image and target in shared memory, runs the separable
 //                         window over the five products (x, y, xx, yy, xy) -- rows, then columns -- evaluates the
 //                         SSIM map and its partial derivatives w.r.t. the windowed means (dmu1, de11, de12;
 //                         12 B per value, the only intermediate that goes to HBM) and reduces the L1 and SSIM sums.
@@ -19,7 +19,7 @@
 #define SS_TY 32
 #define SS_R 5
 #define SS_HX (SS_TX + 2 * SS_R)  // 42
-#define SS_HY (SS_TY + 2 * SS_R)  // 26
+#define SS_HY (SS_TY + 2 * SS_R)  // 42
 #define SS_THREADS 256            // every thread produces 4 outputs of each pass (register-blocked window)
 #define SS_V 4
 #define SS_PITCH (SS_HX + 1)      // 43: with 4-wide column groups the 32 lanes of a warp hit 32 different banks
@@ -85,7 +85,7 @@ ssim_forward_kernel(int H, int W, const float* __restrict__ img, const float* __
     }
   }
   __syncthreads();
-  // rows: 26 rows x 8 groups of 4 adjacent outputs; the 14 staged values (and their products) are reused by the 4
+  // rows: 42 rows x 8 groups of 4 adjacent outputs; the 14 staged values (and their products) are reused by the 4
   for (int k = tid; k < SS_HY * (SS_TX / SS_V); k += SS_THREADS) {
     const int r = k / (SS_TX / SS_V), c = (k - r * (SS_TX / SS_V)) * SS_V;
     float xv[SS_V + 2 * SS_R], yv[SS_V + 2 * SS_R];
