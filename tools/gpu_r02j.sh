@@ -3,6 +3,7 @@
 # lines of every BASELINE.json config, the ncu launch list and one --set full capture of a steady-state step
 T=${1:-r02j}
 mkdir -p gpurun_out
+python -c "import __graft_entry__ as g; g.smoke(); print(\"smoke ok\")" 2>&1 | tail -1
 python -m pytest tests/test_zz_no_alloc.py -m gpu -q > gpurun_out/${T}_noalloc_alone.log 2>&1; tail -3 gpurun_out/${T}_noalloc_alone.log
 python -m pytest tests -m gpu -x -q --durations=8 > gpurun_out/${T}_pytest.log 2>&1; tail -14 gpurun_out/${T}_pytest.log
 python bench.py > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err || tail -5 gpurun_out/${T}_bench.err
