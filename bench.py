@@ -697,12 +697,23 @@ def run_ours(args, rank, world, local_rank):
         # adam_peer_kernel, local HBM bytes of one rank: the `world` gradient slots + m, v, p of its R-row shard read;
         # m, v, p of the active vectors written; plus what the other ranks' kernels store into this replica
         wfl, R = 11 + 3 * K, sharded.R
-        by["adam_stats"] = (4 * world + 12) * wfl * R + 12 * active_floats + 4 * active_floats * (world - 1) + 36 * N_vis
+        share = 1.0
+        if getattr(sharded, "split", False):
+            # split-phase step: the stage timed on the caller's stream is the GEOMETRY phase (11 of the 11 + 3 K floats
+            # of a Gaussian); the SH phase runs beside the next forward and is reported in peer_phases_ms
+            share = 11.0 / wfl
+            wfl = 11
+        act = active_floats * share
+        by["adam_stats"] = int((4 * world + 12) * wfl * R + 12 * act + 4 * act * (world - 1) + 36 * N_vis)
     elif world > 1 and args.dp_mode == "sharded":
         wfl = 11 + 3 * K
         by["adam_stats"] = 28 * wfl * N // world + 36 * N_vis
     peak, peak_kind = peaks()
-    dom = max(stage_ms, key=lambda k: stage_ms[k])
+    # the roofline object is for the dominant HBM-bound stage (the blend kernels are bound by issue slots and dependency
+    # latency by construction -- their share of the HBM peak says nothing; `stages` carries it for completeness)
+    hbm_bound = [k for k in stage_ms if k in ("preprocess_bwd_adam", "adam_stats", "preprocess_bwd", "preprocess",
+                                              "sh_color", "loss")]
+    dom = max(hbm_bound or stage_ms, key=lambda k: stage_ms[k])
     ach = by[dom] / (stage_ms[dom] * 1e-3) / 1e9
     by = {k: v for k, v in by.items() if k in stage_ms}
     step_bytes = sum(by.values())
