@@ -852,8 +852,13 @@ def run_ours(args, rank, world, local_rank):
                             "step": "Trainer.train_step: one synchronous call per step"}[
                                 args.e2e_api if world == 1 or args.e2e_api != "native" else "loop"]},
             "pair_capacity": trainer.pair_capacity, "capacity_retries": trainer.retries,
-            # own kernels only (NCCL's are not counted); the routed K4b of the peer mode is one launch per owner rank
-            "gpu_launches": (OWN_KERNELS_PER_STEP - (1 if world == 1 and trainer.fused_step else 0) + (world - 1 if world > 1 and args.dp_mode == "peer" else 0)
+            # own kernels only (NCCL's are not counted).  Peer mode: the routed K4b is ONE launch for all owners; two
+            # flag-barrier kernels per step; the split-phase step adds the colour kernel, a second Adam launch and a
+            # third barrier kernel
+            "gpu_launches": (OWN_KERNELS_PER_STEP - (1 if world == 1 and trainer.fused_step else 0)
+                             + ((2 if getattr(sharded, "flag_barriers", False) else 0)
+                                + (3 if getattr(sharded, "split", False) else 0)
+                                if world > 1 and args.dp_mode == "peer" else 0)
                              + (1 if world > 1 and args.dp_mode == "sharded" else 0)) * args.steps,
             "library_launches": LIB_KERNELS_PER_STEP * args.steps,
             "clocks": clocks,
