@@ -839,7 +839,10 @@ def run_ours(args, rank, world, local_rank):
             "raster_fwd_bwd_ms": fwd_bwd_ms, "raster_fwd_bwd_includes_adam": bool(fused), "train_it_per_s_per_gpu": 1e3 / ms_per_step,
             "stages": stages,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
-                         "frac": ach / peak, "traffic": measured_traffic(dom), "peak_kind": peak_kind,
+                         "frac": ach / peak,
+                         # (the committed ncu captures are single-GPU: the peer kernels of N > 1 have none)
+                         "traffic": measured_traffic(dom) if world == 1 or dom not in ("adam_stats", "preprocess_bwd") else None,
+                         "peak_kind": peak_kind,
                          "step_frac": step_bytes / (ms_per_step * 1e-3) / 1e9 / peak},
             "cpu_baseline": cpu_baseline,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / args.steps,
