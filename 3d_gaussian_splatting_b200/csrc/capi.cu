@@ -445,6 +445,7 @@ int gs_forward(gs_ctx* c, const gs_settings* st, int N, const gs_gaussians* in, 
   }
   const int defer_color = (c->color_gate != nullptr && !in->colors_precomp) ? 1 : 0;
   bool color_on_side = false;
+  if (!defer_color) c->ev_valid[8] = false;  // (no colour kernel in this forward: no stale stage time)
   if (N > 0) {
     // The depth argsort reads only the view depth, so it is forked onto the context's second stream and runs
     // beside K1 (the latency-bound N-sized sort fills the issue slots K1 leaves); the scan joins the two.

@@ -117,7 +117,7 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
             c = [x.strip() for x in r.split(",")]
@@ -127,11 +127,16 @@ class ClockSampler:
                 sm.append(float(c[1])); mx.append(float(c[2]))
             except ValueError:
                 continue
+            try:
+                pw.append(float(c[3]))
+            except ValueError:
+                pass
             for n, v in zip(names, c[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "sm_min_mhz": min(sm) if sm else None,
+                "power_w_max": max(pw) if pw else None}
 
 
 # ---- algorithmic bytes ---------------------------------------------------
